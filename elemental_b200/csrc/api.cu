@@ -1,25 +1,193 @@
 // extern "C" surface of libhydrogen_b200.so (declared in include/hydrogen_b200.h).
 #include "../../include/hydrogen_b200.h"
+#include "grid.h"
 #include "hyd_internal.h"
+#include <string.h>
 
 namespace hyd {
 const char* last_error();
 int probe_peak(int kind, int iters, int ctas_per_sm, double* tflops);
+template <typename T>
+int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A, const DM& B, T beta, const DM& C, i64 blocksize,
+              cudaStream_t s);
 }  // namespace hyd
+
+struct hyd_world { hyd::World* w; };
+struct hyd_grid { hyd::Grid* g; };
+struct hyd_local_group { hyd::LocalShared* sh; };
+
+using hyd::set_error;
+
+static hyd::DM to_dm(const hyd_dm* a) {
+    hyd::DM d;
+    d.buf = a->buf; d.ldim = a->ldim; d.height = a->height; d.width = a->width;
+    d.colDist = a->colDist; d.rowDist = a->rowDist; d.colAlign = a->colAlign; d.rowAlign = a->rowAlign; d.root = a->root;
+    return d;
+}
+static void from_dm(const hyd::DM& d, hyd_dm* a) {
+    a->buf = d.buf; a->ldim = d.ldim; a->height = d.height; a->width = d.width;
+    a->colDist = d.colDist; a->rowDist = d.rowDist; a->colAlign = d.colAlign; a->rowAlign = d.rowAlign; a->root = d.root;
+    a->reserved = 0;
+}
+static int check_dm(const hyd::GridShape& sh, const hyd_dm* a, const char* who) {
+    if (!a) return set_error("%s: null matrix", who);
+    if (a->height < 0 || a->width < 0) return set_error("%s: negative dimension", who);
+    if (!hyd::pair_supported(a->colDist, a->rowDist))
+        return set_error("%s: unsupported distribution pair [%d,%d]", who, a->colDist, a->rowDist);
+    if (a->colAlign < 0 || a->colAlign >= sh.stride(a->colDist) || a->rowAlign < 0 || a->rowAlign >= sh.stride(a->rowDist))
+        return set_error("%s: alignment out of range", who);
+    return 0;
+}
 
 extern "C" {
 
 const char* hyd_last_error(void) { return hyd::last_error(); }
 int hyd_version(void) { return 100; }
+long long hyd_launch_count(void) { return hyd::g_launches; }
 
-int hyd_lgemm_f64(int tA, int tB, int64_t m, int64_t n, int64_t k, double alpha, const double* A,
-                  int64_t lda, const double* B, int64_t ldb, double beta, double* C, int64_t ldc,
-                  hyd_stream_t stream) {
-    return hyd::lgemm_f64(tA, tB, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, (cudaStream_t)stream);
+int64_t hyd_mod(int64_t a, int64_t b) { return hyd::mod_(a, b); }
+int64_t hyd_shift(int64_t rank, int64_t align, int64_t stride) { return hyd::shift_(rank, align, stride); }
+int64_t hyd_length(int64_t n, int64_t shift, int64_t stride) { return hyd::length_(n, shift, stride); }
+int64_t hyd_max_length(int64_t n, int64_t stride) { return hyd::max_length_(n, stride); }
+
+// ---- local kernels ----
+int hyd_lgemm_f64(int tA, int tB, int64_t m, int64_t n, int64_t k, double alpha, const double* A, int64_t lda,
+                  const double* B, int64_t ldb, double beta, double* C, int64_t ldc, hyd_stream_t stream) {
+    ++hyd::g_launches;
+    return hyd::lgemm_f64(tA ? 1 : 0, tB ? 1 : 0, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, (cudaStream_t)stream);
 }
-
+int hyd_lgemm_f32(int tA, int tB, int64_t m, int64_t n, int64_t k, float alpha, const float* A, int64_t lda,
+                  const float* B, int64_t ldb, float beta, float* C, int64_t ldc, hyd_stream_t stream) {
+    ++hyd::g_launches;
+    return hyd::lgemm_f32(tA ? 1 : 0, tB ? 1 : 0, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, (cudaStream_t)stream);
+}
 int hyd_probe_peak(int kind, int iters, int ctas_per_sm, double* tflops) {
     return hyd::probe_peak(kind, iters, ctas_per_sm, tflops);
+}
+
+// ---- world / grid ----
+int hyd_nccl_unique_id(void* out128) { return hyd::nccl_unique_id(out128); }
+int hyd_world_create_nccl(const void* id128, int rank, int nranks, hyd_world** out) {
+    if (!id128 || !out || nranks <= 0 || rank < 0 || rank >= nranks) return set_error("hyd_world_create_nccl: bad arguments");
+    hyd::World* w = hyd::make_nccl_world(id128, rank, nranks);
+    if (!w) return 1;
+    *out = new hyd_world{w};
+    return 0;
+}
+int hyd_local_group_create(int nranks, hyd_local_group** out) {
+    if (nranks <= 0 || !out) return set_error("hyd_local_group_create: bad arguments");
+    *out = new hyd_local_group{hyd::local_shared_create(nranks)};
+    return 0;
+}
+int hyd_local_group_destroy(hyd_local_group* grp) {
+    if (grp) { hyd::local_shared_destroy(grp->sh); delete grp; }
+    return 0;
+}
+int hyd_world_create_local(hyd_local_group* grp, int rank, hyd_world** out) {
+    if (!grp || !out) return set_error("hyd_world_create_local: bad arguments");
+    *out = new hyd_world{hyd::make_local_world(grp->sh, rank)};
+    return 0;
+}
+int hyd_world_destroy(hyd_world* w) {
+    if (w) { delete w->w; delete w; }
+    return 0;
+}
+int hyd_world_barrier(hyd_world* w) { return w ? w->w->barrier() : set_error("hyd_world_barrier: null world"); }
+
+int hyd_grid_create(hyd_world* w, int height, int order, hyd_grid** out) {
+    if (!w || !out) return set_error("hyd_grid_create: bad arguments");
+    const int size = w->w->size;
+    if (height <= 0 || size % height != 0)
+        return set_error("Grid height, %d, does not evenly divide grid size, %d", height, size);  // Grid.cpp:98-100
+    hyd::Grid* g = new hyd::Grid;
+    g->world = w->w;
+    g->shape.r = height;
+    g->shape.c = size / height;
+    g->shape.col_major = order ? 1 : 0;
+    g->rank = w->w->rank;
+    g->shape.coords(g->rank, g->mc, g->mr);
+    *out = new hyd_grid{g};
+    return 0;
+}
+int hyd_grid_destroy(hyd_grid* g) {
+    if (g) { hyd::grid_destroy(g->g); delete g; }
+    return 0;
+}
+int hyd_grid_height(const hyd_grid* g) { return g->g->shape.r; }
+int hyd_grid_width(const hyd_grid* g) { return g->g->shape.c; }
+int hyd_grid_size(const hyd_grid* g) { return g->g->shape.size(); }
+int hyd_grid_rank(const hyd_grid* g) { return g->g->rank; }
+int hyd_grid_row(const hyd_grid* g) { return g->g->mc; }
+int hyd_grid_col(const hyd_grid* g) { return g->g->mr; }
+int hyd_grid_vc_rank(const hyd_grid* g) { return g->g->vc(); }
+int hyd_grid_vr_rank(const hyd_grid* g) { return g->g->vr(); }
+int hyd_grid_set_overlap(hyd_grid* g, int overlap, int sm_reserve) {
+    g->g->overlap = overlap != 0;
+    if (sm_reserve >= 0) g->g->sm_reserve = sm_reserve;
+    return 0;
+}
+int hyd_dist_stride(const hyd_grid* g, int dist) { return g->g->shape.stride(dist); }
+int hyd_dist_rank(const hyd_grid* g, int dist) { return g->g->shape.dist_rank(dist, g->g->mc, g->g->mr); }
+
+int hyd_local_shape_of(int gh, int gw, int order, int rank, const hyd_dm* a, int64_t* cs, int64_t* rs, int64_t* lh,
+                       int64_t* lw) {
+    hyd::GridShape sh;
+    sh.r = gh; sh.c = gw; sh.col_major = order ? 1 : 0;
+    if (gh <= 0 || gw <= 0 || rank < 0 || rank >= gh * gw) return set_error("hyd_local_shape_of: bad grid/rank");
+    if (check_dm(sh, a, "hyd_local_shape_of")) return 1;
+    int mc, mr;
+    sh.coords(rank, mc, mr);
+    const hyd::LocalShape L = hyd::local_shape(sh, to_dm(a), mc, mr);
+    if (cs) *cs = L.colShift;
+    if (rs) *rs = L.rowShift;
+    if (lh) *lh = L.lh;
+    if (lw) *lw = L.lw;
+    return 0;
+}
+int hyd_local_shape(const hyd_grid* g, const hyd_dm* a, int64_t* cs, int64_t* rs, int64_t* lh, int64_t* lw) {
+    const hyd::GridShape& sh = g->g->shape;
+    return hyd_local_shape_of(sh.r, sh.c, sh.col_major, g->g->rank, a, cs, rs, lh, lw);
+}
+int hyd_view(const hyd_grid* g, const hyd_dm* a, int64_t i, int64_t j, int64_t h, int64_t w, int es, hyd_dm* out) {
+    if (check_dm(g->g->shape, a, "hyd_view")) return 1;
+    if (i < 0 || j < 0 || h < 0 || w < 0 || i + h > a->height || j + w > a->width)
+        return set_error("hyd_view: range out of bounds");
+    from_dm(hyd::view(g->g->shape, to_dm(a), g->g->mc, g->g->mr, i, j, h, w, es), out);
+    return 0;
+}
+
+// ---- distributed operations ----
+int hyd_redist_f64(hyd_grid* g, const hyd_dm* src, const hyd_dm* dst, int transpose, hyd_stream_t stream) {
+    if (check_dm(g->g->shape, src, "hyd_redist") || check_dm(g->g->shape, dst, "hyd_redist")) return 1;
+    return hyd::redistribute<double>(*g->g, to_dm(src), to_dm(dst), transpose != 0, 3, (cudaStream_t)stream);
+}
+int hyd_redist_f32(hyd_grid* g, const hyd_dm* src, const hyd_dm* dst, int transpose, hyd_stream_t stream) {
+    if (check_dm(g->g->shape, src, "hyd_redist") || check_dm(g->g->shape, dst, "hyd_redist")) return 1;
+    return hyd::redistribute<float>(*g->g, to_dm(src), to_dm(dst), transpose != 0, 3, (cudaStream_t)stream);
+}
+int hyd_axpy_contract_f64(hyd_grid* g, double alpha, const hyd_dm* src, const hyd_dm* dst, int transpose,
+                          hyd_stream_t stream) {
+    if (check_dm(g->g->shape, src, "hyd_axpy_contract") || check_dm(g->g->shape, dst, "hyd_axpy_contract")) return 1;
+    return hyd::reduce_into<double>(*g->g, alpha, to_dm(src), to_dm(dst), transpose != 0, 3, (cudaStream_t)stream);
+}
+int hyd_axpy_contract_f32(hyd_grid* g, float alpha, const hyd_dm* src, const hyd_dm* dst, int transpose,
+                          hyd_stream_t stream) {
+    if (check_dm(g->g->shape, src, "hyd_axpy_contract") || check_dm(g->g->shape, dst, "hyd_axpy_contract")) return 1;
+    return hyd::reduce_into<float>(*g->g, alpha, to_dm(src), to_dm(dst), transpose != 0, 3, (cudaStream_t)stream);
+}
+int hyd_gemm_f64(hyd_grid* g, int oA, int oB, int alg, double alpha, const hyd_dm* A, const hyd_dm* B, double beta,
+                 const hyd_dm* C, int64_t blocksize, hyd_stream_t stream) {
+    const hyd::GridShape& sh = g->g->shape;
+    if (check_dm(sh, A, "hyd_gemm(A)") || check_dm(sh, B, "hyd_gemm(B)") || check_dm(sh, C, "hyd_gemm(C)")) return 1;
+    return hyd::dist_gemm<double>(*g->g, oA, oB, alg, alpha, to_dm(A), to_dm(B), beta, to_dm(C), blocksize,
+                                  (cudaStream_t)stream);
+}
+int hyd_gemm_f32(hyd_grid* g, int oA, int oB, int alg, float alpha, const hyd_dm* A, const hyd_dm* B, float beta,
+                 const hyd_dm* C, int64_t blocksize, hyd_stream_t stream) {
+    const hyd::GridShape& sh = g->g->shape;
+    if (check_dm(sh, A, "hyd_gemm(A)") || check_dm(sh, B, "hyd_gemm(B)") || check_dm(sh, C, "hyd_gemm(C)")) return 1;
+    return hyd::dist_gemm<float>(*g->g, oA, oB, alg, alpha, to_dm(A), to_dm(B), beta, to_dm(C), blocksize,
+                                 (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -1,0 +1,42 @@
+// Communication backends behind the redistribution engine.
+//
+// The reference routes every redistribution through El::mpi::{AllGather,AllToAll,
+// ReduceScatter,SendRecv,Broadcast} on the grid's MC/MR/VC/VR communicators
+// (include/El/core/imports/mpi.hpp; src/core/imports/mpi/*.hpp; Aluminum -> NCCL for some,
+// MPI for AllToAll/SendRecv, include/El/core/imports/aluminum.hpp:99-116).
+// On NVSwitch every peer is one hop at full bandwidth, so this build needs exactly one
+// primitive: a variable-size all-to-all ("exchange") among the ranks of the grid, issued
+// as one NCCL group of ncclSend/ncclRecv.  Sub-communicators are not needed.
+//
+// Two implementations:
+//   * NcclWorld  : one process per GPU, NCCL over NVLink 5 (the product path);
+//   * LocalWorld : P rank-threads of ONE process sharing ONE GPU, exchange done with
+//                  stream-ordered device copies (no kernel ever waits on another kernel).
+//                  It exists so the complete multi-rank engine can be parity-tested on a
+//                  single-GPU box; it is still all-GPU, not a CPU fallback.
+#pragma once
+#include <cuda_runtime.h>
+#include "dist.h"
+
+namespace hyd {
+
+struct World {
+    int rank = 0, size = 1;
+    virtual ~World() {}
+    // Counts/offsets are in BYTES, indexed by world rank.  Entries for `rank` itself are ignored
+    // (the engine moves its own part without the network).  Asynchronous on `s`.
+    virtual int exchange(const void* send, const i64* scount, const i64* soff, void* recv,
+                         const i64* rcount, const i64* roff, cudaStream_t s) = 0;
+    virtual int barrier() = 0;  // host-side
+    virtual const char* kind() const = 0;
+};
+
+World* make_nccl_world(const void* unique_id_128B, int rank, int size);
+int nccl_unique_id(void* out_128B);
+
+struct LocalShared;
+LocalShared* local_shared_create(int size);
+void local_shared_destroy(LocalShared*);
+World* make_local_world(LocalShared* sh, int rank);
+
+}  // namespace hyd

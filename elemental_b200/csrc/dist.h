@@ -1,0 +1,98 @@
+// Host-side integer model of element-cyclic distributions on an r x c process grid.
+// Restates (as closed forms, 64-bit) the reference's definitions:
+//   Shift_/Length_/MaxLength_/Mod_   include/El/core/indexing/impl.hpp:33-66,229-245
+//   grid rank maps                   src/core/Grid.cpp:139-150
+//   per-distribution stride / rank   src/core/DistMatrix/ElementMatrix/*.cpp (bottom of each file)
+//   view alignment                   include/El/core/DistMatrix/... View: align = (align + i) mod stride
+// No CUDA in this header: it is also used by the CPU-only C-ABI entry points.
+#pragma once
+#include <stdint.h>
+
+namespace hyd {
+
+typedef long long i64;
+
+enum Dist { MC = 0, MD = 1, MR = 2, VC = 3, VR = 4, STAR = 5, CIRC = 6 };  // types.hpp:208-216
+
+inline i64 mod_(i64 a, i64 b) { i64 r = a % b; return r >= 0 ? r : r + b; }
+inline i64 shift_(i64 rank, i64 align, i64 stride) { return mod_(rank - align, stride); }
+inline i64 length_(i64 n, i64 shift, i64 stride) { return n > shift ? (n - shift - 1) / stride + 1 : 0; }
+inline i64 max_length_(i64 n, i64 stride) { return n > 0 ? (n - 1) / stride + 1 : 0; }
+inline i64 gcd_(i64 a, i64 b) { while (b) { i64 t = a % b; a = b; b = t; } return a; }
+
+struct GridShape {
+    int r = 1, c = 1;      // Height(), Width()
+    int col_major = 1;     // GridOrder COLUMN_MAJOR (default)
+    int size() const { return r * c; }
+    // world (owning-comm) rank <-> (mc, mr); Grid.cpp:121-148
+    void coords(int rank, int& mc, int& mr) const {
+        if (col_major) { mc = rank % r; mr = rank / r; }
+        else           { mc = rank / c; mr = rank % c; }
+    }
+    int rank_of(int mc, int mr) const { return col_major ? mc + r * mr : mr + c * mc; }
+    int vc(int mc, int mr) const { return mc + r * mr; }
+    int vr(int mc, int mr) const { return mr + c * mc; }
+    int stride(int d) const {
+        switch (d) { case MC: return r; case MR: return c; case VC: case VR: return r * c; default: return 1; }
+    }
+    int dist_rank(int d, int mc, int mr) const {
+        switch (d) { case MC: return mc; case MR: return mr; case VC: return vc(mc, mr); case VR: return vr(mc, mr); default: return 0; }
+    }
+};
+
+inline bool dist_supported(int d) { return d == MC || d == MR || d == VC || d == VR || d == STAR; }
+// legal (colDist,rowDist) pairs among the GPU-valid element distributions
+inline bool pair_supported(int u, int v) {
+    if (!dist_supported(u) || !dist_supported(v)) return false;
+    if (u == STAR || v == STAR) return true;
+    return (u == MC && v == MR) || (u == MR && v == MC);
+}
+
+// Metadata of one distributed matrix (the POD the C ABI passes, include/hydrogen_b200.h hyd_dm).
+struct DM {
+    void* buf = nullptr;
+    i64 ldim = 0, height = 0, width = 0;
+    int colDist = MC, rowDist = MR, colAlign = 0, rowAlign = 0, root = 0;
+};
+
+struct LocalShape { i64 colShift, rowShift, lh, lw; int colStride, rowStride; };
+
+inline LocalShape local_shape(const GridShape& g, const DM& a, int mc, int mr) {
+    LocalShape s;
+    s.colStride = g.stride(a.colDist);
+    s.rowStride = g.stride(a.rowDist);
+    s.colShift = shift_(g.dist_rank(a.colDist, mc, mr), a.colAlign, s.colStride);
+    s.rowShift = shift_(g.dist_rank(a.rowDist, mc, mr), a.rowAlign, s.rowStride);
+    s.lh = length_(a.height, s.colShift, s.colStride);
+    s.lw = length_(a.width, s.rowShift, s.rowStride);
+    return s;
+}
+
+// One arithmetic progression of global indices i = first + t*step, t < count,
+// together with where it sits in the source's and the destination's local index space.
+struct Prog { i64 count = 0, src0 = 0, srcStep = 1, dst0 = 0, dstStep = 1; };
+
+// Intersect { i ≡ s1 (mod n1) } and { i ≡ s2 (mod n2) } on [0, n).  (CRT; n1, n2 small.)
+inline Prog intersect(i64 n, i64 s1, i64 n1, i64 s2, i64 n2) {
+    Prog p;
+    const i64 g = gcd_(n1, n2);
+    if (mod_(s1 - s2, g) != 0) return p;
+    const i64 L = n1 / g * n2;
+    i64 x = s1;
+    while (mod_(x - s2, n2) != 0) x += n1;  // at most n2/g steps
+    p.count = length_(n, x, L);
+    p.src0 = (x - s1) / n1; p.srcStep = L / n1;
+    p.dst0 = (x - s2) / n2; p.dstStep = L / n2;
+    return p;
+}
+
+// Which coordinates of a rank does distribution pair (U,V) leave undetermined?
+// (free coordinate == the data is replicated, or -- on the reduce side -- partially summed, along it)
+inline void free_coords(int u, int v, bool& mcFree, bool& mrFree) {
+    auto uses_mc = [](int d) { return d == MC || d == VC || d == VR; };
+    auto uses_mr = [](int d) { return d == MR || d == VC || d == VR; };
+    mcFree = !(uses_mc(u) || uses_mc(v));
+    mrFree = !(uses_mr(u) || uses_mr(v));
+}
+
+}  // namespace hyd

@@ -1,0 +1,53 @@
+// Process grid object behind hyd_grid (reference: El::Grid, include/El/core/Grid.hpp:15-146,
+// src/core/Grid.cpp:66-216).  Owns the communication world handle, this rank's grid
+// coordinates and the persistent staging workspaces that replace the reference's per-call
+// simple_buffer allocations (include/hydrogen/utils/SimpleBuffer.hpp; CUB pool, src/core/imports/cub.cpp).
+#pragma once
+#include "comm.h"
+#include "dist.h"
+#include <cuda_runtime.h>
+
+namespace hyd {
+
+constexpr int kSlots = 4;  // independent in-flight redistributions (SUMMA double-buffers two panels)
+
+struct Workspace {
+    char* buf = nullptr;
+    size_t cap = 0;
+};
+
+struct Grid {
+    World* world = nullptr;
+    bool owns_world = false;
+    GridShape shape;
+    int rank = 0, mc = 0, mr = 0;
+    Workspace ws[kSlots];
+    // SUMMA engine resources (created lazily)
+    cudaStream_t comm_stream[2] = {nullptr, nullptr};
+    cudaEvent_t ev_panel_ready[2] = {nullptr, nullptr}, ev_panel_free[2] = {nullptr, nullptr};
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    Workspace panel[4];  // gathered panels (A/B x double buffer) or reduce temporaries
+    bool overlap = true;
+    int sm_reserve = 8;  // SMs the local GEMM leaves to NCCL / pack kernels while overlapping
+    long long launches = 0;
+
+    int vc() const { return shape.vc(mc, mr); }
+    int vr() const { return shape.vr(mc, mr); }
+};
+
+int ws_reserve(Workspace& w, size_t bytes);
+void grid_destroy(Grid* g);
+
+// dst := src (or src^T), any pair of supported element distributions / alignments.
+template <typename T>
+int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot, cudaStream_t s);
+// dst += alpha * (sum over the ranks along which src is a partial sum)  (optionally of src^T)
+template <typename T>
+int reduce_into(Grid& g, T alpha, const DM& src, const DM& dst, bool transpose, int slot, cudaStream_t s);
+
+// view of rows [i0,i0+h) x cols [j0,j0+w) of a distributed matrix, as seen by rank (mc,mr)
+DM view(const GridShape& g, const DM& a, int mc, int mr, i64 i0, i64 j0, i64 h, i64 w, int elem_size);
+
+extern long long g_launches;  // kernels launched by this library in this process
+
+}  // namespace hyd

@@ -22,6 +22,12 @@ tensor_map_encode_fn tensor_map_encode();
 int lgemm_f64(int tA, int tB, long long m, long long n, long long k, double alpha, const double* A,
               long long lda, const double* B, long long ldb, double beta, double* C, long long ldc,
               cudaStream_t s);
+int lgemm_f64_ex(int tA, int tB, long long m, long long n, long long k, double alpha, const double* A,
+                 long long lda, const double* B, long long ldb, double beta, double* C, long long ldc,
+                 cudaStream_t s, int sm_reserve);
+int lgemm_f32_ex(int tA, int tB, long long m, long long n, long long k, float alpha, const float* A,
+                 long long lda, const float* B, long long ldb, float beta, float* C, long long ldc,
+                 cudaStream_t s, int sm_reserve);
 int lgemm_f32(int tA, int tB, long long m, long long n, long long k, float alpha, const float* A,
               long long lda, const float* B, long long ldb, float beta, float* C, long long ldc,
               cudaStream_t s);

@@ -1,0 +1,174 @@
+// Lattice copy / reduce kernels: the pack and unpack side of every redistribution.
+//
+// A "lattice" is an nr x nc sub-grid of a column-major local matrix picked by two
+// arithmetic progressions (rows r0 + a*rstep, columns c0 + b*cstep).  Every pack /
+// unpack loop of the reference (copy::util::InterleaveMatrix, {Row,Col}Strided{Pack,Unpack},
+// Partial{Row,Col}Strided*, Strided{Pack,Unpack}: include/El/blas_like/level1/Copy/util.hpp:122-230,
+// 363-533,671-722; GPU forms :244-421 = one cudaMemcpy2DAsync / copy_2d_kernel per peer)
+// is a set of such lattices, one per peer.  Here ALL peers of a redistribution are
+// served by ONE launch: blockIdx.y selects the peer's descriptor, blockIdx.x strides
+// over that lattice's tiles.  Index math is 64-bit (32768^2 locals overflow int32).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace hyd {
+
+typedef long long i64;
+
+// logical element (a,b), a < nr, b < nc:  dst[a*d_rs + b*d_cs] = src[a*s_rs + b*s_cs]
+// (absolute base pointers, so one batch can mix staging buffers and matrices)
+struct CopyDesc {
+    const void* src;
+    void* dst;
+    i64 s_rs, s_cs;
+    i64 d_rs, d_cs;
+    i64 nr, nc;
+};
+constexpr int kMaxDesc = 24;
+struct CopyBatch {
+    CopyDesc d[kMaxDesc];
+    int n;
+};
+
+// dst lattice += alpha * sum_{q<nq} member[q][a + b*nr]   (fixed ascending member order)
+constexpr int kMaxMembers = 16;
+struct ReduceDesc {
+    void* dst;
+    i64 d_rs, d_cs;
+    i64 nr, nc;
+    const void* member[kMaxMembers];
+    int nq;
+};
+constexpr int kMaxRDesc = 8;
+struct ReduceBatch {
+    ReduceDesc d[kMaxRDesc];
+    int n;
+};
+
+template <typename T> struct Vec16;
+template <> struct Vec16<double> { typedef double2 type; static constexpr int N = 2; };
+template <> struct Vec16<float> { typedef float4 type; static constexpr int N = 4; };
+
+// Tile: 32 x 32 elements through shared memory when the source is contiguous along b
+// and the destination along a (a transposing pack); otherwise straight copies with the
+// thread index along a, 16-byte vectors when both sides are contiguous and aligned.
+template <typename T>
+__global__ void __launch_bounds__(256) lattice_copy_kernel(const __grid_constant__ CopyBatch batch) {
+    const CopyDesc& D = batch.d[blockIdx.y];
+    const i64 nr = D.nr, nc = D.nc;
+    if (nr == 0 || nc == 0) return;
+    const T* __restrict__ s = static_cast<const T*>(D.src);
+    T* __restrict__ d = static_cast<T*>(D.dst);
+    constexpr int V = Vec16<T>::N;
+    typedef typename Vec16<T>::type VT;
+
+    if (D.s_rs == 1 && D.d_rs == 1) {
+        const bool vec_ok = (nr >= V) && (D.s_cs % V == 0) && (D.d_cs % V == 0) &&
+                            (((uintptr_t)s % 16) == 0) && (((uintptr_t)d % 16) == 0);
+        if (vec_ok) {
+            // contiguous columns on both sides: 256 threads x 16 B along a, 4 columns per pass
+            const i64 nrv = nr / V;
+            const i64 chunks_a = (nrv + 255) / 256;
+            const i64 col_groups = (nc + 3) / 4;
+            for (i64 tile = blockIdx.x; tile < chunks_a * col_groups; tile += gridDim.x) {
+                const i64 ca = tile % chunks_a, cg = tile / chunks_a;
+                const i64 av = ca * 256 + threadIdx.x;
+                const i64 b0 = cg * 4;
+                if (av < nrv) {
+                    VT v[4];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+                        if (b0 + q < nc) v[q] = __ldg(reinterpret_cast<const VT*>(s + (b0 + q) * D.s_cs) + av);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+                        if (b0 + q < nc) reinterpret_cast<VT*>(d + (b0 + q) * D.d_cs)[av] = v[q];
+                }
+                if (ca == 0) {  // scalar tail rows
+                    const i64 tail = nr - nrv * V;
+                    for (i64 e = threadIdx.x; e < tail * 4; e += 256) {
+                        const i64 a = nrv * V + e % tail, b = b0 + e / tail;
+                        if (b < nc) d[a + b * D.d_cs] = s[a + b * D.s_cs];
+                    }
+                }
+            }
+            return;
+        }
+    }
+    if (D.s_cs == 1 && D.d_rs == 1 && D.s_rs != 1) {
+        // transposing: read along b (source-contiguous), write along a (destination-contiguous)
+        __shared__ T tile_s[32][33];
+        const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+        const i64 ta = (nr + 31) / 32, tb = (nc + 31) / 32;
+        for (i64 tile = blockIdx.x; tile < ta * tb; tile += gridDim.x) {
+            const i64 a0 = (tile % ta) * 32, b0 = (tile / ta) * 32;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const i64 a = a0 + ty + 8 * q, b = b0 + tx;
+                if (a < nr && b < nc) tile_s[ty + 8 * q][tx] = s[a * D.s_rs + b];
+            }
+            __syncthreads();
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const i64 a = a0 + tx, b = b0 + ty + 8 * q;
+                if (a < nr && b < nc) d[a + b * D.d_cs] = tile_s[tx][ty + 8 * q];
+            }
+            __syncthreads();
+        }
+        return;
+    }
+    {
+        // general strides: thread index along a, 8 columns per pass
+        const i64 chunks_a = (nr + 255) / 256;
+        const i64 col_groups = (nc + 7) / 8;
+        for (i64 tile = blockIdx.x; tile < chunks_a * col_groups; tile += gridDim.x) {
+            const i64 a = (tile % chunks_a) * 256 + threadIdx.x;
+            const i64 b0 = (tile / chunks_a) * 8;
+            if (a < nr) {
+                T v[8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q)
+                    if (b0 + q < nc) v[q] = s[a * D.s_rs + (b0 + q) * D.s_cs];
+#pragma unroll
+                for (int q = 0; q < 8; ++q)
+                    if (b0 + q < nc) d[a * D.d_rs + (b0 + q) * D.d_cs] = v[q];
+            }
+        }
+    }
+}
+
+// Reduce-side unpack (reference: ReduceScatter + axpy::util::InterleaveMatrixUpdate,
+// include/El/blas_like/level1/AxpyContract.hpp:60-86,  Axpy/util.hpp:23-51):
+// the member partial sums are added in ascending member order, then B += alpha * sum
+// (one rounding for alpha*sum, one for the add: no FMA contraction, as `B += alpha*A`
+// compiled without -fmad would give; see __dmul_rn/__dadd_rn below).
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
+
+template <typename T>
+__global__ void __launch_bounds__(256) lattice_reduce_kernel(T alpha, const __grid_constant__ ReduceBatch batch) {
+    const ReduceDesc& D = batch.d[blockIdx.y];
+    const i64 nr = D.nr, nc = D.nc;
+    if (nr == 0 || nc == 0) return;
+    T* d = static_cast<T*>(D.dst);
+    const i64 chunks_a = (nr + 255) / 256;
+    const i64 col_groups = (nc + 3) / 4;
+    for (i64 tile = blockIdx.x; tile < chunks_a * col_groups; tile += gridDim.x) {
+        const i64 a = (tile % chunks_a) * 256 + threadIdx.x;
+        const i64 b0 = (tile / chunks_a) * 4;
+        if (a >= nr) continue;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const i64 b = b0 + q;
+            if (b >= nc) break;
+            T acc = static_cast<const T*>(D.member[0])[a + b * nr];
+            for (int m = 1; m < D.nq; ++m) acc = add_rn(acc, static_cast<const T*>(D.member[m])[a + b * nr]);
+            T* p = d + a * D.d_rs + b * D.d_cs;
+            *p = add_rn(*p, mul_rn(alpha, acc));
+        }
+    }
+}
+
+}  // namespace hyd

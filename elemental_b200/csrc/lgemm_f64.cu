@@ -303,7 +303,7 @@ static bool make_map_f64(CUtensorMap* map, int type, const double* base, long lo
 
 template <int TA, int TB>
 static cudaError_t launch_tma(const CUtensorMap& ma, const CUtensorMap& mb, double* C, long long ldc,
-                              int M, int N, int K, double alpha, double beta, cudaStream_t s) {
+                              int M, int N, int K, double alpha, double beta, cudaStream_t s, int sm_reserve) {
     static bool attr_set = false;
     auto kern = dgemm_tma_kernel<TA, TB>;
     if (!attr_set) {
@@ -312,7 +312,7 @@ static cudaError_t launch_tma(const CUtensorMap& ma, const CUtensorMap& mb, doub
         attr_set = true;
     }
     const int tiles_m = (M + BM - 1) / BM, tiles_n = (N + BN - 1) / BN;
-    const int grid = min(tiles_m * tiles_n, num_sms());
+    const int grid = max(1, min(tiles_m * tiles_n, num_sms() - sm_reserve));
     const int group_m = 16;
     kern<<<grid, kThreads, kSmemBytes, s>>>(ma, mb, C, ldc, M, N, K, alpha, beta, tiles_m, tiles_n, group_m);
     return cudaGetLastError();
@@ -321,6 +321,13 @@ static cudaError_t launch_tma(const CUtensorMap& ma, const CUtensorMap& mb, doub
 int lgemm_f64(int tA, int tB, long long m, long long n, long long k, double alpha, const double* A,
               long long lda, const double* B, long long ldb, double beta, double* C, long long ldc,
               cudaStream_t s) {
+    return lgemm_f64_ex(tA, tB, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, s, 0);
+}
+
+// sm_reserve: SMs left free for concurrently running communication kernels (SUMMA overlap)
+int lgemm_f64_ex(int tA, int tB, long long m, long long n, long long k, double alpha, const double* A,
+                 long long lda, const double* B, long long ldb, double beta, double* C, long long ldc,
+                 cudaStream_t s, int sm_reserve) {
     if (m < 0 || n < 0 || k < 0) return set_error("hyd_lgemm_f64: negative dimension");
     if (m == 0 || n == 0) return 0;
     if (m > INT32_MAX || n > INT32_MAX || k > INT32_MAX) return set_error("hyd_lgemm_f64: dimension exceeds 2^31-1");
@@ -342,10 +349,10 @@ int lgemm_f64(int tA, int tB, long long m, long long n, long long k, double alph
     if (tma_ok && make_map_f64(&ma, typeA, A, lda, (int)m, (int)k, BM) &&
         make_map_f64(&mb, typeB, B, ldb, (int)n, (int)k, BN)) {
         cudaError_t e;
-        if (typeA == MT && typeB == MT) e = launch_tma<MT, MT>(ma, mb, C, ldc, m, n, k, alpha, beta, s);
-        else if (typeA == MT && typeB == KT) e = launch_tma<MT, KT>(ma, mb, C, ldc, m, n, k, alpha, beta, s);
-        else if (typeA == KT && typeB == MT) e = launch_tma<KT, MT>(ma, mb, C, ldc, m, n, k, alpha, beta, s);
-        else e = launch_tma<KT, KT>(ma, mb, C, ldc, m, n, k, alpha, beta, s);
+        if (typeA == MT && typeB == MT) e = launch_tma<MT, MT>(ma, mb, C, ldc, m, n, k, alpha, beta, s, sm_reserve);
+        else if (typeA == MT && typeB == KT) e = launch_tma<MT, KT>(ma, mb, C, ldc, m, n, k, alpha, beta, s, sm_reserve);
+        else if (typeA == KT && typeB == MT) e = launch_tma<KT, MT>(ma, mb, C, ldc, m, n, k, alpha, beta, s, sm_reserve);
+        else e = launch_tma<KT, KT>(ma, mb, C, ldc, m, n, k, alpha, beta, s, sm_reserve);
         return check_cuda(e, "dgemm_tma_kernel");
     }
     dim3 grid((unsigned)((m + 63) / 64), (unsigned)((n + 63) / 64));

@@ -1,0 +1,338 @@
+// Redistribution engine: dst := src (or src^T) and dst += alpha * sum(src partials)
+// between any two supported element-cyclic distributions with arbitrary alignments.
+//
+// What it replaces in the reference (per (dst,src) pair one of, or a chain of):
+//   copy::RowAllGather / ColAllGather / Partial{Row,Col}AllGather / {Row,Col}AllToAllDemote /
+//   {Row,Col}AllToAllPromote / Exchange / {Col,Row}wiseVectorExchange / *Filter / TransposeDist
+//     (include/El/blas_like/level1/Copy/*.hpp, dispatch tables src/core/DistMatrix/ElementMatrix/*.cpp),
+//   dist Transpose (include/El/blas_like/level1/Transpose.hpp:191-250, Transpose/*.hpp),
+//   AxpyContract / Contract / TransposeAxpyContract (AxpyContract.hpp:14-544, Contract.hpp,
+//     TransposeAxpyContract.hpp:14-48).
+//
+// B200-first design: every such operation is ONE plan of per-peer lattices (closed-form CRT
+// intersection of the source rank's and the destination rank's index progressions, dist.h),
+// executed as  pack kernel (all peers, one launch)  ->  one NCCL group of send/recv over
+// NVSwitch  ->  unpack kernel (all peers, one launch).  Multi-hop chains of the reference
+// (e.g. [MC,MR] -> [VC,*] -> [VR,*] -> transpose -> [*,MR]) collapse to one hop because every
+// peer is one NVSwitch hop away; the transpose is folded into the pack.  The element
+// permutation is identical to the reference's, so results are bit-exact.
+#include "grid.h"
+#include "hyd_internal.h"
+#include "lattice.cuh"
+#include <algorithm>
+#include <vector>
+
+namespace hyd {
+
+long long g_launches = 0;
+
+int ws_reserve(Workspace& w, size_t bytes) {
+    if (bytes <= w.cap) return 0;
+    if (w.buf) {
+        if (check_cuda(cudaDeviceSynchronize(), "workspace sync")) return 1;
+        cudaFree(w.buf);
+        w.buf = nullptr;
+        w.cap = 0;
+    }
+    size_t cap = std::max(bytes + bytes / 4, (size_t)1 << 20);
+    cap = (cap + 255) & ~(size_t)255;
+    if (check_cuda(cudaMalloc(&w.buf, cap), "workspace cudaMalloc")) return 1;
+    w.cap = cap;
+    return 0;
+}
+
+DM view(const GridShape& g, const DM& a, int mc, int mr, i64 i0, i64 j0, i64 h, i64 w, int es) {
+    const LocalShape L = local_shape(g, a, mc, mr);
+    DM v = a;
+    v.height = h;
+    v.width = w;
+    v.colAlign = (int)mod_(a.colAlign + i0, L.colStride);
+    v.rowAlign = (int)mod_(a.rowAlign + j0, L.rowStride);
+    const i64 iLoc = length_(i0, L.colShift, L.colStride);
+    const i64 jLoc = length_(j0, L.rowShift, L.rowStride);
+    v.buf = a.buf ? (char*)a.buf + (iLoc + jLoc * a.ldim) * es : nullptr;
+    return v;
+}
+
+namespace {
+
+struct Msg {
+    int peer;
+    Prog pa, pb;  // logical rows / cols of the message, in destination orientation
+    i64 count() const { return pa.count * pb.count; }
+    i64 off = 0;  // byte offset inside the send or recv region
+};
+
+inline void progs(const DM& src, bool transpose, const LocalShape& Ls, const LocalShape& Ld, Prog& pa, Prog& pb) {
+    if (!transpose) {
+        pa = intersect(src.height, Ls.colShift, Ls.colStride, Ld.colShift, Ld.colStride);
+        pb = intersect(src.width, Ls.rowShift, Ls.rowStride, Ld.rowShift, Ld.rowStride);
+    } else {
+        pa = intersect(src.width, Ls.rowShift, Ls.rowStride, Ld.colShift, Ld.colStride);
+        pb = intersect(src.height, Ls.colShift, Ls.colStride, Ld.rowShift, Ld.rowStride);
+    }
+}
+
+template <typename T>
+CopyDesc pack_desc(const DM& src, bool transpose, const Msg& m, void* out) {
+    CopyDesc d;
+    const T* base = static_cast<const T*>(src.buf);
+    if (!transpose) {
+        d.src = base + m.pa.src0 + m.pb.src0 * src.ldim;
+        d.s_rs = m.pa.srcStep;
+        d.s_cs = m.pb.srcStep * src.ldim;
+    } else {  // logical rows run over the source's local columns
+        d.src = base + m.pb.src0 + m.pa.src0 * src.ldim;
+        d.s_rs = m.pa.srcStep * src.ldim;
+        d.s_cs = m.pb.srcStep;
+    }
+    d.dst = out;
+    d.d_rs = 1;
+    d.d_cs = m.pa.count;
+    d.nr = m.pa.count;
+    d.nc = m.pb.count;
+    return d;
+}
+template <typename T>
+void dst_lattice(const DM& dst, const Msg& m, void*& p, i64& rs, i64& cs) {
+    p = static_cast<T*>(dst.buf) + m.pa.dst0 + m.pb.dst0 * dst.ldim;
+    rs = m.pa.dstStep;
+    cs = m.pb.dstStep * dst.ldim;
+}
+
+template <typename T>
+int launch_copies(const std::vector<CopyDesc>& v, cudaStream_t s) {
+    for (size_t i0 = 0; i0 < v.size(); i0 += kMaxDesc) {
+        CopyBatch b;
+        b.n = (int)std::min((size_t)kMaxDesc, v.size() - i0);
+        i64 mx = 0;
+        for (int i = 0; i < b.n; ++i) { b.d[i] = v[i0 + i]; mx = std::max(mx, b.d[i].nr * b.d[i].nc); }
+        if (mx == 0) continue;
+        const i64 want = (mx + 4095) / 4096;
+        const i64 cap = std::max<i64>(1, (i64)num_sms() * 8 / b.n);
+        dim3 grid((unsigned)std::max<i64>(1, std::min(want, cap)), (unsigned)b.n);
+        lattice_copy_kernel<T><<<grid, 256, 0, s>>>(b);
+        ++g_launches;
+        if (check_cuda(cudaGetLastError(), "lattice_copy_kernel")) return 1;
+    }
+    return 0;
+}
+
+template <typename T>
+int launch_reduces(const std::vector<ReduceDesc>& v, T alpha, cudaStream_t s) {
+    for (size_t i0 = 0; i0 < v.size(); i0 += kMaxRDesc) {
+        ReduceBatch b;
+        b.n = (int)std::min((size_t)kMaxRDesc, v.size() - i0);
+        i64 mx = 0;
+        for (int i = 0; i < b.n; ++i) { b.d[i] = v[i0 + i]; mx = std::max(mx, b.d[i].nr * b.d[i].nc); }
+        if (mx == 0) continue;
+        const i64 want = (mx + 1023) / 1024;
+        const i64 cap = std::max<i64>(1, (i64)num_sms() * 8 / b.n);
+        dim3 grid((unsigned)std::max<i64>(1, std::min(want, cap)), (unsigned)b.n);
+        lattice_reduce_kernel<T><<<grid, 256, 0, s>>>(alpha, b);
+        ++g_launches;
+        if (check_cuda(cudaGetLastError(), "lattice_reduce_kernel")) return 1;
+    }
+    return 0;
+}
+
+inline i64 align16(i64 x) { return (x + 15) & ~(i64)15; }
+
+int check_pair(const GridShape& sh, const DM& src, const DM& dst, bool transpose, const char* who) {
+    if (!pair_supported(src.colDist, src.rowDist) || !pair_supported(dst.colDist, dst.rowDist))
+        return set_error("%s: unsupported distribution pair (only MC/MR/VC/VR/STAR element distributions)", who);
+    const i64 sh_ = transpose ? src.width : src.height, sw_ = transpose ? src.height : src.width;
+    if (dst.height != sh_ || dst.width != sw_)
+        return set_error("%s: nonconformal: src %lldx%lld%s dst %lldx%lld", who, src.height, src.width,
+                         transpose ? "^T" : "", dst.height, dst.width);
+    if (src.colAlign < 0 || src.colAlign >= sh.stride(src.colDist) || src.rowAlign < 0 ||
+        src.rowAlign >= sh.stride(src.rowDist) || dst.colAlign < 0 || dst.colAlign >= sh.stride(dst.colDist) ||
+        dst.rowAlign < 0 || dst.rowAlign >= sh.stride(dst.rowDist))
+        return set_error("%s: alignment out of range", who);
+    return 0;
+}
+
+}  // namespace
+
+template <typename T>
+int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot, cudaStream_t s) {
+    const GridShape& sh = g.shape;
+    if (check_pair(sh, src, dst, transpose, "hyd_redist")) return 1;
+    if (src.height == 0 || src.width == 0) return 0;
+    const int P = sh.size();
+    bool mcFree, mrFree;
+    free_coords(src.colDist, src.rowDist, mcFree, mrFree);
+    const LocalShape Ls_me = local_shape(sh, src, g.mc, g.mr), Ld_me = local_shape(sh, dst, g.mc, g.mr);
+    if (Ls_me.lh > 0 && Ls_me.lw > 0 && (!src.buf || src.ldim < Ls_me.lh))
+        return set_error("hyd_redist: bad source buffer / ldim");
+    if (Ld_me.lh > 0 && Ld_me.lw > 0 && (!dst.buf || dst.ldim < Ld_me.lh))
+        return set_error("hyd_redist: bad destination buffer / ldim");
+
+    std::vector<Msg> sends, recvs;
+    Msg self_msg;
+    bool has_self = false;
+    i64 send_bytes = 0, recv_bytes = 0;
+    for (int p = 0; p < P; ++p) {
+        int pmc, pmr;
+        sh.coords(p, pmc, pmr);
+        const bool same_free = (!mcFree || pmc == g.mc) && (!mrFree || pmr == g.mr);
+        if (!same_free) continue;
+        Msg m;
+        m.peer = p;
+        if (p == g.rank) {
+            progs(src, transpose, Ls_me, Ld_me, m.pa, m.pb);
+            if (m.count() > 0) { self_msg = m; has_self = true; }
+            continue;
+        }
+        progs(src, transpose, Ls_me, local_shape(sh, dst, pmc, pmr), m.pa, m.pb);
+        if (m.count() > 0) { m.off = send_bytes; send_bytes = align16(send_bytes + m.count() * (i64)sizeof(T)); sends.push_back(m); }
+        progs(src, transpose, local_shape(sh, src, pmc, pmr), Ld_me, m.pa, m.pb);
+        if (m.count() > 0) { m.off = recv_bytes; recv_bytes = align16(recv_bytes + m.count() * (i64)sizeof(T)); recvs.push_back(m); }
+    }
+    Workspace& w = g.ws[slot];
+    if (send_bytes + recv_bytes > 0 && ws_reserve(w, (size_t)(send_bytes + recv_bytes))) return 1;
+    char* send_base = w.buf;
+    char* recv_base = w.buf + send_bytes;
+
+    // pack (+ the local part straight from source lattice to destination lattice)
+    std::vector<CopyDesc> descs;
+    for (const Msg& m : sends) descs.push_back(pack_desc<T>(src, transpose, m, send_base + m.off));
+    if (has_self) {
+        CopyDesc d = pack_desc<T>(src, transpose, self_msg, nullptr);
+        dst_lattice<T>(dst, self_msg, d.dst, d.d_rs, d.d_cs);
+        descs.push_back(d);
+    }
+    if (launch_copies<T>(descs, s)) return 1;
+
+    if (!sends.empty() || !recvs.empty() || P > 1) {
+        std::vector<i64> sc(P, 0), so(P, 0), rc(P, 0), ro(P, 0);
+        for (const Msg& m : sends) { sc[m.peer] = m.count() * (i64)sizeof(T); so[m.peer] = m.off; }
+        for (const Msg& m : recvs) { rc[m.peer] = m.count() * (i64)sizeof(T); ro[m.peer] = m.off; }
+        if (g.world->exchange(send_base, sc.data(), so.data(), recv_base, rc.data(), ro.data(), s)) return 1;
+    }
+    descs.clear();
+    for (const Msg& m : recvs) {
+        CopyDesc d;
+        d.src = recv_base + m.off;
+        d.s_rs = 1;
+        d.s_cs = m.pa.count;
+        dst_lattice<T>(dst, m, d.dst, d.d_rs, d.d_cs);
+        d.nr = m.pa.count;
+        d.nc = m.pb.count;
+        descs.push_back(d);
+    }
+    return launch_copies<T>(descs, s);
+}
+
+template <typename T>
+int reduce_into(Grid& g, T alpha, const DM& src, const DM& dst, bool transpose, int slot, cudaStream_t s) {
+    const GridShape& sh = g.shape;
+    if (check_pair(sh, src, dst, transpose, "hyd_axpy_contract")) return 1;
+    if (src.height == 0 || src.width == 0) return 0;
+    const int P = sh.size();
+    bool mcFree, mrFree;
+    free_coords(src.colDist, src.rowDist, mcFree, mrFree);
+    const LocalShape Ls_me = local_shape(sh, src, g.mc, g.mr), Ld_me = local_shape(sh, dst, g.mc, g.mr);
+    if (Ls_me.lh > 0 && Ls_me.lw > 0 && (!src.buf || src.ldim < Ls_me.lh))
+        return set_error("hyd_axpy_contract: bad source buffer / ldim");
+    if (Ld_me.lh > 0 && Ld_me.lw > 0 && (!dst.buf || dst.ldim < Ld_me.lh))
+        return set_error("hyd_axpy_contract: bad destination buffer / ldim");
+
+    struct Group { int kmc, kmr; Msg m; std::vector<i64> member_off; };
+    std::vector<Msg> sends, recvs;
+    std::vector<Group> groups;
+    i64 send_bytes = 0, recv_bytes = 0, self_off = -1;
+    Msg self_msg;
+    // senders: every rank contributes its partial sum to every destination that owns the element
+    for (int p = 0; p < P; ++p) {
+        if (p == g.rank) continue;
+        int pmc, pmr;
+        sh.coords(p, pmc, pmr);
+        Msg m;
+        m.peer = p;
+        progs(src, transpose, Ls_me, local_shape(sh, dst, pmc, pmr), m.pa, m.pb);
+        if (m.count() > 0) { m.off = send_bytes; send_bytes = align16(send_bytes + m.count() * (i64)sizeof(T)); sends.push_back(m); }
+    }
+    // receivers: ascending VC rank fixes the summation order (the oracle uses the same order)
+    for (int v = 0; v < P; ++v) {
+        const int pmc = v % sh.r, pmr = v / sh.r;
+        const int p = sh.rank_of(pmc, pmr);
+        Msg m;
+        m.peer = p;
+        progs(src, transpose, local_shape(sh, src, pmc, pmr), Ld_me, m.pa, m.pb);
+        if (m.count() == 0) continue;
+        m.off = recv_bytes;
+        recv_bytes = align16(recv_bytes + m.count() * (i64)sizeof(T));
+        recvs.push_back(m);
+        if (p == g.rank) { self_off = m.off; self_msg = m; }
+        const int kmc = mcFree ? -1 : pmc, kmr = mrFree ? -1 : pmr;
+        Group* grp = nullptr;
+        for (auto& q : groups) if (q.kmc == kmc && q.kmr == kmr) grp = &q;
+        if (!grp) { groups.push_back(Group{kmc, kmr, m, {}}); grp = &groups.back(); }
+        grp->member_off.push_back(m.off);
+    }
+    Workspace& w = g.ws[slot];
+    if (send_bytes + recv_bytes > 0 && ws_reserve(w, (size_t)(send_bytes + recv_bytes))) return 1;
+    char* send_base = w.buf;
+    char* recv_base = w.buf + send_bytes;
+
+    std::vector<CopyDesc> descs;
+    for (const Msg& m : sends) descs.push_back(pack_desc<T>(src, transpose, m, send_base + m.off));
+    if (self_off >= 0) descs.push_back(pack_desc<T>(src, transpose, self_msg, recv_base + self_off));
+    if (launch_copies<T>(descs, s)) return 1;
+
+    if (P > 1) {
+        std::vector<i64> sc(P, 0), so(P, 0), rc(P, 0), ro(P, 0);
+        for (const Msg& m : sends) { sc[m.peer] = m.count() * (i64)sizeof(T); so[m.peer] = m.off; }
+        for (const Msg& m : recvs) if (m.peer != g.rank) { rc[m.peer] = m.count() * (i64)sizeof(T); ro[m.peer] = m.off; }
+        if (g.world->exchange(send_base, sc.data(), so.data(), recv_base, rc.data(), ro.data(), s)) return 1;
+    }
+
+    std::vector<ReduceDesc> rdescs;
+    for (const Group& q : groups) {
+        for (size_t m0 = 0; m0 < q.member_off.size(); m0 += kMaxMembers) {
+            ReduceDesc d;
+            i64 rs, cs;
+            dst_lattice<T>(dst, q.m, d.dst, rs, cs);
+            d.d_rs = rs;
+            d.d_cs = cs;
+            d.nr = q.m.pa.count;
+            d.nc = q.m.pb.count;
+            d.nq = (int)std::min((size_t)kMaxMembers, q.member_off.size() - m0);
+            for (int i = 0; i < d.nq; ++i) d.member[i] = recv_base + q.member_off[m0 + i];
+            rdescs.push_back(d);
+        }
+    }
+    // groups touch disjoint destination lattices, but chunks of one group do not: launch chunk by chunk
+    bool chunked = false;
+    for (const Group& q : groups) if (q.member_off.size() > (size_t)kMaxMembers) chunked = true;
+    if (!chunked) return launch_reduces<T>(rdescs, alpha, s);
+    for (const ReduceDesc& d : rdescs) {
+        std::vector<ReduceDesc> one(1, d);
+        if (launch_reduces<T>(one, alpha, s)) return 1;
+    }
+    return 0;
+}
+
+template int redistribute<double>(Grid&, const DM&, const DM&, bool, int, cudaStream_t);
+template int redistribute<float>(Grid&, const DM&, const DM&, bool, int, cudaStream_t);
+template int reduce_into<double>(Grid&, double, const DM&, const DM&, bool, int, cudaStream_t);
+template int reduce_into<float>(Grid&, float, const DM&, const DM&, bool, int, cudaStream_t);
+
+void grid_destroy(Grid* g) {
+    if (!g) return;
+    cudaDeviceSynchronize();
+    for (auto& w : g->ws) if (w.buf) cudaFree(w.buf);
+    for (auto& w : g->panel) if (w.buf) cudaFree(w.buf);
+    for (int i = 0; i < 2; ++i) {
+        if (g->comm_stream[i]) cudaStreamDestroy(g->comm_stream[i]);
+        if (g->ev_panel_ready[i]) cudaEventDestroy(g->ev_panel_ready[i]);
+        if (g->ev_panel_free[i]) cudaEventDestroy(g->ev_panel_free[i]);
+    }
+    if (g->ev_fork) cudaEventDestroy(g->ev_fork);
+    if (g->ev_join) cudaEventDestroy(g->ev_join);
+    if (g->owns_world) delete g->world;
+    delete g;
+}
+
+}  // namespace hyd

@@ -1,0 +1,318 @@
+// Distributed GEMM: C := alpha op(A) op(B) + beta C on an r x c grid -- SUMMA A / B / C / Dot.
+//
+// Reference entry point and algorithms this replaces:
+//   El::Gemm(orientA,orientB,alpha,A,B,beta,C,alg)   src/blas_like/level3/Gemm.cpp:278-307
+//     -> Scale(beta,C) then gemm::SUMMA_{NN,NT,TN,TT}  Gemm/NN.hpp:881-932, NT.hpp:353-403,
+//        TN.hpp:350-400, TT.hpp:379-437 (GEMM_DEFAULT heuristic, blockSizeDot = 2000)
+//     -> SUMMA_xxA (NN.hpp:107-206, NT.hpp:15-55, TN.hpp:15-57, TT.hpp:17-61)
+//        SUMMA_xxB (NN.hpp:244-287, NT.hpp:96-138, TN.hpp:98-137, TT.hpp:105-152)
+//        SUMMA_xxC (NN.hpp:325-367, NT.hpp:178-221, TN.hpp:178-217, TT.hpp:195-240)
+//        SUMMA_xxDot (NN.hpp:792-841, NT.hpp:265-310, TN.hpp:262-307, TT.hpp:287-333)
+//
+// Not a port: one engine serves all sixteen variants.
+//   C   : per k-panel gather op(A)(:,K1) as [MC,*] and op(B)(K1,:)^T as [MR,*] (each ONE
+//         lattice exchange, transposes folded into the pack), then a local rank-nb update
+//         C_loc += alpha Ap Bp^T with the sm_100a DMMA kernel.  Panels are double-buffered and
+//         gathered on a separate stream so NVLink traffic hides under the previous update.
+//   A/B : the moving operand's panel is gathered in the layout the stationary operand's local
+//         block needs, multiplied locally, and the partial result is reduce-scattered straight
+//         into the [MC,MR] panel of C (one lattice reduce; the reference's Contract -> [MR,MC]
+//         -> Axpy detour is a single hop here).
+//   Dot : operands in [*,VC]/[VC,*], local products of <= 2000 x 2000 tiles, P-wide lattice reduce.
+// The k-summation order differs from the reference only in rounding (tolerance parity);
+// the data movement is the same permutation (bit-exact).
+#include "grid.h"
+#include "hyd_internal.h"
+#include <algorithm>
+#include <type_traits>
+#include <vector>
+
+namespace hyd {
+
+template <typename T> __global__ void scale2d_kernel(i64 m, i64 n, T beta, T* __restrict__ C, i64 ldc) {
+    const i64 total = m * n;
+    for (i64 e = blockIdx.x * (i64)blockDim.x + threadIdx.x; e < total; e += (i64)gridDim.x * blockDim.x) {
+        const i64 j = e / m, i = e - j * m;
+        T* p = C + i + j * ldc;
+        *p = (beta == T(0)) ? T(0) : beta * *p;
+    }
+}
+
+template <typename T>
+int scale_local(i64 m, i64 n, T beta, T* C, i64 ldc, cudaStream_t s) {
+    if (m == 0 || n == 0 || beta == T(1)) return 0;
+    const i64 blocks = std::min<i64>((m * n + 1023) / 1024, (i64)num_sms() * 8);
+    scale2d_kernel<T><<<(unsigned)std::max<i64>(1, blocks), 256, 0, s>>>(m, n, beta, C, ldc);
+    ++g_launches;
+    return check_cuda(cudaGetLastError(), "scale2d_kernel");
+}
+template int scale_local<double>(i64, i64, double, double*, i64, cudaStream_t);
+template int scale_local<float>(i64, i64, float, float*, i64, cudaStream_t);
+
+namespace {
+
+template <typename T>
+int lgemm(int tA, int tB, i64 m, i64 n, i64 k, T alpha, const T* A, i64 lda, const T* B, i64 ldb, T beta, T* C,
+          i64 ldc, cudaStream_t s, int sm_reserve) {
+    ++g_launches;
+    if constexpr (std::is_same<T, double>::value)
+        return lgemm_f64_ex(tA, tB, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, s, sm_reserve);
+    else
+        return lgemm_f32_ex(tA, tB, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, s, sm_reserve);
+}
+
+inline i64 pad_ld(i64 lh, int es) {  // TMA wants 16-byte multiples; keep at least 1
+    const i64 q = 16 / es;
+    return std::max<i64>(q, (lh + q - 1) / q * q);
+}
+
+// temporary distributed matrix living in workspace `w`
+template <typename T>
+int make_tmp(Grid& g, Workspace& w, i64 h, i64 wd, int cd, int rd, int ca, int ra, DM& out) {
+    out = DM();
+    out.height = h; out.width = wd; out.colDist = cd; out.rowDist = rd; out.colAlign = ca; out.rowAlign = ra;
+    const LocalShape L = local_shape(g.shape, out, g.mc, g.mr);
+    out.ldim = pad_ld(L.lh, sizeof(T));
+    if (ws_reserve(w, (size_t)(out.ldim * std::max<i64>(L.lw, 1)) * sizeof(T))) return 1;
+    out.buf = w.buf;
+    return 0;
+}
+
+int ensure_engine(Grid& g) {
+    if (g.comm_stream[0]) return 0;
+    int lo, hi;
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);
+    for (int i = 0; i < 2; ++i) {
+        if (check_cuda(cudaStreamCreateWithPriority(&g.comm_stream[i], cudaStreamNonBlocking, hi), "stream create")) return 1;
+        cudaEventCreateWithFlags(&g.ev_panel_ready[i], cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&g.ev_panel_free[i], cudaEventDisableTiming);
+    }
+    cudaEventCreateWithFlags(&g.ev_fork, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&g.ev_join, cudaEventDisableTiming);
+    return 0;
+}
+
+
+// ---- SUMMA-C (stationary C) -------------------------------------------------
+template <typename T>
+int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, const DM& B, const DM& C, i64 nb,
+            cudaStream_t s) {
+    const GridShape& sh = g.shape;
+    const LocalShape Lc = local_shape(sh, C, g.mc, g.mr);
+    const int es = sizeof(T);
+    if (sh.size() == 1) {
+        // 1x1 grid: [MC,*] and [MR,*] panels coincide with the operands' own storage
+        // (the reference degenerates to local copies, RowAllGather.hpp:35-38); feed views directly.
+        for (i64 k0 = 0; k0 < k; k0 += nb) {
+            const i64 kb = std::min(nb, k - k0);
+            const T* a = static_cast<const T*>(A.buf) + (oA ? k0 : k0 * A.ldim);
+            const T* b = static_cast<const T*>(B.buf) + (oB ? k0 * B.ldim : k0);
+            if (lgemm<T>(oA, oB, m, n, kb, alpha, a, A.ldim, b, B.ldim, T(1), static_cast<T*>(C.buf), C.ldim, s, 0))
+                return 1;
+        }
+        return 0;
+    }
+    if (ensure_engine(g)) return 1;
+    const bool overlap = g.overlap;
+    cudaStream_t cs = overlap ? g.comm_stream[0] : s;
+    if (overlap) {
+        if (check_cuda(cudaEventRecord(g.ev_fork, s), "fork")) return 1;
+        cudaStreamWaitEvent(cs, g.ev_fork, 0);
+    }
+    i64 step = 0;
+    for (i64 k0 = 0; k0 < k; k0 += nb, ++step) {
+        const i64 kb = std::min(nb, k - k0);
+        const int buf = (int)(step & 1);
+        DM Ap, Bp;
+        if (make_tmp<T>(g, g.panel[buf], m, nb, MC, STAR, C.colAlign, 0, Ap)) return 1;
+        if (make_tmp<T>(g, g.panel[2 + buf], n, nb, MR, STAR, C.rowAlign, 0, Bp)) return 1;
+        Ap.width = kb;
+        Bp.width = kb;
+        if (overlap && step >= 2) cudaStreamWaitEvent(cs, g.ev_panel_free[buf], 0);
+        const DM A1 = oA ? view(sh, A, g.mc, g.mr, k0, 0, kb, m, es) : view(sh, A, g.mc, g.mr, 0, k0, m, kb, es);
+        const DM B1 = oB ? view(sh, B, g.mc, g.mr, 0, k0, n, kb, es) : view(sh, B, g.mc, g.mr, k0, 0, kb, n, es);
+        if (redistribute<T>(g, A1, Ap, oA != 0, 0, cs)) return 1;
+        if (redistribute<T>(g, B1, Bp, oB == 0, 1, cs)) return 1;
+        if (overlap) {
+            cudaEventRecord(g.ev_panel_ready[buf], cs);
+            cudaStreamWaitEvent(s, g.ev_panel_ready[buf], 0);
+        }
+        if (lgemm<T>(0, 1, Lc.lh, Lc.lw, kb, alpha, static_cast<const T*>(Ap.buf), Ap.ldim,
+                     static_cast<const T*>(Bp.buf), Bp.ldim, T(1), static_cast<T*>(C.buf), C.ldim, s,
+                     overlap ? g.sm_reserve : 0))
+            return 1;
+        if (overlap) cudaEventRecord(g.ev_panel_free[buf], s);
+    }
+    return 0;
+}
+
+// ---- SUMMA-A (stationary A): panels over n, reduce over the comm A's k-dimension lives on ----
+template <typename T>
+int summa_a(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, const DM& B, const DM& C, i64 nb,
+            cudaStream_t s) {
+    const GridShape& sh = g.shape;
+    const LocalShape La = local_shape(sh, A, g.mc, g.mr);
+    const int es = sizeof(T);
+    for (i64 n0 = 0; n0 < n; n0 += nb) {
+        const i64 w = std::min(nb, n - n0);
+        // op(B)(:, n0:n0+w) is k x w; gather it with k distributed like A's k-dimension
+        DM Bp, D1;
+        const int kd = oA ? MC : MR;                     // where A's k index lives
+        const int ka = oA ? A.colAlign : A.rowAlign;
+        if (make_tmp<T>(g, g.panel[0], k, w, kd, STAR, ka, 0, Bp)) return 1;
+        const DM B1 = oB ? view(sh, B, g.mc, g.mr, n0, 0, w, k, es) : view(sh, B, g.mc, g.mr, 0, n0, k, w, es);
+        if (redistribute<T>(g, B1, Bp, oB != 0, 0, s)) return 1;
+        // D1 = alpha op(A_loc) Bp_loc : m_loc x w, [MC,*] (oA = N) or [MR,*] (oA = T), partial over the other comm
+        const int md = oA ? MR : MC;
+        const int ma = oA ? A.rowAlign : A.colAlign;
+        if (make_tmp<T>(g, g.panel[1], m, w, md, STAR, ma, 0, D1)) return 1;
+        const i64 mloc = oA ? La.lw : La.lh, kloc = oA ? La.lh : La.lw;
+        if (lgemm<T>(oA, 0, mloc, w, kloc, alpha, static_cast<const T*>(A.buf), A.ldim, static_cast<const T*>(Bp.buf),
+                     Bp.ldim, T(0), static_cast<T*>(D1.buf), D1.ldim, s, 0))
+            return 1;
+        if (kloc == 0 && scale_local<T>(mloc, w, T(0), static_cast<T*>(D1.buf), D1.ldim, s)) return 1;
+        const DM C1 = view(sh, C, g.mc, g.mr, 0, n0, m, w, es);
+        if (reduce_into<T>(g, T(1), D1, C1, false, 2, s)) return 1;
+    }
+    return 0;
+}
+
+// ---- SUMMA-B (stationary B): panels over m ----
+template <typename T>
+int summa_b(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, const DM& B, const DM& C, i64 nb,
+            cudaStream_t s) {
+    const GridShape& sh = g.shape;
+    const LocalShape Lb = local_shape(sh, B, g.mc, g.mr);
+    const int es = sizeof(T);
+    for (i64 m0 = 0; m0 < m; m0 += nb) {
+        const i64 h = std::min(nb, m - m0);
+        // (op(A)(m0:m0+h, :))^T is k x h; gather it with k distributed like B's k-dimension
+        DM Ap, D1t;
+        const int kd = oB ? MR : MC;
+        const int ka = oB ? B.rowAlign : B.colAlign;
+        if (make_tmp<T>(g, g.panel[0], k, h, kd, STAR, ka, 0, Ap)) return 1;
+        const DM A1 = oA ? view(sh, A, g.mc, g.mr, 0, m0, k, h, es) : view(sh, A, g.mc, g.mr, m0, 0, h, k, es);
+        if (redistribute<T>(g, A1, Ap, oA == 0, 0, s)) return 1;
+        // D1t = alpha op(B_loc)^T Ap_loc : n_loc x h, [MR,*] (oB = N) or [MC,*] (oB = T)
+        const int nd = oB ? MC : MR;
+        const int na = oB ? B.colAlign : B.rowAlign;
+        if (make_tmp<T>(g, g.panel[1], n, h, nd, STAR, na, 0, D1t)) return 1;
+        const i64 nloc = oB ? Lb.lh : Lb.lw, kloc = oB ? Lb.lw : Lb.lh;
+        if (lgemm<T>(oB ? 0 : 1, 0, nloc, h, kloc, alpha, static_cast<const T*>(B.buf), B.ldim,
+                     static_cast<const T*>(Ap.buf), Ap.ldim, T(0), static_cast<T*>(D1t.buf), D1t.ldim, s, 0))
+            return 1;
+        if (kloc == 0 && scale_local<T>(nloc, h, T(0), static_cast<T*>(D1t.buf), D1t.ldim, s)) return 1;
+        const DM C1 = view(sh, C, g.mc, g.mr, m0, 0, h, n, es);
+        if (reduce_into<T>(g, T(1), D1t, C1, true, 2, s)) return 1;
+    }
+    return 0;
+}
+
+// ---- SUMMA-Dot: k distributed over all P ranks, P-wide reduce per C tile ----
+template <typename T>
+int summa_dot(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, const DM& B, const DM& C,
+              i64 blockSize, cudaStream_t s) {
+    const GridShape& sh = g.shape;
+    const int es = sizeof(T);
+    // operands must be  A: [*,VC] (N) / [VC,*] (T),  B: [VC,*] (N) / [*,VC] (T), B aligned to A (proxy, Proxy.hpp:160-260)
+    const LocalShape La = local_shape(sh, A, g.mc, g.mr);
+    const i64 kloc = oA ? La.lh : La.lw;
+    for (i64 i0 = 0; i0 < m; i0 += blockSize) {
+        const i64 mb = std::min(blockSize, m - i0);
+        for (i64 j0 = 0; j0 < n; j0 += blockSize) {
+            const i64 nbk = std::min(blockSize, n - j0);
+            DM C11;
+            if (make_tmp<T>(g, g.panel[0], mb, nbk, STAR, STAR, 0, 0, C11)) return 1;
+            const T* a = static_cast<const T*>(A.buf) + (oA ? i0 * A.ldim : i0);
+            const T* b = static_cast<const T*>(B.buf) + (oB ? j0 : j0 * B.ldim);
+            if (lgemm<T>(oA, oB, mb, nbk, kloc, alpha, a, A.ldim, b, B.ldim, T(0), static_cast<T*>(C11.buf), C11.ldim,
+                         s, 0))
+                return 1;
+            if (kloc == 0 && scale_local<T>(mb, nbk, T(0), static_cast<T*>(C11.buf), C11.ldim, s)) return 1;
+            const DM Cv = view(sh, C, g.mc, g.mr, i0, j0, mb, nbk, es);
+            if (reduce_into<T>(g, T(1), C11, Cv, false, 2, s)) return 1;
+        }
+    }
+    return 0;
+}
+
+struct TempPool {
+    std::vector<void*> bufs;
+    ~TempPool() { for (void* p : bufs) cudaFree(p); }
+};
+
+// read-proxy: return `a` itself if it already has the wanted distribution (and alignment when constrained),
+// else a freshly redistributed temporary (reference: DistMatrixReadProxy, include/El/core/Proxy.hpp:174-260)
+template <typename T>
+int read_proxy(Grid& g, TempPool& pool, const DM& a, int cd, int rd, bool colCon, int ca, bool rowCon, int ra, DM& out,
+               cudaStream_t s) {
+    const bool ok = a.colDist == cd && a.rowDist == rd && (!colCon || a.colAlign == ca) && (!rowCon || a.rowAlign == ra);
+    if (ok) { out = a; return 0; }
+    out = DM();
+    out.height = a.height; out.width = a.width; out.colDist = cd; out.rowDist = rd;
+    out.colAlign = colCon ? ca : (cd == a.colDist ? a.colAlign : 0);
+    out.rowAlign = rowCon ? ra : (rd == a.rowDist ? a.rowAlign : 0);
+    const LocalShape L = local_shape(g.shape, out, g.mc, g.mr);
+    out.ldim = pad_ld(L.lh, sizeof(T));
+    void* p = nullptr;
+    if (check_cuda(cudaMalloc(&p, (size_t)(out.ldim * std::max<i64>(L.lw, 1)) * sizeof(T)), "proxy cudaMalloc")) return 1;
+    pool.bufs.push_back(p);
+    out.buf = p;
+    return redistribute<T>(g, a, out, false, 3, s);
+}
+
+}  // namespace
+
+template <typename T>
+int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A0, const DM& B0, T beta, const DM& C0,
+              i64 blocksize, cudaStream_t s) {
+    oA = oA ? 1 : 0;
+    oB = oB ? 1 : 0;
+    const i64 m = C0.height, n = C0.width;
+    const i64 k = oA ? A0.height : A0.width;
+    const i64 am = oA ? A0.width : A0.height, bk = oB ? B0.width : B0.height, bn = oB ? B0.height : B0.width;
+    if (am != m || bn != n || bk != k)
+        return set_error("hyd_gemm: nonconformal matrices: op(A) %lldx%lld, op(B) %lldx%lld, C %lldx%lld", am, k, bk, bn, m, n);
+    if (blocksize <= 0) return set_error("hyd_gemm: blocksize must be positive");
+    if (alg == 5) return set_error("hyd_gemm: GEMM_CANNON is CPU-only in the reference (NN.hpp:20-103) and not provided");
+    if (alg < 0 || alg > 5) return set_error("hyd_gemm: unsupported Gemm option");
+    if (alg == 0) {  // GEMM_DEFAULT heuristic, NN.hpp:910-925 (identical in NT/TN/TT)
+        if (10.0 * m <= k && 10.0 * n <= k) alg = 4;
+        else if (m <= n && 2.0 * m <= k) alg = 2;
+        else if (n <= m && 2.0 * n <= k) alg = 1;
+        else alg = 3;
+    }
+    TempPool pool;
+    const LocalShape Lc0 = local_shape(g.shape, C0, g.mc, g.mr);
+    // Scale(beta, C) first, exactly as the reference (Gemm.cpp:287): beta*C is rounded before accumulation
+    if (scale_local<T>(Lc0.lh, Lc0.lw, beta, static_cast<T*>(C0.buf), C0.ldim, s)) return 1;
+    if (m == 0 || n == 0) return 0;
+    DM A, B, C;
+    if (read_proxy<T>(g, pool, C0, MC, MR, false, 0, false, 0, C, s)) return 1;
+    int rc;
+    if (alg == 4) {
+        if (oA) { if (read_proxy<T>(g, pool, A0, VC, STAR, false, 0, false, 0, A, s)) return 1; }
+        else    { if (read_proxy<T>(g, pool, A0, STAR, VC, false, 0, false, 0, A, s)) return 1; }
+        const int kalign = oA ? A.colAlign : A.rowAlign;
+        if (oB) { if (read_proxy<T>(g, pool, B0, STAR, VC, false, 0, true, kalign, B, s)) return 1; }
+        else    { if (read_proxy<T>(g, pool, B0, VC, STAR, true, kalign, false, 0, B, s)) return 1; }
+        rc = summa_dot<T>(g, oA, oB, m, n, k, alpha, A, B, C, 2000, s);
+    } else {
+        if (read_proxy<T>(g, pool, A0, MC, MR, false, 0, false, 0, A, s)) return 1;
+        if (read_proxy<T>(g, pool, B0, MC, MR, false, 0, false, 0, B, s)) return 1;
+        if (alg == 1) rc = summa_a<T>(g, oA, oB, m, n, k, alpha, A, B, C, blocksize, s);
+        else if (alg == 2) rc = summa_b<T>(g, oA, oB, m, n, k, alpha, A, B, C, blocksize, s);
+        else rc = summa_c<T>(g, oA, oB, m, n, k, alpha, A, B, C, blocksize, s);
+    }
+    if (rc) return rc;
+    if (C.buf != C0.buf) {  // write-back half of the ReadWrite proxy
+        if (redistribute<T>(g, C, C0, false, 3, s)) return 1;
+    }
+    if (!pool.bufs.empty() && check_cuda(cudaStreamSynchronize(s), "proxy sync")) return 1;
+    return 0;
+}
+
+template int dist_gemm<double>(Grid&, int, int, int, double, const DM&, const DM&, double, const DM&, i64, cudaStream_t);
+template int dist_gemm<float>(Grid&, int, int, int, float, const DM&, const DM&, float, const DM&, i64, cudaStream_t);
+
+}  // namespace hyd

@@ -47,6 +47,103 @@ int hyd_lgemm_f32(int transA, int transB, int64_t m, int64_t n, int64_t k, float
                   const float* A, int64_t lda, const float* B, int64_t ldb, float beta,
                   float* C, int64_t ldc, hyd_stream_t stream);
 
+/* ---- index arithmetic (host, no GPU needed) ------------------------------------
+ * ref: include/El/core/indexing/impl.hpp:33-66 (Length_, MaxLength_), :229-245 (Mod_, Shift_). */
+int64_t hyd_mod(int64_t a, int64_t b);
+int64_t hyd_shift(int64_t rank, int64_t align, int64_t stride);
+int64_t hyd_length(int64_t n, int64_t shift, int64_t stride);
+int64_t hyd_max_length(int64_t n, int64_t stride);
+
+/* ---- distributions / matrices ------------------------------------------------------
+ * Dist values follow El::Dist (include/El/core/types.hpp:208-216). MD and CIRC are not on the Gemm path. */
+enum { HYD_MC = 0, HYD_MD = 1, HYD_MR = 2, HYD_VC = 3, HYD_VR = 4, HYD_STAR = 5, HYD_CIRC = 6 };
+/* Orientation (types.hpp:453-458) and GemmAlgorithm (include/El/blas_like/level3.hpp:23-30) */
+enum { HYD_NORMAL = 0, HYD_TRANSPOSE = 1, HYD_ADJOINT = 2 };
+enum { HYD_GEMM_DEFAULT = 0, HYD_GEMM_SUMMA_A = 1, HYD_GEMM_SUMMA_B = 2, HYD_GEMM_SUMMA_C = 3,
+       HYD_GEMM_SUMMA_DOT = 4, HYD_GEMM_CANNON = 5 };
+
+/* One rank's handle on a distributed matrix: the metadata of El::DistMatrix<T,U,V,ELEMENT,GPU>
+ * (include/El/core/DistMatrix/Abstract.hpp; shifts derive from alignments as in
+ * src/core/DistMatrix/AbstractDistMatrix.cpp:399-430) plus this rank's local device buffer. */
+typedef struct hyd_dm {
+    void* buf;       /* device pointer to the local column-major block (may be NULL if the block is empty) */
+    int64_t ldim;    /* leading dimension of the local block, >= local height */
+    int64_t height;  /* GLOBAL height */
+    int64_t width;   /* GLOBAL width */
+    int32_t colDist, rowDist;   /* HYD_MC ... HYD_STAR */
+    int32_t colAlign, rowAlign; /* 0 <= align < stride of the distribution */
+    int32_t root;               /* unused for these distributions; kept for layout parity */
+    int32_t reserved;
+} hyd_dm;
+
+/* ---- communication world + process grid -------------------------------------------
+ * ref: El::Grid(mpi::Comm, int height, GridOrder), include/El/core/Grid.hpp:19-56, src/core/Grid.cpp:95-186.
+ * One process per GPU: every rank calls hyd_world_create_nccl with the same 128-byte id
+ * (hyd_nccl_unique_id on rank 0, broadcast by the launcher: torchrun/MPI/file). */
+typedef struct hyd_world hyd_world;
+typedef struct hyd_grid hyd_grid;
+typedef struct hyd_local_group hyd_local_group;
+
+int hyd_nccl_unique_id(void* out128);
+int hyd_world_create_nccl(const void* id128, int rank, int nranks, hyd_world** out);
+/* P rank-threads of one process on one GPU (single-GPU multi-rank runs / tests); each thread takes one rank. */
+int hyd_local_group_create(int nranks, hyd_local_group** out);
+int hyd_local_group_destroy(hyd_local_group* grp);
+int hyd_world_create_local(hyd_local_group* grp, int rank, hyd_world** out);
+int hyd_world_destroy(hyd_world* w);
+int hyd_world_barrier(hyd_world* w);
+
+/* order: 0 = ROW_MAJOR, 1 = COLUMN_MAJOR (types.hpp:409-413); height must divide the world size. */
+int hyd_grid_create(hyd_world* w, int height, int order, hyd_grid** out);
+int hyd_grid_destroy(hyd_grid* g);
+int hyd_grid_height(const hyd_grid* g);
+int hyd_grid_width(const hyd_grid* g);
+int hyd_grid_size(const hyd_grid* g);
+int hyd_grid_rank(const hyd_grid* g);     /* rank in the owning communicator */
+int hyd_grid_row(const hyd_grid* g);      /* MCRank */
+int hyd_grid_col(const hyd_grid* g);      /* MRRank */
+int hyd_grid_vc_rank(const hyd_grid* g);
+int hyd_grid_vr_rank(const hyd_grid* g);
+/* engine knobs: overlap panel gathers with the local GEMM (default 1); SMs left to comm kernels (default 8) */
+int hyd_grid_set_overlap(hyd_grid* g, int overlap, int sm_reserve);
+
+/* stride / rank / local shape of a distribution on this grid (host; valid for any rank via mc,mr) */
+int hyd_dist_stride(const hyd_grid* g, int dist);
+int hyd_dist_rank(const hyd_grid* g, int dist);
+int hyd_local_shape(const hyd_grid* g, const hyd_dm* a, int64_t* colShift, int64_t* rowShift,
+                    int64_t* localHeight, int64_t* localWidth);
+/* pure host form for an arbitrary rank of an r x c grid (no handle, no GPU) */
+int hyd_local_shape_of(int gridHeight, int gridWidth, int order, int rank, const hyd_dm* a,
+                       int64_t* colShift, int64_t* rowShift, int64_t* localHeight, int64_t* localWidth);
+/* view of rows [i,i+h) x cols [j,j+w): alignment and buffer offset as El::View / operator()(IR,IR) */
+int hyd_view(const hyd_grid* g, const hyd_dm* a, int64_t i, int64_t j, int64_t h, int64_t w, int elemSize,
+             hyd_dm* out);
+
+/* ---- seam S1: distributed operations (collective over the grid; async on `stream`) --------- */
+
+/* dst := src (transpose = 0) or dst := src^T (transpose = 1) between ANY two supported distributions/alignments.
+ * ref: DistMatrix::operator= tables src/core/DistMatrix/ElementMatrix/<dist>.cpp -> copy:: primitives
+ *      (include/El/blas_like/level1/Copy/<primitive>.hpp); El::Transpose(A,B) include/El/blas_like/level1/Transpose.hpp:191-250,318-356. */
+int hyd_redist_f64(hyd_grid* g, const hyd_dm* src, const hyd_dm* dst, int transpose, hyd_stream_t stream);
+int hyd_redist_f32(hyd_grid* g, const hyd_dm* src, const hyd_dm* dst, int transpose, hyd_stream_t stream);
+
+/* dst += alpha * (sum of src over the ranks along which src's distribution is replicated), optionally of src^T.
+ * ref: El::AxpyContract include/El/blas_like/level1/AxpyContract.hpp:483-544 (RowScatter, ColScatter, PartialRowScatter, PartialColScatter, Scatter :17-479),
+ *      El::Contract Contract.hpp:14-98, El::TransposeAxpyContract TransposeAxpyContract.hpp:14-48. */
+int hyd_axpy_contract_f64(hyd_grid* g, double alpha, const hyd_dm* src, const hyd_dm* dst, int transpose,
+                          hyd_stream_t stream);
+int hyd_axpy_contract_f32(hyd_grid* g, float alpha, const hyd_dm* src, const hyd_dm* dst, int transpose,
+                          hyd_stream_t stream);
+
+/* C := alpha op(A) op(B) + beta C.  ref: El::Gemm(orientA,orientB,alpha,A,B,beta,C,alg),
+ * include/El/blas_like/level3.hpp:66-84, src/blas_like/level3/Gemm.cpp:278-307; blocksize = El::Blocksize()
+ * (src/core/environment.cpp:305-306, default 128). Any supported distribution is accepted for A, B, C
+ * (read / read-write proxies, include/El/core/Proxy.hpp:174-260,694-795). */
+int hyd_gemm_f64(hyd_grid* g, int orientA, int orientB, int alg, double alpha, const hyd_dm* A, const hyd_dm* B,
+                 double beta, const hyd_dm* C, int64_t blocksize, hyd_stream_t stream);
+int hyd_gemm_f32(hyd_grid* g, int orientA, int orientB, int alg, float alpha, const hyd_dm* A, const hyd_dm* B,
+                 float beta, const hyd_dm* C, int64_t blocksize, hyd_stream_t stream);
+
 /* Pipe-peak probe (register-resident loops): kind 0 = FP64 DFMA, 1 = DMMA m8n8k4, 2 = DMMA m16n8k16,
  * 3 = FP32 FFMA.  Writes achieved TFLOP/s.  Measurement aid for the roofline denominator. */
 int hyd_probe_peak(int kind, int iters, int ctas_per_sm, double* tflops);
