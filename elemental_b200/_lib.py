@@ -19,18 +19,79 @@ def _load():
         raise ImportError(
             f"{LIB_PATH} not found: build it with `make -C elemental_b200/csrc` "
             "(or __graft_entry__.build()); there is no CPU fallback.")
-    return C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
+    return C.CDLL(LIB_PATH)
 
 
 lib = _load()
 
 i32, i64, f32, f64, vp = C.c_int, C.c_int64, C.c_float, C.c_double, C.c_void_p
 
-lib.hyd_last_error.restype = C.c_char_p
-lib.hyd_last_error.argtypes = []
-lib.hyd_version.restype = i32
-lib.hyd_lgemm_f64.argtypes = [i32, i32, i64, i64, i64, f64, vp, i64, vp, i64, f64, vp, i64, vp]
-lib.hyd_probe_peak.argtypes = [i32, i32, i32, C.POINTER(f64)]
+
+class hyd_dm(C.Structure):
+    """POD mirror of `hyd_dm` in include/hydrogen_b200.h."""
+    _fields_ = [("buf", vp), ("ldim", i64), ("height", i64), ("width", i64),
+                ("colDist", i32), ("rowDist", i32), ("colAlign", i32), ("rowAlign", i32),
+                ("root", i32), ("reserved", i32)]
+
+
+dmp = C.POINTER(hyd_dm)
+pi64 = C.POINTER(i64)
+
+
+def _sig(name, res, args):
+    f = getattr(lib, name)
+    f.restype = res
+    f.argtypes = args
+    return f
+
+
+_sig("hyd_last_error", C.c_char_p, [])
+_sig("hyd_version", i32, [])
+_sig("hyd_launch_count", C.c_longlong, [])
+_sig("hyd_lgemm_f64", i32, [i32, i32, i64, i64, i64, f64, vp, i64, vp, i64, f64, vp, i64, vp])
+_sig("hyd_lgemm_f32", i32, [i32, i32, i64, i64, i64, f32, vp, i64, vp, i64, f32, vp, i64, vp])
+_sig("hyd_transpose_f64", i32, [i64, i64, vp, i64, vp, i64, vp])
+_sig("hyd_transpose_f32", i32, [i64, i64, vp, i64, vp, i64, vp])
+_sig("hyd_copy2d_f64", i32, [i64, i64, vp, i64, vp, i64, vp])
+_sig("hyd_copy2d_f32", i32, [i64, i64, vp, i64, vp, i64, vp])
+_sig("hyd_axpy2d_f64", i32, [i64, i64, f64, vp, i64, vp, i64, vp])
+_sig("hyd_axpy2d_f32", i32, [i64, i64, f32, vp, i64, vp, i64, vp])
+_sig("hyd_scale2d_f64", i32, [i64, i64, f64, vp, i64, vp])
+_sig("hyd_scale2d_f32", i32, [i64, i64, f32, vp, i64, vp])
+_sig("hyd_mod", i64, [i64, i64])
+_sig("hyd_shift", i64, [i64, i64, i64])
+_sig("hyd_length", i64, [i64, i64, i64])
+_sig("hyd_max_length", i64, [i64, i64])
+_sig("hyd_nccl_unique_id", i32, [vp])
+_sig("hyd_world_create_nccl", i32, [vp, i32, i32, C.POINTER(vp)])
+_sig("hyd_local_group_create", i32, [i32, C.POINTER(vp)])
+_sig("hyd_local_group_destroy", i32, [vp])
+_sig("hyd_world_create_local", i32, [vp, i32, C.POINTER(vp)])
+_sig("hyd_world_destroy", i32, [vp])
+_sig("hyd_world_barrier", i32, [vp])
+_sig("hyd_grid_create", i32, [vp, i32, i32, C.POINTER(vp)])
+_sig("hyd_grid_destroy", i32, [vp])
+for _n in ("hyd_grid_height", "hyd_grid_width", "hyd_grid_size", "hyd_grid_rank", "hyd_grid_row", "hyd_grid_col",
+           "hyd_grid_vc_rank", "hyd_grid_vr_rank"):
+    _sig(_n, i32, [vp])
+_sig("hyd_grid_set_overlap", i32, [vp, i32, i32])
+_sig("hyd_dist_stride", i32, [vp, i32])
+_sig("hyd_dist_rank", i32, [vp, i32])
+_sig("hyd_local_shape", i32, [vp, dmp, pi64, pi64, pi64, pi64])
+_sig("hyd_local_shape_of", i32, [i32, i32, i32, i32, dmp, pi64, pi64, pi64, pi64])
+_sig("hyd_view", i32, [vp, dmp, i64, i64, i64, i64, i32, dmp])
+_sig("hyd_redist_f64", i32, [vp, dmp, dmp, i32, vp])
+_sig("hyd_redist_f32", i32, [vp, dmp, dmp, i32, vp])
+_sig("hyd_axpy_contract_f64", i32, [vp, f64, dmp, dmp, i32, vp])
+_sig("hyd_axpy_contract_f32", i32, [vp, f32, dmp, dmp, i32, vp])
+_sig("hyd_gemm_f64", i32, [vp, i32, i32, i32, f64, dmp, dmp, f64, dmp, i64, vp])
+_sig("hyd_gemm_f32", i32, [vp, i32, i32, i32, f32, dmp, dmp, f32, dmp, i64, vp])
+_sig("hyd_gemm_host_f64", i32, [vp, i32, i32, i32, f64, dmp, dmp, f64, dmp, i64, vp])
+_sig("hyd_gemm_host_f32", i32, [vp, i32, i32, i32, f32, dmp, dmp, f32, dmp, i64, vp])
+_sig("hyd_probe_peak", i32, [i32, i32, i32, C.POINTER(f64)])
+
+# every symbol include/hydrogen_b200.h declares (tests/test_abi.py checks the header against this list)
+EXPORTS = sorted(n for n in dir(lib) if n.startswith("hyd_"))
 
 
 def check(rc):

@@ -39,6 +39,43 @@ static int check_dm(const hyd::GridShape& sh, const hyd_dm* a, const char* who) 
     return 0;
 }
 
+// ---- host-buffer entry points (the call a CPU-resident caller makes) ----
+template <typename T>
+static int gemm_host(hyd_grid* g, int oA, int oB, int alg, T alpha, const hyd_dm* A, const hyd_dm* B, T beta,
+                     const hyd_dm* C, int64_t blocksize, cudaStream_t s) {
+    hyd::Grid& G = *g->g;
+    const hyd::GridShape& sh = G.shape;
+    if (check_dm(sh, A, "hyd_gemm_host(A)") || check_dm(sh, B, "hyd_gemm_host(B)") || check_dm(sh, C, "hyd_gemm_host(C)"))
+        return 1;
+    const hyd_dm* host[3] = {A, B, C};
+    hyd::DM dev[3];
+    hyd::LocalShape L[3];
+    for (int i = 0; i < 3; ++i) {
+        dev[i] = to_dm(host[i]);
+        L[i] = hyd::local_shape(sh, dev[i], G.mc, G.mr);
+        const int64_t q = 16 / (int64_t)sizeof(T);
+        dev[i].ldim = L[i].lh > 0 ? (L[i].lh + q - 1) / q * q : q;
+        const size_t bytes = (size_t)dev[i].ldim * (size_t)(L[i].lw > 0 ? L[i].lw : 1) * sizeof(T);
+        if (hyd::ws_reserve(G.host_stage[i], bytes)) return 1;
+        dev[i].buf = G.host_stage[i].buf;
+        if (L[i].lh > 0 && L[i].lw > 0) {
+            if (!host[i]->buf || host[i]->ldim < L[i].lh) return set_error("hyd_gemm_host: bad host buffer / ldim");
+            if (i == 2 && beta == T(0)) continue;  // C is overwritten: no upload
+            if (hyd::check_cuda(cudaMemcpy2DAsync(dev[i].buf, (size_t)dev[i].ldim * sizeof(T), host[i]->buf,
+                                                  (size_t)host[i]->ldim * sizeof(T), (size_t)L[i].lh * sizeof(T),
+                                                  (size_t)L[i].lw, cudaMemcpyHostToDevice, s),
+                                "hyd_gemm_host: H2D"))
+                return 1;
+        }
+    }
+    if (hyd::dist_gemm<T>(G, oA, oB, alg, alpha, dev[0], dev[1], beta, dev[2], blocksize, s)) return 1;
+    if (L[2].lh > 0 && L[2].lw > 0 &&
+        hyd::check_cuda(cudaMemcpy2DAsync(C->buf, (size_t)C->ldim * sizeof(T), dev[2].buf, (size_t)dev[2].ldim * sizeof(T),
+                                          (size_t)L[2].lh * sizeof(T), (size_t)L[2].lw, cudaMemcpyDeviceToHost, s),
+                        "hyd_gemm_host: D2H"))
+        return 1;
+    return hyd::check_cuda(cudaStreamSynchronize(s), "hyd_gemm_host: sync");
+}
 extern "C" {
 
 const char* hyd_last_error(void) { return hyd::last_error(); }
@@ -188,6 +225,42 @@ int hyd_gemm_f32(hyd_grid* g, int oA, int oB, int alg, float alpha, const hyd_dm
     if (check_dm(sh, A, "hyd_gemm(A)") || check_dm(sh, B, "hyd_gemm(B)") || check_dm(sh, C, "hyd_gemm(C)")) return 1;
     return hyd::dist_gemm<float>(*g->g, oA, oB, alg, alpha, to_dm(A), to_dm(B), beta, to_dm(C), blocksize,
                                  (cudaStream_t)stream);
+}
+
+
+// ---- local BLAS-1-like kernels ----
+int hyd_transpose_f64(int64_t m, int64_t n, const double* A, int64_t lda, double* B, int64_t ldb, hyd_stream_t s) {
+    return hyd::transpose_local<double>(m, n, A, lda, B, ldb, (cudaStream_t)s);
+}
+int hyd_transpose_f32(int64_t m, int64_t n, const float* A, int64_t lda, float* B, int64_t ldb, hyd_stream_t s) {
+    return hyd::transpose_local<float>(m, n, A, lda, B, ldb, (cudaStream_t)s);
+}
+int hyd_copy2d_f64(int64_t m, int64_t n, const double* A, int64_t lda, double* B, int64_t ldb, hyd_stream_t s) {
+    return hyd::copy2d_local<double>(m, n, A, lda, B, ldb, (cudaStream_t)s);
+}
+int hyd_copy2d_f32(int64_t m, int64_t n, const float* A, int64_t lda, float* B, int64_t ldb, hyd_stream_t s) {
+    return hyd::copy2d_local<float>(m, n, A, lda, B, ldb, (cudaStream_t)s);
+}
+int hyd_axpy2d_f64(int64_t m, int64_t n, double alpha, const double* A, int64_t lda, double* B, int64_t ldb, hyd_stream_t s) {
+    return hyd::axpy2d_local<double>(m, n, alpha, A, lda, B, ldb, (cudaStream_t)s);
+}
+int hyd_axpy2d_f32(int64_t m, int64_t n, float alpha, const float* A, int64_t lda, float* B, int64_t ldb, hyd_stream_t s) {
+    return hyd::axpy2d_local<float>(m, n, alpha, A, lda, B, ldb, (cudaStream_t)s);
+}
+int hyd_scale2d_f64(int64_t m, int64_t n, double alpha, double* A, int64_t lda, hyd_stream_t s) {
+    return hyd::scale_local<double>(m, n, alpha, A, lda, (cudaStream_t)s);
+}
+int hyd_scale2d_f32(int64_t m, int64_t n, float alpha, float* A, int64_t lda, hyd_stream_t s) {
+    return hyd::scale_local<float>(m, n, alpha, A, lda, (cudaStream_t)s);
+}
+
+int hyd_gemm_host_f64(hyd_grid* g, int oA, int oB, int alg, double alpha, const hyd_dm* A, const hyd_dm* B, double beta,
+                      const hyd_dm* C, int64_t blocksize, hyd_stream_t stream) {
+    return gemm_host<double>(g, oA, oB, alg, alpha, A, B, beta, C, blocksize, (cudaStream_t)stream);
+}
+int hyd_gemm_host_f32(hyd_grid* g, int oA, int oB, int alg, float alpha, const hyd_dm* A, const hyd_dm* B, float beta,
+                      const hyd_dm* C, int64_t blocksize, hyd_stream_t stream) {
+    return gemm_host<float>(g, oA, oB, alg, alpha, A, B, beta, C, blocksize, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -2,23 +2,52 @@
 #include "comm.h"
 #include "hyd_internal.h"
 #include <nccl.h>
+#include <dlfcn.h>
 #include <pthread.h>
 #include <string.h>
 #include <vector>
 
 namespace hyd {
 
+// NCCL is bound at run time, not link time: a process that already carries an NCCL (e.g. the
+// one bundled with PyTorch, loaded before this library) must keep using that single copy, and a
+// plain C++ host program gets the system libnccl.so.2.
+namespace nccl {
+#define HYD_NCCL_FNS(X) \
+    X(ncclGetUniqueId) X(ncclCommInitRank) X(ncclCommDestroy) X(ncclGroupStart) X(ncclGroupEnd) X(ncclSend) \
+    X(ncclRecv) X(ncclAllReduce) X(ncclGetErrorString) X(ncclAllGather) X(ncclReduceScatter) X(ncclBroadcast)
+#define X(f) static decltype(&::f) f = nullptr;
+HYD_NCCL_FNS(X)
+#undef X
+static int load() {
+    static int state = 0;  // 0 = not tried, 1 = ok, -1 = failed
+    static pthread_mutex_t mu = PTHREAD_MUTEX_INITIALIZER;
+    pthread_mutex_lock(&mu);
+    if (state == 0) {
+        void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+        if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        state = h ? 1 : -1;
+#define X(f) if (h) { f = reinterpret_cast<decltype(f)>(dlsym(h, #f)); if (!f) state = -1; }
+        HYD_NCCL_FNS(X)
+#undef X
+    }
+    pthread_mutex_unlock(&mu);
+    return state == 1 ? 0 : set_error("NCCL (libnccl.so.2) could not be loaded: %s", dlerror() ? dlerror() : "missing symbol");
+}
+}  // namespace nccl
+
 // ---------------------------------------------------------------------------
 // NCCL: one process per GPU
 // ---------------------------------------------------------------------------
 static int check_nccl(ncclResult_t r, const char* what) {
     if (r == ncclSuccess) return 0;
-    return set_error("%s: NCCL error %d (%s)", what, (int)r, ncclGetErrorString(r));
+    return set_error("%s: NCCL error %d (%s)", what, (int)r, nccl::ncclGetErrorString(r));
 }
 
 struct NcclWorld : World {
     ncclComm_t comm = nullptr;
-    ~NcclWorld() override { if (comm) ncclCommDestroy(comm); }
+    ~NcclWorld() override { if (comm) nccl::ncclCommDestroy(comm); }
     const char* kind() const override { return "nccl"; }
     int exchange(const void* send, const i64* scount, const i64* soff, void* recv, const i64* rcount,
                  const i64* roff, cudaStream_t s) override {
@@ -26,24 +55,24 @@ struct NcclWorld : World {
         for (int p = 0; p < size; ++p)
             if (p != rank && (scount[p] > 0 || rcount[p] > 0)) any = true;
         if (!any) return 0;
-        if (check_nccl(ncclGroupStart(), "ncclGroupStart")) return 1;
+        if (check_nccl(nccl::ncclGroupStart(), "ncclGroupStart")) return 1;
         for (int p = 0; p < size; ++p) {
             if (p == rank) continue;
             if (scount[p] > 0 &&
-                check_nccl(ncclSend((const char*)send + soff[p], (size_t)scount[p], ncclChar, p, comm, s), "ncclSend"))
+                check_nccl(nccl::ncclSend((const char*)send + soff[p], (size_t)scount[p], ncclChar, p, comm, s), "ncclSend"))
                 return 1;
             if (rcount[p] > 0 &&
-                check_nccl(ncclRecv((char*)recv + roff[p], (size_t)rcount[p], ncclChar, p, comm, s), "ncclRecv"))
+                check_nccl(nccl::ncclRecv((char*)recv + roff[p], (size_t)rcount[p], ncclChar, p, comm, s), "ncclRecv"))
                 return 1;
         }
-        return check_nccl(ncclGroupEnd(), "ncclGroupEnd");
+        return check_nccl(nccl::ncclGroupEnd(), "ncclGroupEnd");
     }
     int barrier() override {
         // a zero-payload all-reduce would need a buffer; the engine only needs stream order,
         // so the host barrier is an all-reduce on a 4-byte scratch followed by a sync.
         static thread_local int* scratch = nullptr;
         if (!scratch && check_cuda(cudaMalloc(&scratch, 4), "barrier scratch")) return 1;
-        if (check_nccl(ncclAllReduce(scratch, scratch, 1, ncclInt, ncclSum, comm, 0), "ncclAllReduce")) return 1;
+        if (check_nccl(nccl::ncclAllReduce(scratch, scratch, 1, ncclInt, ncclSum, comm, 0), "ncclAllReduce")) return 1;
         return check_cuda(cudaStreamSynchronize(0), "barrier sync");
     }
 };
@@ -51,18 +80,20 @@ struct NcclWorld : World {
 int nccl_unique_id(void* out) {
     ncclUniqueId id;
     static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
-    if (check_nccl(ncclGetUniqueId(&id), "ncclGetUniqueId")) return 1;
+    if (nccl::load()) return 1;
+    if (check_nccl(nccl::ncclGetUniqueId(&id), "ncclGetUniqueId")) return 1;
     memcpy(out, &id, 128);
     return 0;
 }
 
 World* make_nccl_world(const void* uid, int rank, int size) {
+    if (nccl::load()) return nullptr;
     ncclUniqueId id;
     memcpy(&id, uid, 128);
     NcclWorld* w = new NcclWorld;
     w->rank = rank;
     w->size = size;
-    if (check_nccl(ncclCommInitRank(&w->comm, size, id, rank), "ncclCommInitRank")) {
+    if (check_nccl(nccl::ncclCommInitRank(&w->comm, size, id, rank), "ncclCommInitRank")) {
         w->comm = nullptr;
         delete w;
         return nullptr;

@@ -27,6 +27,7 @@ struct Grid {
     cudaEvent_t ev_panel_ready[2] = {nullptr, nullptr}, ev_panel_free[2] = {nullptr, nullptr};
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     Workspace panel[4];  // gathered panels (A/B x double buffer) or reduce temporaries
+    Workspace host_stage[3];  // device images of host operands (hyd_gemm_host_*)
     bool overlap = true;
     int sm_reserve = 8;  // SMs the local GEMM leaves to NCCL / pack kernels while overlapping
     long long launches = 0;
@@ -47,6 +48,12 @@ int reduce_into(Grid& g, T alpha, const DM& src, const DM& dst, bool transpose, 
 
 // view of rows [i0,i0+h) x cols [j0,j0+w) of a distributed matrix, as seen by rank (mc,mr)
 DM view(const GridShape& g, const DM& a, int mc, int mr, i64 i0, i64 j0, i64 h, i64 w, int elem_size);
+
+// local BLAS-1-like kernels (blas1.cu)
+template <typename T> int transpose_local(i64 m, i64 n, const T* A, i64 lda, T* B, i64 ldb, cudaStream_t s);
+template <typename T> int copy2d_local(i64 m, i64 n, const T* A, i64 lda, T* B, i64 ldb, cudaStream_t s);
+template <typename T> int axpy2d_local(i64 m, i64 n, T alpha, const T* A, i64 lda, T* B, i64 ldb, cudaStream_t s);
+template <typename T> int scale_local(i64 m, i64 n, T beta, T* C, i64 ldc, cudaStream_t s);
 
 extern long long g_launches;  // kernels launched by this library in this process
 

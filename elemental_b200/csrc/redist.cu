@@ -324,6 +324,7 @@ void grid_destroy(Grid* g) {
     cudaDeviceSynchronize();
     for (auto& w : g->ws) if (w.buf) cudaFree(w.buf);
     for (auto& w : g->panel) if (w.buf) cudaFree(w.buf);
+    for (auto& w : g->host_stage) if (w.buf) cudaFree(w.buf);
     for (int i = 0; i < 2; ++i) {
         if (g->comm_stream[i]) cudaStreamDestroy(g->comm_stream[i]);
         if (g->ev_panel_ready[i]) cudaEventDestroy(g->ev_panel_ready[i]);

@@ -29,26 +29,6 @@
 
 namespace hyd {
 
-template <typename T> __global__ void scale2d_kernel(i64 m, i64 n, T beta, T* __restrict__ C, i64 ldc) {
-    const i64 total = m * n;
-    for (i64 e = blockIdx.x * (i64)blockDim.x + threadIdx.x; e < total; e += (i64)gridDim.x * blockDim.x) {
-        const i64 j = e / m, i = e - j * m;
-        T* p = C + i + j * ldc;
-        *p = (beta == T(0)) ? T(0) : beta * *p;
-    }
-}
-
-template <typename T>
-int scale_local(i64 m, i64 n, T beta, T* C, i64 ldc, cudaStream_t s) {
-    if (m == 0 || n == 0 || beta == T(1)) return 0;
-    const i64 blocks = std::min<i64>((m * n + 1023) / 1024, (i64)num_sms() * 8);
-    scale2d_kernel<T><<<(unsigned)std::max<i64>(1, blocks), 256, 0, s>>>(m, n, beta, C, ldc);
-    ++g_launches;
-    return check_cuda(cudaGetLastError(), "scale2d_kernel");
-}
-template int scale_local<double>(i64, i64, double, double*, i64, cudaStream_t);
-template int scale_local<float>(i64, i64, float, float*, i64, cudaStream_t);
-
 namespace {
 
 template <typename T>

@@ -1,0 +1,291 @@
+"""Python mirror of the reference's operator interface for the distributed-GEMM path.
+
+Names, argument meaning and error behaviour follow the reference (C++):
+  El::Grid          include/El/core/Grid.hpp:15-146, src/core/Grid.cpp:66-216
+  El::DistMatrix    include/El/core/DistMatrix/**  (ELEMENT wrap, Device::GPU)
+  El::Gemm          include/El/blas_like/level3.hpp:66-84, src/blas_like/level3/Gemm.cpp:278-307
+  El::Copy / operator=, El::Transpose, El::AxpyContract
+  El::SetBlocksize / El::Blocksize   src/core/environment.cpp:305-306
+
+This file is plumbing for tests and bench.py (the C++ shim is include/El.hpp); every
+operation goes through the C ABI of libhydrogen_b200.so.  torch supplies device
+memory and streams only.  There is no CPU fallback.
+"""
+import ctypes as C
+import threading
+
+import numpy as np
+import torch
+
+from ._lib import lib, check, hyd_dm, HydrogenError
+
+MC, MD, MR, VC, VR, STAR, CIRC = range(7)
+NORMAL, TRANSPOSE, ADJOINT = 0, 1, 2
+GEMM_DEFAULT, GEMM_SUMMA_A, GEMM_SUMMA_B, GEMM_SUMMA_C, GEMM_SUMMA_DOT, GEMM_CANNON = range(6)
+ROW_MAJOR, COLUMN_MAJOR = 0, 1
+
+_blocksize_stack = [128]  # environment.cpp:305-306
+
+
+def Blocksize():
+    return _blocksize_stack[-1]
+
+
+def SetBlocksize(nb):
+    _blocksize_stack[-1] = int(nb)
+
+
+def PushBlocksizeStack(nb):
+    _blocksize_stack.append(int(nb))
+
+
+def PopBlocksizeStack():
+    _blocksize_stack.pop()
+
+
+def _stream_ptr(stream=None):
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return C.c_void_p(s.cuda_stream)
+
+
+class World:
+    """Communication world: one rank per GPU over NCCL, or P rank-threads on one GPU (tests)."""
+
+    def __init__(self, handle, rank, size, kind):
+        self.h, self.rank, self.size, self.kind = handle, rank, size, kind
+
+    @staticmethod
+    def nccl_unique_id():
+        buf = (C.c_char * 128)()
+        check(lib.hyd_nccl_unique_id(buf))
+        return bytes(buf)
+
+    @classmethod
+    def nccl(cls, uid, rank, size):
+        h = C.c_void_p()
+        check(lib.hyd_world_create_nccl(C.c_char_p(uid), rank, size, C.byref(h)))
+        return cls(h, rank, size, "nccl")
+
+    @classmethod
+    def from_torch_distributed(cls):
+        """Bootstrap the NCCL world from an initialised torch.distributed process group (any backend)."""
+        import torch.distributed as dist
+        rank, size = dist.get_rank(), dist.get_world_size()
+        obj = [cls.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(obj, src=0)
+        return cls.nccl(obj[0], rank, size)
+
+    @classmethod
+    def local(cls, group, rank):
+        h = C.c_void_p()
+        check(lib.hyd_world_create_local(group.h, rank, C.byref(h)))
+        return cls(h, rank, group.size, "local")
+
+    @classmethod
+    def single(cls):
+        grp = LocalGroup(1)
+        w = cls.local(grp, 0)
+        w._grp = grp
+        return w
+
+    def barrier(self):
+        check(lib.hyd_world_barrier(self.h))
+
+    def destroy(self):
+        if self.h:
+            lib.hyd_world_destroy(self.h)
+            self.h = None
+
+
+class LocalGroup:
+    def __init__(self, size):
+        self.h = C.c_void_p()
+        self.size = size
+        check(lib.hyd_local_group_create(size, C.byref(self.h)))
+
+    def destroy(self):
+        if self.h:
+            lib.hyd_local_group_destroy(self.h)
+            self.h = None
+
+
+class Grid:
+    """El::Grid(comm, height, order)."""
+
+    def __init__(self, world, height=None, order=COLUMN_MAJOR):
+        if height is None:  # Grid::DefaultHeight, Grid.cpp:58-64: largest divisor <= sqrt(p)
+            height = int(np.floor(np.sqrt(world.size)))
+            while world.size % height:
+                height -= 1
+        self.world = world
+        self.h = C.c_void_p()
+        check(lib.hyd_grid_create(world.h, height, order, C.byref(self.h)))
+
+    def Height(self): return lib.hyd_grid_height(self.h)
+    def Width(self): return lib.hyd_grid_width(self.h)
+    def Size(self): return lib.hyd_grid_size(self.h)
+    def Rank(self): return lib.hyd_grid_rank(self.h)
+    def Row(self): return lib.hyd_grid_row(self.h)
+    def Col(self): return lib.hyd_grid_col(self.h)
+    MCRank, MRRank = Row, Col
+    def VCRank(self): return lib.hyd_grid_vc_rank(self.h)
+    def VRRank(self): return lib.hyd_grid_vr_rank(self.h)
+    def Stride(self, dist): return lib.hyd_dist_stride(self.h, dist)
+    def DistRank(self, dist): return lib.hyd_dist_rank(self.h, dist)
+
+    def SetOverlap(self, overlap=True, sm_reserve=-1):
+        check(lib.hyd_grid_set_overlap(self.h, int(overlap), sm_reserve))
+
+    def destroy(self):
+        if self.h:
+            lib.hyd_grid_destroy(self.h)
+            self.h = None
+
+
+_TORCH = {np.dtype(np.float64): torch.float64, np.dtype(np.float32): torch.float32}
+
+
+class DistMatrix:
+    """El::DistMatrix<T,U,V,ELEMENT,Device::GPU>: metadata + this rank's local column-major block."""
+
+    def __init__(self, grid, height, width, colDist=MC, rowDist=MR, dtype=np.float64, colAlign=0, rowAlign=0,
+                 device="cuda", ldim=None, pinned=False):
+        self.grid, self.m, self.n = grid, int(height), int(width)
+        self.cd, self.rd, self.ca, self.ra = colDist, rowDist, int(colAlign), int(rowAlign)
+        self.dtype = np.dtype(dtype)
+        self.es = self.dtype.itemsize
+        meta = hyd_dm(None, 1, self.m, self.n, colDist, rowDist, self.ca, self.ra, 0, 0)
+        cs, rs, lh, lw = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64()
+        check(lib.hyd_local_shape(grid.h, C.byref(meta), C.byref(cs), C.byref(rs), C.byref(lh), C.byref(lw)))
+        self.colShift, self.rowShift, self.lh, self.lw = cs.value, rs.value, lh.value, lw.value
+        q = 16 // self.es
+        self.ld = int(ldim) if ldim is not None else max(q, -(-self.lh // q) * q)
+        if self.ld < max(self.lh, 1):
+            raise HydrogenError("DistMatrix: ldim smaller than the local height")
+        # torch (lw, ld) row-major == column-major (ld, lw)
+        kw = dict(dtype=_TORCH[self.dtype], device=device)
+        if device == "cpu" and pinned:
+            kw["pin_memory"] = True
+        self.store = torch.zeros((max(self.lw, 1), self.ld), **kw)
+
+    # -- reference accessors
+    def Height(self): return self.m
+    def Width(self): return self.n
+    def LocalHeight(self): return self.lh
+    def LocalWidth(self): return self.lw
+    def LDim(self): return self.ld
+    def ColAlign(self): return self.ca
+    def RowAlign(self): return self.ra
+    def ColShift(self): return self.colShift
+    def RowShift(self): return self.rowShift
+    def ColStride(self): return self.grid.Stride(self.cd)
+    def RowStride(self): return self.grid.Stride(self.rd)
+    def Grid(self): return self.grid
+
+    def desc(self):
+        return hyd_dm(C.c_void_p(self.store.data_ptr()), self.ld, self.m, self.n, self.cd, self.rd, self.ca, self.ra, 0, 0)
+
+    def Matrix(self):
+        """The local block as an (lh, lw) view (column-major)."""
+        return self.store[: self.lw, : self.lh].t()
+
+    def set_from_global(self, G):
+        """Fill this rank's block from a full (m, n) host array: local (iLoc, jLoc) = G[colShift + iLoc*colStride, ...]."""
+        blk = np.ascontiguousarray(G[self.colShift::self.ColStride(), self.rowShift::self.RowStride()].T, dtype=self.dtype)
+        assert blk.shape == (self.lw, self.lh), (blk.shape, self.lw, self.lh)
+        if self.lh and self.lw:
+            self.store[: self.lw, : self.lh].copy_(torch.from_numpy(blk))
+        return self
+
+    def local_numpy(self):
+        return self.store[: self.lw, : self.lh].t().cpu().numpy()
+
+    def scatter_into_global(self, G):
+        if self.lh and self.lw:
+            G[self.colShift::self.ColStride(), self.rowShift::self.RowStride()] = self.local_numpy()
+
+
+def _sfx(dtype):
+    return "f64" if np.dtype(dtype) == np.float64 else "f32"
+
+
+def _scalar(dtype, v):
+    return C.c_double(v) if np.dtype(dtype) == np.float64 else C.c_float(v)
+
+
+def Copy(A, B, stream=None):
+    """B = A between any two supported distributions (DistMatrix::operator=)."""
+    a, b = A.desc(), B.desc()
+    check(getattr(lib, "hyd_redist_" + _sfx(A.dtype))(A.grid.h, C.byref(a), C.byref(b), 0, _stream_ptr(stream)))
+
+
+def Transpose(A, B, stream=None):
+    """B = A^T (El::Transpose(A, B), Transpose.hpp:318-356)."""
+    a, b = A.desc(), B.desc()
+    check(getattr(lib, "hyd_redist_" + _sfx(A.dtype))(A.grid.h, C.byref(a), C.byref(b), 1, _stream_ptr(stream)))
+
+
+def AxpyContract(alpha, A, B, stream=None):
+    a, b = A.desc(), B.desc()
+    check(getattr(lib, "hyd_axpy_contract_" + _sfx(A.dtype))(A.grid.h, _scalar(A.dtype, alpha), C.byref(a), C.byref(b), 0,
+                                                             _stream_ptr(stream)))
+
+
+def TransposeAxpyContract(alpha, A, B, stream=None):
+    a, b = A.desc(), B.desc()
+    check(getattr(lib, "hyd_axpy_contract_" + _sfx(A.dtype))(A.grid.h, _scalar(A.dtype, alpha), C.byref(a), C.byref(b), 1,
+                                                             _stream_ptr(stream)))
+
+
+def Gemm(orientA, orientB, alpha, A, B, beta, Cm, alg=GEMM_DEFAULT, stream=None, blocksize=None):
+    """C := alpha op(A) op(B) + beta C  (El::Gemm on AbstractDistMatrix)."""
+    a, b, c = A.desc(), B.desc(), Cm.desc()
+    nb = Blocksize() if blocksize is None else int(blocksize)
+    host = Cm.store.device.type == "cpu"
+    fn = getattr(lib, ("hyd_gemm_host_" if host else "hyd_gemm_") + _sfx(Cm.dtype))
+    check(fn(Cm.grid.h, orientA, orientB, alg, _scalar(Cm.dtype, alpha), C.byref(a), C.byref(b), _scalar(Cm.dtype, beta),
+             C.byref(c), nb, _stream_ptr(stream)))
+
+
+def lgemm(tA, tB, m, n, k, alpha, A, lda, B, ldb, beta, Cm, ldc, dtype=np.float64, stream=None):
+    """gpu_blas::Gemm on raw column-major device buffers held by torch tensors."""
+    fn = getattr(lib, "hyd_lgemm_" + _sfx(dtype))
+    check(fn(tA, tB, m, n, k, _scalar(dtype, alpha), C.c_void_p(A.data_ptr()), lda, C.c_void_p(B.data_ptr()), ldb,
+             _scalar(dtype, beta), C.c_void_p(Cm.data_ptr()), ldc, _stream_ptr(stream)))
+
+
+def run_ranks(P, fn, height=None, order=COLUMN_MAJOR, device=0):
+    """Run fn(grid) on P rank-threads sharing ONE GPU (hyd_local_group); returns the per-rank results.
+
+    Each rank-thread works on its own CUDA stream.  This is how the multi-rank engine is
+    parity-tested on a single-GPU box; the exchange is stream-ordered device copies."""
+    grp = LocalGroup(P)
+    out, err = [None] * P, [None] * P
+
+    def body(rank):
+        try:
+            torch.cuda.set_device(device)
+            st = torch.cuda.Stream()
+            with torch.cuda.stream(st):
+                w = World.local(grp, rank)
+                g = Grid(w, height, order)
+                try:
+                    out[rank] = fn(g)
+                    st.synchronize()
+                finally:
+                    w.barrier()
+                    g.destroy()
+                    w.destroy()
+        except BaseException as e:  # noqa: BLE001
+            err[rank] = e
+
+    th = [threading.Thread(target=body, args=(r,)) for r in range(P)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    grp.destroy()
+    for e in err:
+        if e is not None:
+            raise e
+    return out

@@ -47,6 +47,24 @@ int hyd_lgemm_f32(int transA, int transB, int64_t m, int64_t n, int64_t k, float
                   const float* A, int64_t lda, const float* B, int64_t ldb, float beta,
                   float* C, int64_t ldc, hyd_stream_t stream);
 
+/* B := A^T (A is m x n, B is n x m), bit-exact.
+ * ref: gpu_blas::Copy(TRANSPOSE,...) -> cublas?geam(1,A,0,-) include/hydrogen/blas/GPU_BLAS_impl.hpp:152-172,558-567;
+ *      caller El::Transpose(Matrix<T,GPU>) include/El/blas_like/level1/Transpose.hpp:161-181. */
+int hyd_transpose_f64(int64_t m, int64_t n, const double* A, int64_t lda, double* B, int64_t ldb, hyd_stream_t stream);
+int hyd_transpose_f32(int64_t m, int64_t n, const float* A, int64_t lda, float* B, int64_t ldb, hyd_stream_t stream);
+/* B := A (m x n, both with leading dimensions).  ref: gpu_blas::Copy(NORMAL,...) GPU_BLAS_impl.hpp:84-106;
+ *      copy_2d_kernel src/hydrogen/blas/gpu/Copy.cu:24-69. */
+int hyd_copy2d_f64(int64_t m, int64_t n, const double* A, int64_t lda, double* B, int64_t ldb, hyd_stream_t stream);
+int hyd_copy2d_f32(int64_t m, int64_t n, const float* A, int64_t lda, float* B, int64_t ldb, hyd_stream_t stream);
+/* B += alpha*A.  ref: gpu_blas::Axpy 2-D GPU_BLAS_impl.hpp:108-132; axpy_2d_tiled_kernel src/hydrogen/blas/gpu/Axpy.cu:70-98
+ *      (the tail of axpy::util::InterleaveMatrixUpdate, include/El/blas_like/level1/Axpy/util.hpp:39-51). */
+int hyd_axpy2d_f64(int64_t m, int64_t n, double alpha, const double* A, int64_t lda, double* B, int64_t ldb, hyd_stream_t stream);
+int hyd_axpy2d_f32(int64_t m, int64_t n, float alpha, const float* A, int64_t lda, float* B, int64_t ldb, hyd_stream_t stream);
+/* A *= alpha (alpha == 0 stores exact zeros).  ref: gpu_blas::Scale 2-D GPU_BLAS_impl.hpp:190-209; El::Scale(beta,C) in
+ *      src/blas_like/level3/Gemm.cpp:287. */
+int hyd_scale2d_f64(int64_t m, int64_t n, double alpha, double* A, int64_t lda, hyd_stream_t stream);
+int hyd_scale2d_f32(int64_t m, int64_t n, float alpha, float* A, int64_t lda, hyd_stream_t stream);
+
 /* ---- index arithmetic (host, no GPU needed) ------------------------------------
  * ref: include/El/core/indexing/impl.hpp:33-66 (Length_, MaxLength_), :229-245 (Mod_, Shift_). */
 int64_t hyd_mod(int64_t a, int64_t b);
@@ -143,6 +161,14 @@ int hyd_gemm_f64(hyd_grid* g, int orientA, int orientB, int alg, double alpha, c
                  double beta, const hyd_dm* C, int64_t blocksize, hyd_stream_t stream);
 int hyd_gemm_f32(hyd_grid* g, int orientA, int orientB, int alg, float alpha, const hyd_dm* A, const hyd_dm* B,
                  float beta, const hyd_dm* C, int64_t blocksize, hyd_stream_t stream);
+
+/* Same operation with the local blocks of A, B, C in HOST memory (buf = host pointer; pinned memory makes the copies
+ * asynchronous): uploads the blocks, runs hyd_gemm_*, downloads C's block and synchronises `stream`.  This is the call a
+ * CPU-resident caller of El::Gemm makes (the reference's inter-device DistMatrix copies: MC_STAR.cpp:304-390, then Gemm). */
+int hyd_gemm_host_f64(hyd_grid* g, int orientA, int orientB, int alg, double alpha, const hyd_dm* A, const hyd_dm* B,
+                      double beta, const hyd_dm* C, int64_t blocksize, hyd_stream_t stream);
+int hyd_gemm_host_f32(hyd_grid* g, int orientA, int orientB, int alg, float alpha, const hyd_dm* A, const hyd_dm* B,
+                      float beta, const hyd_dm* C, int64_t blocksize, hyd_stream_t stream);
 
 /* Pipe-peak probe (register-resident loops): kind 0 = FP64 DFMA, 1 = DMMA m8n8k4, 2 = DMMA m16n8k16,
  * 3 = FP32 FFMA.  Writes achieved TFLOP/s.  Measurement aid for the roofline denominator. */

@@ -1,0 +1,134 @@
+"""-m gpu: distributed Gemm parity through hyd_gemm_* (El::Gemm on DistMatrix), every orientation x
+SUMMA variant, against the oracle's restated SUMMA loops (oracle/oracle_gemm.c) on the same inputs.
+
+Tolerances (written here, as BASELINE.json asks): relative Frobenius error <= 1e-13*sqrt(k) (fp64),
+1e-5*sqrt(k) (fp32); and the reference's own bound |x-y| <= 1e-10 / 1e-3 at alpha=2, beta=3
+(tests/blas_like/BasicGemm.cpp:93-94,108)."""
+import itertools
+
+import numpy as np
+import pytest
+import torch
+
+import oracle_lib as O
+from oracle_lib import MC, MR, VC, VR, STAR
+from elemental_b200 import host as H
+import gpu_util as U
+
+pytestmark = pytest.mark.gpu
+
+
+def _gemm_case(r, c, dtype, oA, oB, alg, m, n, k, nb, rng, dists=None, alpha=2.0, beta=3.0):
+    og = O.Grid(r, c, 1)
+    am, an = (k, m) if oA else (m, k)
+    bm, bn = (n, k) if oB else (k, n)
+    dA, dB, dC = dists or ((MC, MR), (MC, MR), (MC, MR))
+    mk = lambda h, w, d, seed: O.DM(og, h, w, d[0], d[1], U.rand_align(rng, og, d[0]), U.rand_align(rng, og, d[1]), dtype).fill(seed)
+    A, B, Cm = mk(am, an, dA, 1), mk(bm, bn, dB, 2), mk(m, n, dC, 3)
+    Cin = O.DM(og, m, n, dC[0], dC[1], Cm.ca, Cm.ra, dtype).fill(3)
+    O.gemm(oA, oB, alg, alpha, A, B, beta, Cm, nb)
+    return (oA, oB, alg, alpha, beta, nb, k), A, B, Cin, Cm
+
+
+def _run_cases(r, c, cases, dtype):
+    def body(grid):
+        res = []
+        for (oA, oB, alg, alpha, beta, nb, k), A, B, Cin, Cexp in cases:
+            a, b, cm = U.to_rank(grid, A), U.to_rank(grid, B), U.to_rank(grid, Cin, ldim_extra=2)
+            H.Gemm(oA, oB, alpha, a, b, beta, cm, alg, blocksize=nb)
+            res.append((U.block_of(cm), U.padding_untouched(cm), U.block_of(a), U.block_of(b)))
+        return res
+
+    out = H.run_ranks(r * c, body, height=r)
+    tol_rel = 1e-13 if dtype == np.float64 else 1e-5
+    tol_abs = 1e-10 if dtype == np.float64 else 1e-3
+    for i, ((oA, oB, alg, alpha, beta, nb, k), A, B, Cin, Cexp) in enumerate(cases):
+        num = den = 0.0
+        for p in range(r * c):
+            got, pad_ok, a_after, b_after = out[p][i]
+            exp = Cexp.block(p)
+            assert pad_ok
+            assert np.array_equal(a_after, A.block(p)) and np.array_equal(b_after, B.block(p))  # inputs untouched
+            d = got.astype(np.float64) - exp.astype(np.float64)
+            num += float((d * d).sum())
+            den += float((exp.astype(np.float64) ** 2).sum())
+            if got.size:
+                assert np.abs(d).max() <= tol_abs, (oA, oB, alg, p, np.abs(d).max())
+        rel = (num / max(den, 1e-300)) ** 0.5
+        assert rel <= tol_rel * max(1.0, k) ** 0.5, (oA, oB, alg, rel)
+
+
+@pytest.mark.parametrize("r,c", [(1, 1), (1, 2), (2, 2), (2, 4), (3, 2)])
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_gemm_all_variants(r, c, dtype):
+    rng = np.random.default_rng(17 * r + c)
+    cases = []
+    for oA, oB in itertools.product((0, 1), (0, 1)):
+        for alg in (H.GEMM_SUMMA_A, H.GEMM_SUMMA_B, H.GEMM_SUMMA_C, H.GEMM_SUMMA_DOT, H.GEMM_DEFAULT):
+            cases.append(_gemm_case(r, c, dtype, oA, oB, alg, 145, 138, 152, 32, rng))
+    _run_cases(r, c, cases, dtype)
+
+
+@pytest.mark.parametrize("r,c", [(1, 1), (2, 2), (2, 4)])
+def test_gemm_basicgemm_config(r, c):
+    """tests/blas_like/BasicGemm.cpp defaults: m=n=k=1000, blocksize 128, alpha=2, beta=3, [MC,MR]."""
+    rng = np.random.default_rng(5)
+    O.use_blas(True)
+    try:
+        cases = [_gemm_case(r, c, np.float64, 0, 0, H.GEMM_SUMMA_C, 1000, 1000, 1000, 128, rng),
+                 _gemm_case(r, c, np.float32, 0, 0, H.GEMM_SUMMA_C, 1000, 1000, 1000, 128, rng)]
+    finally:
+        O.use_blas(False)
+    _run_cases(r, c, cases[:1], np.float64)
+    _run_cases(r, c, cases[1:], np.float32)
+
+
+def test_gemm_default_heuristic_and_dot_operands():
+    """GEMM_DEFAULT picks Dot/B/A/C by shape (NN.hpp:910-925); [*,VC] operands pass the proxies untouched (config 5)."""
+    r, c = 2, 2
+    rng = np.random.default_rng(9)
+    cases = [
+        _gemm_case(r, c, np.float32, 0, 1, H.GEMM_DEFAULT, 40, 24, 600, 16, rng, dists=((STAR, VC), (STAR, VC), (MC, MR))),
+        _gemm_case(r, c, np.float32, 0, 1, H.GEMM_SUMMA_DOT, 2100, 24, 300, 16, rng, dists=((STAR, VC), (STAR, VC), (MC, MR))),
+        _gemm_case(r, c, np.float32, 0, 0, H.GEMM_DEFAULT, 30, 200, 100, 16, rng),   # m <= n, 2m <= k -> B
+        _gemm_case(r, c, np.float32, 0, 0, H.GEMM_DEFAULT, 200, 30, 100, 16, rng),   # n <= m, 2n <= k -> A
+        _gemm_case(r, c, np.float32, 1, 0, H.GEMM_SUMMA_C, 64, 64, 64, 16, rng, dists=((VC, STAR), (STAR, MR), (MR, MC))),
+    ]
+    _run_cases(r, c, cases, np.float32)
+
+
+def test_gemm_degenerate_and_errors():
+    rng = np.random.default_rng(2)
+    cases = [_gemm_case(2, 2, np.float64, 0, 0, H.GEMM_SUMMA_C, 5, 3, 1, 128, rng),
+             _gemm_case(2, 2, np.float64, 0, 0, H.GEMM_SUMMA_A, 1, 1, 7, 2, rng),
+             _gemm_case(2, 2, np.float64, 1, 1, H.GEMM_SUMMA_B, 9, 2, 3, 4, rng),
+             _gemm_case(2, 2, np.float64, 0, 0, H.GEMM_SUMMA_C, 16, 16, 40, 128, rng, alpha=1.0, beta=0.0)]
+    _run_cases(2, 2, cases, np.float64)
+
+    def body(grid):
+        a = H.DistMatrix(grid, 10, 12)
+        b = H.DistMatrix(grid, 13, 9)
+        cm = H.DistMatrix(grid, 10, 9)
+        with pytest.raises(H.HydrogenError, match="nonconformal"):
+            H.Gemm(0, 0, 1.0, a, b, 0.0, cm)
+        with pytest.raises(H.HydrogenError, match="CANNON"):
+            H.Gemm(0, 0, 1.0, a, H.DistMatrix(grid, 12, 9), 0.0, cm, H.GEMM_CANNON)
+        return True
+    assert H.run_ranks(1, body) == [True]
+
+
+def test_gemm_host_buffers_roundtrip():
+    """hyd_gemm_host_*: host-resident operands, copies inside the call."""
+    rng = np.random.default_rng(4)
+    case = _gemm_case(1, 1, np.float64, 0, 1, H.GEMM_SUMMA_C, 200, 150, 90, 32, rng)
+    (oA, oB, alg, alpha, beta, nb, k), A, B, Cin, Cexp = case
+
+    def body(grid):
+        mk = lambda X: H.DistMatrix(grid, X.m, X.n, X.cd, X.rd, X.dtype, X.ca, X.ra, device="cpu", pinned=True)
+        a, b, cm = mk(A), mk(B), mk(Cin)
+        for d, X in ((a, A), (b, B), (cm, Cin)):
+            d.store[: d.lw, : d.lh].copy_(torch.from_numpy(np.ascontiguousarray(X.block(0).T)))
+        H.Gemm(oA, oB, alpha, a, b, beta, cm, alg, blocksize=nb)
+        return cm.local_numpy()
+    got = H.run_ranks(1, body)[0]
+    assert np.abs(got - Cexp.block(0)).max() <= 1e-10
