@@ -75,6 +75,8 @@ for _n in ("hyd_grid_height", "hyd_grid_width", "hyd_grid_size", "hyd_grid_rank"
            "hyd_grid_vc_rank", "hyd_grid_vr_rank"):
     _sig(_n, i32, [vp])
 _sig("hyd_grid_set_overlap", i32, [vp, i32, i32])
+_sig("hyd_grid_profile", i32, [vp, i32])
+_sig("hyd_grid_profile_read", i32, [vp, i32, C.POINTER(C.c_longlong), C.POINTER(f64)])
 _sig("hyd_dist_stride", i32, [vp, i32])
 _sig("hyd_dist_rank", i32, [vp, i32])
 _sig("hyd_local_shape", i32, [vp, dmp, pi64, pi64, pi64, pi64])

@@ -163,6 +163,27 @@ int hyd_grid_set_overlap(hyd_grid* g, int overlap, int sm_reserve) {
     if (sm_reserve >= 0) g->g->sm_reserve = sm_reserve;
     return 0;
 }
+int hyd_grid_profile(hyd_grid* g, int enable) {
+    hyd::Grid& G = *g->g;
+    if (hyd::check_cuda(cudaDeviceSynchronize(), "hyd_grid_profile")) return 1;
+    G.profile = enable != 0;
+    for (auto& u : G.prof_used) u = 0;
+    return 0;
+}
+int hyd_grid_profile_read(hyd_grid* g, int kind, long long* launches, double* total_ms) {
+    hyd::Grid& G = *g->g;
+    if (kind < 0 || kind >= hyd::Grid::PROF_KINDS) return set_error("hyd_grid_profile_read: bad kind");
+    if (hyd::check_cuda(cudaDeviceSynchronize(), "hyd_grid_profile_read")) return 1;
+    double tot = 0;
+    for (size_t i = 0; i + 1 < G.prof_used[kind]; i += 2) {
+        float ms = 0;
+        if (hyd::check_cuda(cudaEventElapsedTime(&ms, G.prof_ev[kind][i], G.prof_ev[kind][i + 1]), "cudaEventElapsedTime")) return 1;
+        tot += ms;
+    }
+    if (launches) *launches = (long long)(G.prof_used[kind] / 2);
+    if (total_ms) *total_ms = tot;
+    return 0;
+}
 int hyd_dist_stride(const hyd_grid* g, int dist) { return g->g->shape.stride(dist); }
 int hyd_dist_rank(const hyd_grid* g, int dist) { return g->g->shape.dist_rank(dist, g->g->mc, g->g->mr); }
 

@@ -6,6 +6,7 @@
 #include "comm.h"
 #include "dist.h"
 #include <cuda_runtime.h>
+#include <vector>
 
 namespace hyd {
 
@@ -31,12 +32,32 @@ struct Grid {
     bool overlap = true;
     int sm_reserve = 8;  // SMs the local GEMM leaves to NCCL / pack kernels while overlapping
     long long launches = 0;
+    // optional per-kernel timing (bench.py's roofline leg): CUDA event pairs around each launch of a kind
+    enum { PROF_LGEMM = 0, PROF_REDIST = 1, PROF_REDUCE = 2, PROF_KINDS = 3 };
+    bool profile = false;
+    std::vector<cudaEvent_t> prof_ev[PROF_KINDS];   // start/stop pairs, in launch order
+    size_t prof_used[PROF_KINDS] = {0, 0, 0};
 
     int vc() const { return shape.vc(mc, mr); }
     int vr() const { return shape.vr(mc, mr); }
 };
 
 int ws_reserve(Workspace& w, size_t bytes);
+// RAII event pair around a launch sequence on stream s (no-op unless g.profile)
+struct ProfScope {
+    Grid& g; int kind; cudaStream_t s; bool on;
+    ProfScope(Grid& g_, int kind_, cudaStream_t s_) : g(g_), kind(kind_), s(s_), on(g_.profile) {
+        if (!on) return;
+        auto& v = g.prof_ev[kind];
+        while (v.size() < g.prof_used[kind] + 2) { cudaEvent_t e; cudaEventCreate(&e); v.push_back(e); }
+        cudaEventRecord(v[g.prof_used[kind]], s);
+    }
+    ~ProfScope() {
+        if (!on) return;
+        cudaEventRecord(g.prof_ev[kind][g.prof_used[kind] + 1], s);
+        g.prof_used[kind] += 2;
+    }
+};
 void grid_destroy(Grid* g);
 
 // dst := src (or src^T), any pair of supported element distributions / alignments.

@@ -159,6 +159,7 @@ int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot
     const GridShape& sh = g.shape;
     if (check_pair(sh, src, dst, transpose, "hyd_redist")) return 1;
     if (src.height == 0 || src.width == 0) return 0;
+    ProfScope prof(g, Grid::PROF_REDIST, s);
     const int P = sh.size();
     bool mcFree, mrFree;
     free_coords(src.colDist, src.rowDist, mcFree, mrFree);
@@ -229,6 +230,7 @@ int reduce_into(Grid& g, T alpha, const DM& src, const DM& dst, bool transpose, 
     const GridShape& sh = g.shape;
     if (check_pair(sh, src, dst, transpose, "hyd_axpy_contract")) return 1;
     if (src.height == 0 || src.width == 0) return 0;
+    ProfScope prof(g, Grid::PROF_REDUCE, s);
     const int P = sh.size();
     bool mcFree, mrFree;
     free_coords(src.colDist, src.rowDist, mcFree, mrFree);
@@ -325,6 +327,7 @@ void grid_destroy(Grid* g) {
     for (auto& w : g->ws) if (w.buf) cudaFree(w.buf);
     for (auto& w : g->panel) if (w.buf) cudaFree(w.buf);
     for (auto& w : g->host_stage) if (w.buf) cudaFree(w.buf);
+    for (auto& v : g->prof_ev) for (cudaEvent_t e : v) cudaEventDestroy(e);
     for (int i = 0; i < 2; ++i) {
         if (g->comm_stream[i]) cudaStreamDestroy(g->comm_stream[i]);
         if (g->ev_panel_ready[i]) cudaEventDestroy(g->ev_panel_ready[i]);

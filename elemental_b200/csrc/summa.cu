@@ -32,9 +32,10 @@ namespace hyd {
 namespace {
 
 template <typename T>
-int lgemm(int tA, int tB, i64 m, i64 n, i64 k, T alpha, const T* A, i64 lda, const T* B, i64 ldb, T beta, T* C,
+int lgemm(Grid& g, int tA, int tB, i64 m, i64 n, i64 k, T alpha, const T* A, i64 lda, const T* B, i64 ldb, T beta, T* C,
           i64 ldc, cudaStream_t s, int sm_reserve) {
     ++g_launches;
+    ProfScope prof(g, Grid::PROF_LGEMM, s);
     if constexpr (std::is_same<T, double>::value)
         return lgemm_f64_ex(tA, tB, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, s, sm_reserve);
     else
@@ -87,7 +88,7 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
             const i64 kb = std::min(nb, k - k0);
             const T* a = static_cast<const T*>(A.buf) + (oA ? k0 : k0 * A.ldim);
             const T* b = static_cast<const T*>(B.buf) + (oB ? k0 * B.ldim : k0);
-            if (lgemm<T>(oA, oB, m, n, kb, alpha, a, A.ldim, b, B.ldim, T(1), static_cast<T*>(C.buf), C.ldim, s, 0))
+            if (lgemm<T>(g, oA, oB, m, n, kb, alpha, a, A.ldim, b, B.ldim, T(1), static_cast<T*>(C.buf), C.ldim, s, 0))
                 return 1;
         }
         return 0;
@@ -117,7 +118,7 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
             cudaEventRecord(g.ev_panel_ready[buf], cs);
             cudaStreamWaitEvent(s, g.ev_panel_ready[buf], 0);
         }
-        if (lgemm<T>(0, 1, Lc.lh, Lc.lw, kb, alpha, static_cast<const T*>(Ap.buf), Ap.ldim,
+        if (lgemm<T>(g, 0, 1, Lc.lh, Lc.lw, kb, alpha, static_cast<const T*>(Ap.buf), Ap.ldim,
                      static_cast<const T*>(Bp.buf), Bp.ldim, T(1), static_cast<T*>(C.buf), C.ldim, s,
                      overlap ? g.sm_reserve : 0))
             return 1;
@@ -147,7 +148,7 @@ int summa_a(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
         const int ma = oA ? A.rowAlign : A.colAlign;
         if (make_tmp<T>(g, g.panel[1], m, w, md, STAR, ma, 0, D1)) return 1;
         const i64 mloc = oA ? La.lw : La.lh, kloc = oA ? La.lh : La.lw;
-        if (lgemm<T>(oA, 0, mloc, w, kloc, alpha, static_cast<const T*>(A.buf), A.ldim, static_cast<const T*>(Bp.buf),
+        if (lgemm<T>(g, oA, 0, mloc, w, kloc, alpha, static_cast<const T*>(A.buf), A.ldim, static_cast<const T*>(Bp.buf),
                      Bp.ldim, T(0), static_cast<T*>(D1.buf), D1.ldim, s, 0))
             return 1;
         if (kloc == 0 && scale_local<T>(mloc, w, T(0), static_cast<T*>(D1.buf), D1.ldim, s)) return 1;
@@ -178,7 +179,7 @@ int summa_b(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
         const int na = oB ? B.colAlign : B.rowAlign;
         if (make_tmp<T>(g, g.panel[1], n, h, nd, STAR, na, 0, D1t)) return 1;
         const i64 nloc = oB ? Lb.lh : Lb.lw, kloc = oB ? Lb.lw : Lb.lh;
-        if (lgemm<T>(oB ? 0 : 1, 0, nloc, h, kloc, alpha, static_cast<const T*>(B.buf), B.ldim,
+        if (lgemm<T>(g, oB ? 0 : 1, 0, nloc, h, kloc, alpha, static_cast<const T*>(B.buf), B.ldim,
                      static_cast<const T*>(Ap.buf), Ap.ldim, T(0), static_cast<T*>(D1t.buf), D1t.ldim, s, 0))
             return 1;
         if (kloc == 0 && scale_local<T>(nloc, h, T(0), static_cast<T*>(D1t.buf), D1t.ldim, s)) return 1;
@@ -205,7 +206,7 @@ int summa_dot(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A
             if (make_tmp<T>(g, g.panel[0], mb, nbk, STAR, STAR, 0, 0, C11)) return 1;
             const T* a = static_cast<const T*>(A.buf) + (oA ? i0 * A.ldim : i0);
             const T* b = static_cast<const T*>(B.buf) + (oB ? j0 : j0 * B.ldim);
-            if (lgemm<T>(oA, oB, mb, nbk, kloc, alpha, a, A.ldim, b, B.ldim, T(0), static_cast<T*>(C11.buf), C11.ldim,
+            if (lgemm<T>(g, oA, oB, mb, nbk, kloc, alpha, a, A.ldim, b, B.ldim, T(0), static_cast<T*>(C11.buf), C11.ldim,
                          s, 0))
                 return 1;
             if (kloc == 0 && scale_local<T>(mb, nbk, T(0), static_cast<T*>(C11.buf), C11.ldim, s)) return 1;

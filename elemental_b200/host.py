@@ -136,6 +136,15 @@ class Grid:
     def SetOverlap(self, overlap=True, sm_reserve=-1):
         check(lib.hyd_grid_set_overlap(self.h, int(overlap), sm_reserve))
 
+    def Profile(self, enable=True):
+        check(lib.hyd_grid_profile(self.h, int(enable)))
+
+    def ProfileRead(self, kind=0):
+        """(launches, total device ms) of kind 0 = local GEMM, 1 = redistribution, 2 = reduce-scatter."""
+        n, ms = C.c_longlong(), C.c_double()
+        check(lib.hyd_grid_profile_read(self.h, kind, C.byref(n), C.byref(ms)))
+        return n.value, ms.value
+
     def destroy(self):
         if self.h:
             lib.hyd_grid_destroy(self.h)

@@ -125,6 +125,11 @@ int hyd_grid_vr_rank(const hyd_grid* g);
 /* engine knobs: overlap panel gathers with the local GEMM (default 1); SMs left to comm kernels (default 8) */
 int hyd_grid_set_overlap(hyd_grid* g, int overlap, int sm_reserve);
 
+/* per-kernel device timing: enable (also resets), then read launches and summed CUDA-event time of
+ * kind 0 = local GEMM launches, 1 = redistributions, 2 = reduce-scatters issued through this grid. */
+int hyd_grid_profile(hyd_grid* g, int enable);
+int hyd_grid_profile_read(hyd_grid* g, int kind, long long* launches, double* total_ms);
+
 /* stride / rank / local shape of a distribution on this grid (host; valid for any rank via mc,mr) */
 int hyd_dist_stride(const hyd_grid* g, int dist);
 int hyd_dist_rank(const hyd_grid* g, int dist);
