@@ -20,17 +20,26 @@
 //     product is unchanged.
 #include "ptx.cuh"
 #include "hyd_internal.h"
+#include <stdlib.h>
 
 namespace hyd {
 
-constexpr int BM = 128, BN = 128, BK = 16;
-constexpr int kConsumerWarps = 8;
-constexpr int kThreads = (kConsumerWarps + 4) * 32;  // 2 consumer warpgroups + 1 producer warpgroup
-constexpr int kStageBytesA = BM * BK * 8;  // 16 KiB
-constexpr int kStageBytesB = BN * BK * 8;  // 16 KiB
-constexpr int kStageBytes = kStageBytesA + kStageBytesB;
-constexpr int kStages = 6;  // 192 KiB ring
-constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int BM = 128, BK = 16;
+// Two tile configurations (template parameter WN = consumer warps along n):
+//   WN = 4 : 128 x 128 tile, 8 consumer warps (2 x 4), 6-stage ring, ONE CTA per SM  (setmaxnreg split)
+//   WN = 2 : 128 x  64 tile, 4 consumer warps (2 x 2), 4-stage ring, TWO CTAs per SM -- while one CTA
+//            runs its epilogue (C read-modify-write) the other keeps the DMMA pipe busy.
+template <int WN> struct Cfg {
+    static constexpr int BN = 32 * WN;
+    static constexpr int kConsumerWarps = 2 * WN;
+    static constexpr int kThreads = (WN == 4) ? (kConsumerWarps + 4) * 32 : (kConsumerWarps + 1) * 32;
+    static constexpr int kCtasPerSm = (WN == 4) ? 1 : 2;
+    static constexpr int kStageBytesA = BM * BK * 8;
+    static constexpr int kStageBytesB = BN * BK * 8;
+    static constexpr int kStageBytes = kStageBytesA + kStageBytesB;
+    static constexpr int kStages = (WN == 4) ? 6 : 4;
+    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+};
 
 // Operand staging type.
 //  MT (outer-contiguous): global element (o,k) at o + k*ld.  smem = BM/16 boxes of
@@ -39,19 +48,20 @@ constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*
 //      (128 B lines, SWIZZLE_128B, XOR key = o & 7).
 enum { MT = 0, KT = 1 };
 
-// kmap: which contraction index (0..15 inside a stage) fragment slot (t, j) carries.
-//  KM_M is conflict-free for MT operands, KM_K for KT operands.
-template <int KM>
+// kmap: which contraction index (0..15 inside a stage) fragment slot (t, j) carries.  Any bijection
+// works as long as A and B use the same one.  This one is bank-conflict free for BOTH staging types:
+//   MT needs bits {1,2} of k to be a bijection of t (for fixed j), KT needs bits {0,3} of k to be one;
+//   k = b0 | b1<<1 | b2<<2 | b3<<3 with (b1,b2) = t and (b0,b3) = t xor j (a Latin square in t, j).
 __device__ __forceinline__ int kmap(int t, int j) {
-    if (KM == MT) return 2 * t + (j & 1) + 8 * (j >> 1);
-    return (t & 1) + 8 * (t >> 1) + 2 * j;
+    const int x = t ^ j;
+    return (x & 1) | (t << 1) | ((x >> 1) << 3);
 }
 
 // Per-thread byte offset (inside an operand stage) of fragment slot j for the
 // 8-row group starting at outer index 0; the caller adds the group's base.
-template <int TYPE, int KM>
+template <int TYPE>
 __device__ __forceinline__ uint32_t frag_off(int g, int t, int j) {
-    const int k = kmap<KM>(t, j);
+    const int k = kmap(t, j);
     if (TYPE == MT) return k * 128 + ((g * 8) ^ ((k & 7) << 4));
     return g * 128 + ((k * 8) ^ (g << 4));
 }
@@ -62,12 +72,14 @@ __device__ __forceinline__ uint32_t group_base(int o8) {
     return o8 * 128;
 }
 
-template <int TA, int TB>
-__global__ void __launch_bounds__(kThreads, 1)
+template <int TA, int TB, int WN>
+__global__ void __launch_bounds__(Cfg<WN>::kThreads, Cfg<WN>::kCtasPerSm)
 dgemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                  double* __restrict__ C, long long ldc, int M, int N, int K, double alpha,
                  double beta, int tiles_m, int tiles_n, int group_m) {
-    constexpr int KM = (TA == KT && TB == KT) ? KT : MT;
+    typedef Cfg<WN> G;
+    constexpr int BN = G::BN, kStages = G::kStages, kStageBytes = G::kStageBytes, kStageBytesA = G::kStageBytesA;
+    constexpr int kConsumerWarps = G::kConsumerWarps;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t bar_base = smem_base + kStages * kStageBytes;
@@ -98,8 +110,8 @@ dgemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     };
 
     if (warp >= kConsumerWarps) {
-        // ===================== TMA producer warpgroup =====================
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        // ===================== TMA producer =====================
+        if (WN == 4) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
         if (warp == kConsumerWarps && lane == 0) {
             tma_prefetch_desc(&mapA);
             tma_prefetch_desc(&mapB);
@@ -136,14 +148,14 @@ dgemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     }
 
     // ===================== DMMA consumers =====================
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+    if (WN == 4) asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
     const int g = lane >> 2, t = lane & 3;
-    const int wm = warp & 1, wn = warp >> 1;  // 2 x 4 warps, warp tile 64 x 32
+    const int wm = warp & 1, wn = warp >> 1;  // 2 x WN warps, warp tile 64 x 32
     uint32_t offA[4], offB[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-        offA[j] = group_base<TA>(wm * 64) + frag_off<TA, KM>(g, t, j);
-        offB[j] = kStageBytesA + group_base<TB>(wn * 32) + frag_off<TB, KM>(g, t, j);
+        offA[j] = group_base<TA>(wm * 64) + frag_off<TA>(g, t, j);
+        offB[j] = kStageBytesA + group_base<TB>(wn * 32) + frag_off<TB>(g, t, j);
     }
     const uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
 
@@ -163,54 +175,85 @@ dgemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         for (int kb = 0; kb < num_kb; ++kb) {
             mbar_wait(full_bar(stage), phase);
             const uint8_t* st = smem_gen + stage * kStageBytes;
-            double bf[4][4];
+            // two k8 halves per stage (m16n8k8: 24 operand registers live instead of 48)
 #pragma unroll
-            for (int nt = 0; nt < 4; ++nt) {
+            for (int h = 0; h < 2; ++h) {
+                double bf[4][2];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    uint32_t o;
-                    if (TB == MT) o = (offB[j] + (nt >> 1) * 2048) ^ ((nt & 1) * 64);
-                    else          o = offB[j] + nt * 1024;
-                    bf[nt][j] = *reinterpret_cast<const double*>(st + o);
-                }
-            }
+                for (int nt = 0; nt < 4; ++nt) {
 #pragma unroll
-            for (int mt = 0; mt < 4; ++mt) {
-                double af[8];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    uint32_t o;
-                    if (TA == MT) o = (offA[i >> 1] + mt * 2048) ^ ((i & 1) * 64);
-                    else          o = offA[i >> 1] + mt * 2048 + (i & 1) * 1024;
-                    af[i] = *reinterpret_cast<const double*>(st + o);
+                    for (int j = 0; j < 2; ++j) {
+                        uint32_t o;
+                        if (TB == MT) o = (offB[2 * h + j] + (nt >> 1) * 2048) ^ ((nt & 1) * 64);
+                        else          o = offB[2 * h + j] + nt * 1024;
+                        bf[nt][j] = *reinterpret_cast<const double*>(st + o);
+                    }
                 }
 #pragma unroll
-                for (int nt = 0; nt < 4; ++nt) dmma_16816(acc[mt][nt], af, bf[nt]);
+                for (int mt = 0; mt < 4; ++mt) {
+                    double af[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        uint32_t o;
+                        if (TA == MT) o = (offA[2 * h + (i >> 1)] + mt * 2048) ^ ((i & 1) * 64);
+                        else          o = offA[2 * h + (i >> 1)] + mt * 2048 + (i & 1) * 1024;
+                        af[i] = *reinterpret_cast<const double*>(st + o);
+                    }
+#pragma unroll
+                    for (int nt = 0; nt < 4; ++nt)
+                        dmma_1688(acc[mt][nt], af[0], af[1], af[2], af[3], bf[nt][0], bf[nt][1]);
+                }
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(empty_bar(stage));
             if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
 
-        // ---- epilogue: C = alpha*acc + beta*C, straight from registers ----
+        // ---- epilogue: C = alpha*acc + beta*C straight from registers.  Loads of the old C values are
+        // issued in batches of 16 (one 8-column group), the next batch is in flight while the current one
+        // is combined and stored, so the tile costs ~5 memory round trips instead of 64. ----
         const int row0 = tm * BM + wm * 64 + g;
         const int col0 = tn * BN + wn * 32 + 2 * t;
+        const bool full = (tm * BM + BM <= M) && (tn * BN + BN <= N);
+        if (full) {
+            double* cb = C + (long long)col0 * ldc + row0;
+            // batch b = (nt, c): one column, 8 rows (q); double-buffered
+            double old[2][8];
+            const bool rd = (beta != 0.0);
+            auto load_batch = [&](int b, double (&o)[8]) {
 #pragma unroll
-        for (int nt = 0; nt < 4; ++nt) {
+                for (int q = 0; q < 8; ++q) o[q] = __ldcs(cb + (long long)((b >> 1) * 8 + (b & 1)) * ldc + q * 8);
+            };
+            if (rd) load_batch(0, old[0]);
 #pragma unroll
-            for (int c = 0; c < 2; ++c) {
-                const int col = col0 + nt * 8 + c;
-                if (col < N) {
-                    double* cp = C + (long long)col * ldc;
+            for (int b = 0; b < 8; ++b) {
+                if (rd && b + 1 < 8) load_batch(b + 1, old[(b + 1) & 1]);
+                const int nt = b >> 1, c = b & 1;
 #pragma unroll
-                    for (int mt = 0; mt < 4; ++mt) {
+                for (int q = 0; q < 8; ++q) {
+                    double v = alpha * acc[q >> 1][nt][(q & 1) * 2 + c];
+                    if (rd) v += beta * old[b & 1][q];
+                    __stcs(cb + (long long)(nt * 8 + c) * ldc + q * 8, v);
+                }
+            }
+        } else {
 #pragma unroll
-                        for (int h = 0; h < 2; ++h) {
-                            const int row = row0 + mt * 16 + h * 8;
-                            if (row < M) {
-                                const double v = alpha * acc[mt][nt][h * 2 + c];
-                                if (beta == 0.0) cp[row] = v;
-                                else cp[row] = v + beta * cp[row];
+            for (int nt = 0; nt < 4; ++nt) {
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    const int col = col0 + nt * 8 + c;
+                    if (col < N) {
+                        double* cp = C + (long long)col * ldc;
+#pragma unroll
+                        for (int mt = 0; mt < 4; ++mt) {
+#pragma unroll
+                            for (int h = 0; h < 2; ++h) {
+                                const int row = row0 + mt * 16 + h * 8;
+                                if (row < M) {
+                                    const double v = alpha * acc[mt][nt][h * 2 + c];
+                                    if (beta == 0.0) cp[row] = v;
+                                    else cp[row] = v + beta * cp[row];
+                                }
                             }
                         }
                     }
@@ -301,21 +344,42 @@ static bool make_map_f64(CUtensorMap* map, int type, const double* base, long lo
     return r == CUDA_SUCCESS;
 }
 
-template <int TA, int TB>
+// HYD_DGEMM_WN = 2 | 4 overrides the tile configuration (experiments / ncu A-B runs)
+static int dgemm_cfg() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("HYD_DGEMM_WN");
+        v = (e && atoi(e) == 4) ? 4 : (e && atoi(e) == 2) ? 2 : 0;
+    }
+    return v;
+}
+
+template <int TA, int TB, int WN>
 static cudaError_t launch_tma(const CUtensorMap& ma, const CUtensorMap& mb, double* C, long long ldc,
                               int M, int N, int K, double alpha, double beta, cudaStream_t s, int sm_reserve) {
+    typedef Cfg<WN> G;
     static bool attr_set = false;
-    auto kern = dgemm_tma_kernel<TA, TB>;
+    auto kern = dgemm_tma_kernel<TA, TB, WN>;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::kSmemBytes);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    const int tiles_m = (M + BM - 1) / BM, tiles_n = (N + BN - 1) / BN;
-    const int grid = max(1, min(tiles_m * tiles_n, num_sms() - sm_reserve));
+    const int tiles_m = (M + BM - 1) / BM, tiles_n = (N + G::BN - 1) / G::BN;
+    const int grid = max(1, min(tiles_m * tiles_n, (num_sms() - sm_reserve) * G::kCtasPerSm));
     const int group_m = 16;
-    kern<<<grid, kThreads, kSmemBytes, s>>>(ma, mb, C, ldc, M, N, K, alpha, beta, tiles_m, tiles_n, group_m);
+    kern<<<grid, G::kThreads, G::kSmemBytes, s>>>(ma, mb, C, ldc, M, N, K, alpha, beta, tiles_m, tiles_n, group_m);
     return cudaGetLastError();
+}
+
+template <int WN>
+static cudaError_t dispatch_tma(int typeA, int typeB, const CUtensorMap& ma, const CUtensorMap& mb, double* C,
+                                long long ldc, int M, int N, int K, double alpha, double beta, cudaStream_t s,
+                                int sm_reserve) {
+    if (typeA == MT && typeB == MT) return launch_tma<MT, MT, WN>(ma, mb, C, ldc, M, N, K, alpha, beta, s, sm_reserve);
+    if (typeA == MT && typeB == KT) return launch_tma<MT, KT, WN>(ma, mb, C, ldc, M, N, K, alpha, beta, s, sm_reserve);
+    if (typeA == KT && typeB == MT) return launch_tma<KT, MT, WN>(ma, mb, C, ldc, M, N, K, alpha, beta, s, sm_reserve);
+    return launch_tma<KT, KT, WN>(ma, mb, C, ldc, M, N, K, alpha, beta, s, sm_reserve);
 }
 
 int lgemm_f64(int tA, int tB, long long m, long long n, long long k, double alpha, const double* A,
@@ -346,13 +410,12 @@ int lgemm_f64_ex(int tA, int tB, long long m, long long n, long long k, double a
     const bool tma_ok = ((uintptr_t)A % 16 == 0) && ((uintptr_t)B % 16 == 0) && (lda % 2 == 0) &&
                         (ldb % 2 == 0);
     CUtensorMap ma, mb;
+    const int wn = dgemm_cfg() ? dgemm_cfg() : 4;
     if (tma_ok && make_map_f64(&ma, typeA, A, lda, (int)m, (int)k, BM) &&
-        make_map_f64(&mb, typeB, B, ldb, (int)n, (int)k, BN)) {
-        cudaError_t e;
-        if (typeA == MT && typeB == MT) e = launch_tma<MT, MT>(ma, mb, C, ldc, m, n, k, alpha, beta, s, sm_reserve);
-        else if (typeA == MT && typeB == KT) e = launch_tma<MT, KT>(ma, mb, C, ldc, m, n, k, alpha, beta, s, sm_reserve);
-        else if (typeA == KT && typeB == MT) e = launch_tma<KT, MT>(ma, mb, C, ldc, m, n, k, alpha, beta, s, sm_reserve);
-        else e = launch_tma<KT, KT>(ma, mb, C, ldc, m, n, k, alpha, beta, s, sm_reserve);
+        make_map_f64(&mb, typeB, B, ldb, (int)n, (int)k, wn == 4 ? 128 : 64)) {
+        cudaError_t e = (wn == 4)
+            ? dispatch_tma<4>(typeA, typeB, ma, mb, C, ldc, (int)m, (int)n, (int)k, alpha, beta, s, sm_reserve)
+            : dispatch_tma<2>(typeA, typeB, ma, mb, C, ldc, (int)m, (int)n, (int)k, alpha, beta, s, sm_reserve);
         return check_cuda(e, "dgemm_tma_kernel");
     }
     dim3 grid((unsigned)((m + 63) / 64), (unsigned)((n + 63) / 64));

@@ -76,8 +76,10 @@ int ensure_engine(Grid& g) {
 
 // ---- SUMMA-C (stationary C) -------------------------------------------------
 template <typename T>
-int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, const DM& B, const DM& C, i64 nb,
+int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, const DM& B, T beta, const DM& C, i64 nb,
             cudaStream_t s) {
+    // `beta` is applied by the first panel's update (C = alpha A1 B1^T + beta C) instead of a separate
+    // Scale(beta, C) pass (reference Gemm.cpp:287): one full read+write of C saved, and beta == 0 never reads C.
     const GridShape& sh = g.shape;
     const LocalShape Lc = local_shape(sh, C, g.mc, g.mr);
     const int es = sizeof(T);
@@ -88,7 +90,8 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
             const i64 kb = std::min(nb, k - k0);
             const T* a = static_cast<const T*>(A.buf) + (oA ? k0 : k0 * A.ldim);
             const T* b = static_cast<const T*>(B.buf) + (oB ? k0 * B.ldim : k0);
-            if (lgemm<T>(g, oA, oB, m, n, kb, alpha, a, A.ldim, b, B.ldim, T(1), static_cast<T*>(C.buf), C.ldim, s, 0))
+            if (lgemm<T>(g, oA, oB, m, n, kb, alpha, a, A.ldim, b, B.ldim, k0 == 0 ? beta : T(1), static_cast<T*>(C.buf),
+                         C.ldim, s, 0))
                 return 1;
         }
         return 0;
@@ -119,7 +122,7 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
             cudaStreamWaitEvent(s, g.ev_panel_ready[buf], 0);
         }
         if (lgemm<T>(g, 0, 1, Lc.lh, Lc.lw, kb, alpha, static_cast<const T*>(Ap.buf), Ap.ldim,
-                     static_cast<const T*>(Bp.buf), Bp.ldim, T(1), static_cast<T*>(C.buf), C.ldim, s,
+                     static_cast<const T*>(Bp.buf), Bp.ldim, k0 == 0 ? beta : T(1), static_cast<T*>(C.buf), C.ldim, s,
                      overlap ? g.sm_reserve : 0))
             return 1;
         if (overlap) cudaEventRecord(g.ev_panel_free[buf], s);
@@ -265,9 +268,11 @@ int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A0, const DM&
     }
     TempPool pool;
     const LocalShape Lc0 = local_shape(g.shape, C0, g.mc, g.mr);
-    // Scale(beta, C) first, exactly as the reference (Gemm.cpp:287): beta*C is rounded before accumulation
-    if (scale_local<T>(Lc0.lh, Lc0.lw, beta, static_cast<T*>(C0.buf), C0.ldim, s)) return 1;
     if (m == 0 || n == 0) return 0;
+    // Scale(beta, C) (reference Gemm.cpp:287).  SUMMA-C on a C that needs no proxy folds it into the first panel's
+    // epilogue; every other path (and k == 0) scales first, as the reference does.
+    const bool fuse_beta = (alg == 3) && k > 0 && C0.colDist == MC && C0.rowDist == MR;
+    if (!fuse_beta && scale_local<T>(Lc0.lh, Lc0.lw, beta, static_cast<T*>(C0.buf), C0.ldim, s)) return 1;
     DM A, B, C;
     if (read_proxy<T>(g, pool, C0, MC, MR, false, 0, false, 0, C, s)) return 1;
     int rc;
@@ -283,7 +288,7 @@ int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A0, const DM&
         if (read_proxy<T>(g, pool, B0, MC, MR, false, 0, false, 0, B, s)) return 1;
         if (alg == 1) rc = summa_a<T>(g, oA, oB, m, n, k, alpha, A, B, C, blocksize, s);
         else if (alg == 2) rc = summa_b<T>(g, oA, oB, m, n, k, alpha, A, B, C, blocksize, s);
-        else rc = summa_c<T>(g, oA, oB, m, n, k, alpha, A, B, C, blocksize, s);
+        else rc = summa_c<T>(g, oA, oB, m, n, k, alpha, A, B, fuse_beta ? beta : T(1), C, blocksize, s);
     }
     if (rc) return rc;
     if (C.buf != C0.buf) {  // write-back half of the ReadWrite proxy
