@@ -256,8 +256,12 @@ def run_ours(args):
             e2e = {"value": round(flops / (ems * 1e-3) / 1e12, 3), "unit": "TFLOP/s", "ms_per_step": round(ems, 3),
                    "h2d_bytes_per_step": int((hA.lh * hA.lw + hB.lh * hB.lw) * es), "d2h_bytes_per_step": int(hC.lh * hC.lw * es),
                    "api": "hyd_gemm_host_f64 (El::Gemm on host-resident DistMatrix blocks)", "steps": esteps}
-            same = torch.equal(hC.store[: hC.lw, : hC.lh], Cm.store[: Cm.lw, : Cm.lh].cpu())
-            e2e["matches_device_run"] = bool(same)
+            # the host path streams a narrower first panel, so the k-sum is grouped differently: compare with the
+            # device-resident run in the relative Frobenius norm (BASELINE.json tolerance 1e-13*sqrt(k) for fp64)
+            dd = hC.store[: hC.lw, : hC.lh].cuda() - Cm.store[: Cm.lw, : Cm.lh]
+            rel = float(dd.norm() / Cm.store[: Cm.lw, : Cm.lh].norm())
+            e2e["rel_frobenius_vs_device_run"] = rel
+            assert rel <= 1e-13 * n ** 0.5, rel
 
     cpu = None
     if rank == 0 and args.gpus == 1 and not args.no_cpu:

@@ -82,6 +82,7 @@ _sig("hyd_dist_rank", i32, [vp, i32])
 _sig("hyd_local_shape", i32, [vp, dmp, pi64, pi64, pi64, pi64])
 _sig("hyd_local_shape_of", i32, [i32, i32, i32, i32, dmp, pi64, pi64, pi64, pi64])
 _sig("hyd_view", i32, [vp, dmp, i64, i64, i64, i64, i32, dmp])
+_sig("hyd_redist_plan", i32, [i32, i32, i32, i32, dmp, dmp, i32, i32, pi64, pi64])
 _sig("hyd_redist_f64", i32, [vp, dmp, dmp, i32, vp])
 _sig("hyd_redist_f32", i32, [vp, dmp, dmp, i32, vp])
 _sig("hyd_axpy_contract_f64", i32, [vp, f64, dmp, dmp, i32, vp])

@@ -9,7 +9,7 @@ const char* last_error();
 int probe_peak(int kind, int iters, int ctas_per_sm, double* tflops);
 template <typename T>
 int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A, const DM& B, T beta, const DM& C, i64 blocksize,
-              cudaStream_t s);
+              cudaStream_t s, const void* hostA, i64 hostLdA, const void* hostB, i64 hostLdB);
 }  // namespace hyd
 
 struct hyd_world { hyd::World* w; };
@@ -61,6 +61,7 @@ static int gemm_host(hyd_grid* g, int oA, int oB, int alg, T alpha, const hyd_dm
         if (L[i].lh > 0 && L[i].lw > 0) {
             if (!host[i]->buf || host[i]->ldim < L[i].lh) return set_error("hyd_gemm_host: bad host buffer / ldim");
             if (i == 2 && beta == T(0)) continue;  // C is overwritten: no upload
+            if (i < 2) continue;                   // A, B: uploaded by dist_gemm (panel-pipelined for SUMMA-C)
             if (hyd::check_cuda(cudaMemcpy2DAsync(dev[i].buf, (size_t)dev[i].ldim * sizeof(T), host[i]->buf,
                                                   (size_t)host[i]->ldim * sizeof(T), (size_t)L[i].lh * sizeof(T),
                                                   (size_t)L[i].lw, cudaMemcpyHostToDevice, s),
@@ -68,7 +69,7 @@ static int gemm_host(hyd_grid* g, int oA, int oB, int alg, T alpha, const hyd_dm
                 return 1;
         }
     }
-    if (hyd::dist_gemm<T>(G, oA, oB, alg, alpha, dev[0], dev[1], beta, dev[2], blocksize, s)) return 1;
+    if (hyd::dist_gemm<T>(G, oA, oB, alg, alpha, dev[0], dev[1], beta, dev[2], blocksize, s, A->buf, A->ldim, B->buf, B->ldim)) return 1;
     if (L[2].lh > 0 && L[2].lw > 0 &&
         hyd::check_cuda(cudaMemcpy2DAsync(C->buf, (size_t)C->ldim * sizeof(T), dev[2].buf, (size_t)dev[2].ldim * sizeof(T),
                                           (size_t)L[2].lh * sizeof(T), (size_t)L[2].lw, cudaMemcpyDeviceToHost, s),
@@ -214,6 +215,15 @@ int hyd_view(const hyd_grid* g, const hyd_dm* a, int64_t i, int64_t j, int64_t h
     return 0;
 }
 
+int hyd_redist_plan(int gh, int gw, int order, int rank, const hyd_dm* src, const hyd_dm* dst, int transpose, int es,
+                    int64_t* sendBytes, int64_t* recvBytes) {
+    hyd::GridShape sh;
+    sh.r = gh; sh.c = gw; sh.col_major = order ? 1 : 0;
+    if (gh <= 0 || gw <= 0 || rank < 0 || rank >= gh * gw || !sendBytes || !recvBytes) return set_error("hyd_redist_plan: bad arguments");
+    if (check_dm(sh, src, "hyd_redist_plan") || check_dm(sh, dst, "hyd_redist_plan")) return 1;
+    return hyd::redist_plan(sh, rank, to_dm(src), to_dm(dst), transpose != 0, es, (hyd::i64*)sendBytes, (hyd::i64*)recvBytes);
+}
+
 // ---- distributed operations ----
 int hyd_redist_f64(hyd_grid* g, const hyd_dm* src, const hyd_dm* dst, int transpose, hyd_stream_t stream) {
     if (check_dm(g->g->shape, src, "hyd_redist") || check_dm(g->g->shape, dst, "hyd_redist")) return 1;
@@ -238,14 +248,14 @@ int hyd_gemm_f64(hyd_grid* g, int oA, int oB, int alg, double alpha, const hyd_d
     const hyd::GridShape& sh = g->g->shape;
     if (check_dm(sh, A, "hyd_gemm(A)") || check_dm(sh, B, "hyd_gemm(B)") || check_dm(sh, C, "hyd_gemm(C)")) return 1;
     return hyd::dist_gemm<double>(*g->g, oA, oB, alg, alpha, to_dm(A), to_dm(B), beta, to_dm(C), blocksize,
-                                  (cudaStream_t)stream);
+                                  (cudaStream_t)stream, nullptr, 0, nullptr, 0);
 }
 int hyd_gemm_f32(hyd_grid* g, int oA, int oB, int alg, float alpha, const hyd_dm* A, const hyd_dm* B, float beta,
                  const hyd_dm* C, int64_t blocksize, hyd_stream_t stream) {
     const hyd::GridShape& sh = g->g->shape;
     if (check_dm(sh, A, "hyd_gemm(A)") || check_dm(sh, B, "hyd_gemm(B)") || check_dm(sh, C, "hyd_gemm(C)")) return 1;
     return hyd::dist_gemm<float>(*g->g, oA, oB, alg, alpha, to_dm(A), to_dm(B), beta, to_dm(C), blocksize,
-                                 (cudaStream_t)stream);
+                                 (cudaStream_t)stream, nullptr, 0, nullptr, 0);
 }
 
 

@@ -4,6 +4,7 @@
 #include <nccl.h>
 #include <dlfcn.h>
 #include <pthread.h>
+#include <stdlib.h>
 #include <string.h>
 #include <vector>
 
@@ -14,7 +15,7 @@ namespace hyd {
 // plain C++ host program gets the system libnccl.so.2.
 namespace nccl {
 #define HYD_NCCL_FNS(X) \
-    X(ncclGetUniqueId) X(ncclCommInitRank) X(ncclCommDestroy) X(ncclGroupStart) X(ncclGroupEnd) X(ncclSend) \
+    X(ncclGetUniqueId) X(ncclCommInitRank) X(ncclCommInitRankConfig) X(ncclCommDestroy) X(ncclGroupStart) X(ncclGroupEnd) X(ncclSend) \
     X(ncclRecv) X(ncclAllReduce) X(ncclGetErrorString) X(ncclAllGather) X(ncclReduceScatter) X(ncclBroadcast)
 #define X(f) static decltype(&::f) f = nullptr;
 HYD_NCCL_FNS(X)
@@ -93,7 +94,14 @@ World* make_nccl_world(const void* uid, int rank, int size) {
     NcclWorld* w = new NcclWorld;
     w->rank = rank;
     w->size = size;
-    if (check_nccl(nccl::ncclCommInitRank(&w->comm, size, id, rank), "ncclCommInitRank")) {
+    // Communication kernels must fit into the few SMs the persistent local GEMM leaves free while panels
+    // are gathered under it: cap NCCL's CTA count and turn off CGA clusters (a 4-CTA cluster needs 4 free SMs
+    // of one GPC).  HYD_NCCL_MAX_CTAS overrides (0 = NCCL defaults).
+    ncclConfig_t cfg = NCCL_CONFIG_INITIALIZER;
+    int max_ctas = 8;
+    if (const char* e = getenv("HYD_NCCL_MAX_CTAS")) max_ctas = atoi(e);
+    if (max_ctas > 0) { cfg.minCTAs = 1; cfg.maxCTAs = max_ctas; cfg.cgaClusterSize = 0; }
+    if (check_nccl(nccl::ncclCommInitRankConfig(&w->comm, size, id, rank, &cfg), "ncclCommInitRankConfig")) {
         w->comm = nullptr;
         delete w;
         return nullptr;

@@ -27,10 +27,11 @@ struct Grid {
     cudaStream_t comm_stream[2] = {nullptr, nullptr};
     cudaEvent_t ev_panel_ready[2] = {nullptr, nullptr}, ev_panel_free[2] = {nullptr, nullptr};
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    std::vector<cudaEvent_t> upload_ev;  // per-panel H2D completion (hyd_gemm_host_*)
     Workspace panel[4];  // gathered panels (A/B x double buffer) or reduce temporaries
     Workspace host_stage[3];  // device images of host operands (hyd_gemm_host_*)
     bool overlap = true;
-    int sm_reserve = 8;  // SMs the local GEMM leaves to NCCL / pack kernels while overlapping
+    int sm_reserve = 4;  // SMs the local GEMM leaves to NCCL / pack kernels while overlapping
     long long launches = 0;
     // optional per-kernel timing (bench.py's roofline leg): CUDA event pairs around each launch of a kind
     enum { PROF_LGEMM = 0, PROF_REDIST = 1, PROF_REDUCE = 2, PROF_KINDS = 3 };
@@ -67,6 +68,8 @@ int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot
 template <typename T>
 int reduce_into(Grid& g, T alpha, const DM& src, const DM& dst, bool transpose, int slot, cudaStream_t s);
 
+int redist_plan(const GridShape& sh, int rank, const DM& src, const DM& dst, bool transpose, int es, i64* sendBytes,
+                i64* recvBytes);
 // view of rows [i0,i0+h) x cols [j0,j0+w) of a distributed matrix, as seen by rank (mc,mr)
 DM view(const GridShape& g, const DM& a, int mc, int mr, i64 i0, i64 j0, i64 h, i64 w, int elem_size);
 

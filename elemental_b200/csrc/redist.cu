@@ -154,6 +154,31 @@ int check_pair(const GridShape& sh, const DM& src, const DM& dst, bool transpose
 
 }  // namespace
 
+// Host-only: bytes rank `rank` sends to / receives from every owning-comm rank for dst := src (or src^T).
+// Entry [rank] is the part that stays local.  Used by the planner tests (no GPU needed).
+int redist_plan(const GridShape& sh, int rank, const DM& src, const DM& dst, bool transpose, int es, i64* sendBytes,
+                i64* recvBytes) {
+    if (check_pair(sh, src, dst, transpose, "hyd_redist_plan")) return 1;
+    const int P = sh.size();
+    int mc, mr;
+    sh.coords(rank, mc, mr);
+    bool mcFree, mrFree;
+    free_coords(src.colDist, src.rowDist, mcFree, mrFree);
+    const LocalShape Ls_me = local_shape(sh, src, mc, mr), Ld_me = local_shape(sh, dst, mc, mr);
+    for (int p = 0; p < P; ++p) {
+        sendBytes[p] = recvBytes[p] = 0;
+        int pmc, pmr;
+        sh.coords(p, pmc, pmr);
+        if ((mcFree && pmc != mc) || (mrFree && pmr != mr)) continue;
+        Prog pa, pb;
+        progs(src, transpose, Ls_me, local_shape(sh, dst, pmc, pmr), pa, pb);
+        sendBytes[p] = pa.count * pb.count * es;
+        progs(src, transpose, local_shape(sh, src, pmc, pmr), Ld_me, pa, pb);
+        recvBytes[p] = pa.count * pb.count * es;
+    }
+    return 0;
+}
+
 template <typename T>
 int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot, cudaStream_t s) {
     const GridShape& sh = g.shape;
@@ -328,6 +353,7 @@ void grid_destroy(Grid* g) {
     for (auto& w : g->panel) if (w.buf) cudaFree(w.buf);
     for (auto& w : g->host_stage) if (w.buf) cudaFree(w.buf);
     for (auto& v : g->prof_ev) for (cudaEvent_t e : v) cudaEventDestroy(e);
+    for (cudaEvent_t e : g->upload_ev) cudaEventDestroy(e);
     for (int i = 0; i < 2; ++i) {
         if (g->comm_stream[i]) cudaStreamDestroy(g->comm_stream[i]);
         if (g->ev_panel_ready[i]) cudaEventDestroy(g->ev_panel_ready[i]);

@@ -74,20 +74,75 @@ int ensure_engine(Grid& g) {
 }
 
 
+// Host images of A's and B's local blocks (hyd_gemm_host_*): SUMMA-C streams them to the device panel by panel
+// on an upload stream, so the H2D copies hide under the previous panels' GEMMs instead of preceding the whole Gemm.
+struct HostOperands { const void* A; i64 lda; const void* B; i64 ldb; };
+
+// upload the slice of a local block that holds global rows/cols [k0, k0+kb) of the k-dimension
+template <typename T>
+int upload_k_slice(const GridShape& sh, const DM& X, int mc, int mr, bool k_is_rows, i64 k0, i64 kb, const void* host,
+                   i64 ldh, cudaStream_t us) {
+    const LocalShape L = local_shape(sh, X, mc, mr);
+    if (L.lh == 0 || L.lw == 0) return 0;
+    if (k_is_rows) {
+        const i64 i0 = length_(k0, L.colShift, L.colStride), i1 = length_(k0 + kb, L.colShift, L.colStride);
+        if (i1 <= i0) return 0;
+        return check_cuda(cudaMemcpy2DAsync(static_cast<T*>(X.buf) + i0, (size_t)X.ldim * sizeof(T),
+                                            static_cast<const T*>(host) + i0, (size_t)ldh * sizeof(T),
+                                            (size_t)(i1 - i0) * sizeof(T), (size_t)L.lw, cudaMemcpyHostToDevice, us),
+                          "hyd_gemm_host: H2D rows");
+    }
+    const i64 j0 = length_(k0, L.rowShift, L.rowStride), j1 = length_(k0 + kb, L.rowShift, L.rowStride);
+    if (j1 <= j0) return 0;
+    return check_cuda(cudaMemcpy2DAsync(static_cast<T*>(X.buf) + j0 * X.ldim, (size_t)X.ldim * sizeof(T),
+                                        static_cast<const T*>(host) + j0 * ldh, (size_t)ldh * sizeof(T),
+                                        (size_t)L.lh * sizeof(T), (size_t)(j1 - j0), cudaMemcpyHostToDevice, us),
+                      "hyd_gemm_host: H2D cols");
+}
+
 // ---- SUMMA-C (stationary C) -------------------------------------------------
 template <typename T>
 int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, const DM& B, T beta, const DM& C, i64 nb,
-            cudaStream_t s) {
+            cudaStream_t s, const HostOperands* ho) {
     // `beta` is applied by the first panel's update (C = alpha A1 B1^T + beta C) instead of a separate
     // Scale(beta, C) pass (reference Gemm.cpp:287): one full read+write of C saved, and beta == 0 never reads C.
     const GridShape& sh = g.shape;
     const LocalShape Lc = local_shape(sh, C, g.mc, g.mr);
     const int es = sizeof(T);
+    if (ensure_engine(g)) return 1;
+    const bool overlap = g.overlap && sh.size() > 1;
+    // panel schedule.  The first panel's gather / upload cannot hide under a GEMM, so it is narrower
+    // (nb/4, >= 128): the exposed prologue shrinks 4x; only the grouping of the k-sum changes.
+    std::vector<i64> ks;
+    {
+        const i64 nb0 = (overlap || ho) ? std::min(nb, std::max<i64>(128, nb / 4)) : nb;
+        for (i64 k0 = 0; k0 < k; k0 += (k0 == 0 ? nb0 : nb)) ks.push_back(k0);
+        ks.push_back(k);
+    }
+    const size_t npanels = ks.size() - 1;
+    if (ho) {
+        // all uploads are enqueued now, in panel order, on the upload stream; consumers wait per panel
+        cudaStream_t us = g.comm_stream[1];
+        while (g.upload_ev.size() < npanels) {
+            cudaEvent_t e;
+            cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+            g.upload_ev.push_back(e);
+        }
+        if (check_cuda(cudaEventRecord(g.ev_join, s), "upload fork")) return 1;
+        cudaStreamWaitEvent(us, g.ev_join, 0);
+        for (size_t p = 0; p < npanels; ++p) {
+            const i64 k0 = ks[p], kb = ks[p + 1] - ks[p];
+            if (upload_k_slice<T>(sh, A, g.mc, g.mr, oA != 0, k0, kb, ho->A, ho->lda, us)) return 1;
+            if (upload_k_slice<T>(sh, B, g.mc, g.mr, oB == 0, k0, kb, ho->B, ho->ldb, us)) return 1;
+            cudaEventRecord(g.upload_ev[p], us);
+        }
+    }
     if (sh.size() == 1) {
         // 1x1 grid: [MC,*] and [MR,*] panels coincide with the operands' own storage
         // (the reference degenerates to local copies, RowAllGather.hpp:35-38); feed views directly.
-        for (i64 k0 = 0; k0 < k; k0 += nb) {
-            const i64 kb = std::min(nb, k - k0);
+        for (size_t p = 0; p < npanels; ++p) {
+            const i64 k0 = ks[p], kb = ks[p + 1] - ks[p];
+            if (ho) cudaStreamWaitEvent(s, g.upload_ev[p], 0);
             const T* a = static_cast<const T*>(A.buf) + (oA ? k0 : k0 * A.ldim);
             const T* b = static_cast<const T*>(B.buf) + (oB ? k0 * B.ldim : k0);
             if (lgemm<T>(g, oA, oB, m, n, kb, alpha, a, A.ldim, b, B.ldim, k0 == 0 ? beta : T(1), static_cast<T*>(C.buf),
@@ -96,17 +151,15 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
         }
         return 0;
     }
-    if (ensure_engine(g)) return 1;
-    const bool overlap = g.overlap;
     cudaStream_t cs = overlap ? g.comm_stream[0] : s;
     if (overlap) {
         if (check_cuda(cudaEventRecord(g.ev_fork, s), "fork")) return 1;
         cudaStreamWaitEvent(cs, g.ev_fork, 0);
     }
-    i64 step = 0;
-    for (i64 k0 = 0; k0 < k; k0 += nb, ++step) {
-        const i64 kb = std::min(nb, k - k0);
+    for (size_t step = 0; step < npanels; ++step) {
+        const i64 k0 = ks[step], kb = ks[step + 1] - ks[step];
         const int buf = (int)(step & 1);
+        if (ho) cudaStreamWaitEvent(cs, g.upload_ev[step], 0);
         DM Ap, Bp;
         if (make_tmp<T>(g, g.panel[buf], m, nb, MC, STAR, C.colAlign, 0, Ap)) return 1;
         if (make_tmp<T>(g, g.panel[2 + buf], n, nb, MR, STAR, C.rowAlign, 0, Bp)) return 1;
@@ -249,7 +302,7 @@ int read_proxy(Grid& g, TempPool& pool, const DM& a, int cd, int rd, bool colCon
 
 template <typename T>
 int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A0, const DM& B0, T beta, const DM& C0,
-              i64 blocksize, cudaStream_t s) {
+              i64 blocksize, cudaStream_t s, const void* hostA, i64 hostLdA, const void* hostB, i64 hostLdB) {
     oA = oA ? 1 : 0;
     oB = oB ? 1 : 0;
     const i64 m = C0.height, n = C0.width;
@@ -269,6 +322,15 @@ int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A0, const DM&
     TempPool pool;
     const LocalShape Lc0 = local_shape(g.shape, C0, g.mc, g.mr);
     if (m == 0 || n == 0) return 0;
+    // host-resident A/B (hyd_gemm_host_*): SUMMA-C on [MC,MR] operands streams them panel by panel under the
+    // GEMMs; every other path uploads both blocks first.
+    HostOperands ho{hostA, hostLdA, hostB, hostLdB};
+    const bool stream_ops = hostA && hostB && alg == 3 && k > 0 && A0.colDist == MC && A0.rowDist == MR &&
+                            B0.colDist == MC && B0.rowDist == MR;
+    if (hostA && hostB && !stream_ops) {
+        if (upload_k_slice<T>(g.shape, A0, g.mc, g.mr, false, 0, A0.width, hostA, hostLdA, s)) return 1;
+        if (upload_k_slice<T>(g.shape, B0, g.mc, g.mr, false, 0, B0.width, hostB, hostLdB, s)) return 1;
+    }
     // Scale(beta, C) (reference Gemm.cpp:287).  SUMMA-C on a C that needs no proxy folds it into the first panel's
     // epilogue; every other path (and k == 0) scales first, as the reference does.
     const bool fuse_beta = (alg == 3) && k > 0 && C0.colDist == MC && C0.rowDist == MR;
@@ -288,7 +350,7 @@ int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A0, const DM&
         if (read_proxy<T>(g, pool, B0, MC, MR, false, 0, false, 0, B, s)) return 1;
         if (alg == 1) rc = summa_a<T>(g, oA, oB, m, n, k, alpha, A, B, C, blocksize, s);
         else if (alg == 2) rc = summa_b<T>(g, oA, oB, m, n, k, alpha, A, B, C, blocksize, s);
-        else rc = summa_c<T>(g, oA, oB, m, n, k, alpha, A, B, fuse_beta ? beta : T(1), C, blocksize, s);
+        else rc = summa_c<T>(g, oA, oB, m, n, k, alpha, A, B, fuse_beta ? beta : T(1), C, blocksize, s, stream_ops ? &ho : nullptr);
     }
     if (rc) return rc;
     if (C.buf != C0.buf) {  // write-back half of the ReadWrite proxy
@@ -298,7 +360,7 @@ int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A0, const DM&
     return 0;
 }
 
-template int dist_gemm<double>(Grid&, int, int, int, double, const DM&, const DM&, double, const DM&, i64, cudaStream_t);
-template int dist_gemm<float>(Grid&, int, int, int, float, const DM&, const DM&, float, const DM&, i64, cudaStream_t);
+template int dist_gemm<double>(Grid&, int, int, int, double, const DM&, const DM&, double, const DM&, i64, cudaStream_t, const void*, i64, const void*, i64);
+template int dist_gemm<float>(Grid&, int, int, int, float, const DM&, const DM&, float, const DM&, i64, cudaStream_t, const void*, i64, const void*, i64);
 
 }  // namespace hyd

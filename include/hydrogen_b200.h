@@ -122,7 +122,7 @@ int hyd_grid_row(const hyd_grid* g);      /* MCRank */
 int hyd_grid_col(const hyd_grid* g);      /* MRRank */
 int hyd_grid_vc_rank(const hyd_grid* g);
 int hyd_grid_vr_rank(const hyd_grid* g);
-/* engine knobs: overlap panel gathers with the local GEMM (default 1); SMs left to comm kernels (default 8) */
+/* engine knobs: overlap panel gathers with the local GEMM (default 1); SMs left to comm kernels (default 4) */
 int hyd_grid_set_overlap(hyd_grid* g, int overlap, int sm_reserve);
 
 /* per-kernel device timing: enable (also resets), then read launches and summed CUDA-event time of
@@ -141,6 +141,12 @@ int hyd_local_shape_of(int gridHeight, int gridWidth, int order, int rank, const
 /* view of rows [i,i+h) x cols [j,j+w): alignment and buffer offset as El::View / operator()(IR,IR) */
 int hyd_view(const hyd_grid* g, const hyd_dm* a, int64_t i, int64_t j, int64_t h, int64_t w, int elemSize,
              hyd_dm* out);
+
+/* Host-only planner: bytes `rank` of an r x c grid sends to / receives from every rank for dst := src (transpose: src^T)
+ * in the one-hop exchange that replaces the reference's pack -> collective -> unpack chains
+ * (the headers under include/El/blas_like/level1/Copy/).  Arrays have gridHeight*gridWidth entries; entry [rank] is the local part. */
+int hyd_redist_plan(int gridHeight, int gridWidth, int order, int rank, const hyd_dm* src, const hyd_dm* dst, int transpose,
+                    int elemSize, int64_t* sendBytes, int64_t* recvBytes);
 
 /* ---- seam S1: distributed operations (collective over the grid; async on `stream`) --------- */
 

@@ -1,0 +1,99 @@
+"""CPU-only: the C-ABI library loads, exports every symbol include/hydrogen_b200.h declares, and its
+host-only entry points (index arithmetic, local shapes, views' metadata, redistribution planner) agree
+with the oracle.  No kernels are launched here."""
+import ctypes as C
+import itertools
+import os
+import re
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from elemental_b200 import lib, hyd_dm, LIB_PATH
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    src = open(os.path.join(ROOT, "include", "hydrogen_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(hyd_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    names = declared_symbols()
+    assert len(names) >= 50
+    raw = C.CDLL(LIB_PATH)
+    missing = [n for n in names if not hasattr(raw, n)]
+    assert not missing, missing
+    assert lib.hyd_version() >= 100
+
+
+def test_no_link_time_dependency_on_the_oracle_or_nccl():
+    import subprocess
+    out = subprocess.run(["ldd", LIB_PATH], capture_output=True, text=True).stdout
+    assert "oracle" not in out and "libnccl" not in out  # NCCL is bound at run time (comm.cu)
+
+
+def test_index_arithmetic_matches_oracle():
+    for n in range(0, 50):
+        for stride in range(1, 9):
+            assert lib.hyd_max_length(n, stride) == O.lib.orc_max_length(n, stride)
+            for shift in range(stride):
+                assert lib.hyd_length(n, shift, stride) == O.lib.orc_length(n, shift, stride)
+    for a in range(-20, 20):
+        for b in range(1, 9):
+            assert lib.hyd_mod(a, b) == O.lib.orc_mod(a, b) == a % b
+            assert lib.hyd_shift(a % b, (a * 7) % b, b) == O.lib.orc_shift(a % b, (a * 7) % b, b)
+
+
+@pytest.mark.parametrize("r,c", [(1, 1), (2, 2), (2, 4), (4, 2), (3, 2)])
+def test_local_shapes_match_oracle(r, c):
+    og = O.Grid(r, c, 1)
+    rng = np.random.default_rng(r + 10 * c)
+    for (cd, rd) in O.PAIRS:
+        for (m, n) in [(0, 0), (1, 1), (37, 23), (129, 131)]:
+            ca = int(rng.integers(0, O.lib.orc_dist_stride(og, cd)))
+            ra = int(rng.integers(0, O.lib.orc_dist_stride(og, rd)))
+            A = O.DM(og, m, n, cd, rd, ca, ra)
+            d = hyd_dm(None, 1, m, n, cd, rd, ca, ra, 0, 0)
+            for p in range(r * c):
+                cs, rs, lh, lw = (C.c_int64() for _ in range(4))
+                assert lib.hyd_local_shape_of(r, c, 1, p, C.byref(d), C.byref(cs), C.byref(rs), C.byref(lh), C.byref(lw)) == 0
+                assert (lh.value, lw.value) == (A.lh(p), A.lw(p))
+
+
+def test_errors_are_reported_not_thrown():
+    d = hyd_dm(None, 1, 4, 4, O.MC, O.MC, 0, 0, 0, 0)  # [MC,MC] is not a legal pair
+    x = C.c_int64()
+    assert lib.hyd_local_shape_of(2, 2, 1, 0, C.byref(d), C.byref(x), C.byref(x), C.byref(x), C.byref(x)) != 0
+    assert b"unsupported distribution" in lib.hyd_last_error()
+    d = hyd_dm(None, 1, 4, 4, O.MC, O.MR, 5, 0, 0, 0)
+    assert lib.hyd_local_shape_of(2, 2, 1, 0, C.byref(d), C.byref(x), C.byref(x), C.byref(x), C.byref(x)) != 0
+    assert b"alignment" in lib.hyd_last_error()
+
+
+@pytest.mark.parametrize("r,c", [(1, 2), (2, 2), (2, 4), (3, 2)])
+def test_redist_plan_is_a_consistent_permutation(r, c):
+    """Planner invariants for every pair: what p sends to q is what q receives from p, and every rank receives
+    exactly its local block (bit-exact redistribution is a permutation of elements)."""
+    P = r * c
+    og = O.Grid(r, c, 1)
+    rng = np.random.default_rng(3)
+    for tr in (0, 1):
+        for (scd, srd), (dcd, drd) in itertools.product(O.PAIRS, O.PAIRS):
+            m, n = 61, 47
+            sa = [int(rng.integers(0, O.lib.orc_dist_stride(og, x))) for x in (scd, srd, dcd, drd)]
+            s = hyd_dm(None, 1, m, n, scd, srd, sa[0], sa[1], 0, 0)
+            dm, dn = (n, m) if tr else (m, n)
+            d = hyd_dm(None, 1, dm, dn, dcd, drd, sa[2], sa[3], 0, 0)
+            send = np.zeros((P, P), dtype=np.int64)
+            recv = np.zeros((P, P), dtype=np.int64)
+            for p in range(P):
+                assert lib.hyd_redist_plan(r, c, 1, p, C.byref(s), C.byref(d), tr, 8, send[p].ctypes.data_as(C.POINTER(C.c_int64)),
+                                           recv[p].ctypes.data_as(C.POINTER(C.c_int64))) == 0
+            assert np.array_equal(send, recv.T)
+            D = O.DM(og, dm, dn, dcd, drd, sa[2], sa[3])
+            for p in range(P):
+                assert recv[p].sum() == D.lh(p) * D.lw(p) * 8

@@ -1,0 +1,71 @@
+"""CPU-only, world_size-2 gloo: the host-side logic of the N>1 path -- NCCL-id bootstrap over torch.distributed,
+per-rank local shapes tiling the global matrix, and the redistribution planner's send/recv symmetry ACROSS
+processes (each rank plans only for itself; the counts are exchanged with all_gather)."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, size, port, ret):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import ctypes as C
+    from elemental_b200 import lib, hyd_dm
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=size)
+    try:
+        # 1. bootstrap payload: rank 0's 128-byte id reaches every rank unchanged
+        obj = [bytes(range(128)) if rank == 0 else None]
+        dist.broadcast_object_list(obj, src=0)
+        assert obj[0] == bytes(range(128))
+        # 2. local shapes of a [MC,MR] and a [STAR,VR] matrix tile the global matrix
+        r, c = 1, size
+        for (cd, rd) in ((0, 2), (5, 4)):
+            d = hyd_dm(None, 1, 101, 67, cd, rd, 0, 1 % max(1, size), 0, 0)
+            cs, rs, lh, lw = (C.c_int64() for _ in range(4))
+            assert lib.hyd_local_shape_of(r, c, 1, rank, C.byref(d), C.byref(cs), C.byref(rs), C.byref(lh), C.byref(lw)) == 0
+            t = torch.tensor([lh.value * lw.value])
+            dist.all_reduce(t)
+            assert int(t.item()) == 101 * 67
+        # 3. planner symmetry across processes
+        s = hyd_dm(None, 1, 101, 67, 0, 2, 0, 1, 0, 0)        # [MC,MR]
+        d = hyd_dm(None, 1, 67, 101, 2, 5, 1, 0, 0, 0)        # ^T -> [MR,*]
+        send = np.zeros(size, dtype=np.int64)
+        recv = np.zeros(size, dtype=np.int64)
+        assert lib.hyd_redist_plan(r, c, 1, rank, C.byref(s), C.byref(d), 1, 8, send.ctypes.data_as(C.POINTER(C.c_int64)),
+                                   recv.ctypes.data_as(C.POINTER(C.c_int64))) == 0
+        allsend = [torch.zeros(size, dtype=torch.int64) for _ in range(size)]
+        dist.all_gather(allsend, torch.from_numpy(send))
+        for p in range(size):
+            assert int(allsend[p][rank]) == int(recv[p]), (p, rank)
+        # 4. max-over-ranks reduction used by bench.py
+        t = torch.tensor([float(rank + 1)], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        assert t.item() == float(size)
+        ret[rank] = 1
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_host_logic_gloo():
+    size = 2
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_worker, args=(size, _free_port(), ret), nprocs=size, join=True)
+    assert dict(ret) == {0: 1, 1: 1}
