@@ -1,6 +1,7 @@
 // NCCL and in-process communication backends (see comm.h).
 #include "comm.h"
 #include "hyd_internal.h"
+#include "push.h"
 #include <nccl.h>
 #include <dlfcn.h>
 #include <pthread.h>
@@ -48,8 +49,115 @@ static int check_nccl(ncclResult_t r, const char* what) {
 
 struct NcclWorld : World {
     ncclComm_t comm = nullptr;
-    ~NcclWorld() override { if (comm) nccl::ncclCommDestroy(comm); }
-    const char* kind() const override { return "nccl"; }
+    // push transport over CUDA-IPC peer mappings (NVLink): bootstrapped through this NCCL communicator
+    PushCore pc;
+    bool push_ok = false;
+    char* hs_dev = nullptr;  // device scratch for the handle all-gather
+    ~NcclWorld() override {
+        cudaDeviceSynchronize();
+        for (int sl = 0; sl < kPushSlots; ++sl) release_region(sl);
+        for (int p = 0; p < size; ++p)
+            if (p != rank && pc.ctrl_peer[p]) cudaIpcCloseMemHandle(pc.ctrl_peer[p]);
+        if (pc.ctrl_local) cudaFree(pc.ctrl_local);
+        if (hs_dev) cudaFree(hs_dev);
+        if (comm) nccl::ncclCommDestroy(comm);
+    }
+    const char* kind() const override { return push_ok ? "nvlink-push(ipc)+nccl" : "nccl"; }
+    bool can_push() const override { return push_ok; }
+    char* shared_local(int slot) override { return pc.region_local[slot]; }
+    char* shared_peer(int slot, int p) override { return pc.region_peer[slot][p]; }
+    int push_open(int slot, const unsigned char* to, cudaStream_t s) override { return pc.open(slot, to, s); }
+    int push_post(int slot, const unsigned char* to, cudaStream_t s) override { return pc.post(slot, to, s); }
+    int push_wait(int slot, const unsigned char* from, cudaStream_t s) override { return pc.wait(slot, from, s); }
+    int push_close(int slot, cudaStream_t s) override { return pc.close(slot, s); }
+
+    struct HandleMsg { cudaIpcMemHandle_t h; int ok; int pad[15]; };  // 128 bytes
+    // all-gather one handle (+ ok flag) per rank through NCCL; returns 1 on a local failure
+    int gather_handles(const HandleMsg& mine, std::vector<HandleMsg>& all) {
+        static_assert(sizeof(HandleMsg) == 128, "HandleMsg is 128 bytes");
+        if (!hs_dev && check_cuda(cudaMalloc(&hs_dev, sizeof(HandleMsg) * (size + 1)), "ipc scratch")) return 1;
+        all.resize(size);
+        if (check_cuda(cudaMemcpy(hs_dev, &mine, sizeof(HandleMsg), cudaMemcpyHostToDevice), "ipc h2d")) return 1;
+        if (check_nccl(nccl::ncclAllGather(hs_dev, hs_dev + sizeof(HandleMsg), sizeof(HandleMsg), ncclChar, comm, 0), "ncclAllGather(handles)")) return 1;
+        if (check_cuda(cudaStreamSynchronize(0), "ipc sync")) return 1;
+        return check_cuda(cudaMemcpy(all.data(), hs_dev + sizeof(HandleMsg), sizeof(HandleMsg) * size, cudaMemcpyDeviceToHost), "ipc d2h");
+    }
+    void release_region(int sl) {
+        for (int p = 0; p < size; ++p)
+            if (p != rank && pc.region_peer[sl][p]) { cudaIpcCloseMemHandle(pc.region_peer[sl][p]); pc.region_peer[sl][p] = nullptr; }
+        if (pc.region_local[sl]) cudaFree(pc.region_local[sl]);
+        pc.region_local[sl] = nullptr;
+        pc.region_cap[sl] = 0;
+    }
+    // allocate `bytes`, exchange IPC handles, map every peer's allocation; collective
+    int map_all(size_t bytes, char** local, char** peers /*[size]*/) {
+        HandleMsg mine;
+        memset(&mine, 0, sizeof(mine));
+        void* p = nullptr;
+        mine.ok = (cudaMalloc(&p, bytes) == cudaSuccess) && (cudaMemset(p, 0, bytes) == cudaSuccess) &&
+                  (cudaIpcGetMemHandle(&mine.h, p) == cudaSuccess) && (cudaDeviceSynchronize() == cudaSuccess);
+        std::vector<HandleMsg> all;
+        if (gather_handles(mine, all)) return 1;
+        bool ok = true;
+        for (int q = 0; q < size; ++q) ok = ok && all[q].ok;
+        if (ok) {
+            for (int q = 0; q < size && ok; ++q) {
+                if (q == rank) { peers[q] = (char*)p; continue; }
+                void* m = nullptr;
+                if (cudaIpcOpenMemHandle(&m, all[q].h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { ok = false; break; }
+                peers[q] = (char*)m;
+            }
+        }
+        // agree on the outcome (a rank that failed to map must not leave the others pushing)
+        HandleMsg st;
+        memset(&st, 0, sizeof(st));
+        st.ok = ok ? 1 : 0;
+        if (gather_handles(st, all)) return 1;
+        bool all_ok = true;
+        for (int q = 0; q < size; ++q) all_ok = all_ok && all[q].ok;
+        if (!all_ok) {
+            cudaGetLastError();
+            for (int q = 0; q < size; ++q) {
+                if (q != rank && peers[q]) cudaIpcCloseMemHandle(peers[q]);
+                peers[q] = nullptr;
+            }
+            if (p) cudaFree(p);
+            *local = nullptr;
+            return set_error("CUDA IPC peer mapping failed on at least one rank");
+        }
+        *local = (char*)p;
+        return 0;
+    }
+    int init_push() {
+        const char* e = getenv("HYD_TRANSPORT");
+        if (e && strcmp(e, "nccl") == 0) return 0;
+        if (size < 2 || size > kPushMaxRanks) return 0;
+        pc.rank = rank;
+        pc.size = size;
+        char* local = nullptr;
+        char* peers[kPushMaxRanks] = {};
+        if (map_all(PushCore::ctrl_bytes(), &local, peers)) return 0;  // fall back to staged NCCL send/recv
+        pc.ctrl_local = (uint32_t*)local;
+        for (int p = 0; p < size; ++p) pc.ctrl_peer[p] = (uint32_t*)peers[p];
+        push_ok = true;
+        return 0;
+    }
+    int shared_reserve(int slot, size_t bytes) override {
+        if (bytes <= pc.region_cap[slot]) return 0;
+        // every rank takes this branch together (same `bytes`, same history): drain all work that may still
+        // touch the old mappings, everywhere, before they go away
+        if (check_cuda(cudaDeviceSynchronize(), "shared_reserve sync")) return 1;
+        if (barrier()) return 1;
+        release_region(slot);
+        const size_t cap = push_grow(bytes);
+        char* local = nullptr;
+        char* peers[kPushMaxRanks] = {};
+        if (map_all(cap, &local, peers)) return 1;
+        pc.region_local[slot] = local;
+        pc.region_cap[slot] = cap;
+        for (int p = 0; p < size; ++p) pc.region_peer[slot][p] = peers[p];
+        return barrier();
+    }
     int exchange(const void* send, const i64* scount, const i64* soff, void* recv, const i64* rcount,
                  const i64* roff, cudaStream_t s) override {
         bool any = false;
@@ -106,6 +214,7 @@ World* make_nccl_world(const void* uid, int rank, int size) {
         delete w;
         return nullptr;
     }
+    w->init_push();
     return w;
 }
 
@@ -122,6 +231,9 @@ struct LocalShared {
     pthread_barrier_t bar;
     std::vector<LocalSlot> slots;
     int error = 0;
+    // push transport: every rank-thread's control block and receive regions (plain device pointers: one process)
+    std::vector<uint32_t*> ctrl;
+    std::vector<char*> region[kPushSlots];
 };
 
 LocalShared* local_shared_create(int size) {
@@ -129,6 +241,8 @@ LocalShared* local_shared_create(int size) {
     sh->size = size;
     pthread_barrier_init(&sh->bar, nullptr, size);
     sh->slots.resize(size);
+    sh->ctrl.assign(size, nullptr);
+    for (auto& r : sh->region) r.assign(size, nullptr);
     for (auto& s : sh->slots) {
         s.scount.assign(size, 0);
         s.soff.assign(size, 0);
@@ -147,8 +261,62 @@ void local_shared_destroy(LocalShared* sh) {
 
 struct LocalWorld : World {
     LocalShared* sh = nullptr;
-    const char* kind() const override { return "local"; }
+    PushCore pc;
+    bool push_ok = false, ctrl_linked = false;
+    ~LocalWorld() override {
+        cudaDeviceSynchronize();
+        for (int sl = 0; sl < kPushSlots; ++sl) if (pc.region_local[sl]) cudaFree(pc.region_local[sl]);
+        if (pc.ctrl_local) cudaFree(pc.ctrl_local);
+    }
+    const char* kind() const override { return push_ok ? "local-push" : "local"; }
     int barrier() override { pthread_barrier_wait(&sh->bar); return 0; }
+    bool can_push() const override { return push_ok; }
+    char* shared_local(int slot) override { return pc.region_local[slot]; }
+    char* shared_peer(int slot, int p) override { return pc.region_peer[slot][p]; }
+    int push_open(int slot, const unsigned char* to, cudaStream_t s) override { return pc.open(slot, to, s); }
+    int push_post(int slot, const unsigned char* to, cudaStream_t s) override { return pc.post(slot, to, s); }
+    int push_wait(int slot, const unsigned char* from, cudaStream_t s) override { return pc.wait(slot, from, s); }
+    int push_close(int slot, cudaStream_t s) override { return pc.close(slot, s); }
+    int init_push() {
+        const char* e = getenv("HYD_TRANSPORT");
+        // opt-in (HYD_TRANSPORT=push): rank-threads of one process share the GPU's few hardware queues, and a stream blocked in a
+        // flag wait can hold up another rank's stream aliased onto the same queue; one process per GPU has no such coupling
+        if (!(e && strcmp(e, "push") == 0) || size < 2 || size > 4) return 0;
+        pc.rank = rank;
+        pc.size = size;
+        void* p = nullptr;
+        if (check_cuda(cudaMalloc(&p, PushCore::ctrl_bytes()), "push ctrl")) return 1;
+        cudaMemset(p, 0, PushCore::ctrl_bytes());
+        cudaDeviceSynchronize();
+        pc.ctrl_local = (uint32_t*)p;
+        sh->ctrl[rank] = pc.ctrl_local;
+        push_ok = true;
+        return 0;
+    }
+    int shared_reserve(int slot, size_t bytes) override {
+        if (ctrl_linked && bytes <= pc.region_cap[slot]) return 0;
+        // same decision on every rank-thread (same `bytes`, same history)
+        cudaDeviceSynchronize();
+        pthread_barrier_wait(&sh->bar);
+        int rc = 0;
+        if (bytes > pc.region_cap[slot]) {
+            if (pc.region_local[slot]) cudaFree(pc.region_local[slot]);
+            const size_t cap = push_grow(bytes);
+            void* p = nullptr;
+            rc = check_cuda(cudaMalloc(&p, cap), "push region");
+            pc.region_local[slot] = (char*)p;
+            pc.region_cap[slot] = rc ? 0 : cap;
+            sh->region[slot][rank] = (char*)p;
+        }
+        pthread_barrier_wait(&sh->bar);
+        for (int q = 0; q < size; ++q) {
+            pc.region_peer[slot][q] = sh->region[slot][q];
+            pc.ctrl_peer[q] = sh->ctrl[q];
+        }
+        ctrl_linked = true;
+        pthread_barrier_wait(&sh->bar);
+        return rc;
+    }
     int exchange(const void* send, const i64* scount, const i64* soff, void* recv, const i64* rcount,
                  const i64* roff, cudaStream_t s) override {
         LocalSlot& me = sh->slots[rank];
@@ -190,6 +358,7 @@ World* make_local_world(LocalShared* sh, int rank) {
     w->sh = sh;
     w->rank = rank;
     w->size = sh->size;
+    w->init_push();
     return w;
 }
 

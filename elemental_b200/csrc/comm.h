@@ -29,7 +29,27 @@ struct World {
                          const i64* rcount, const i64* roff, cudaStream_t s) = 0;
     virtual int barrier() = 0;  // host-side
     virtual const char* kind() const = 0;
+
+    // ---- push transport over peer-mapped memory (NVLink P2P stores; see push.cu) -------------------
+    // When can_push() is true the redistribution engine does not stage-and-send: the pack kernel of rank q
+    // stores each message straight into rank p's receive region through a peer-mapped pointer (pack + NVLink
+    // transfer fused in one kernel), and rounds are ordered by 32-bit flags in peer-mapped control blocks,
+    // waited on with stream memory operations (no kernel ever spins).  A "slot" is one receive region +
+    // flag set; all ranks use a slot in the same order (every exchange is collective over the world).
+    virtual bool can_push() const { return false; }
+    // collective: every rank's region `slot` holds >= bytes afterwards (same `bytes` on every rank)
+    virtual int shared_reserve(int /*slot*/, size_t /*bytes*/) { return 1; }
+    virtual char* shared_local(int /*slot*/) { return nullptr; }
+    virtual char* shared_peer(int /*slot*/, int /*p*/) { return nullptr; }
+    // to[p] != 0: I store into p's region this round; from[q] != 0: q stores into mine
+    virtual int push_open(int /*slot*/, const unsigned char* /*to*/, cudaStream_t) { return 1; }   // wait: receivers consumed previous round
+    virtual int push_post(int /*slot*/, const unsigned char* /*to*/, cudaStream_t) { return 1; }   // signal: my stores have landed
+    virtual int push_wait(int /*slot*/, const unsigned char* /*from*/, cudaStream_t) { return 1; } // wait for my senders
+    virtual int push_close(int /*slot*/, cudaStream_t) { return 1; }                                // broadcast: round consumed
 };
+
+constexpr int kPushSlots = 4;
+constexpr int kPushMaxRanks = 64;
 
 World* make_nccl_world(const void* unique_id_128B, int rank, int size);
 int nccl_unique_id(void* out_128B);

@@ -185,44 +185,82 @@ int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot
     if (check_pair(sh, src, dst, transpose, "hyd_redist")) return 1;
     if (src.height == 0 || src.width == 0) return 0;
     ProfScope prof(g, Grid::PROF_REDIST, s);
-    const int P = sh.size();
+    const int P = sh.size(), me = g.rank;
     bool mcFree, mrFree;
     free_coords(src.colDist, src.rowDist, mcFree, mrFree);
-    const LocalShape Ls_me = local_shape(sh, src, g.mc, g.mr), Ld_me = local_shape(sh, dst, g.mc, g.mr);
-    if (Ls_me.lh > 0 && Ls_me.lw > 0 && (!src.buf || src.ldim < Ls_me.lh))
+    std::vector<LocalShape> Ls(P), Ld(P);
+    std::vector<int> pmc(P), pmr(P);
+    for (int p = 0; p < P; ++p) {
+        sh.coords(p, pmc[p], pmr[p]);
+        Ls[p] = local_shape(sh, src, pmc[p], pmr[p]);
+        Ld[p] = local_shape(sh, dst, pmc[p], pmr[p]);
+    }
+    if (Ls[me].lh > 0 && Ls[me].lw > 0 && (!src.buf || src.ldim < Ls[me].lh))
         return set_error("hyd_redist: bad source buffer / ldim");
-    if (Ld_me.lh > 0 && Ld_me.lw > 0 && (!dst.buf || dst.ldim < Ld_me.lh))
+    if (Ld[me].lh > 0 && Ld[me].lw > 0 && (!dst.buf || dst.ldim < Ld[me].lh))
         return set_error("hyd_redist: bad destination buffer / ldim");
+    // data moves only between ranks that agree on the coordinates along which the source is replicated
+    auto talks = [&](int q, int p) { return (!mcFree || pmc[q] == pmc[p]) && (!mrFree || pmr[q] == pmr[p]); };
 
     std::vector<Msg> sends, recvs;
     Msg self_msg;
     bool has_self = false;
     i64 send_bytes = 0, recv_bytes = 0;
     for (int p = 0; p < P; ++p) {
-        int pmc, pmr;
-        sh.coords(p, pmc, pmr);
-        const bool same_free = (!mcFree || pmc == g.mc) && (!mrFree || pmr == g.mr);
-        if (!same_free) continue;
+        if (!talks(me, p)) continue;
         Msg m;
         m.peer = p;
-        if (p == g.rank) {
-            progs(src, transpose, Ls_me, Ld_me, m.pa, m.pb);
+        if (p == me) {
+            progs(src, transpose, Ls[me], Ld[me], m.pa, m.pb);
             if (m.count() > 0) { self_msg = m; has_self = true; }
             continue;
         }
-        progs(src, transpose, Ls_me, local_shape(sh, dst, pmc, pmr), m.pa, m.pb);
+        progs(src, transpose, Ls[me], Ld[p], m.pa, m.pb);
         if (m.count() > 0) { m.off = send_bytes; send_bytes = align16(send_bytes + m.count() * (i64)sizeof(T)); sends.push_back(m); }
-        progs(src, transpose, local_shape(sh, src, pmc, pmr), Ld_me, m.pa, m.pb);
+        progs(src, transpose, Ls[p], Ld[me], m.pa, m.pb);
         if (m.count() > 0) { m.off = recv_bytes; recv_bytes = align16(recv_bytes + m.count() * (i64)sizeof(T)); recvs.push_back(m); }
     }
-    Workspace& w = g.ws[slot];
-    if (send_bytes + recv_bytes > 0 && ws_reserve(w, (size_t)(send_bytes + recv_bytes))) return 1;
-    char* send_base = w.buf;
-    char* recv_base = w.buf + send_bytes;
 
-    // pack (+ the local part straight from source lattice to destination lattice)
+    const bool push = P > 1 && g.world->can_push();
+    char* send_base = nullptr;   // staged path only
+    char* recv_base = nullptr;
+    std::vector<unsigned char> to(P, 0), from(P, 0);
+    i64 need = 0;
+    if (push) {
+        // Receive-region layout at EVERY rank (senders in ascending rank order), computed identically everywhere,
+        // so that each sender knows where its message lands and all ranks agree on the region size.
+        std::vector<i64> my_send_off(P, 0);
+        for (int p = 0; p < P; ++p) {
+            i64 run = 0;
+            for (int q = 0; q < P; ++q) {
+                if (q == p || !talks(q, p)) continue;
+                Prog pa, pb;
+                progs(src, transpose, Ls[q], Ld[p], pa, pb);
+                const i64 bytes = pa.count * pb.count * (i64)sizeof(T);
+                if (bytes == 0) continue;
+                if (q == me) my_send_off[p] = run;
+                if (p == me) for (Msg& m : recvs) if (m.peer == q) m.off = run;
+                run = align16(run + bytes);
+            }
+            need = std::max(need, run);
+        }
+        for (Msg& m : sends) { m.off = my_send_off[m.peer]; to[m.peer] = 1; }
+        for (const Msg& m : recvs) from[m.peer] = 1;
+        if (need > 0 && g.world->shared_reserve(slot, (size_t)need)) return 1;
+        recv_base = g.world->shared_local(slot);
+    } else {
+        Workspace& w = g.ws[slot];
+        if (send_bytes + recv_bytes > 0 && ws_reserve(w, (size_t)(send_bytes + recv_bytes))) return 1;
+        send_base = w.buf;
+        recv_base = w.buf + send_bytes;
+    }
+
+    // pack (+ the local part straight from source lattice to destination lattice).  On the push path the pack
+    // kernel's destinations are the peers' receive regions: packing and the NVLink transfer are one kernel.
     std::vector<CopyDesc> descs;
-    for (const Msg& m : sends) descs.push_back(pack_desc<T>(src, transpose, m, send_base + m.off));
+    if (push && need > 0 && g.world->push_open(slot, to.data(), s)) return 1;
+    for (const Msg& m : sends)
+        descs.push_back(pack_desc<T>(src, transpose, m, push ? g.world->shared_peer(slot, m.peer) + m.off : send_base + m.off));
     if (has_self) {
         CopyDesc d = pack_desc<T>(src, transpose, self_msg, nullptr);
         dst_lattice<T>(dst, self_msg, d.dst, d.d_rs, d.d_cs);
@@ -230,7 +268,9 @@ int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot
     }
     if (launch_copies<T>(descs, s)) return 1;
 
-    if (!sends.empty() || !recvs.empty() || P > 1) {
+    if (push) {
+        if (need > 0 && (g.world->push_post(slot, to.data(), s) || g.world->push_wait(slot, from.data(), s))) return 1;
+    } else if (!sends.empty() || !recvs.empty() || P > 1) {
         std::vector<i64> sc(P, 0), so(P, 0), rc(P, 0), ro(P, 0);
         for (const Msg& m : sends) { sc[m.peer] = m.count() * (i64)sizeof(T); so[m.peer] = m.off; }
         for (const Msg& m : recvs) { rc[m.peer] = m.count() * (i64)sizeof(T); ro[m.peer] = m.off; }
@@ -247,7 +287,9 @@ int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot
         d.nc = m.pb.count;
         descs.push_back(d);
     }
-    return launch_copies<T>(descs, s);
+    if (launch_copies<T>(descs, s)) return 1;
+    if (push && need > 0) return g.world->push_close(slot, s);
+    return 0;
 }
 
 template <typename T>
@@ -298,17 +340,53 @@ int reduce_into(Grid& g, T alpha, const DM& src, const DM& dst, bool transpose, 
         if (!grp) { groups.push_back(Group{kmc, kmr, m, {}}); grp = &groups.back(); }
         grp->member_off.push_back(m.off);
     }
-    Workspace& w = g.ws[slot];
-    if (send_bytes + recv_bytes > 0 && ws_reserve(w, (size_t)(send_bytes + recv_bytes))) return 1;
-    char* send_base = w.buf;
-    char* recv_base = w.buf + send_bytes;
+    const bool push = P > 1 && g.world->can_push();
+    char* send_base = nullptr;
+    char* recv_base = nullptr;
+    std::vector<unsigned char> to(P, 0), from(P, 0);
+    i64 need = 0;
+    if (push) {
+        // receive-region layout at every rank: members in ascending VC rank (the summation order), self included --
+        // exactly the order the recvs / member offsets above were built in, so only the senders' view is new here
+        std::vector<i64> my_send_off(P, 0);
+        for (int p = 0; p < P; ++p) {
+            int dmc, dmr;
+            sh.coords(p, dmc, dmr);
+            const LocalShape Ldp = local_shape(sh, dst, dmc, dmr);
+            i64 run = 0;
+            for (int v = 0; v < P; ++v) {
+                const int qmc = v % sh.r, qmr = v / sh.r;
+                const int q = sh.rank_of(qmc, qmr);
+                Prog pa, pb;
+                progs(src, transpose, local_shape(sh, src, qmc, qmr), Ldp, pa, pb);
+                const i64 bytes = pa.count * pb.count * (i64)sizeof(T);
+                if (bytes == 0) continue;
+                if (q == g.rank) my_send_off[p] = run;
+                run = align16(run + bytes);
+            }
+            need = std::max(need, run);
+        }
+        for (Msg& m : sends) { m.off = my_send_off[m.peer]; to[m.peer] = 1; }
+        for (const Msg& m : recvs) if (m.peer != g.rank) from[m.peer] = 1;
+        if (need > 0 && g.world->shared_reserve(slot, (size_t)need)) return 1;
+        recv_base = g.world->shared_local(slot);
+    } else {
+        Workspace& w = g.ws[slot];
+        if (send_bytes + recv_bytes > 0 && ws_reserve(w, (size_t)(send_bytes + recv_bytes))) return 1;
+        send_base = w.buf;
+        recv_base = w.buf + send_bytes;
+    }
 
     std::vector<CopyDesc> descs;
-    for (const Msg& m : sends) descs.push_back(pack_desc<T>(src, transpose, m, send_base + m.off));
+    if (push && need > 0 && g.world->push_open(slot, to.data(), s)) return 1;
+    for (const Msg& m : sends)
+        descs.push_back(pack_desc<T>(src, transpose, m, push ? g.world->shared_peer(slot, m.peer) + m.off : send_base + m.off));
     if (self_off >= 0) descs.push_back(pack_desc<T>(src, transpose, self_msg, recv_base + self_off));
     if (launch_copies<T>(descs, s)) return 1;
 
-    if (P > 1) {
+    if (push) {
+        if (need > 0 && (g.world->push_post(slot, to.data(), s) || g.world->push_wait(slot, from.data(), s))) return 1;
+    } else if (P > 1) {
         std::vector<i64> sc(P, 0), so(P, 0), rc(P, 0), ro(P, 0);
         for (const Msg& m : sends) { sc[m.peer] = m.count() * (i64)sizeof(T); so[m.peer] = m.off; }
         for (const Msg& m : recvs) if (m.peer != g.rank) { rc[m.peer] = m.count() * (i64)sizeof(T); ro[m.peer] = m.off; }
@@ -333,11 +411,15 @@ int reduce_into(Grid& g, T alpha, const DM& src, const DM& dst, bool transpose, 
     // groups touch disjoint destination lattices, but chunks of one group do not: launch chunk by chunk
     bool chunked = false;
     for (const Group& q : groups) if (q.member_off.size() > (size_t)kMaxMembers) chunked = true;
-    if (!chunked) return launch_reduces<T>(rdescs, alpha, s);
-    for (const ReduceDesc& d : rdescs) {
-        std::vector<ReduceDesc> one(1, d);
-        if (launch_reduces<T>(one, alpha, s)) return 1;
+    if (!chunked) {
+        if (launch_reduces<T>(rdescs, alpha, s)) return 1;
+    } else {
+        for (const ReduceDesc& d : rdescs) {
+            std::vector<ReduceDesc> one(1, d);
+            if (launch_reduces<T>(one, alpha, s)) return 1;
+        }
     }
+    if (push && need > 0) return g.world->push_close(slot, s);
     return 0;
 }
 

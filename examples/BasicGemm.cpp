@@ -30,7 +30,12 @@ static int run(int P, int height, El::Int n, El::Int nb, double tol, const char*
             {
                 El::Grid grid(comm, height);
                 El::SetBlocksize(nb);
+                // rank-threads that share one GPU must work on distinct non-blocking streams (the legacy null stream
+                // would serialise one rank's flag wait against another rank's signal); one process per GPU may use any
+                cudaStream_t st;
+                cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
                 El::DistMatrix<T, El::MC, El::MR> A(n, n, grid), B(n, n, grid), C(n, n, grid);
+                A.SetStream(st); B.SetStream(st); C.SetStream(st);
                 auto fill = [&](El::AbstractDistMatrix<T>& X, unsigned long long seed) {
                     std::vector<T> h((size_t)X.LocalHeight() * X.LocalWidth());
                     for (El::Int j = 0; j < X.LocalWidth(); ++j)
@@ -52,13 +57,16 @@ static int run(int P, int height, El::Int n, El::Int nb, double tol, const char*
                     }
                 // a redistribution through operator=, checked bit-exactly against the ownership formula
                 El::DistMatrix<T, El::STAR, El::VR> S(grid);
+                S.SetStream(st);
                 S = A;
                 std::vector<T> sh((size_t)S.LocalHeight() * S.LocalWidth());
                 S.GetLocalToHost(sh.data(), S.LocalHeight());
                 for (El::Int j = 0; j < S.LocalWidth(); ++j)
                     for (El::Int i = 0; i < S.LocalHeight(); ++i)
                         if (sh[i + j * S.LocalHeight()] != uni<T>(1, S.GlobalRow(i) + S.GlobalCol(j) * n)) failed[rank] = 1;
+                cudaStreamSynchronize(st);
                 comm.Barrier();
+                cudaStreamDestroy(st);
             }
             comm.Free();
         } catch (const std::exception& e) {
