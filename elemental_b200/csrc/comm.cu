@@ -234,6 +234,8 @@ struct LocalShared {
     // push transport: every rank-thread's control block and receive regions (plain device pointers: one process)
     std::vector<uint32_t*> ctrl;
     std::vector<char*> region[kPushSlots];
+    // in-process rounds are ordered with CUDA events + host barriers instead of flag waits (see LocalWorld)
+    std::vector<cudaEvent_t> posted[kPushSlots], consumed[kPushSlots];
 };
 
 LocalShared* local_shared_create(int size) {
@@ -243,6 +245,7 @@ LocalShared* local_shared_create(int size) {
     sh->slots.resize(size);
     sh->ctrl.assign(size, nullptr);
     for (auto& r : sh->region) r.assign(size, nullptr);
+    for (int sl = 0; sl < kPushSlots; ++sl) { sh->posted[sl].assign(size, nullptr); sh->consumed[sl].assign(size, nullptr); }
     for (auto& s : sh->slots) {
         s.scount.assign(size, 0);
         s.soff.assign(size, 0);
@@ -254,6 +257,10 @@ void local_shared_destroy(LocalShared* sh) {
     for (auto& s : sh->slots) {
         if (s.ready) cudaEventDestroy(s.ready);
         if (s.done) cudaEventDestroy(s.done);
+    }
+    for (int sl = 0; sl < kPushSlots; ++sl) {
+        for (cudaEvent_t e : sh->posted[sl]) if (e) cudaEventDestroy(e);
+        for (cudaEvent_t e : sh->consumed[sl]) if (e) cudaEventDestroy(e);
     }
     pthread_barrier_destroy(&sh->bar);
     delete sh;
@@ -273,23 +280,38 @@ struct LocalWorld : World {
     bool can_push() const override { return push_ok; }
     char* shared_local(int slot) override { return pc.region_local[slot]; }
     char* shared_peer(int slot, int p) override { return pc.region_peer[slot][p]; }
-    int push_open(int slot, const unsigned char* to, cudaStream_t s) override { return pc.open(slot, to, s); }
-    int push_post(int slot, const unsigned char* to, cudaStream_t s) override { return pc.post(slot, to, s); }
-    int push_wait(int slot, const unsigned char* from, cudaStream_t s) override { return pc.wait(slot, from, s); }
-    int push_close(int slot, cudaStream_t s) override { return pc.close(slot, s); }
+    // Rank-threads of ONE process share the GPU's hardware queues: a stream parked in a flag wait could hold up another
+    // rank's stream aliased onto the same queue.  So in-process rounds use what one process can use instead -- CUDA
+    // events recorded/waited across the ranks' streams, with a host barrier making sure the record was issued before
+    // the wait.  Same peer stores, same region layout, same call sequence as the NVLink flag protocol (push.cu).
+    cudaEvent_t ev(std::vector<cudaEvent_t>& v, int r) {
+        if (!v[r]) cudaEventCreateWithFlags(&v[r], cudaEventDisableTiming);
+        return v[r];
+    }
+    int push_open(int slot, const unsigned char* to, cudaStream_t s) override {
+        pthread_barrier_wait(&sh->bar);  // every rank has issued the previous round's close
+        for (int p = 0; p < size; ++p)
+            if (p != rank && to[p] && sh->consumed[slot][p] &&
+                check_cuda(cudaStreamWaitEvent(s, sh->consumed[slot][p], 0), "push_open(local)")) return 1;
+        return 0;
+    }
+    int push_post(int slot, const unsigned char*, cudaStream_t s) override {
+        return check_cuda(cudaEventRecord(ev(sh->posted[slot], rank), s), "push_post(local)");
+    }
+    int push_wait(int slot, const unsigned char* from, cudaStream_t s) override {
+        pthread_barrier_wait(&sh->bar);  // every rank has issued its post
+        for (int q = 0; q < size; ++q)
+            if (q != rank && from[q] && check_cuda(cudaStreamWaitEvent(s, sh->posted[slot][q], 0), "push_wait(local)")) return 1;
+        return 0;
+    }
+    int push_close(int slot, cudaStream_t s) override {
+        return check_cuda(cudaEventRecord(ev(sh->consumed[slot], rank), s), "push_close(local)");
+    }
     int init_push() {
         const char* e = getenv("HYD_TRANSPORT");
-        // opt-in (HYD_TRANSPORT=push): rank-threads of one process share the GPU's few hardware queues, and a stream blocked in a
-        // flag wait can hold up another rank's stream aliased onto the same queue; one process per GPU has no such coupling
-        if (!(e && strcmp(e, "push") == 0) || size < 2 || size > 4) return 0;
+        if ((e && strcmp(e, "staged") == 0) || size < 2 || size > kPushMaxRanks) return 0;
         pc.rank = rank;
         pc.size = size;
-        void* p = nullptr;
-        if (check_cuda(cudaMalloc(&p, PushCore::ctrl_bytes()), "push ctrl")) return 1;
-        cudaMemset(p, 0, PushCore::ctrl_bytes());
-        cudaDeviceSynchronize();
-        pc.ctrl_local = (uint32_t*)p;
-        sh->ctrl[rank] = pc.ctrl_local;
         push_ok = true;
         return 0;
     }

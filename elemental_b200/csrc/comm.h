@@ -48,7 +48,7 @@ struct World {
     virtual int push_close(int /*slot*/, cudaStream_t) { return 1; }                                // broadcast: round consumed
 };
 
-constexpr int kPushSlots = 4;
+constexpr int kPushSlots = 8;   // 0-3: exchange workspaces, 4-7: SUMMA panels (A/B x double buffer)
 constexpr int kPushMaxRanks = 64;
 
 World* make_nccl_world(const void* unique_id_128B, int rank, int size);

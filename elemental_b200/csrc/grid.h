@@ -64,6 +64,12 @@ void grid_destroy(Grid* g);
 // dst := src (or src^T), any pair of supported element distributions / alignments.
 template <typename T>
 int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot, cudaStream_t s);
+// Direct form for library-owned destinations (SUMMA panels): dst lives at the base of push region `slot` on every rank
+// (ldim = 16-byte-padded local height, room for alloc_width columns).  Every sender stores its part straight into the
+// final positions of every receiver's panel through the peer mapping -- one kernel, no staging, no unpack.  Leaves the
+// round open: the consumer calls world->push_close(slot, stream) once it has read the panel.  Fills dst.buf / dst.ldim.
+template <typename T>
+int redistribute_direct(Grid& g, const DM& src, DM& dst, bool transpose, int slot, i64 alloc_width, cudaStream_t s);
 // dst += alpha * (sum over the ranks along which src is a partial sum)  (optionally of src^T)
 template <typename T>
 int reduce_into(Grid& g, T alpha, const DM& src, const DM& dst, bool transpose, int slot, cudaStream_t s);

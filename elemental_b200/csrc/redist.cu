@@ -293,6 +293,59 @@ int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot
 }
 
 template <typename T>
+int redistribute_direct(Grid& g, const DM& src, DM& dst, bool transpose, int slot, i64 alloc_width, cudaStream_t s) {
+    const GridShape& sh = g.shape;
+    if (check_pair(sh, src, dst, transpose, "hyd_redist(direct)")) return 1;
+    ProfScope prof(g, Grid::PROF_REDIST, s);
+    const int P = sh.size(), me = g.rank;
+    bool mcFree, mrFree;
+    free_coords(src.colDist, src.rowDist, mcFree, mrFree);
+    std::vector<LocalShape> Ls(P), Ld(P);
+    std::vector<int> pmc(P), pmr(P);
+    std::vector<i64> ldp(P);
+    const i64 q16 = 16 / (i64)sizeof(T);
+    i64 need = 0;
+    for (int p = 0; p < P; ++p) {
+        sh.coords(p, pmc[p], pmr[p]);
+        Ls[p] = local_shape(sh, src, pmc[p], pmr[p]);
+        Ld[p] = local_shape(sh, dst, pmc[p], pmr[p]);
+        ldp[p] = std::max<i64>(q16, (Ld[p].lh + q16 - 1) / q16 * q16);
+        need = std::max(need, ldp[p] * std::max<i64>(alloc_width, 1) * (i64)sizeof(T));
+    }
+    if (g.world->shared_reserve(slot, (size_t)need)) return 1;
+    dst.buf = g.world->shared_local(slot);
+    dst.ldim = ldp[me];
+    if (Ls[me].lh > 0 && Ls[me].lw > 0 && (!src.buf || src.ldim < Ls[me].lh))
+        return set_error("hyd_redist(direct): bad source buffer / ldim");
+    auto talks = [&](int q, int p) { return (!mcFree || pmc[q] == pmc[p]) && (!mrFree || pmr[q] == pmr[p]); };
+    std::vector<unsigned char> to(P, 0), from(P, 0);
+    std::vector<CopyDesc> descs;
+    for (int p = 0; p < P; ++p) {
+        if (!talks(me, p)) continue;
+        Msg m;
+        m.peer = p;
+        progs(src, transpose, Ls[me], Ld[p], m.pa, m.pb);
+        if (m.count() > 0) {
+            CopyDesc d = pack_desc<T>(src, transpose, m, nullptr);
+            d.dst = reinterpret_cast<T*>(g.world->shared_peer(slot, p)) + m.pa.dst0 + m.pb.dst0 * ldp[p];
+            d.d_rs = m.pa.dstStep;
+            d.d_cs = m.pb.dstStep * ldp[p];
+            descs.push_back(d);
+            if (p != me) to[p] = 1;
+        }
+        if (p != me) {
+            Prog pa, pb;
+            progs(src, transpose, Ls[p], Ld[me], pa, pb);
+            if (pa.count * pb.count > 0) from[p] = 1;
+        }
+    }
+    if (g.world->push_open(slot, to.data(), s)) return 1;
+    if (launch_copies<T>(descs, s)) return 1;
+    if (g.world->push_post(slot, to.data(), s)) return 1;
+    return g.world->push_wait(slot, from.data(), s);
+}
+
+template <typename T>
 int reduce_into(Grid& g, T alpha, const DM& src, const DM& dst, bool transpose, int slot, cudaStream_t s) {
     const GridShape& sh = g.shape;
     if (check_pair(sh, src, dst, transpose, "hyd_axpy_contract")) return 1;
@@ -425,6 +478,8 @@ int reduce_into(Grid& g, T alpha, const DM& src, const DM& dst, bool transpose, 
 
 template int redistribute<double>(Grid&, const DM&, const DM&, bool, int, cudaStream_t);
 template int redistribute<float>(Grid&, const DM&, const DM&, bool, int, cudaStream_t);
+template int redistribute_direct<double>(Grid&, const DM&, DM&, bool, int, i64, cudaStream_t);
+template int redistribute_direct<float>(Grid&, const DM&, DM&, bool, int, i64, cudaStream_t);
 template int reduce_into<double>(Grid&, double, const DM&, const DM&, bool, int, cudaStream_t);
 template int reduce_into<float>(Grid&, float, const DM&, const DM&, bool, int, cudaStream_t);
 

@@ -152,6 +152,7 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
         return 0;
     }
     cudaStream_t cs = overlap ? g.comm_stream[0] : s;
+    const bool direct = g.world->can_push();
     if (overlap) {
         if (check_cuda(cudaEventRecord(g.ev_fork, s), "fork")) return 1;
         cudaStreamWaitEvent(cs, g.ev_fork, 0);
@@ -161,15 +162,23 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
         const int buf = (int)(step & 1);
         if (ho) cudaStreamWaitEvent(cs, g.upload_ev[step], 0);
         DM Ap, Bp;
-        if (make_tmp<T>(g, g.panel[buf], m, nb, MC, STAR, C.colAlign, 0, Ap)) return 1;
-        if (make_tmp<T>(g, g.panel[2 + buf], n, nb, MR, STAR, C.rowAlign, 0, Bp)) return 1;
-        Ap.width = kb;
-        Bp.width = kb;
-        if (overlap && step >= 2) cudaStreamWaitEvent(cs, g.ev_panel_free[buf], 0);
         const DM A1 = oA ? view(sh, A, g.mc, g.mr, k0, 0, kb, m, es) : view(sh, A, g.mc, g.mr, 0, k0, m, kb, es);
         const DM B1 = oB ? view(sh, B, g.mc, g.mr, 0, k0, n, kb, es) : view(sh, B, g.mc, g.mr, k0, 0, kb, n, es);
-        if (redistribute<T>(g, A1, Ap, oA != 0, 0, cs)) return 1;
-        if (redistribute<T>(g, B1, Bp, oB == 0, 1, cs)) return 1;
+        if (overlap && step >= 2) cudaStreamWaitEvent(cs, g.ev_panel_free[buf], 0);
+        if (direct) {
+            // panels live in peer-mapped regions: every owner stores its columns straight into every reader's panel
+            Ap.height = m; Ap.width = kb; Ap.colDist = MC; Ap.rowDist = STAR; Ap.colAlign = C.colAlign;
+            Bp.height = n; Bp.width = kb; Bp.colDist = MR; Bp.rowDist = STAR; Bp.colAlign = C.rowAlign;
+            if (redistribute_direct<T>(g, A1, Ap, oA != 0, 4 + buf, nb, cs)) return 1;
+            if (redistribute_direct<T>(g, B1, Bp, oB == 0, 6 + buf, nb, cs)) return 1;
+        } else {
+            if (make_tmp<T>(g, g.panel[buf], m, nb, MC, STAR, C.colAlign, 0, Ap)) return 1;
+            if (make_tmp<T>(g, g.panel[2 + buf], n, nb, MR, STAR, C.rowAlign, 0, Bp)) return 1;
+            Ap.width = kb;
+            Bp.width = kb;
+            if (redistribute<T>(g, A1, Ap, oA != 0, 0, cs)) return 1;
+            if (redistribute<T>(g, B1, Bp, oB == 0, 1, cs)) return 1;
+        }
         if (overlap) {
             cudaEventRecord(g.ev_panel_ready[buf], cs);
             cudaStreamWaitEvent(s, g.ev_panel_ready[buf], 0);
@@ -179,6 +188,8 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
                      overlap ? g.sm_reserve : 0))
             return 1;
         if (overlap) cudaEventRecord(g.ev_panel_free[buf], s);
+        // tell the panel's writers it has been consumed (ordered after the GEMM that read it)
+        if (direct && (g.world->push_close(4 + buf, s) || g.world->push_close(6 + buf, s))) return 1;
     }
     return 0;
 }

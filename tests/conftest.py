@@ -3,6 +3,9 @@ import sys
 
 import pytest
 
+# rank-threads of the single-GPU multi-rank tests use several streams each; keep them on distinct hardware queues
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 for p in (ROOT, os.path.join(ROOT, "tests")):
     if p not in sys.path:

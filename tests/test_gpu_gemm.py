@@ -132,3 +132,10 @@ def test_gemm_host_buffers_roundtrip():
         return cm.local_numpy()
     got = H.run_ranks(1, body)[0]
     assert np.abs(got - Cexp.block(0)).max() <= 1e-10
+
+
+def test_gemm_over_staged_transport(monkeypatch):
+    """Every orientation x algorithm on a 2x4 grid with the staged (pack -> exchange -> unpack) transport; the default
+    for rank-threads is the push transport with panels written directly into the readers' buffers."""
+    monkeypatch.setenv("HYD_TRANSPORT", "staged")
+    test_gemm_all_variants(2, 4, np.float64)

@@ -166,3 +166,29 @@ def test_axpy_contract(r, c, dtype):
             got, pad_ok = out[p][i]
             assert pad_ok
             assert np.array_equal(got, B1.block(p)), (cases[i], p, np.abs(got - B1.block(p)).max())
+
+
+@pytest.fixture
+def staged_transport(monkeypatch):
+    """Rank-threads default to the push transport (peer stores into receive regions, the layout one-process-per-GPU
+    runs use over NVLink); this fixture routes exchanges through the staged pack -> exchange -> unpack path
+    (the NCCL send/recv fallback's data layout) instead."""
+    monkeypatch.setenv("HYD_TRANSPORT", "staged")
+    yield
+
+
+@pytest.mark.parametrize("r,c", [(1, 2), (2, 2), (2, 4)])
+def test_staged_transport_all_pairs(r, c, staged_transport):
+    og = O.Grid(r, c, 1)
+    rng = np.random.default_rng(41 * r + c)
+    for tr in (False, True):
+        cases = []
+        for (scd, srd), (dcd, drd) in itertools.product(O.PAIRS, O.PAIRS):
+            m, n = [(50, 50), (7, 5), (129, 67)][len(cases) % 3]
+            cases.append((m, n, (scd, srd, U.rand_align(rng, og, scd), U.rand_align(rng, og, srd)),
+                          (dcd, drd, U.rand_align(rng, og, dcd), U.rand_align(rng, og, drd))))
+        _check_redist(r, c, cases, np.float64, transpose=tr)
+
+
+def test_staged_transport_axpy_contract(staged_transport):
+    test_axpy_contract(2, 2, np.float64)
