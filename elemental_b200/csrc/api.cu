@@ -160,7 +160,7 @@ int hyd_grid_col(const hyd_grid* g) { return g->g->mr; }
 int hyd_grid_vc_rank(const hyd_grid* g) { return g->g->vc(); }
 int hyd_grid_vr_rank(const hyd_grid* g) { return g->g->vr(); }
 int hyd_grid_set_overlap(hyd_grid* g, int overlap, int sm_reserve) {
-    g->g->overlap = overlap != 0;
+    g->g->overlap = overlap;
     if (sm_reserve >= 0) g->g->sm_reserve = sm_reserve;
     return 0;
 }

@@ -28,6 +28,8 @@ int lgemm_f64_ex(int tA, int tB, long long m, long long n, long long k, double a
 int lgemm_f32_ex(int tA, int tB, long long m, long long n, long long k, float alpha, const float* A,
                  long long lda, const float* B, long long ldb, float beta, float* C, long long ldc,
                  cudaStream_t s, int sm_reserve);
+int lgemm_f32_tc(int tA, int tB, long long m, long long n, long long k, float alpha, const float* A, long long lda,
+                 const float* B, long long ldb, float beta, float* C, long long ldc, cudaStream_t s, int sm_reserve);
 int lgemm_f32(int tA, int tB, long long m, long long n, long long k, float alpha, const float* A,
               long long lda, const float* B, long long ldb, float beta, float* C, long long ldc,
               cudaStream_t s);

@@ -156,7 +156,7 @@ int lgemm_f32(int tA, int tB, long long m, long long n, long long k, float alpha
 }
 
 int lgemm_f32_ex(int tA, int tB, long long m, long long n, long long k, float alpha, const float* A, long long lda,
-                 const float* B, long long ldb, float beta, float* C, long long ldc, cudaStream_t s, int) {
+                 const float* B, long long ldb, float beta, float* C, long long ldc, cudaStream_t s, int sm_reserve) {
     using namespace f32;
     if (m < 0 || n < 0 || k < 0) return set_error("hyd_lgemm_f32: negative dimension");
     if (m == 0 || n == 0) return 0;
@@ -170,6 +170,10 @@ int lgemm_f32_ex(int tA, int tB, long long m, long long n, long long k, float al
             return check_cuda(cudaGetLastError(), "sscale_kernel");
         }
         return 0;
+    }
+    {   // large, TMA-compatible operands: split-TF32 on the tcgen05 tensor cores (lgemm_f32_tc.cu)
+        const int rc = lgemm_f32_tc(tA, tB, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, s, sm_reserve);
+        if (rc >= 0) return rc;
     }
     const bool aoc = !tA, boc = tB != 0;  // outer-contiguous?
     const int vecA = aoc && ((uintptr_t)A % 16 == 0) && (lda % 4 == 0);

@@ -110,7 +110,9 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
     const LocalShape Lc = local_shape(sh, C, g.mc, g.mr);
     const int es = sizeof(T);
     if (ensure_engine(g)) return 1;
-    const bool overlap = g.overlap && sh.size() > 1;
+    // with the push transport a panel gather costs a few % of its GEMM, less than the wave the persistent GEMM loses
+    // when it leaves SMs to communication kernels: auto mode overlaps only the staged (NCCL) transport
+    const bool overlap = sh.size() > 1 && (g.overlap < 0 ? !g.world->can_push() : g.overlap != 0);
     // panel schedule.  The first panel's gather / upload cannot hide under a GEMM, so it is narrower
     // (nb/4, >= 128): the exposed prologue shrinks 4x; only the grouping of the k-sum changes.
     std::vector<i64> ks;

@@ -122,7 +122,8 @@ int hyd_grid_row(const hyd_grid* g);      /* MCRank */
 int hyd_grid_col(const hyd_grid* g);      /* MRRank */
 int hyd_grid_vc_rank(const hyd_grid* g);
 int hyd_grid_vr_rank(const hyd_grid* g);
-/* engine knobs: overlap panel gathers with the local GEMM (default 1); SMs left to comm kernels (default 4) */
+/* engine knobs: overlap panel gathers with the local GEMM (-1 = auto (default): only for the staged NCCL transport,
+ * 0 = off, 1 = on); SMs the GEMM leaves to communication kernels while overlapping (default 4, < 0 keeps the value) */
 int hyd_grid_set_overlap(hyd_grid* g, int overlap, int sm_reserve);
 
 /* per-kernel device timing: enable (also resets), then read launches and summed CUDA-event time of

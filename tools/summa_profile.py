@@ -33,7 +33,8 @@ def main():
         for d in (A, B, Cm):
             d.store.uniform_(-1, 1)
         for nb in [int(x) for x in os.environ.get("PROF_NB", "256,512,1024,2048").split(",")]:
-            for overlap, res in ((True, 8), (True, 4), (True, 16), (False, 0)):
+            modes = [tuple(int(v) for v in x.split(':')) for x in os.environ.get('PROF_MODES', '1:8,1:4,1:16,0:0').split(',')]
+            for overlap, res in [(bool(a), b) for a, b in modes]:
                 grid.SetOverlap(overlap, res)
                 f = lambda: H.Gemm(oA, oB, 1.0, A, B, 0.0, Cm, alg, blocksize=nb)
                 f(); f()
