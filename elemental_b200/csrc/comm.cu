@@ -59,6 +59,7 @@ struct NcclWorld : World {
         for (int p = 0; p < size; ++p)
             if (p != rank && pc.ctrl_peer[p]) cudaIpcCloseMemHandle(pc.ctrl_peer[p]);
         if (pc.ctrl_local) cudaFree(pc.ctrl_local);
+        if (pc.seq_scratch) cudaFree(pc.seq_scratch);
         if (hs_dev) cudaFree(hs_dev);
         if (comm) nccl::ncclCommDestroy(comm);
     }
@@ -68,6 +69,7 @@ struct NcclWorld : World {
     char* shared_peer(int slot, int p) override { return pc.region_peer[slot][p]; }
     int push_open(int slot, const unsigned char* to, cudaStream_t s) override { return pc.open(slot, to, s); }
     int push_post(int slot, const unsigned char* to, cudaStream_t s) override { return pc.post(slot, to, s); }
+    int push_post_ce(int slot, const unsigned char* to, cudaStream_t s) override { return pc.post_ce(slot, to, s); }
     int push_wait(int slot, const unsigned char* from, cudaStream_t s) override { return pc.wait(slot, from, s); }
     int push_close(int slot, cudaStream_t s) override { return pc.close(slot, s); }
 
@@ -139,6 +141,8 @@ struct NcclWorld : World {
         if (map_all(PushCore::ctrl_bytes(), &local, peers)) return 0;  // fall back to staged NCCL send/recv
         pc.ctrl_local = (uint32_t*)local;
         for (int p = 0; p < size; ++p) pc.ctrl_peer[p] = (uint32_t*)peers[p];
+        void* sq = nullptr;
+        if (cudaMalloc(&sq, sizeof(uint32_t) * kPushSlots) == cudaSuccess) pc.seq_scratch = (uint32_t*)sq;
         push_ok = true;
         return 0;
     }

@@ -44,6 +44,9 @@ struct World {
     // to[p] != 0: I store into p's region this round; from[q] != 0: q stores into mine
     virtual int push_open(int /*slot*/, const unsigned char* /*to*/, cudaStream_t) { return 1; }   // wait: receivers consumed previous round
     virtual int push_post(int /*slot*/, const unsigned char* /*to*/, cudaStream_t) { return 1; }   // signal: my stores have landed
+    // same signal issued without any kernel (stream memory op + 4-byte copy-engine writes): for rounds whose data moved
+    // with copy engines while a persistent GEMM holds every SM
+    virtual int push_post_ce(int slot, const unsigned char* to, cudaStream_t s) { return push_post(slot, to, s); }
     virtual int push_wait(int /*slot*/, const unsigned char* /*from*/, cudaStream_t) { return 1; } // wait for my senders
     virtual int push_close(int /*slot*/, cudaStream_t) { return 1; }                                // broadcast: round consumed
 };

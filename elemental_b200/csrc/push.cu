@@ -9,6 +9,16 @@ namespace {
 
 typedef CUresult (*wait32_fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
 
+wait32_fn stream_write32() {
+    static wait32_fn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuStreamWriteValue32", &p, cudaEnableDefault, &q) == cudaSuccess) fn = reinterpret_cast<wait32_fn>(p);
+    }
+    return fn;
+}
+
 wait32_fn stream_wait32() {
     static wait32_fn fn = nullptr;
     if (!fn) {
@@ -67,6 +77,24 @@ int PushCore::post(int slot, const unsigned char* to, cudaStream_t s) {
     if (a.n == 0) return 0;
     push_signal_kernel<<<1, kPushMaxRanks, 0, s>>>(a);
     return check_cuda(cudaGetLastError(), "push_signal_kernel(post)");
+}
+
+int PushCore::post_ce(int slot, const unsigned char* to, cudaStream_t s) {
+    wait32_fn wr = stream_write32();
+    if (!wr || !seq_scratch) return post(slot, to, s);
+    bool any = false;
+    for (int p = 0; p < size; ++p) any = any || (p != rank && to[p]);
+    if (!any) return 0;
+    // stage the round number in local memory (stream memory op), then copy it onto every receiver's flag word with the
+    // copy engine: both are ordered after the preceding copies of this stream and neither needs an SM
+    if (wr((CUstream)s, (CUdeviceptr)(uintptr_t)(seq_scratch + slot), round[slot], 0) != CUDA_SUCCESS)
+        return set_error("push_post_ce: cuStreamWriteValue32 failed");
+    for (int p = 0; p < size; ++p)
+        if (p != rank && to[p] &&
+            check_cuda(cudaMemcpyAsync(ctrl_peer[p] + flag_index(slot, rank), seq_scratch + slot, 4, cudaMemcpyDeviceToDevice, s),
+                       "push_post_ce: flag copy"))
+            return 1;
+    return 0;
 }
 
 int PushCore::wait(int slot, const unsigned char* from, cudaStream_t s) {

@@ -30,6 +30,8 @@ struct PushCore {
 
     int open(int slot, const unsigned char* to, cudaStream_t s);
     int post(int slot, const unsigned char* to, cudaStream_t s);
+    int post_ce(int slot, const unsigned char* to, cudaStream_t s);
+    uint32_t* seq_scratch = nullptr;  // [kPushSlots] device words: round numbers staged for the 4-byte flag copies
     int wait(int slot, const unsigned char* from, cudaStream_t s);
     int close(int slot, cudaStream_t s);
 };

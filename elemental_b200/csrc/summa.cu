@@ -24,6 +24,7 @@
 #include "grid.h"
 #include "hyd_internal.h"
 #include <algorithm>
+#include <stdlib.h>
 #include <type_traits>
 #include <vector>
 
@@ -100,6 +101,105 @@ int upload_k_slice(const GridShape& sh, const DM& X, int mc, int mr, bool k_is_r
                       "hyd_gemm_host: H2D cols");
 }
 
+// ---- copy-engine panel gather for SUMMA-C, NN orientation --------------------------------------------------------
+// With peer-mapped panel buffers the two panel gathers need no kernel at all: the A panel is a set of whole local
+// columns, and -- if the k index inside the panel is stored owner-by-owner instead of interleaved (any permutation of k
+// applied to both panels leaves A_p * B_p unchanged) -- the B panel is a set of contiguous local row blocks kept
+// k-contiguous ([*,MR], fed to the GEMM as a non-transposed operand).  Every piece is one strided 2-D copy that the copy
+// engines push over NVLink straight into the readers' panels, flags go out as 4-byte copies, waits are stream memory
+// operations: zero SMs, so the persistent GEMM keeps all of them while the next panel arrives.
+// Position of panel-local k index t: owners q = grid row holding B's row k0+t, in ascending q, each owner's rows in
+// ascending order:  pos(t) = off[q(t)] + (t - first[q(t)]) / r.
+template <typename T>
+int gather_panels_ce(Grid& g, const DM& A, const DM& B, const DM& C, i64 k0, i64 kb, i64 nb, int buf, cudaStream_t cs,
+                     DM& Ap, DM& Bp) {
+    const GridShape& sh = g.shape;
+    const int r = sh.r, c = sh.c, P = sh.size(), me = g.rank;
+    const i64 es = sizeof(T), q16 = 16 / es;
+    const int slotA = 4 + buf, slotB = 6 + buf;
+    ProfScope prof(g, Grid::PROF_REDIST, cs);
+    const LocalShape La = local_shape(sh, A, g.mc, g.mr), Lb = local_shape(sh, B, g.mc, g.mr), Lc = local_shape(sh, C, g.mc, g.mr);
+    // geometry of the panels: identical on every rank of my grid row (A) / grid column (B)
+    i64 maxlh = 0, maxlw = 0;
+    for (int p = 0; p < P; ++p) {
+        int pmc, pmr;
+        sh.coords(p, pmc, pmr);
+        const LocalShape L = local_shape(sh, C, pmc, pmr);
+        maxlh = std::max(maxlh, L.lh);
+        maxlw = std::max(maxlw, L.lw);
+    }
+    const i64 ldA = std::max<i64>(q16, (Lc.lh + q16 - 1) / q16 * q16);
+    const i64 ldAmax = std::max<i64>(q16, (maxlh + q16 - 1) / q16 * q16);
+    const i64 ldB = std::max<i64>(q16, (nb + q16 - 1) / q16 * q16);  // k-contiguous columns of the B panel
+    if (g.world->shared_reserve(slotA, (size_t)(ldAmax * nb * es))) return 1;
+    if (g.world->shared_reserve(slotB, (size_t)(ldB * std::max<i64>(maxlw, 1) * es))) return 1;
+    Ap = DM(); Bp = DM();
+    Ap.buf = g.world->shared_local(slotA); Ap.ldim = ldA; Ap.height = C.height; Ap.width = kb;
+    Bp.buf = g.world->shared_local(slotB); Bp.ldim = ldB; Bp.height = kb; Bp.width = C.width;
+    // owner blocks of the panel's k range: B's row k0+t lives on grid row (k0 + t + B.colAlign) mod r
+    std::vector<i64> first(r), cnt(r), off(r);
+    i64 run = 0;
+    for (int q = 0; q < r; ++q) {
+        first[q] = mod_((i64)q - B.colAlign - k0, r);       // smallest t >= 0 owned by grid row q
+        cnt[q] = length_(kb, first[q], r);
+        off[q] = run;
+        run += cnt[q];
+    }
+    std::vector<unsigned char> toA(P, 0), fromA(P, 0), toB(P, 0), fromB(P, 0);
+    // ---- A: my panel columns t = tA0 + j*c, j < nA
+    const i64 tA0 = mod_((i64)g.mr - A.rowAlign - k0, c);
+    const i64 nA = length_(kb, tA0, c);
+    const i64 jLoc0 = length_(k0, La.rowShift, c);            // local column index of the first one
+    for (int pmr = 0; pmr < c; ++pmr) {
+        const int p = sh.rank_of(g.mc, pmr);
+        if (p != me) {
+            if (nA > 0 && La.lh > 0) toA[p] = 1;
+            if (length_(kb, mod_((i64)pmr - A.rowAlign - k0, c), c) > 0 && Lc.lh > 0) fromA[p] = 1;
+        }
+    }
+    // ---- B: my panel rows are the contiguous local rows [iLoc0, iLoc0 + nB)
+    const i64 iLoc0 = length_(k0, Lb.colShift, r);
+    const i64 nB = cnt[g.mc];
+    for (int pmc = 0; pmc < r; ++pmc) {
+        const int p = sh.rank_of(pmc, g.mr);
+        if (p != me) {
+            if (nB > 0 && Lb.lw > 0) toB[p] = 1;
+            if (cnt[pmc] > 0 && Lc.lw > 0) fromB[p] = 1;
+        }
+    }
+    if (g.world->push_open(slotA, toA.data(), cs) || g.world->push_open(slotB, toB.data(), cs)) return 1;
+    if (nA > 0 && La.lh > 0) {
+        const i64 gg = gcd_(r, c), R = r / gg;                // columns of one class (j = u mod R) share their B owner
+        for (i64 u = 0; u < R && u < nA; ++u) {
+            const i64 t = tA0 + u * c;
+            const int q = (int)mod_(k0 + t + B.colAlign, r);
+            const i64 pos0 = off[q] + (t - first[q]) / r, nv = (nA - u + R - 1) / R;
+            const T* src = static_cast<const T*>(A.buf) + (jLoc0 + u) * A.ldim;
+            for (int pmr = 0; pmr < c; ++pmr) {
+                const int p = sh.rank_of(g.mc, pmr);
+                T* dst = reinterpret_cast<T*>(g.world->shared_peer(slotA, p)) + pos0 * ldA;
+                if (check_cuda(cudaMemcpy2DAsync(dst, (size_t)((c / gg) * ldA * es), src, (size_t)(R * A.ldim * es), (size_t)(La.lh * es),
+                                                 (size_t)nv, cudaMemcpyDeviceToDevice, cs),
+                               "panel push (A)"))
+                    return 1;
+            }
+        }
+    }
+    if (nB > 0 && Lb.lw > 0) {
+        const T* src = static_cast<const T*>(B.buf) + iLoc0;
+        for (int pmc = 0; pmc < r; ++pmc) {
+            const int p = sh.rank_of(pmc, g.mr);
+            T* dst = reinterpret_cast<T*>(g.world->shared_peer(slotB, p)) + off[g.mc];
+            if (check_cuda(cudaMemcpy2DAsync(dst, (size_t)(ldB * es), src, (size_t)(B.ldim * es), (size_t)(nB * es), (size_t)Lb.lw,
+                                             cudaMemcpyDeviceToDevice, cs),
+                           "panel push (B)"))
+                return 1;
+        }
+    }
+    if (g.world->push_post_ce(slotA, toA.data(), cs) || g.world->push_post_ce(slotB, toB.data(), cs)) return 1;
+    return g.world->push_wait(slotA, fromA.data(), cs) || g.world->push_wait(slotB, fromB.data(), cs);
+}
+
 // ---- SUMMA-C (stationary C) -------------------------------------------------
 template <typename T>
 int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, const DM& B, T beta, const DM& C, i64 nb,
@@ -110,9 +210,14 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
     const LocalShape Lc = local_shape(sh, C, g.mc, g.mr);
     const int es = sizeof(T);
     if (ensure_engine(g)) return 1;
-    // with the push transport a panel gather costs a few % of its GEMM, less than the wave the persistent GEMM loses
-    // when it leaves SMs to communication kernels: auto mode overlaps only the staged (NCCL) transport
-    const bool overlap = sh.size() > 1 && (g.overlap < 0 ? !g.world->can_push() : g.overlap != 0);
+    // NN with matching alignments on the push transport: panels are gathered by the copy engines alone (gather_panels_ce),
+    // so the gather always runs under the previous GEMM and the GEMM keeps every SM.
+    static const bool ce_enabled = !(getenv("HYD_PANEL_CE") && atoi(getenv("HYD_PANEL_CE")) == 0);
+    const bool ce = ce_enabled && sh.size() > 1 && g.world->can_push() && oA == 0 && oB == 0 && A.colAlign == C.colAlign &&
+                    B.rowAlign == C.rowAlign && g.overlap != 0;
+    // Otherwise: with the push transport a panel gather costs a few % of its GEMM, less than the wave the persistent GEMM
+    // loses when it leaves SMs to communication kernels: auto mode overlaps only the staged (NCCL) transport
+    const bool overlap = sh.size() > 1 && (ce || (g.overlap < 0 ? !g.world->can_push() : g.overlap != 0));
     // panel schedule.  The first panel's gather / upload cannot hide under a GEMM, so it is narrower
     // (nb/4, >= 128): the exposed prologue shrinks 4x; only the grouping of the k-sum changes.
     std::vector<i64> ks;
@@ -167,7 +272,9 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
         const DM A1 = oA ? view(sh, A, g.mc, g.mr, k0, 0, kb, m, es) : view(sh, A, g.mc, g.mr, 0, k0, m, kb, es);
         const DM B1 = oB ? view(sh, B, g.mc, g.mr, 0, k0, n, kb, es) : view(sh, B, g.mc, g.mr, k0, 0, kb, n, es);
         if (overlap && step >= 2) cudaStreamWaitEvent(cs, g.ev_panel_free[buf], 0);
-        if (direct) {
+        if (ce) {
+            if (gather_panels_ce<T>(g, A, B, C, k0, kb, nb, buf, cs, Ap, Bp)) return 1;
+        } else if (direct) {
             // panels live in peer-mapped regions: every owner stores its columns straight into every reader's panel
             Ap.height = m; Ap.width = kb; Ap.colDist = MC; Ap.rowDist = STAR; Ap.colAlign = C.colAlign;
             Bp.height = n; Bp.width = kb; Bp.colDist = MR; Bp.rowDist = STAR; Bp.colAlign = C.rowAlign;
@@ -185,9 +292,9 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
             cudaEventRecord(g.ev_panel_ready[buf], cs);
             cudaStreamWaitEvent(s, g.ev_panel_ready[buf], 0);
         }
-        if (lgemm<T>(g, 0, 1, Lc.lh, Lc.lw, kb, alpha, static_cast<const T*>(Ap.buf), Ap.ldim,
+        if (lgemm<T>(g, 0, ce ? 0 : 1, Lc.lh, Lc.lw, kb, alpha, static_cast<const T*>(Ap.buf), Ap.ldim,
                      static_cast<const T*>(Bp.buf), Bp.ldim, k0 == 0 ? beta : T(1), static_cast<T*>(C.buf), C.ldim, s,
-                     overlap ? g.sm_reserve : 0))
+                     (overlap && !ce) ? g.sm_reserve : 0))
             return 1;
         if (overlap) cudaEventRecord(g.ev_panel_free[buf], s);
         // tell the panel's writers it has been consumed (ordered after the GEMM that read it)
