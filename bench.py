@@ -261,6 +261,10 @@ def run_ours(args):
             dd = hC.store[: hC.lw, : hC.lh].cuda() - Cm.store[: Cm.lw, : Cm.lh]
             rel = float(dd.norm() / Cm.store[: Cm.lw, : Cm.lh].norm())
             e2e["rel_frobenius_vs_device_run"] = rel
+            if rel > 1e-13 * n ** 0.5:
+                bad = (dd.abs() > 1e-9).nonzero()
+                print(f"[rank {rank}] e2e mismatch: rel={rel:.3e} bad={bad.shape[0]} first={bad[:8].tolist()} max={float(dd.abs().max()):.3e}",
+                      file=sys.stderr, flush=True)
             assert rel <= 1e-13 * n ** 0.5, rel
 
     cpu = None

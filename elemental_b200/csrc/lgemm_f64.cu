@@ -175,6 +175,7 @@ dgemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         for (int kb = 0; kb < num_kb; ++kb) {
             mbar_wait(full_bar(stage), phase);
             const uint8_t* st = smem_gen + stage * kStageBytes;
+            uint32_t dep = 0;  // OR of every loaded fragment's high word: orders the stage release after the loads
             // two k8 halves per stage (m16n8k8: 24 operand registers live instead of 48)
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
@@ -187,6 +188,7 @@ dgemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                         if (TB == MT) o = (offB[2 * h + j] + (nt >> 1) * 2048) ^ ((nt & 1) * 64);
                         else          o = offB[2 * h + j] + nt * 1024;
                         bf[nt][j] = *reinterpret_cast<const double*>(st + o);
+                        dep |= (uint32_t)__double2hiint(bf[nt][j]);
                     }
                 }
 #pragma unroll
@@ -198,6 +200,7 @@ dgemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                         if (TA == MT) o = (offA[2 * h + (i >> 1)] + mt * 2048) ^ ((i & 1) * 64);
                         else          o = offA[2 * h + (i >> 1)] + mt * 2048 + (i & 1) * 1024;
                         af[i] = *reinterpret_cast<const double*>(st + o);
+                        dep |= (uint32_t)__double2hiint(af[i]);
                     }
 #pragma unroll
                     for (int nt = 0; nt < 4; ++nt)
@@ -205,7 +208,7 @@ dgemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                 }
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(empty_bar(stage));
+            if (lane == 0) mbar_arrive_after_loads(empty_bar(stage), dep);
             if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
 

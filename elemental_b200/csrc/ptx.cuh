@@ -25,6 +25,23 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+// Consumer release of a TMA-refilled stage that was read with ld.shared.  ptxas issues a plain mbarrier.arrive right
+// behind the last ld.shared without waiting for its data, and under LSU back-pressure (other warps' epilogue
+// stores) the arrive can overtake a queued load by more than a TMA round trip: the load then returns the NEXT
+// fill of the slot (observed: ~1 wrong 8x32 block per 16384^3 Gemm).  `dep` must be an OR over bits of every
+// value loaded from the stage; the arrive count is computed from it (always 1), so the instruction cannot
+// issue before all of those loads have returned.
+__device__ __forceinline__ void mbar_arrive_after_loads(uint32_t bar, uint32_t dep) {
+    asm volatile(
+        "{\n\t"
+        ".reg .b32 t, c;\n\t"
+        "or.b32 t, %1, 1;\n\t"
+        "min.u32 c, t, 1;\n\t"
+        "mbarrier.arrive.shared::cta.b64 _, [%0], c;\n\t"
+        "}" ::"r"(bar),
+        "r"(dep)
+        : "memory");
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     asm volatile(
         "{\n\t"

@@ -83,6 +83,39 @@ def test_lgemm_large_vs_torch(dtype, tA, tB):
 
 
 @pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_lgemm_repeatable_under_copy_traffic(dtype):
+    """Regression for the stage-release race of the TMA ring (a queued ld.shared overtaken by the consumer's
+    mbarrier.arrive read the slot's NEXT fill: one wrong 8x32 block per ~1e13 flops, more often with copy
+    traffic on the device).  The kernel is deterministic, so repeated launches must agree bit for bit."""
+    tdt = torch.float64 if dtype == np.float64 else torch.float32
+    fn = lib.hyd_lgemm_f64 if dtype == np.float64 else lib.hyd_lgemm_f32
+    sc = C.c_double if dtype == np.float64 else C.c_float
+    m = n = 8192
+    k = 4096
+    gen = torch.Generator(device=DEV).manual_seed(77)
+    A = torch.rand((k, m), dtype=tdt, device=DEV, generator=gen) * 2 - 1
+    B = torch.rand((n, k), dtype=tdt, device=DEV, generator=gen) * 2 - 1
+    outs = [torch.empty((n, m), dtype=tdt, device=DEV) for _ in range(2)]
+    src = torch.empty(64 << 20, dtype=torch.uint8, pin_memory=True)
+    dst = torch.empty(64 << 20, dtype=torch.uint8, device=DEV)
+    side = torch.cuda.Stream()
+    s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    first = None
+    for it in range(6):
+        with torch.cuda.stream(side):
+            for _ in range(4):
+                dst.copy_(src, non_blocking=True)
+        o = outs[it & 1]
+        check(fn(0, 0, m, n, k, sc(1.0), C.c_void_p(A.data_ptr()), m, C.c_void_p(B.data_ptr()), k, sc(0.0),
+                 C.c_void_p(o.data_ptr()), m, s))
+        torch.cuda.synchronize()
+        if first is None:
+            first = o.clone()
+        else:
+            assert torch.equal(o, first), f"launch {it}: {(o != first).sum().item()} elements differ from launch 0"
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
 def test_lgemm_edge_cases(dtype):
     tdt = torch.float64 if dtype == np.float64 else torch.float32
     fn = lib.hyd_lgemm_f64 if dtype == np.float64 else lib.hyd_lgemm_f32

@@ -38,6 +38,16 @@ def main():
                 grid.SetOverlap(overlap, res)
                 f = lambda: H.Gemm(oA, oB, 1.0, A, B, 0.0, Cm, alg, blocksize=nb)
                 f(); f()
+                if os.environ.get("PROF_CHECK"):
+                    torch.cuda.synchronize()
+                    got = Cm.store.clone()
+                    grid.SetOverlap(0, 0)
+                    f()
+                    torch.cuda.synchronize()
+                    rel = float((got - Cm.store).norm() / Cm.store.norm())
+                    bad = int(((got - Cm.store).abs() > 1e-6 * Cm.store.abs().max()).sum())
+                    print(f"[rank {rank}] nb={nb} overlap={overlap}: rel diff vs non-overlapped direct path {rel:.3e}, bad elements {bad}", flush=True)
+                    grid.SetOverlap(overlap, res)
                 if size > 1:
                     dist.barrier()
                 torch.cuda.synchronize()
