@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libhydrogen_b200.so")
+LIB_PATH = os.environ.get("HYD_LIB") or os.path.join(_HERE, "libhydrogen_b200.so")  # HYD_LIB: developer A/B builds
 
 
 class HydrogenError(RuntimeError):

@@ -175,7 +175,7 @@ dgemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         for (int kb = 0; kb < num_kb; ++kb) {
             mbar_wait(full_bar(stage), phase);
             const uint8_t* st = smem_gen + stage * kStageBytes;
-            uint32_t dep = 0;  // OR of every loaded fragment's high word: orders the stage release after the loads
+            uint32_t dep = 0;
             // two k8 halves per stage (m16n8k8: 24 operand registers live instead of 48)
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
@@ -188,7 +188,6 @@ dgemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                         if (TB == MT) o = (offB[2 * h + j] + (nt >> 1) * 2048) ^ ((nt & 1) * 64);
                         else          o = offB[2 * h + j] + nt * 1024;
                         bf[nt][j] = *reinterpret_cast<const double*>(st + o);
-                        dep |= (uint32_t)__double2hiint(bf[nt][j]);
                     }
                 }
 #pragma unroll
@@ -200,15 +199,19 @@ dgemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                         if (TA == MT) o = (offA[2 * h + (i >> 1)] + mt * 2048) ^ ((i & 1) * 64);
                         else          o = offA[2 * h + (i >> 1)] + mt * 2048 + (i & 1) * 1024;
                         af[i] = *reinterpret_cast<const double*>(st + o);
-                        dep |= (uint32_t)__double2hiint(af[i]);
                     }
 #pragma unroll
                     for (int nt = 0; nt < 4; ++nt)
                         dmma_1688(acc[mt][nt], af[0], af[1], af[2], af[3], bf[nt][0], bf[nt][1]);
                 }
             }
+            // release the stage only after every fragment load has returned (see mbar_arrive_after_loads): the diagonal
+            // accumulators' rows g (c0) and g+8 (c2) depend on all A fragments (a0..a3 of every mt) and all B fragments
+            // (every nt) of both k8 halves, so 8 high words carry a dependency on all 48 loads of the stage
+#pragma unroll
+            for (int i = 0; i < 4; ++i) dep |= (uint32_t)__double2hiint(acc[i][i][0]) | (uint32_t)__double2hiint(acc[i][i][2]);
             __syncwarp();
-            if (lane == 0) mbar_arrive_after_loads(empty_bar(stage), dep);
+            mbar_arrive_after_loads(empty_bar(stage), dep, lane == 0);
             if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
 

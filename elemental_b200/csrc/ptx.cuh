@@ -28,18 +28,21 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 // Consumer release of a TMA-refilled stage that was read with ld.shared.  ptxas issues a plain mbarrier.arrive right
 // behind the last ld.shared without waiting for its data, and under LSU back-pressure (other warps' epilogue
 // stores) the arrive can overtake a queued load by more than a TMA round trip: the load then returns the NEXT
-// fill of the slot (observed: ~1 wrong 8x32 block per 16384^3 Gemm).  `dep` must be an OR over bits of every
-// value loaded from the stage; the arrive count is computed from it (always 1), so the instruction cannot
-// issue before all of those loads have returned.
-__device__ __forceinline__ void mbar_arrive_after_loads(uint32_t bar, uint32_t dep) {
+// fill of the slot (observed: ~1 wrong 8x32 block per 16384^3 Gemm, see tools/e2e_check.py).  `dep` must carry a
+// register dependency on every value loaded from the stage (an OR over bits of the loads, or of MMA results
+// computed from them); the arrive count is computed from it (always 1), so the instruction cannot issue before
+// all of those loads have returned.  Branch-free so ptxas can schedule it inside the MMA stream.
+__device__ __forceinline__ void mbar_arrive_after_loads(uint32_t bar, uint32_t dep, bool elected) {
     asm volatile(
         "{\n\t"
         ".reg .b32 t, c;\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.u32 p, %2, 0;\n\t"
         "or.b32 t, %1, 1;\n\t"
         "min.u32 c, t, 1;\n\t"
-        "mbarrier.arrive.shared::cta.b64 _, [%0], c;\n\t"
+        "@p mbarrier.arrive.shared::cta.b64 _, [%0], c;\n\t"
         "}" ::"r"(bar),
-        "r"(dep)
+        "r"(dep), "r"((uint32_t)elected)
         : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
