@@ -21,6 +21,7 @@ import sys
 import threading
 import time
 
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")  # before CUDA init: one hardware queue per engine stream
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -224,10 +225,13 @@ def run_ours(args):
         check(lib.hyd_probe_peak(2, 20000, 2, C.byref(peak)))
         flops_per_launch = 2.0 * Cm.lh * Cm.lw * min(nb, n)
         achieved = flops_per_launch / (gemm_ms / max(n_gemm, 1) * 1e-3) / 1e12 if n_gemm else None
-        roofline = {"bound": "tensor", "kernel": "dgemm_tma_kernel (FP64 DMMA m16n8k16, TMA-fed)",
+        roofline = {"bound": "tensor", "kernel": "dgemm_tma_kernel (FP64 DMMA m16n8k8, TMA-fed)",
                     "achieved": round(achieved, 3) if achieved else None, "peak": round(peak.value, 3), "unit": "TFLOP/s",
-                    "frac": round(achieved / peak.value, 4) if achieved else None, "traffic": None,
-                    "peak_source": "FP64 tensor pipe measured live (hyd_probe_peak: register-resident DMMA m16n8k16 loop); "
+                    "frac": round(achieved / peak.value, 4) if achieved else None,
+                    # DRAM bytes per launch from the ncu --set full capture of this launch shape (profiles/r01_ncu_dgemm_tma_kernel.txt:
+                    # 3.37 GB read + 2.10 GB written; algorithmic 8*(2*m*n + (m+n)*k) = 4.56 GB); other shapes were not captured
+                    "traffic": 5.48e9 if (args.gpus == 1 and nb == 1024 and n == 16384) else None, "traffic_unit": "bytes/launch",
+                    "peak_source": "FP64 tensor pipe measured live (hyd_probe_peak: register-resident DMMA loop); "
                                    "MEASURED_PEAKS.json has no fp64 figure",
                     "flops_per_launch": flops_per_launch, "launches": n_gemm, "mean_launch_ms": round(gemm_ms / max(n_gemm, 1), 4),
                     "kernel_share_of_step": round(gemm_ms / (ms * args.steps), 4),

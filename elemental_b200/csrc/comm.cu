@@ -72,6 +72,8 @@ struct NcclWorld : World {
     int push_post_ce(int slot, const unsigned char* to, cudaStream_t s) override { return pc.post_ce(slot, to, s); }
     int push_wait(int slot, const unsigned char* from, cudaStream_t s) override { return pc.wait(slot, from, s); }
     int push_close(int slot, cudaStream_t s) override { return pc.close(slot, s); }
+    bool push_chunks() const override { return true; }
+    void push_next(int slot) override { pc.next(slot); }
 
     struct HandleMsg { cudaIpcMemHandle_t h; int ok; int pad[15]; };  // 128 bytes
     // all-gather one handle (+ ok flag) per rank through NCCL; returns 1 on a local failure

@@ -49,6 +49,9 @@ struct World {
     virtual int push_post_ce(int slot, const unsigned char* to, cudaStream_t s) { return push_post(slot, to, s); }
     virtual int push_wait(int /*slot*/, const unsigned char* /*from*/, cudaStream_t) { return 1; } // wait for my senders
     virtual int push_close(int /*slot*/, cudaStream_t) { return 1; }                                // broadcast: round consumed
+    // chunked rounds (see push.h): true if push_next() is supported; push_next starts the next chunk of the open round
+    virtual bool push_chunks() const { return false; }
+    virtual void push_next(int /*slot*/) {}
 };
 
 constexpr int kPushSlots = 8;   // 0-3: exchange workspaces, 4-7: SUMMA panels (A/B x double buffer)

@@ -27,6 +27,8 @@ struct Grid {
     cudaStream_t comm_stream[2] = {nullptr, nullptr};
     cudaEvent_t ev_panel_ready[2] = {nullptr, nullptr}, ev_panel_free[2] = {nullptr, nullptr};
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaStream_t unpack_stream = nullptr;           // chunk-pipelined redistributions: unpack of chunk q under the push of q+1
+    cudaEvent_t ev_unpack_fork = nullptr, ev_unpack_join = nullptr;
     std::vector<cudaEvent_t> upload_ev;  // per-panel H2D completion (hyd_gemm_host_*)
     Workspace panel[4];  // gathered panels (A/B x double buffer) or reduce temporaries
     Workspace host_stage[3];  // device images of host operands (hyd_gemm_host_*)
@@ -34,10 +36,10 @@ struct Grid {
     int sm_reserve = 4;  // SMs the local GEMM leaves to NCCL / pack kernels while overlapping
     long long launches = 0;
     // optional per-kernel timing (bench.py's roofline leg): CUDA event pairs around each launch of a kind
-    enum { PROF_LGEMM = 0, PROF_REDIST = 1, PROF_REDUCE = 2, PROF_KINDS = 3 };
+    enum { PROF_LGEMM = 0, PROF_REDIST = 1, PROF_REDUCE = 2, PROF_PACK = 3, PROF_UNPACK = 4, PROF_KINDS = 5 };
     bool profile = false;
     std::vector<cudaEvent_t> prof_ev[PROF_KINDS];   // start/stop pairs, in launch order
-    size_t prof_used[PROF_KINDS] = {0, 0, 0};
+    size_t prof_used[PROF_KINDS] = {};
 
     int vc() const { return shape.vc(mc, mr); }
     int vr() const { return shape.vr(mc, mr); }

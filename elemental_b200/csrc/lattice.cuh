@@ -6,7 +6,7 @@
 // Partial{Row,Col}Strided*, Strided{Pack,Unpack}: include/El/blas_like/level1/Copy/util.hpp:122-230,
 // 363-533,671-722; GPU forms :244-421 = one cudaMemcpy2DAsync / copy_2d_kernel per peer)
 // is a set of such lattices, one per peer.  Here ALL peers of a redistribution are
-// served by ONE launch: blockIdx.y selects the peer's descriptor, blockIdx.x strides
+// served by ONE launch: block x serves descriptor x mod n and strides
 // over that lattice's tiles.  Index math is 64-bit (32768^2 locals overflow int32).
 #pragma once
 #include <cuda_runtime.h>
@@ -55,7 +55,10 @@ template <> struct Vec16<float> { typedef float4 type; static constexpr int N = 
 // thread index along a, 16-byte vectors when both sides are contiguous and aligned.
 template <typename T>
 __global__ void __launch_bounds__(256) lattice_copy_kernel(const __grid_constant__ CopyBatch batch) {
-    const CopyDesc& D = batch.d[blockIdx.y];
+    // descriptors are interleaved along the grid (block x serves descriptor x mod n) so that the NVLink-bound peer
+    // parts and the HBM-bound local part are resident together instead of one after the other
+    const CopyDesc& D = batch.d[blockIdx.x % batch.n];
+    const i64 bx = blockIdx.x / batch.n, gx = gridDim.x / batch.n;
     const i64 nr = D.nr, nc = D.nc;
     if (nr == 0 || nc == 0) return;
     const T* __restrict__ s = static_cast<const T*>(D.src);
@@ -71,7 +74,7 @@ __global__ void __launch_bounds__(256) lattice_copy_kernel(const __grid_constant
             const i64 nrv = nr / V;
             const i64 chunks_a = (nrv + 255) / 256;
             const i64 col_groups = (nc + 3) / 4;
-            for (i64 tile = blockIdx.x; tile < chunks_a * col_groups; tile += gridDim.x) {
+            for (i64 tile = bx; tile < chunks_a * col_groups; tile += gx) {
                 const i64 ca = tile % chunks_a, cg = tile / chunks_a;
                 const i64 av = ca * 256 + threadIdx.x;
                 const i64 b0 = cg * 4;
@@ -96,24 +99,101 @@ __global__ void __launch_bounds__(256) lattice_copy_kernel(const __grid_constant
         }
     }
     if (D.s_cs == 1 && D.d_rs == 1 && D.s_rs != 1) {
-        // transposing: read along b (source-contiguous), write along a (destination-contiguous)
-        __shared__ T tile_s[32][33];
+        // transposing: read along b (source-contiguous), write along a (destination-contiguous).  The tile is staged
+        // transposed ([b][a], pitch TA + V) so the write phase is one 16-byte vector per thread (peer stores are
+        // issued per request: see the gather path below); TA = 32 V-vectors of a, 32 columns of b.
+        constexpr int TA = 32 * V;
+        __shared__ __align__(16) T tile_s[32][TA + V];
         const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
-        const i64 ta = (nr + 31) / 32, tb = (nc + 31) / 32;
-        for (i64 tile = blockIdx.x; tile < ta * tb; tile += gridDim.x) {
-            const i64 a0 = (tile % ta) * 32, b0 = (tile / ta) * 32;
+        const bool vec_st = (D.d_cs % V == 0) && (((uintptr_t)d % 16) == 0);
+        const i64 ta = (nr + TA - 1) / TA, tb = (nc + 31) / 32;
+        for (i64 tile = bx; tile < ta * tb; tile += gx) {
+            const i64 a0 = (tile % ta) * TA, b0 = (tile / ta) * 32;
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
+            for (int q = 0; q < TA / 8; ++q) {
                 const i64 a = a0 + ty + 8 * q, b = b0 + tx;
-                if (a < nr && b < nc) tile_s[ty + 8 * q][tx] = s[a * D.s_rs + b];
+                if (a < nr && b < nc) tile_s[tx][ty + 8 * q] = s[a * D.s_rs + b];
             }
             __syncthreads();
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-                const i64 a = a0 + tx, b = b0 + ty + 8 * q;
-                if (a < nr && b < nc) d[a + b * D.d_cs] = tile_s[tx][ty + 8 * q];
+                const i64 a = a0 + (i64)tx * V, b = b0 + ty + 8 * q;
+                if (b < nc) {
+                    if (vec_st && a + V <= nr) {
+                        *reinterpret_cast<VT*>(d + a + b * D.d_cs) = *reinterpret_cast<const VT*>(&tile_s[ty + 8 * q][tx * V]);
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < V; ++e)
+                            if (a + e < nr) d[a + e + b * D.d_cs] = tile_s[ty + 8 * q][tx * V + e];
+                    }
+                }
             }
             __syncthreads();
+        }
+        return;
+    }
+    if (D.d_rs == 1 && D.s_rs != 1 && nr >= V && D.d_cs % V == 0 && ((uintptr_t)d % 16) == 0) {
+        // strided source rows, contiguous destination (the usual pack into a message / a peer's receive region):
+        // gather V source elements, ONE 16-byte store per thread -- peer stores over NVLink are issued per request,
+        // so halving (fp64) / quartering (fp32) their number is what the push rate follows
+        const i64 nrv = nr / V;
+        const i64 chunks_a = (nrv + 255) / 256;
+        const i64 col_groups = (nc + 3) / 4;
+        for (i64 tile = bx; tile < chunks_a * col_groups; tile += gx) {
+            const i64 ca = tile % chunks_a, cg = tile / chunks_a;
+            const i64 av = ca * 256 + threadIdx.x;
+            const i64 b0 = cg * 4;
+            if (av < nrv) {
+                T v[4][V];
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (b0 + q < nc) {
+#pragma unroll
+                        for (int e = 0; e < V; ++e) v[q][e] = __ldg(s + (av * V + e) * D.s_rs + (b0 + q) * D.s_cs);
+                    }
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (b0 + q < nc) reinterpret_cast<VT*>(d + (b0 + q) * D.d_cs)[av] = *reinterpret_cast<const VT*>(v[q]);
+            }
+            if (ca == 0) {  // scalar tail rows
+                const i64 tail = nr - nrv * V;
+                for (i64 e = threadIdx.x; e < tail * 4; e += 256) {
+                    const i64 a = nrv * V + e % tail, b = b0 + e / tail;
+                    if (b < nc) d[a + b * D.d_cs] = s[a * D.s_rs + b * D.s_cs];
+                }
+            }
+        }
+        return;
+    }
+    if (D.s_rs == 1 && D.d_rs != 1 && nr >= V && D.s_cs % V == 0 && ((uintptr_t)s % 16) == 0) {
+        // contiguous source (a received message), strided destination rows: one 16-byte load, V scalar stores
+        const i64 nrv = nr / V;
+        const i64 chunks_a = (nrv + 255) / 256;
+        const i64 col_groups = (nc + 3) / 4;
+        for (i64 tile = bx; tile < chunks_a * col_groups; tile += gx) {
+            const i64 ca = tile % chunks_a, cg = tile / chunks_a;
+            const i64 av = ca * 256 + threadIdx.x;
+            const i64 b0 = cg * 4;
+            if (av < nrv) {
+                VT v[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (b0 + q < nc) v[q] = __ldg(reinterpret_cast<const VT*>(s + (b0 + q) * D.s_cs) + av);
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (b0 + q < nc) {
+                        const T* e4 = reinterpret_cast<const T*>(&v[q]);
+#pragma unroll
+                        for (int e = 0; e < V; ++e) d[(av * V + e) * D.d_rs + (b0 + q) * D.d_cs] = e4[e];
+                    }
+            }
+            if (ca == 0) {
+                const i64 tail = nr - nrv * V;
+                for (i64 e = threadIdx.x; e < tail * 4; e += 256) {
+                    const i64 a = nrv * V + e % tail, b = b0 + e / tail;
+                    if (b < nc) d[a * D.d_rs + b * D.d_cs] = s[a + b * D.s_cs];
+                }
+            }
         }
         return;
     }
@@ -121,7 +201,7 @@ __global__ void __launch_bounds__(256) lattice_copy_kernel(const __grid_constant
         // general strides: thread index along a, 8 columns per pass
         const i64 chunks_a = (nr + 255) / 256;
         const i64 col_groups = (nc + 7) / 8;
-        for (i64 tile = blockIdx.x; tile < chunks_a * col_groups; tile += gridDim.x) {
+        for (i64 tile = bx; tile < chunks_a * col_groups; tile += gx) {
             const i64 a = (tile % chunks_a) * 256 + threadIdx.x;
             const i64 b0 = (tile / chunks_a) * 8;
             if (a < nr) {

@@ -232,7 +232,9 @@ sgemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
                     l.y = to_tf32_rna(v.y - h.y);
                     l.z = to_tf32_rna(v.z - h.z);
                     l.w = to_tf32_rna(v.w - h.w);
+#ifndef HYD_TC_NO_HI_WRITE
                     raw[i] = h;
+#endif
                     lo[i] = l;
                 }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the tensor core

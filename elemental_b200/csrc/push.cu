@@ -61,10 +61,11 @@ size_t push_grow(size_t bytes) {
 }
 
 int PushCore::open(int slot, const unsigned char* to, cudaStream_t s) {
-    const uint32_t r = ++round[slot];
-    if (r == 1) return 0;
+    ++round[slot];
+    const uint32_t prev = closed[slot];
+    if (prev == 0) return 0;
     for (int p = 0; p < size; ++p)
-        if (p != rank && to[p] && wait_geq(ctrl_local + ack_index(slot, p), r - 1, s, "push_open")) return 1;
+        if (p != rank && to[p] && wait_geq(ctrl_local + ack_index(slot, p), prev, s, "push_open")) return 1;
     return 0;
 }
 
@@ -106,7 +107,7 @@ int PushCore::wait(int slot, const unsigned char* from, cudaStream_t s) {
 int PushCore::close(int slot, cudaStream_t s) {
     SignalArgs a;
     a.n = 0;
-    a.value = round[slot];
+    a.value = closed[slot] = round[slot];
     for (int p = 0; p < size; ++p)
         if (p != rank) a.addr[a.n++] = ctrl_peer[p] + ack_index(slot, rank);
     if (a.n == 0) return 0;

@@ -9,6 +9,8 @@
 //   wait : wait  flag[q] >= r  for every q that stores into me     (cuStreamWaitValue32: no SM is held)
 //   unpack kernel reads my region
 //   close: one tiny kernel: ack[me] := r on every peer
+// A round may be split into chunks (disjoint parts of the region): pack, post, next, pack, post, ... with the
+// receiver waiting and unpacking chunk by chunk; every post carries a fresh flag value, only open/close touch acks.
 #pragma once
 #include "comm.h"
 #include <stdint.h>
@@ -23,12 +25,14 @@ struct PushCore {
     size_t region_cap[kPushSlots] = {};
     char* region_peer[kPushSlots][kPushMaxRanks] = {};    // peers' regions as mapped here (self = region_local)
     uint32_t round[kPushSlots] = {};
+    uint32_t closed[kPushSlots] = {};                     // round number of the last close (what the next open waits for)
 
     static size_t ctrl_bytes() { return sizeof(uint32_t) * 2 * kPushSlots * kPushMaxRanks; }
     static size_t flag_index(int slot, int r) { return (size_t)slot * kPushMaxRanks + r; }
     static size_t ack_index(int slot, int r) { return (size_t)(kPushSlots + slot) * kPushMaxRanks + r; }
 
     int open(int slot, const unsigned char* to, cudaStream_t s);
+    void next(int slot) { ++round[slot]; }             // next chunk of an open round: new flag value, same region, no ack wait
     int post(int slot, const unsigned char* to, cudaStream_t s);
     int post_ce(int slot, const unsigned char* to, cudaStream_t s);
     uint32_t* seq_scratch = nullptr;  // [kPushSlots] device words: round numbers staged for the 4-byte flag copies

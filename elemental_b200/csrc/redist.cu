@@ -110,7 +110,7 @@ int launch_copies(const std::vector<CopyDesc>& v, cudaStream_t s) {
         if (mx == 0) continue;
         const i64 want = (mx + 4095) / 4096;
         const i64 cap = std::max<i64>(1, (i64)num_sms() * 8 / b.n);
-        dim3 grid((unsigned)std::max<i64>(1, std::min(want, cap)), (unsigned)b.n);
+        dim3 grid((unsigned)(std::max<i64>(1, std::min(want, cap)) * b.n));
         lattice_copy_kernel<T><<<grid, 256, 0, s>>>(b);
         ++g_launches;
         if (check_cuda(cudaGetLastError(), "lattice_copy_kernel")) return 1;
@@ -257,37 +257,80 @@ int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot
 
     // pack (+ the local part straight from source lattice to destination lattice).  On the push path the pack
     // kernel's destinations are the peers' receive regions: packing and the NVLink transfer are one kernel.
+    // Large exchanges are split into K column chunks of every message: chunk q is unpacked on a side stream while
+    // chunk q+1 is still being pushed, so the (HBM-bound) unpack and local part hide under the (NVLink-bound) push.
+    int K = 1;
+    if (push && need >= ((i64)48 << 20) && g.world->push_chunks()) K = (int)std::min<i64>(8, need / ((i64)24 << 20));
+    auto chunk = [&](const Msg& m, int q, Msg& out) {  // columns [c0, c1) of message m
+        const i64 c0 = m.pb.count * q / K, c1 = m.pb.count * (q + 1) / K;
+        out = m;
+        out.pb.count = c1 - c0;
+        out.pb.src0 = m.pb.src0 + c0 * m.pb.srcStep;
+        out.pb.dst0 = m.pb.dst0 + c0 * m.pb.dstStep;
+        out.off = m.off + c0 * m.pa.count * (i64)sizeof(T);
+        return out.pb.count > 0;
+    };
+    cudaStream_t us = s;
+    if (K > 1) {
+        if (!g.unpack_stream) {
+            int lo, hi;
+            cudaDeviceGetStreamPriorityRange(&lo, &hi);
+            if (check_cuda(cudaStreamCreateWithPriority(&g.unpack_stream, cudaStreamNonBlocking, hi), "unpack stream")) return 1;
+            cudaEventCreateWithFlags(&g.ev_unpack_fork, cudaEventDisableTiming);
+            cudaEventCreateWithFlags(&g.ev_unpack_join, cudaEventDisableTiming);
+        }
+        us = g.unpack_stream;
+        if (check_cuda(cudaEventRecord(g.ev_unpack_fork, s), "unpack fork")) return 1;
+        cudaStreamWaitEvent(us, g.ev_unpack_fork, 0);
+    }
     std::vector<CopyDesc> descs;
     if (push && need > 0 && g.world->push_open(slot, to.data(), s)) return 1;
-    for (const Msg& m : sends)
-        descs.push_back(pack_desc<T>(src, transpose, m, push ? g.world->shared_peer(slot, m.peer) + m.off : send_base + m.off));
-    if (has_self) {
-        CopyDesc d = pack_desc<T>(src, transpose, self_msg, nullptr);
-        dst_lattice<T>(dst, self_msg, d.dst, d.d_rs, d.d_cs);
-        descs.push_back(d);
-    }
-    if (launch_copies<T>(descs, s)) return 1;
+    for (int q = 0; q < K; ++q) {
+        if (q > 0) g.world->push_next(slot);
+        descs.clear();
+        Msg c;
+        for (const Msg& m : sends)
+            if (chunk(m, q, c))
+                descs.push_back(pack_desc<T>(src, transpose, c, push ? g.world->shared_peer(slot, c.peer) + c.off : send_base + c.off));
+        if (has_self && chunk(self_msg, q, c)) {
+            CopyDesc d = pack_desc<T>(src, transpose, c, nullptr);
+            dst_lattice<T>(dst, c, d.dst, d.d_rs, d.d_cs);
+            descs.push_back(d);
+        }
+        {
+            ProfScope pk(g, Grid::PROF_PACK, s);
+            if (launch_copies<T>(descs, s)) return 1;
+        }
 
-    if (push) {
-        if (need > 0 && (g.world->push_post(slot, to.data(), s) || g.world->push_wait(slot, from.data(), s))) return 1;
-    } else if (!sends.empty() || !recvs.empty() || P > 1) {
-        std::vector<i64> sc(P, 0), so(P, 0), rc(P, 0), ro(P, 0);
-        for (const Msg& m : sends) { sc[m.peer] = m.count() * (i64)sizeof(T); so[m.peer] = m.off; }
-        for (const Msg& m : recvs) { rc[m.peer] = m.count() * (i64)sizeof(T); ro[m.peer] = m.off; }
-        if (g.world->exchange(send_base, sc.data(), so.data(), recv_base, rc.data(), ro.data(), s)) return 1;
+        if (push) {
+            if (need > 0 && (g.world->push_post(slot, to.data(), s) || g.world->push_wait(slot, from.data(), us))) return 1;
+        } else if (!sends.empty() || !recvs.empty() || P > 1) {
+            std::vector<i64> sc(P, 0), so(P, 0), rc(P, 0), ro(P, 0);
+            for (const Msg& m : sends) { sc[m.peer] = m.count() * (i64)sizeof(T); so[m.peer] = m.off; }
+            for (const Msg& m : recvs) { rc[m.peer] = m.count() * (i64)sizeof(T); ro[m.peer] = m.off; }
+            if (g.world->exchange(send_base, sc.data(), so.data(), recv_base, rc.data(), ro.data(), s)) return 1;
+        }
+        descs.clear();
+        for (const Msg& m : recvs) {
+            if (!chunk(m, q, c)) continue;
+            CopyDesc d;
+            d.src = recv_base + c.off;
+            d.s_rs = 1;
+            d.s_cs = c.pa.count;
+            dst_lattice<T>(dst, c, d.dst, d.d_rs, d.d_cs);
+            d.nr = c.pa.count;
+            d.nc = c.pb.count;
+            descs.push_back(d);
+        }
+        {
+            ProfScope pu(g, Grid::PROF_UNPACK, us);
+            if (launch_copies<T>(descs, us)) return 1;
+        }
     }
-    descs.clear();
-    for (const Msg& m : recvs) {
-        CopyDesc d;
-        d.src = recv_base + m.off;
-        d.s_rs = 1;
-        d.s_cs = m.pa.count;
-        dst_lattice<T>(dst, m, d.dst, d.d_rs, d.d_cs);
-        d.nr = m.pa.count;
-        d.nc = m.pb.count;
-        descs.push_back(d);
+    if (K > 1) {
+        if (check_cuda(cudaEventRecord(g.ev_unpack_join, us), "unpack join")) return 1;
+        cudaStreamWaitEvent(s, g.ev_unpack_join, 0);
     }
-    if (launch_copies<T>(descs, s)) return 1;
     if (push && need > 0) return g.world->push_close(slot, s);
     return 0;
 }
@@ -498,6 +541,9 @@ void grid_destroy(Grid* g) {
     }
     if (g->ev_fork) cudaEventDestroy(g->ev_fork);
     if (g->ev_join) cudaEventDestroy(g->ev_join);
+    if (g->unpack_stream) cudaStreamDestroy(g->unpack_stream);
+    if (g->ev_unpack_fork) cudaEventDestroy(g->ev_unpack_fork);
+    if (g->ev_unpack_join) cudaEventDestroy(g->ev_unpack_join);
     if (g->owns_world) delete g->world;
     delete g;
 }

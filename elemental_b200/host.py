@@ -140,7 +140,8 @@ class Grid:
         check(lib.hyd_grid_profile(self.h, int(enable)))
 
     def ProfileRead(self, kind=0):
-        """(launches, total device ms) of kind 0 = local GEMM, 1 = redistribution, 2 = reduce-scatter."""
+        """(launches, total device ms) of kind 0 = local GEMM, 1 = redistribution, 2 = reduce-scatter,
+        3 = pack (+ peer push) kernels, 4 = unpack kernels of redistributions."""
         n, ms = C.c_longlong(), C.c_double()
         check(lib.hyd_grid_profile_read(self.h, kind, C.byref(n), C.byref(ms)))
         return n.value, ms.value

@@ -127,7 +127,8 @@ int hyd_grid_vr_rank(const hyd_grid* g);
 int hyd_grid_set_overlap(hyd_grid* g, int overlap, int sm_reserve);
 
 /* per-kernel device timing: enable (also resets), then read launches and summed CUDA-event time of
- * kind 0 = local GEMM launches, 1 = redistributions, 2 = reduce-scatters issued through this grid. */
+ * kind 0 = local GEMM launches, 1 = redistributions, 2 = reduce-scatters issued through this grid,
+ * 3 = pack (+ peer push) kernel groups, 4 = unpack kernel groups inside the redistributions. */
 int hyd_grid_profile(hyd_grid* g, int enable);
 int hyd_grid_profile_read(hyd_grid* g, int kind, long long* launches, double* total_ms);
 

@@ -7,6 +7,7 @@ product path (hyd_redist_* / hyd_axpy_contract_* / hyd_gemm_* over NCCL send/rec
 with the oracle's: bit-exact for redistributions, tolerance for Gemm."""
 import itertools
 import os
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 import sys
 
 import numpy as np

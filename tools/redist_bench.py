@@ -5,6 +5,7 @@ GB/s = algorithmic HBM bytes per GPU (2 * local bytes) / device time 
 import ctypes as C
 import json
 import os
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 import sys
 
 import numpy as np
@@ -50,7 +51,17 @@ def main():
     st = torch.cuda.Stream()
     out = []
 
-    def report(name, ms, hbm_bytes, nvl_bytes=0):
+    def breakdown(f):
+        """one profiled call: (whole redistribution, pack+push kernels, unpack kernels) in ms on this rank"""
+        grid.Profile(True)
+        f()
+        st.synchronize()
+        r = [grid.ProfileRead(k)[1] for k in (1, 3, 4)]
+        grid.Profile(False)
+        return [round(x, 3) for x in r]
+
+    def report(name, ms, hbm_bytes, nvl_bytes=0, f=None):
+        bd = breakdown(f) if f is not None else None
         if rank == 0:
             gbs = hbm_bytes / ms / 1e6
             row = {"op": name, "n": n, "gpus": size, "ms": round(ms, 3), "hbm_GBps_per_gpu": round(gbs, 1), "frac_of_measured_hbm": round(gbs / HBM, 3)}
@@ -59,6 +70,8 @@ def main():
                 row["frac_of_770_nvlink"] = round(nvl_bytes / ms / 1e6 / 770.0, 3)
                 bound = max(hbm_bytes / HBM, nvl_bytes / 770.0) / 1e6
                 row["frac_of_roofline"] = round(bound / ms, 3)
+            if bd is not None:
+                row["rank0_ms_total_pack_unpack"] = bd
             print(json.dumps(row), flush=True)
             out.append(row)
 
@@ -84,11 +97,26 @@ def main():
                  ("Transpose [MC,MR] -> [MR,MC] (local transpose only)", (H.MR, H.MC), 1, 0),
                  ("Copy [MC,MR] -> [MR,MC] (TransposeDist)", (H.MR, H.MC), 0, loc * (1 - (1.0 / P if r != c else 1.0 / P))),
                  ("Transpose [MC,MR] -> [MC,MR]", (H.MC, H.MR), 1, loc * (1 - 1.0 / P))]
+        if size > 1:
+            # pure shift: every local block moves whole to the next grid column (contiguous 16-byte path on both sides):
+            # the raw peer-store rate of the push transport
+            Y = H.DistMatrix(grid, n, n, H.MC, H.MR, rowAlign=1)
+            report("[MC,MR] -> [MC,MR] rowAlign+1 (whole-block shift)", timeit(lambda: H.Copy(X, Y, stream=st), st, size), 2 * loc, loc, lambda: H.Copy(X, Y, stream=st))
+            del Y
         for name, (cd, rd), tr, nvl in cases:
             Y = H.DistMatrix(grid, n, n, cd, rd)
             f = (lambda: H.Transpose(X, Y, stream=st)) if tr else (lambda: H.Copy(X, Y, stream=st))
-            report(name, timeit(f, st, size), 2 * loc, nvl if size > 1 else 0)
-            del Y
+            report(name, timeit(f, st, size), 2 * loc, nvl if size > 1 else 0, f)
+            # size-independent parity property: the way back restores X bit for bit (chunk-pipelined path included)
+            Z = H.DistMatrix(grid, n, n, H.MC, H.MR)
+            Z.store.zero_()
+            (H.Transpose if tr else H.Copy)(Y, Z, stream=st)
+            st.synchronize()
+            ok = bool(torch.equal(Z.store[: Z.lw, : Z.lh], X.store[: X.lw, : X.lh]))
+            if not ok:
+                print(f"[rank {rank}] ROUND TRIP MISMATCH for {name}", flush=True)
+            assert ok, name
+            del Y, Z
         # SUMMA panel gathers at panel width nb (algorithmic HBM bytes: read local slice + write gathered panel)
         for nb in (128, 512, 2048):
             Ap = H.DistMatrix(grid, n, nb, H.MC, H.STAR)

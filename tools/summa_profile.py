@@ -1,6 +1,7 @@
 """Phase breakdown of the SUMMA engine under torchrun: Gemm time with overlap on/off, and the
 event-timed share of local GEMM launches vs redistributions (accurate with overlap off: one stream)."""
 import os
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 import sys
 
 import torch
