@@ -29,6 +29,7 @@ struct Grid {
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cudaStream_t unpack_stream = nullptr;           // chunk-pipelined redistributions: unpack of chunk q under the push of q+1
     cudaEvent_t ev_unpack_fork = nullptr, ev_unpack_join = nullptr;
+    cudaEvent_t ev_chunk[8] = {};                   // chunk q's own part has been packed
     std::vector<cudaEvent_t> upload_ev;  // per-panel H2D completion (hyd_gemm_host_*)
     Workspace panel[4];  // gathered panels (A/B x double buffer) or reduce temporaries
     Workspace host_stage[3];  // device images of host operands (hyd_gemm_host_*)

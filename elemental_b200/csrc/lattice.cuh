@@ -50,9 +50,11 @@ template <typename T> struct Vec16;
 template <> struct Vec16<double> { typedef double2 type; static constexpr int N = 2; };
 template <> struct Vec16<float> { typedef float4 type; static constexpr int N = 4; };
 
-// Tile: 32 x 32 elements through shared memory when the source is contiguous along b
-// and the destination along a (a transposing pack); otherwise straight copies with the
-// thread index along a, 16-byte vectors when both sides are contiguous and aligned.
+// Paths, by the four strides: (1) both sides contiguous along a: 16-byte vector copy; (2) destination contiguous
+// along a, source closer to contiguous along b (a transposing pack): (32 V) x 32 tile through shared memory,
+// 16-byte stores; (3) destination contiguous, source strided along a (cyclic pack): V gathered loads, one
+// 16-byte store; (4) source contiguous, destination strided (cyclic unpack): one 16-byte load, V stores;
+// (5) anything else: scalar, thread index along a.
 template <typename T>
 __global__ void __launch_bounds__(256) lattice_copy_kernel(const __grid_constant__ CopyBatch batch) {
     // descriptors are interleaved along the grid (block x serves descriptor x mod n) so that the NVLink-bound peer
@@ -98,33 +100,40 @@ __global__ void __launch_bounds__(256) lattice_copy_kernel(const __grid_constant
             return;
         }
     }
-    if (D.s_cs == 1 && D.d_rs == 1 && D.s_rs != 1) {
-        // transposing: read along b (source-contiguous), write along a (destination-contiguous).  The tile is staged
+    if (D.s_rs != 1 && D.s_cs < D.s_rs && (D.d_rs == 1 || D.d_rs < D.d_cs)) {
+        // transposing: read along b (where the source is contiguous or has the small cyclic stride; a-steps jump whole
+        // columns), write along a (destination-contiguous).  The tile is staged
         // transposed ([b][a], pitch TA + V) so the write phase is one 16-byte vector per thread (peer stores are
         // issued per request: see the gather path below); TA = 32 V-vectors of a, 32 columns of b.
-        constexpr int TA = 32 * V;
+        constexpr int NV = 2;            // 16-byte vectors of a per thread in the write phase
+        constexpr int TA = 32 * V * NV;  // 128 (fp64) / 256 (fp32) rows: 1 KiB contiguous destination runs
         __shared__ __align__(16) T tile_s[32][TA + V];
         const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
-        const bool vec_st = (D.d_cs % V == 0) && (((uintptr_t)d % 16) == 0);
+        const bool vec_st = (D.d_rs == 1) && (D.d_cs % V == 0) && (((uintptr_t)d % 16) == 0);
         const i64 ta = (nr + TA - 1) / TA, tb = (nc + 31) / 32;
         for (i64 tile = bx; tile < ta * tb; tile += gx) {
             const i64 a0 = (tile % ta) * TA, b0 = (tile / ta) * 32;
 #pragma unroll
             for (int q = 0; q < TA / 8; ++q) {
                 const i64 a = a0 + ty + 8 * q, b = b0 + tx;
-                if (a < nr && b < nc) tile_s[tx][ty + 8 * q] = s[a * D.s_rs + b];
+                if (a < nr && b < nc) tile_s[tx][ty + 8 * q] = s[a * D.s_rs + b * D.s_cs];
             }
             __syncthreads();
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-                const i64 a = a0 + (i64)tx * V, b = b0 + ty + 8 * q;
+                const i64 b = b0 + ty + 8 * q;
                 if (b < nc) {
-                    if (vec_st && a + V <= nr) {
-                        *reinterpret_cast<VT*>(d + a + b * D.d_cs) = *reinterpret_cast<const VT*>(&tile_s[ty + 8 * q][tx * V]);
-                    } else {
+                    if (vec_st && a0 + TA <= nr) {  // uniform per tile: the two branches map lanes to elements differently
 #pragma unroll
-                        for (int e = 0; e < V; ++e)
-                            if (a + e < nr) d[a + e + b * D.d_cs] = tile_s[ty + 8 * q][tx * V + e];
+                        for (int h = 0; h < NV; ++h)
+                            *reinterpret_cast<VT*>(d + a0 + (h * 32 + tx) * V + b * D.d_cs) =
+                                *reinterpret_cast<const VT*>(&tile_s[ty + 8 * q][(h * 32 + tx) * V]);
+                    } else {  // strided destination rows (the local part of a transposing copy) or a ragged edge
+#pragma unroll
+                        for (int e = 0; e < V * NV; ++e) {
+                            const i64 ae = a0 + e * 32 + tx;
+                            if (ae < nr) d[ae * D.d_rs + b * D.d_cs] = tile_s[ty + 8 * q][e * 32 + tx];
+                        }
                     }
                 }
             }
@@ -214,6 +223,70 @@ __global__ void __launch_bounds__(256) lattice_copy_kernel(const __grid_constant
                     if (b0 + q < nc) d[a * D.d_rs + (b0 + q) * D.d_cs] = v[q];
             }
         }
+    }
+}
+
+// Merged unpack.  When the S parts that make up a destination block interleave its ROWS (part k holds local rows
+// k, k+S, k+2S, ...: the element-cyclic case, e.g. two grid rows feeding a [*,VR] block, or a distributed
+// transpose), unpacking them one after the other writes every 32-byte sector S times, a quarter or half at a time,
+// and each pass is a read-modify-write in DRAM.  Here one pass writes full 16-byte vectors of consecutive
+// destination rows, fetching each element from the part that owns it (part k stored contiguously: element t of
+// column b at src[k][t + b*s_cs[k]]); across a warp every part is still read as contiguous runs.
+constexpr int kMaxMerge = 16;
+struct MergeDesc {
+    const void* src[kMaxMerge];
+    i64 s_cs[kMaxMerge];
+    void* dst;      // element (0, 0) of the destination block (rows contiguous)
+    i64 d_cs;
+    i64 nr, nc;     // rows of the whole block (all parts together), columns
+    int S;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(256) lattice_merge_kernel(const __grid_constant__ MergeDesc D) {
+    constexpr int V = Vec16<T>::N;
+    typedef typename Vec16<T>::type VT;
+    const i64 nr = D.nr, nc = D.nc;
+    const int S = D.S;
+    T* __restrict__ d = static_cast<T*>(D.dst);
+    const bool vec_ok = (D.d_cs % V == 0) && (((uintptr_t)d % 16) == 0);
+    const i64 nrv = (nr + V - 1) / V;
+    const i64 chunks_a = (nrv + 255) / 256;
+    constexpr int CP = 8;  // columns per pass: 8 x V independent loads per thread keep a quarter-occupancy grid near HBM speed
+    const i64 col_groups = (nc + CP - 1) / CP;
+    for (i64 tile = blockIdx.x; tile < chunks_a * col_groups; tile += gridDim.x) {
+        const i64 av = (tile % chunks_a) * 256 + threadIdx.x;
+        const i64 b0 = (tile / chunks_a) * CP;
+        if (av >= nrv) continue;
+        const i64 a = av * V;
+        const T* p[V];
+        i64 cs[V];
+#pragma unroll
+        for (int e = 0; e < V; ++e) {
+            const i64 ae = (a + e < nr) ? a + e : a;   // clamp: the value is not stored
+            const int k = (int)(ae % S);
+            p[e] = static_cast<const T*>(D.src[k]) + ae / S;
+            cs[e] = D.s_cs[k];
+        }
+        T v[CP][V];
+#pragma unroll
+        for (int q = 0; q < CP; ++q)
+            if (b0 + q < nc) {
+#pragma unroll
+                for (int e = 0; e < V; ++e) v[q][e] = __ldg(p[e] + (b0 + q) * cs[e]);
+            }
+#pragma unroll
+        for (int q = 0; q < CP; ++q)
+            if (b0 + q < nc) {
+                T* o = d + a + (b0 + q) * D.d_cs;
+                if (vec_ok && a + V <= nr) {
+                    *reinterpret_cast<VT*>(o) = *reinterpret_cast<const VT*>(v[q]);
+                } else {
+#pragma unroll
+                    for (int e = 0; e < V; ++e)
+                        if (a + e < nr) o[e] = v[q][e];
+                }
+            }
     }
 }
 

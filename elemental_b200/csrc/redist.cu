@@ -17,6 +17,7 @@
 // peer is one NVSwitch hop away; the transpose is folded into the pack.  The element
 // permutation is identical to the reference's, so results are bit-exact.
 #include "grid.h"
+#include <stdlib.h>
 #include "hyd_internal.h"
 #include "lattice.cuh"
 #include <algorithm>
@@ -100,8 +101,10 @@ void dst_lattice(const DM& dst, const Msg& m, void*& p, i64& rs, i64& cs) {
     cs = m.pb.dstStep * dst.ldim;
 }
 
+// ctas_per_sm: grid cap.  Chunk-pipelined exchanges run the pack (+ push) of chunk q+1 and the unpack of chunk q at
+// the same time; each gets half of the 4 resident CTAs per SM, so neither queues behind the other's grid.
 template <typename T>
-int launch_copies(const std::vector<CopyDesc>& v, cudaStream_t s) {
+int launch_copies(const std::vector<CopyDesc>& v, cudaStream_t s, int ctas_per_sm = 8) {
     for (size_t i0 = 0; i0 < v.size(); i0 += kMaxDesc) {
         CopyBatch b;
         b.n = (int)std::min((size_t)kMaxDesc, v.size() - i0);
@@ -109,7 +112,7 @@ int launch_copies(const std::vector<CopyDesc>& v, cudaStream_t s) {
         for (int i = 0; i < b.n; ++i) { b.d[i] = v[i0 + i]; mx = std::max(mx, b.d[i].nr * b.d[i].nc); }
         if (mx == 0) continue;
         const i64 want = (mx + 4095) / 4096;
-        const i64 cap = std::max<i64>(1, (i64)num_sms() * 8 / b.n);
+        const i64 cap = std::max<i64>(1, (i64)num_sms() * ctas_per_sm / b.n);
         dim3 grid((unsigned)(std::max<i64>(1, std::min(want, cap)) * b.n));
         lattice_copy_kernel<T><<<grid, 256, 0, s>>>(b);
         ++g_launches;
@@ -225,7 +228,7 @@ int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot
     char* send_base = nullptr;   // staged path only
     char* recv_base = nullptr;
     std::vector<unsigned char> to(P, 0), from(P, 0);
-    i64 need = 0;
+    i64 need = 0, self_off = 0;
     if (push) {
         // Receive-region layout at EVERY rank (senders in ascending rank order), computed identically everywhere,
         // so that each sender knows where its message lands and all ranks agree on the region size.
@@ -242,7 +245,11 @@ int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot
                 if (p == me) for (Msg& m : recvs) if (m.peer == q) m.off = run;
                 run = align16(run + bytes);
             }
-            need = std::max(need, run);
+            // room for p's own part behind its peers' messages (used by the merged unpack, see below)
+            Prog pa, pb;
+            progs(src, transpose, Ls[p], Ld[p], pa, pb);
+            if (p == me) self_off = run;
+            need = std::max(need, align16(run + pa.count * pb.count * (i64)sizeof(T)));
         }
         for (Msg& m : sends) { m.off = my_send_off[m.peer]; to[m.peer] = 1; }
         for (const Msg& m : recvs) from[m.peer] = 1;
@@ -270,6 +277,33 @@ int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot
         out.off = m.off + c0 * m.pa.count * (i64)sizeof(T);
         return out.pb.count > 0;
     };
+    // Merged unpack (lattice_merge_kernel): the parts of my destination block -- the received messages and my own
+    // part -- interleave its rows with period S = number of parts.  My own part is then packed like a message (into
+    // my receive region) and ONE pass writes the block in full vectors instead of S strided partial-sector passes.
+    std::vector<Msg> parts;
+    bool merge = false;
+    if (push && need > 0) {
+        parts = recvs;
+        if (has_self) { Msg m = self_msg; m.off = self_off; parts.push_back(m); }
+        const i64 S = (i64)parts.size();
+        if (S >= 2 && S <= kMaxMerge) {
+            merge = true;
+            i64 R = 0;
+            std::vector<char> seen(S, 0);
+            for (const Msg& m : parts) R += m.pa.count;
+            for (const Msg& m : parts) {
+                const Prog& b0 = parts[0].pb;
+                if (m.pa.dstStep != S || m.pa.dst0 < 0 || m.pa.dst0 >= S || seen[m.pa.dst0] || m.pb.count != b0.count ||
+                    m.pb.dst0 != b0.dst0 || m.pb.dstStep != b0.dstStep || m.pa.count != length_(R, m.pa.dst0, S)) {
+                    merge = false;
+                    break;
+                }
+                seen[m.pa.dst0] = 1;
+            }
+        }
+    }
+    static const int chunk_ctas = getenv("HYD_CHUNK_CTAS_PER_SM") ? std::max(1, atoi(getenv("HYD_CHUNK_CTAS_PER_SM"))) : 3;
+    const int per_sm = K > 1 ? chunk_ctas : 8;
     cudaStream_t us = s;
     if (K > 1) {
         if (!g.unpack_stream) {
@@ -278,6 +312,7 @@ int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot
             if (check_cuda(cudaStreamCreateWithPriority(&g.unpack_stream, cudaStreamNonBlocking, hi), "unpack stream")) return 1;
             cudaEventCreateWithFlags(&g.ev_unpack_fork, cudaEventDisableTiming);
             cudaEventCreateWithFlags(&g.ev_unpack_join, cudaEventDisableTiming);
+            for (cudaEvent_t& e : g.ev_chunk) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
         }
         us = g.unpack_stream;
         if (check_cuda(cudaEventRecord(g.ev_unpack_fork, s), "unpack fork")) return 1;
@@ -292,14 +327,18 @@ int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot
         for (const Msg& m : sends)
             if (chunk(m, q, c))
                 descs.push_back(pack_desc<T>(src, transpose, c, push ? g.world->shared_peer(slot, c.peer) + c.off : send_base + c.off));
-        if (has_self && chunk(self_msg, q, c)) {
+        if (has_self && merge) {
+            Msg m = self_msg;
+            m.off = self_off;
+            if (chunk(m, q, c)) descs.push_back(pack_desc<T>(src, transpose, c, recv_base + c.off));
+        } else if (has_self && chunk(self_msg, q, c)) {
             CopyDesc d = pack_desc<T>(src, transpose, c, nullptr);
             dst_lattice<T>(dst, c, d.dst, d.d_rs, d.d_cs);
             descs.push_back(d);
         }
         {
             ProfScope pk(g, Grid::PROF_PACK, s);
-            if (launch_copies<T>(descs, s)) return 1;
+            if (launch_copies<T>(descs, s, per_sm)) return 1;
         }
 
         if (push) {
@@ -309,6 +348,35 @@ int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot
             for (const Msg& m : sends) { sc[m.peer] = m.count() * (i64)sizeof(T); so[m.peer] = m.off; }
             for (const Msg& m : recvs) { rc[m.peer] = m.count() * (i64)sizeof(T); ro[m.peer] = m.off; }
             if (g.world->exchange(send_base, sc.data(), so.data(), recv_base, rc.data(), ro.data(), s)) return 1;
+        }
+        if (merge) {
+            if (us != s) {  // my own part of this chunk was packed on s
+                if (check_cuda(cudaEventRecord(g.ev_chunk[q], s), "chunk event")) return 1;
+                cudaStreamWaitEvent(us, g.ev_chunk[q], 0);
+            }
+            MergeDesc md;
+            md.S = (int)parts.size();
+            md.nr = 0;
+            md.nc = 0;
+            for (const Msg& m : parts) {
+                md.nr += m.pa.count;
+                if (!chunk(m, q, c)) continue;
+                md.src[m.pa.dst0] = recv_base + c.off;
+                md.s_cs[m.pa.dst0] = c.pa.count;
+                md.nc = c.pb.count;
+                md.dst = static_cast<T*>(dst.buf) + c.pb.dst0 * dst.ldim;
+                md.d_cs = c.pb.dstStep * dst.ldim;
+            }
+            if (md.nc > 0 && md.nr > 0) {
+                ProfScope pu(g, Grid::PROF_UNPACK, us);
+                const i64 V = 16 / (i64)sizeof(T);
+                const i64 want = ((md.nr + V - 1) / V + 255) / 256 * ((md.nc + 7) / 8);
+                const unsigned grid = (unsigned)std::max<i64>(1, std::min<i64>(want, (i64)num_sms() * per_sm));
+                lattice_merge_kernel<T><<<grid, 256, 0, us>>>(md);
+                ++g_launches;
+                if (check_cuda(cudaGetLastError(), "lattice_merge_kernel")) return 1;
+            }
+            continue;
         }
         descs.clear();
         for (const Msg& m : recvs) {
@@ -324,7 +392,7 @@ int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot
         }
         {
             ProfScope pu(g, Grid::PROF_UNPACK, us);
-            if (launch_copies<T>(descs, us)) return 1;
+            if (launch_copies<T>(descs, us, per_sm)) return 1;
         }
     }
     if (K > 1) {
@@ -544,6 +612,7 @@ void grid_destroy(Grid* g) {
     if (g->unpack_stream) cudaStreamDestroy(g->unpack_stream);
     if (g->ev_unpack_fork) cudaEventDestroy(g->ev_unpack_fork);
     if (g->ev_unpack_join) cudaEventDestroy(g->ev_unpack_join);
+    for (cudaEvent_t e : g->ev_chunk) if (e) cudaEventDestroy(e);
     if (g->owns_world) delete g->world;
     delete g;
 }
