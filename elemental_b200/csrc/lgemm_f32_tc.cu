@@ -14,7 +14,7 @@
 //
 // Structure (one persistent CTA per SM, warp-specialised, three pipelines):
 //   warp 0        TMA producer: raw fp32 tiles of A and B -> shared memory ring (cp.async.bulk.tensor, swizzled)
-//   warps 8-11    splitters: raw tile -> hi (in place) and lo (second buffer), same swizzled byte positions,
+//   warps 8-11    splitters: raw tile (= hi: the MMA ignores the low 13 bits) -> lo (second buffer), same swizzled byte positions,
 //                 fence.proxy.async, then hand the stage to the MMA warp
 //   warp 1        MMA issuer (one elected lane): per k-step three tcgen05.mma.kind::tf32 into a TMEM accumulator,
 //                 tcgen05.commit releases the stage / publishes the accumulator
@@ -23,6 +23,7 @@
 //   warp 2        TMEM allocator
 #include "ptx.cuh"
 #include "hyd_internal.h"
+#include <algorithm>
 #include <stdlib.h>
 #include <string.h>
 
@@ -232,9 +233,10 @@ sgemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
                     l.y = to_tf32_rna(v.y - h.y);
                     l.z = to_tf32_rna(v.z - h.z);
                     l.w = to_tf32_rna(v.w - h.w);
-#ifndef HYD_TC_NO_HI_WRITE
-                    raw[i] = h;
-#endif
+                    // hi is NOT written back: kind::tf32 reads the upper 19 bits of each 32-bit container and ignores the
+                    // low 13 mantissa bits, so the raw fp32 tile already is the hi operand (bit-identical results with
+                    // and without the store on B200; a rounding tensor core would fail the parity tests at 2^-11).
+                    // Saves a third of the splitters' shared-memory traffic, the kernel's limiter (+5 %).
                     lo[i] = l;
                 }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the tensor core
@@ -348,7 +350,14 @@ int lgemm_f32_tc(int tA, int tB, long long m, long long n, long long k, float al
         mode_env = !e ? -1 : (!strcmp(e, "ffma") ? 0 : (!strcmp(e, "tc256") ? 256 : (!strcmp(e, "tc128") ? 128 : -1)));
     }
     if (mode_env == 0) return -1;
-    const int mode = mode_env > 0 ? mode_env : (n >= 192 ? 256 : 128);
+    // tile choice by estimated time: waves of the persistent grid x tile area, the 128x256 tile being ~15 % faster per
+    // flop when the grid is full (fewer A re-reads per MMA); tall-skinny shapes quantise badly with it
+    auto waves_cost = [&](int bn, double speed) {
+        const long long tiles = ((m + BM - 1) / BM) * ((n + bn - 1) / bn);
+        const long long ctas = std::max(1, num_sms() - sm_reserve);
+        return (double)((tiles + ctas - 1) / ctas) * bn / speed;
+    };
+    const int mode = mode_env > 0 ? mode_env : ((n >= 192 && waves_cost(256, 1.15) <= waves_cost(128, 1.0)) ? 256 : 128);
     if (m < 128 || n < 64 || k < 32 || m * n < 128LL * 128 * 8) return -1;             // too small to fill the machine
     if (((uintptr_t)A % 16) || ((uintptr_t)B % 16) || (lda % 4) || (ldb % 4)) return -1;  // TMA needs 16-byte strides
     const int typeA = tA ? KT : MT, typeB = tB ? MT : KT;

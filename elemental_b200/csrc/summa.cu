@@ -368,16 +368,16 @@ int summa_b(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
 // ---- SUMMA-Dot: k distributed over all P ranks, P-wide reduce per C tile ----
 template <typename T>
 int summa_dot(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, const DM& B, const DM& C,
-              i64 blockSize, cudaStream_t s) {
+              i64 blockM, i64 blockN, cudaStream_t s) {
     const GridShape& sh = g.shape;
     const int es = sizeof(T);
     // operands must be  A: [*,VC] (N) / [VC,*] (T),  B: [VC,*] (N) / [*,VC] (T), B aligned to A (proxy, Proxy.hpp:160-260)
     const LocalShape La = local_shape(sh, A, g.mc, g.mr);
     const i64 kloc = oA ? La.lh : La.lw;
-    for (i64 i0 = 0; i0 < m; i0 += blockSize) {
-        const i64 mb = std::min(blockSize, m - i0);
-        for (i64 j0 = 0; j0 < n; j0 += blockSize) {
-            const i64 nbk = std::min(blockSize, n - j0);
+    for (i64 i0 = 0; i0 < m; i0 += blockM) {
+        const i64 mb = std::min(blockM, m - i0);
+        for (i64 j0 = 0; j0 < n; j0 += blockN) {
+            const i64 nbk = std::min(blockN, n - j0);
             DM C11;
             if (make_tmp<T>(g, g.panel[0], mb, nbk, STAR, STAR, 0, 0, C11)) return 1;
             const T* a = static_cast<const T*>(A.buf) + (oA ? i0 * A.ldim : i0);
@@ -464,7 +464,12 @@ int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A0, const DM&
         const int kalign = oA ? A.colAlign : A.rowAlign;
         if (oB) { if (read_proxy<T>(g, pool, B0, STAR, VC, false, 0, true, kalign, B, s)) return 1; }
         else    { if (read_proxy<T>(g, pool, B0, VC, STAR, true, kalign, false, 0, B, s)) return 1; }
-        rc = summa_dot<T>(g, oA, oB, m, n, k, alpha, A, B, C, 2000, s);
+        // tile of C reduced at a time.  The reference's default is 2000 x 2000 (NN.hpp SUMMA_NNDot blockSize) to bound the
+        // [*,*] temporary; a 2000-row tile of a tall-skinny C leaves most SMs idle, so the tile grows until the
+        // temporary reaches 256 MiB (180 GB of HBM): m=16384, n=512 is one tile
+        const i64 bn = std::min<i64>(n, 8192);
+        const i64 bm = std::max<i64>(2000, ((i64)256 << 20) / (bn * (i64)sizeof(T)));
+        rc = summa_dot<T>(g, oA, oB, m, n, k, alpha, A, B, C, bm, bn, s);
     } else {
         if (read_proxy<T>(g, pool, A0, MC, MR, false, 0, false, 0, A, s)) return 1;
         if (read_proxy<T>(g, pool, B0, MC, MR, false, 0, false, 0, B, s)) return 1;
