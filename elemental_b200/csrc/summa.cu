@@ -468,7 +468,9 @@ int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A0, const DM&
         // [*,*] temporary; a 2000-row tile of a tall-skinny C leaves most SMs idle, so the tile grows until the
         // temporary reaches 256 MiB (180 GB of HBM): m=16384, n=512 is one tile
         const i64 bn = std::min<i64>(n, 8192);
-        const i64 bm = std::max<i64>(2000, ((i64)256 << 20) / (bn * (i64)sizeof(T)));
+        const char* tb = getenv("HYD_DOT_TILE_BYTES");   // bound of the [*,*] temporary (tests shrink it to cover the tile loops)
+        const i64 tile_bytes = tb ? std::max<i64>(1, atoll(tb)) : ((i64)256 << 20);
+        const i64 bm = std::max<i64>(2000, tile_bytes / (bn * (i64)sizeof(T)));
         rc = summa_dot<T>(g, oA, oB, m, n, k, alpha, A, B, C, bm, bn, s);
     } else {
         if (read_proxy<T>(g, pool, A0, MC, MR, false, 0, false, 0, A, s)) return 1;

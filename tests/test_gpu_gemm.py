@@ -83,8 +83,9 @@ def test_gemm_basicgemm_config(r, c):
     _run_cases(r, c, cases[1:], np.float32)
 
 
-def test_gemm_default_heuristic_and_dot_operands():
+def test_gemm_default_heuristic_and_dot_operands(monkeypatch):
     """GEMM_DEFAULT picks Dot/B/A/C by shape (NN.hpp:910-925); [*,VC] operands pass the proxies untouched (config 5)."""
+    monkeypatch.setenv("HYD_DOT_TILE_BYTES", "1")  # reference tile (2000 rows): the m=2100 case covers two tiles
     r, c = 2, 2
     rng = np.random.default_rng(9)
     cases = [
@@ -139,3 +140,42 @@ def test_gemm_over_staged_transport(monkeypatch):
     for rank-threads is the push transport with panels written directly into the readers' buffers."""
     monkeypatch.setenv("HYD_TRANSPORT", "staged")
     test_gemm_all_variants(2, 4, np.float64)
+
+
+def _associativity(grid, dtype, oA, oB, n, nb, alpha, beta, seed):
+    """The reference's own Gemm test (tests/blas_like/Gemm.cpp:27-61, TestAssociativity):
+    (alpha op(A) op(B) + beta C) X  ==  alpha op(A) (op(B) X) + beta C X   for 100 random right-hand sides.
+    Returns this rank's (||E||_F^2, ||Y||_F^2)."""
+    tdt = torch.float64 if dtype == np.float64 else torch.float32
+    gen = torch.Generator(device="cuda").manual_seed(seed + 31 * grid.Rank())
+    mk = lambda h, w: H.DistMatrix(grid, h, w, H.MC, H.MR, dtype=dtype)
+    A, B, C0, Cf = mk(n, n), mk(n, n), mk(n, n), mk(n, n)
+    X, Y, Z = mk(n, 100), mk(n, 100), mk(n, 100)
+    for d in (A, B, C0, X):
+        d.store.copy_(torch.rand(d.store.shape, dtype=tdt, device="cuda", generator=gen) * 2 - 1)
+    Cf.store.copy_(C0.store)
+    H.Gemm(oA, oB, alpha, A, B, beta, Cf, H.GEMM_SUMMA_C, blocksize=nb)        # the Gemm under test
+    H.Gemm(oB, H.NORMAL, 1.0, B, X, 0.0, Z, blocksize=nb)
+    H.Gemm(oA, H.NORMAL, alpha, A, Z, 0.0, Y, blocksize=nb)
+    H.Gemm(H.NORMAL, H.NORMAL, beta, C0, X, 1.0, Y, blocksize=nb)
+    torch.cuda.current_stream().synchronize()
+    y2 = float((Y.store[: Y.lw, : Y.lh].double() ** 2).sum())
+    H.Gemm(H.NORMAL, H.NORMAL, -1.0, Cf, X, 1.0, Y, blocksize=nb)
+    torch.cuda.current_stream().synchronize()
+    e2 = float((Y.store[: Y.lw, : Y.lh].double() ** 2).sum())
+    return e2, y2
+
+
+@pytest.mark.parametrize("r,c,n,dtype,oA,oB", [(1, 1, 16384, np.float64, 0, 0),     # BASELINE.json configs[1] size, one GPU
+                                               (2, 4, 8192, np.float64, 0, 0),      # the 2x4 grid of configs[1] (rank-threads)
+                                               (2, 2, 8192, np.float32, 1, 0),      # configs[2] orientations
+                                               (2, 2, 8192, np.float32, 0, 1)])
+def test_gemm_associativity_at_scale(r, c, n, dtype, oA, oB):
+    """Size-independent parity property at (or near) the benchmark sizes, where the oracle is too slow:
+    ||E||_F / ||Y||_F <= tol * sqrt(k), tol = 1e-13 (fp64) / 1e-5 (fp32) as in BASELINE.json."""
+    out = H.run_ranks(r * c, lambda grid: _associativity(grid, dtype, oA, oB, n, 1024, 2.0, 3.0, 7), height=r)
+    e2 = sum(o[0] for o in out)
+    y2 = sum(o[1] for o in out)
+    rel = (e2 / y2) ** 0.5
+    tol = (1e-13 if dtype == np.float64 else 1e-5) * n ** 0.5
+    assert rel <= tol, (rel, tol)
