@@ -92,6 +92,27 @@ _sig("hyd_gemm_f32", i32, [vp, i32, i32, i32, f32, dmp, dmp, f32, dmp, i64, vp])
 _sig("hyd_gemm_host_f64", i32, [vp, i32, i32, i32, f64, dmp, dmp, f64, dmp, i64, vp])
 _sig("hyd_gemm_host_f32", i32, [vp, i32, i32, i32, f32, dmp, dmp, f32, dmp, i64, vp])
 _sig("hyd_probe_peak", i32, [i32, i32, i32, C.POINTER(f64)])
+# seam S2: copy::util pack / unpack and axpy::util::InterleaveMatrixUpdate with the reference's argument lists
+for _sf, _ft in (("f64", f64), ("f32", f32)):
+    _sig("hyd_interleave_" + _sf, i32, [i64, i64, vp, i64, i64, vp, i64, i64, vp])
+    _sig("hyd_interleave_update_" + _sf, i32, [_ft, i64, i64, vp, i64, i64, vp, i64, i64, vp])
+    for _n in ("row", "col"):
+        _sig(f"hyd_{_n}_strided_pack_{_sf}", i32, [i64, i64, i64, i64, vp, i64, vp, i64, vp])
+        _sig(f"hyd_{_n}_strided_unpack_{_sf}", i32, [i64, i64, i64, i64, vp, i64, vp, i64, vp])
+        _sig(f"hyd_partial_{_n}_strided_pack_{_sf}", i32, [i64] * 8 + [vp, i64, vp, i64, vp])
+        _sig(f"hyd_partial_{_n}_strided_unpack_{_sf}", i32, [i64] * 8 + [vp, i64, vp, i64, vp])
+    _sig("hyd_strided_pack_" + _sf, i32, [i64] * 6 + [vp, i64, vp, i64, vp])
+    _sig("hyd_strided_unpack_" + _sf, i32, [i64] * 6 + [vp, i64, vp, i64, vp])
+# seam S2: collectives on the grid's sub-communicators
+for _n in ("hyd_comm_size", "hyd_comm_rank"):
+    _sig(_n, i32, [vp, i32])
+_sig("hyd_comm_world_rank", i32, [vp, i32, i32])
+_sig("hyd_allgather", i32, [vp, i32, vp, i64, vp, vp])
+_sig("hyd_alltoall", i32, [vp, i32, vp, i64, vp, vp])
+_sig("hyd_sendrecv", i32, [vp, i32, vp, i64, i32, vp, i64, i32, vp])
+_sig("hyd_bcast", i32, [vp, i32, vp, i64, i32, vp])
+_sig("hyd_reducescatter_f64", i32, [vp, i32, vp, vp, i64, vp])
+_sig("hyd_reducescatter_f32", i32, [vp, i32, vp, vp, i64, vp])
 
 # every symbol include/hydrogen_b200.h declares (tests/test_abi.py checks the header against this list)
 EXPORTS = sorted(n for n in dir(lib) if n.startswith("hyd_"))

@@ -43,6 +43,13 @@ def PopBlocksizeStack():
     _blocksize_stack.pop()
 
 
+COMM_MC, COMM_MR, COMM_VC, COMM_VR = range(4)  # Grid::MCComm() (my grid column), MRComm() (my grid row), VCComm(), VRComm()
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr())
+
+
 def _stream_ptr(stream=None):
     s = stream if stream is not None else torch.cuda.current_stream()
     return C.c_void_p(s.cuda_stream)
@@ -145,6 +152,31 @@ class Grid:
         n, ms = C.c_longlong(), C.c_double()
         check(lib.hyd_grid_profile_read(self.h, kind, C.byref(n), C.byref(ms)))
         return n.value, ms.value
+
+    # -- sub-communicators and the typed collectives on them (mpi::AllGather ... on Grid::MCComm() etc.; seam S2)
+    def CommSize(self, comm): return lib.hyd_comm_size(self.h, comm)
+    def CommRank(self, comm): return lib.hyd_comm_rank(self.h, comm)
+    def CommWorldRank(self, comm, k): return lib.hyd_comm_world_rank(self.h, comm, k)
+
+    def AllGather(self, comm, sbuf, rbuf, stream=None):
+        """mpi::AllGather(sbuf, sc, rbuf, rc, comm, syncInfo): member k's sbuf lands at rbuf[k*sc:(k+1)*sc]."""
+        check(lib.hyd_allgather(self.h, comm, _ptr(sbuf), sbuf.numel() * sbuf.element_size(), _ptr(rbuf), _stream_ptr(stream)))
+
+    def AllToAll(self, comm, sbuf, rbuf, stream=None):
+        n = sbuf.numel() * sbuf.element_size() // max(1, self.CommSize(comm))
+        check(lib.hyd_alltoall(self.h, comm, _ptr(sbuf), n, _ptr(rbuf), _stream_ptr(stream)))
+
+    def SendRecv(self, comm, sbuf, to, rbuf, frm, stream=None):
+        check(lib.hyd_sendrecv(self.h, comm, _ptr(sbuf), sbuf.numel() * sbuf.element_size(), to, _ptr(rbuf),
+                               rbuf.numel() * rbuf.element_size(), frm, _stream_ptr(stream)))
+
+    def Broadcast(self, comm, buf, root, stream=None):
+        check(lib.hyd_bcast(self.h, comm, _ptr(buf), buf.numel() * buf.element_size(), root, _stream_ptr(stream)))
+
+    def ReduceScatter(self, comm, sbuf, rbuf, stream=None):
+        """mpi::ReduceScatter(sbuf, rbuf, rc, comm, syncInfo): rbuf = sum over members of their block [me*rc:(me+1)*rc]."""
+        fn = lib.hyd_reducescatter_f64 if sbuf.dtype == torch.float64 else lib.hyd_reducescatter_f32
+        check(fn(self.h, comm, _ptr(sbuf), _ptr(rbuf), rbuf.numel(), _stream_ptr(stream)))
 
     def destroy(self):
         if self.h:

@@ -103,9 +103,48 @@ public:
     int VCSize() const { return Size(); }
     int VRSize() const { return Size(); }
     hyd_grid* handle() const { return g_; }
+    // sub-communicators (Grid.hpp:31-54): a (grid, kind) pair -- every member is one NVSwitch hop away, there is no
+    // communicator object to create.  ColComm == MCComm (my grid column), RowComm == MRComm (my grid row).
+    struct Comm {
+        hyd_grid* g; int kind;
+        int Size() const { return hyd_comm_size(g, kind); }
+        int Rank() const { return hyd_comm_rank(g, kind); }
+    };
+    Comm MCComm() const { return Comm{g_, HYD_COMM_MC}; }
+    Comm MRComm() const { return Comm{g_, HYD_COMM_MR}; }
+    Comm VCComm() const { return Comm{g_, HYD_COMM_VC}; }
+    Comm VRComm() const { return Comm{g_, HYD_COMM_VR}; }
+    Comm ColComm() const { return MCComm(); }
+    Comm RowComm() const { return MRComm(); }
 private:
     hyd_grid* g_ = nullptr;
 };
+
+// ---- typed collectives on device buffers (src/core/imports/mpi/*.hpp, Device::GPU overloads): counts in elements ----
+namespace mpi {
+template <typename T>
+void AllGather(const T* sbuf, Int sc, T* rbuf, Int /*rc*/, const Grid::Comm& comm, const SyncInfoGPU& si) {
+    detail::check(hyd_allgather(comm.g, comm.kind, sbuf, sc * (Int)sizeof(T), rbuf, si.stream_));
+}
+template <typename T>
+void AllToAll(const T* sbuf, Int sc, T* rbuf, Int /*rc*/, const Grid::Comm& comm, const SyncInfoGPU& si) {
+    detail::check(hyd_alltoall(comm.g, comm.kind, sbuf, sc * (Int)sizeof(T), rbuf, si.stream_));
+}
+template <typename T>
+void SendRecv(const T* sbuf, Int sc, int to, T* rbuf, Int rc, int from, const Grid::Comm& comm, const SyncInfoGPU& si) {
+    detail::check(hyd_sendrecv(comm.g, comm.kind, sbuf, sc * (Int)sizeof(T), to, rbuf, rc * (Int)sizeof(T), from, si.stream_));
+}
+template <typename T>
+void Broadcast(T* buf, Int count, int root, const Grid::Comm& comm, const SyncInfoGPU& si) {
+    detail::check(hyd_bcast(comm.g, comm.kind, buf, count * (Int)sizeof(T), root, si.stream_));
+}
+inline void ReduceScatter(const double* sbuf, double* rbuf, Int rc, const Grid::Comm& comm, const SyncInfoGPU& si) {
+    detail::check(hyd_reducescatter_f64(comm.g, comm.kind, sbuf, rbuf, rc, si.stream_));
+}
+inline void ReduceScatter(const float* sbuf, float* rbuf, Int rc, const Grid::Comm& comm, const SyncInfoGPU& si) {
+    detail::check(hyd_reducescatter_f32(comm.g, comm.kind, sbuf, rbuf, rc, si.stream_));
+}
+}  // namespace mpi
 
 namespace detail {
 template <> struct Sfx<double> {
@@ -113,12 +152,44 @@ template <> struct Sfx<double> {
     static int contract(hyd_grid* g, double al, const hyd_dm* a, const hyd_dm* b, int t, void* s) { return hyd_axpy_contract_f64(g, al, a, b, t, s); }
     static int gemm(hyd_grid* g, int oA, int oB, int alg, double al, const hyd_dm* A, const hyd_dm* B, double be, const hyd_dm* C, int64_t nb, void* s) { return hyd_gemm_f64(g, oA, oB, alg, al, A, B, be, C, nb, s); }
     static int lgemm(int tA, int tB, int64_t m, int64_t n, int64_t k, double al, const double* A, int64_t lda, const double* B, int64_t ldb, double be, double* C, int64_t ldc, void* s) { return hyd_lgemm_f64(tA, tB, m, n, k, al, A, lda, B, ldb, be, C, ldc, s); }
+    static int transpose(int64_t m, int64_t n, const double* A, int64_t lda, double* B, int64_t ldb, void* s) { return hyd_transpose_f64(m, n, A, lda, B, ldb, s); }
+    static int copy2d(int64_t m, int64_t n, const double* A, int64_t lda, double* B, int64_t ldb, void* s) { return hyd_copy2d_f64(m, n, A, lda, B, ldb, s); }
+    static int axpy2d(int64_t m, int64_t n, double al, const double* A, int64_t lda, double* B, int64_t ldb, void* s) { return hyd_axpy2d_f64(m, n, al, A, lda, B, ldb, s); }
+    static int scale2d(int64_t m, int64_t n, double al, double* A, int64_t lda, void* s) { return hyd_scale2d_f64(m, n, al, A, lda, s); }
+    static int interleave(int64_t h, int64_t w, const double* A, int64_t csA, int64_t rsA, double* B, int64_t csB, int64_t rsB, void* s) { return hyd_interleave_f64(h, w, A, csA, rsA, B, csB, rsB, s); }
+    static int interleave_update(double al, int64_t h, int64_t w, const double* A, int64_t csA, int64_t rsA, double* B, int64_t csB, int64_t rsB, void* s) { return hyd_interleave_update_f64(al, h, w, A, csA, rsA, B, csB, rsB, s); }
+    static int row_pack(int64_t h, int64_t w, int64_t al, int64_t st, const double* A, int64_t ld, double* P, int64_t ps, void* s) { return hyd_row_strided_pack_f64(h, w, al, st, A, ld, P, ps, s); }
+    static int row_unpack(int64_t h, int64_t w, int64_t al, int64_t st, const double* P, int64_t ps, double* B, int64_t ld, void* s) { return hyd_row_strided_unpack_f64(h, w, al, st, P, ps, B, ld, s); }
+    static int col_pack(int64_t h, int64_t w, int64_t al, int64_t st, const double* A, int64_t ld, double* P, int64_t ps, void* s) { return hyd_col_strided_pack_f64(h, w, al, st, A, ld, P, ps, s); }
+    static int col_unpack(int64_t h, int64_t w, int64_t al, int64_t st, const double* P, int64_t ps, double* B, int64_t ld, void* s) { return hyd_col_strided_unpack_f64(h, w, al, st, P, ps, B, ld, s); }
+    static int prow_pack(int64_t h, int64_t w, int64_t al, int64_t st, int64_t un, int64_t pt, int64_t rp, int64_t sh, const double* A, int64_t ld, double* P, int64_t ps, void* s) { return hyd_partial_row_strided_pack_f64(h, w, al, st, un, pt, rp, sh, A, ld, P, ps, s); }
+    static int prow_unpack(int64_t h, int64_t w, int64_t al, int64_t st, int64_t un, int64_t pt, int64_t rp, int64_t sh, const double* P, int64_t ps, double* B, int64_t ld, void* s) { return hyd_partial_row_strided_unpack_f64(h, w, al, st, un, pt, rp, sh, P, ps, B, ld, s); }
+    static int pcol_pack(int64_t h, int64_t w, int64_t al, int64_t st, int64_t un, int64_t pt, int64_t rp, int64_t sh, const double* A, int64_t ld, double* P, int64_t ps, void* s) { return hyd_partial_col_strided_pack_f64(h, w, al, st, un, pt, rp, sh, A, ld, P, ps, s); }
+    static int pcol_unpack(int64_t h, int64_t w, int64_t al, int64_t st, int64_t un, int64_t pt, int64_t rp, int64_t sh, const double* P, int64_t ps, double* B, int64_t ld, void* s) { return hyd_partial_col_strided_unpack_f64(h, w, al, st, un, pt, rp, sh, P, ps, B, ld, s); }
+    static int pack2d(int64_t h, int64_t w, int64_t ca, int64_t cs, int64_t ra, int64_t rs, const double* A, int64_t ld, double* P, int64_t ps, void* s) { return hyd_strided_pack_f64(h, w, ca, cs, ra, rs, A, ld, P, ps, s); }
+    static int unpack2d(int64_t h, int64_t w, int64_t ca, int64_t cs, int64_t ra, int64_t rs, const double* P, int64_t ps, double* B, int64_t ld, void* s) { return hyd_strided_unpack_f64(h, w, ca, cs, ra, rs, P, ps, B, ld, s); }
 };
 template <> struct Sfx<float> {
     static int redist(hyd_grid* g, const hyd_dm* a, const hyd_dm* b, int t, void* s) { return hyd_redist_f32(g, a, b, t, s); }
     static int contract(hyd_grid* g, float al, const hyd_dm* a, const hyd_dm* b, int t, void* s) { return hyd_axpy_contract_f32(g, al, a, b, t, s); }
     static int gemm(hyd_grid* g, int oA, int oB, int alg, float al, const hyd_dm* A, const hyd_dm* B, float be, const hyd_dm* C, int64_t nb, void* s) { return hyd_gemm_f32(g, oA, oB, alg, al, A, B, be, C, nb, s); }
     static int lgemm(int tA, int tB, int64_t m, int64_t n, int64_t k, float al, const float* A, int64_t lda, const float* B, int64_t ldb, float be, float* C, int64_t ldc, void* s) { return hyd_lgemm_f32(tA, tB, m, n, k, al, A, lda, B, ldb, be, C, ldc, s); }
+    static int transpose(int64_t m, int64_t n, const float* A, int64_t lda, float* B, int64_t ldb, void* s) { return hyd_transpose_f32(m, n, A, lda, B, ldb, s); }
+    static int copy2d(int64_t m, int64_t n, const float* A, int64_t lda, float* B, int64_t ldb, void* s) { return hyd_copy2d_f32(m, n, A, lda, B, ldb, s); }
+    static int axpy2d(int64_t m, int64_t n, float al, const float* A, int64_t lda, float* B, int64_t ldb, void* s) { return hyd_axpy2d_f32(m, n, al, A, lda, B, ldb, s); }
+    static int scale2d(int64_t m, int64_t n, float al, float* A, int64_t lda, void* s) { return hyd_scale2d_f32(m, n, al, A, lda, s); }
+    static int interleave(int64_t h, int64_t w, const float* A, int64_t csA, int64_t rsA, float* B, int64_t csB, int64_t rsB, void* s) { return hyd_interleave_f32(h, w, A, csA, rsA, B, csB, rsB, s); }
+    static int interleave_update(float al, int64_t h, int64_t w, const float* A, int64_t csA, int64_t rsA, float* B, int64_t csB, int64_t rsB, void* s) { return hyd_interleave_update_f32(al, h, w, A, csA, rsA, B, csB, rsB, s); }
+    static int row_pack(int64_t h, int64_t w, int64_t al, int64_t st, const float* A, int64_t ld, float* P, int64_t ps, void* s) { return hyd_row_strided_pack_f32(h, w, al, st, A, ld, P, ps, s); }
+    static int row_unpack(int64_t h, int64_t w, int64_t al, int64_t st, const float* P, int64_t ps, float* B, int64_t ld, void* s) { return hyd_row_strided_unpack_f32(h, w, al, st, P, ps, B, ld, s); }
+    static int col_pack(int64_t h, int64_t w, int64_t al, int64_t st, const float* A, int64_t ld, float* P, int64_t ps, void* s) { return hyd_col_strided_pack_f32(h, w, al, st, A, ld, P, ps, s); }
+    static int col_unpack(int64_t h, int64_t w, int64_t al, int64_t st, const float* P, int64_t ps, float* B, int64_t ld, void* s) { return hyd_col_strided_unpack_f32(h, w, al, st, P, ps, B, ld, s); }
+    static int prow_pack(int64_t h, int64_t w, int64_t al, int64_t st, int64_t un, int64_t pt, int64_t rp, int64_t sh, const float* A, int64_t ld, float* P, int64_t ps, void* s) { return hyd_partial_row_strided_pack_f32(h, w, al, st, un, pt, rp, sh, A, ld, P, ps, s); }
+    static int prow_unpack(int64_t h, int64_t w, int64_t al, int64_t st, int64_t un, int64_t pt, int64_t rp, int64_t sh, const float* P, int64_t ps, float* B, int64_t ld, void* s) { return hyd_partial_row_strided_unpack_f32(h, w, al, st, un, pt, rp, sh, P, ps, B, ld, s); }
+    static int pcol_pack(int64_t h, int64_t w, int64_t al, int64_t st, int64_t un, int64_t pt, int64_t rp, int64_t sh, const float* A, int64_t ld, float* P, int64_t ps, void* s) { return hyd_partial_col_strided_pack_f32(h, w, al, st, un, pt, rp, sh, A, ld, P, ps, s); }
+    static int pcol_unpack(int64_t h, int64_t w, int64_t al, int64_t st, int64_t un, int64_t pt, int64_t rp, int64_t sh, const float* P, int64_t ps, float* B, int64_t ld, void* s) { return hyd_partial_col_strided_unpack_f32(h, w, al, st, un, pt, rp, sh, P, ps, B, ld, s); }
+    static int pack2d(int64_t h, int64_t w, int64_t ca, int64_t cs, int64_t ra, int64_t rs, const float* A, int64_t ld, float* P, int64_t ps, void* s) { return hyd_strided_pack_f32(h, w, ca, cs, ra, rs, A, ld, P, ps, s); }
+    static int unpack2d(int64_t h, int64_t w, int64_t ca, int64_t cs, int64_t ra, int64_t rs, const float* P, int64_t ps, float* B, int64_t ld, void* s) { return hyd_strided_unpack_f32(h, w, ca, cs, ra, rs, P, ps, B, ld, s); }
 };
 }  // namespace detail
 
@@ -257,7 +328,124 @@ void Gemm(Orientation tA, Orientation tB, Int m, Int n, Int k, T alpha, const T*
           Int ldc, const SyncInfoGPU& si) {
     detail::check(detail::Sfx<T>::lgemm(tA != NORMAL, tB != NORMAL, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, si.stream_));
 }
+// 2-D copy / transposing copy / axpy / scale on raw device buffers (include/hydrogen/blas/GPU_BLAS_impl.hpp:84-209,558-567)
+template <typename T>
+void Copy(Orientation trans, Int m, Int n, const T* A, Int lda, T* B, Int ldb, const SyncInfoGPU& si) {
+    // as in the reference, m x n is the shape of A; a transposing copy writes the n x m matrix B
+    detail::check(trans == NORMAL ? detail::Sfx<T>::copy2d(m, n, A, lda, B, ldb, si.stream_)
+                                  : detail::Sfx<T>::transpose(m, n, A, lda, B, ldb, si.stream_));
+}
+template <typename T>
+void Axpy(Int m, Int n, T alpha, const T* A, Int lda, T* B, Int ldb, const SyncInfoGPU& si) {
+    detail::check(detail::Sfx<T>::axpy2d(m, n, alpha, A, lda, B, ldb, si.stream_));
+}
+template <typename T>
+void Scale(Int m, Int n, T alpha, T* A, Int lda, const SyncInfoGPU& si) {
+    detail::check(detail::Sfx<T>::scale2d(m, n, alpha, A, lda, si.stream_));
+}
 }  // namespace gpu_blas
+
+// ---- copy::util / axpy::util on device buffers (include/El/blas_like/level1/Copy/util.hpp, Axpy/util.hpp): the
+// reference's names and argument order; each call is one kernel launch for all portions ----
+namespace copy { namespace util {
+template <typename T>
+void InterleaveMatrix(Int height, Int width, const T* A, Int colStrideA, Int rowStrideA, T* B, Int colStrideB, Int rowStrideB, const SyncInfoGPU& si) {
+    detail::check(detail::Sfx<T>::interleave(height, width, A, colStrideA, rowStrideA, B, colStrideB, rowStrideB, si.stream_));
+}
+template <typename T>
+void RowStridedPack(Int height, Int width, Int rowAlign, Int rowStride, const T* A, Int ALDim, T* BPortions, Int portionSize, const SyncInfoGPU& si) {
+    detail::check(detail::Sfx<T>::row_pack(height, width, rowAlign, rowStride, A, ALDim, BPortions, portionSize, si.stream_));
+}
+template <typename T>
+void RowStridedUnpack(Int height, Int width, Int rowAlign, Int rowStride, const T* APortions, Int portionSize, T* B, Int BLDim, const SyncInfoGPU& si) {
+    detail::check(detail::Sfx<T>::row_unpack(height, width, rowAlign, rowStride, APortions, portionSize, B, BLDim, si.stream_));
+}
+template <typename T>
+void PartialRowStridedPack(Int height, Int width, Int rowAlign, Int rowStride, Int rowStrideUnion, Int rowStridePart, Int rowRankPart, Int rowShiftA,
+                           const T* A, Int ALDim, T* BPortions, Int portionSize, const SyncInfoGPU& si) {
+    detail::check(detail::Sfx<T>::prow_pack(height, width, rowAlign, rowStride, rowStrideUnion, rowStridePart, rowRankPart, rowShiftA, A, ALDim, BPortions, portionSize, si.stream_));
+}
+template <typename T>
+void PartialRowStridedUnpack(Int height, Int width, Int rowAlign, Int rowStride, Int rowStrideUnion, Int rowStridePart, Int rowRankPart, Int rowShiftB,
+                             const T* APortions, Int portionSize, T* B, Int BLDim, const SyncInfoGPU& si) {
+    detail::check(detail::Sfx<T>::prow_unpack(height, width, rowAlign, rowStride, rowStrideUnion, rowStridePart, rowRankPart, rowShiftB, APortions, portionSize, B, BLDim, si.stream_));
+}
+template <typename T>
+void ColStridedPack(Int height, Int width, Int colAlign, Int colStride, const T* A, Int ALDim, T* BPortions, Int portionSize, const SyncInfoGPU& si) {
+    detail::check(detail::Sfx<T>::col_pack(height, width, colAlign, colStride, A, ALDim, BPortions, portionSize, si.stream_));
+}
+template <typename T>
+void ColStridedUnpack(Int height, Int width, Int colAlign, Int colStride, const T* APortions, Int portionSize, T* B, Int BLDim, const SyncInfoGPU& si) {
+    detail::check(detail::Sfx<T>::col_unpack(height, width, colAlign, colStride, APortions, portionSize, B, BLDim, si.stream_));
+}
+template <typename T>
+void PartialColStridedPack(Int height, Int width, Int colAlign, Int colStride, Int colStrideUnion, Int colStridePart, Int colRankPart, Int colShiftA,
+                           const T* A, Int ALDim, T* BPortions, Int portionSize, const SyncInfoGPU& si) {
+    detail::check(detail::Sfx<T>::pcol_pack(height, width, colAlign, colStride, colStrideUnion, colStridePart, colRankPart, colShiftA, A, ALDim, BPortions, portionSize, si.stream_));
+}
+template <typename T>
+void PartialColStridedUnpack(Int height, Int width, Int colAlign, Int colStride, Int colStrideUnion, Int colStridePart, Int colRankPart, Int colShiftB,
+                             const T* APortions, Int portionSize, T* B, Int BLDim, const SyncInfoGPU& si) {
+    detail::check(detail::Sfx<T>::pcol_unpack(height, width, colAlign, colStride, colStrideUnion, colStridePart, colRankPart, colShiftB, APortions, portionSize, B, BLDim, si.stream_));
+}
+template <typename T>
+void StridedPack(Int height, Int width, Int colAlign, Int colStride, Int rowAlign, Int rowStride, const T* A, Int ALDim, T* BPortions, Int portionSize, const SyncInfoGPU& si) {
+    detail::check(detail::Sfx<T>::pack2d(height, width, colAlign, colStride, rowAlign, rowStride, A, ALDim, BPortions, portionSize, si.stream_));
+}
+template <typename T>
+void StridedUnpack(Int height, Int width, Int colAlign, Int colStride, Int rowAlign, Int rowStride, const T* APortions, Int portionSize, T* B, Int BLDim, const SyncInfoGPU& si) {
+    detail::check(detail::Sfx<T>::unpack2d(height, width, colAlign, colStride, rowAlign, rowStride, APortions, portionSize, B, BLDim, si.stream_));
+}
+} }  // namespace copy::util
+namespace axpy { namespace util {
+template <typename T>
+void InterleaveMatrixUpdate(T alpha, Int height, Int width, const T* A, Int colStrideA, Int rowStrideA, T* B, Int colStrideB, Int rowStrideB, const SyncInfoGPU& si) {
+    detail::check(detail::Sfx<T>::interleave_update(alpha, height, width, A, colStrideA, rowStrideA, B, colStrideB, rowStrideB, si.stream_));
+}
+} }  // namespace axpy::util
+
+// C := alpha op(A) op(B) + beta C on the LOCAL blocks of conformally distributed matrices (Gemm.cpp:323-431): the
+// distribution / alignment / shape checks of the reference's debug build, then the local kernel
+template <typename T>
+void LocalGemm(Orientation orientA, Orientation orientB, T alpha, const AbstractDistMatrix<T>& A, const AbstractDistMatrix<T>& B,
+               T beta, AbstractDistMatrix<T>& C) {
+    const bool tA = orientA != NORMAL, tB = orientB != NORMAL;
+    const Dist aOut = tA ? A.RowDist() : A.ColDist(), aIn = tA ? A.ColDist() : A.RowDist();
+    const Dist bIn = tB ? B.RowDist() : B.ColDist(), bOut = tB ? B.ColDist() : B.RowDist();
+    if (aOut != C.ColDist() || aIn != bIn || bOut != C.RowDist()) LogicError("LocalGemm: nonconformal distributions");
+    const int aOutAl = tA ? A.RowAlign() : A.ColAlign(), aInAl = tA ? A.ColAlign() : A.RowAlign();
+    const int bInAl = tB ? B.RowAlign() : B.ColAlign(), bOutAl = tB ? B.ColAlign() : B.RowAlign();
+    if (aOutAl != C.ColAlign() || aInAl != bInAl || bOutAl != C.RowAlign()) LogicError("LocalGemm: operands are not aligned");
+    const Int m = tA ? A.Width() : A.Height(), k = tA ? A.Height() : A.Width();
+    const Int kB = tB ? B.Width() : B.Height(), n = tB ? B.Height() : B.Width();
+    if (m != C.Height() || k != kB || n != C.Width()) LogicError("Nonconformal LocalGemm");
+    const Int kLoc = tA ? A.LocalHeight() : A.LocalWidth();
+    detail::check(detail::Sfx<T>::lgemm(tA, tB, C.LocalHeight(), C.LocalWidth(), kLoc, alpha, A.LockedBuffer(), A.LDim(), B.LockedBuffer(),
+                                        B.LDim(), beta, C.Buffer(), C.LDim(), C.Stream()));
+}
+template <typename T>
+void LocalGemm(Orientation orientA, Orientation orientB, T alpha, const AbstractDistMatrix<T>& A, const AbstractDistMatrix<T>& B,
+               AbstractDistMatrix<T>& C) {
+    C.Resize(orientA == NORMAL ? A.Height() : A.Width(), orientB == NORMAL ? B.Width() : B.Height());
+    LocalGemm(orientA, orientB, alpha, A, B, T(0), C);
+}
+
+// local scaling of a distributed matrix (El::Scale(beta, C), Gemm.cpp:287) and Zero
+template <typename T>
+void Scale(T alpha, AbstractDistMatrix<T>& A) {
+    detail::check(detail::Sfx<T>::scale2d(A.LocalHeight(), A.LocalWidth(), alpha, A.Buffer(), A.LDim(), A.Stream()));
+}
+template <typename T>
+void Zero(AbstractDistMatrix<T>& A) { Scale(T(0), A); }
+// B := sum of A over the ranks along which A is a partial sum (Contract.hpp:14-98): align with A, zero, AxpyContract
+template <typename T>
+void Contract(const AbstractDistMatrix<T>& A, AbstractDistMatrix<T>& B) {
+    if (A.ColDist() == B.ColDist() && A.RowDist() == B.RowDist()) { Copy(A, B); return; }
+    B.AlignWith(A);
+    B.Resize(A.Height(), A.Width());
+    Zero(B);
+    AxpyContract(T(1), A, B);
+}
 
 }  // namespace El
 #endif  // EL_B200_SHIM_HPP

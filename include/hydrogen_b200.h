@@ -65,6 +65,73 @@ int hyd_axpy2d_f32(int64_t m, int64_t n, float alpha, const float* A, int64_t ld
 int hyd_scale2d_f64(int64_t m, int64_t n, double alpha, double* A, int64_t lda, hyd_stream_t stream);
 int hyd_scale2d_f32(int64_t m, int64_t n, float alpha, float* A, int64_t lda, hyd_stream_t stream);
 
+/* ---- seam S2: the reference's pack / unpack utilities, same argument lists (device buffers) --------------------
+ * ref: copy::util::* in include/El/blas_like/level1/Copy/util.hpp -- InterleaveMatrix :122-146 (GPU :244-267),
+ *      RowStridedPack/Unpack :148-184 (:269-309), PartialRowStridedPack/Unpack :186-230 (:311-359),
+ *      ColStridedPack/Unpack :363-421, PartialColStridedPack/Unpack :464-533, StridedPack/Unpack :671-722;
+ *      axpy::util::InterleaveMatrixUpdate include/El/blas_like/level1/Axpy/util.hpp:23-51.
+ * As in the reference, "colStride" is the element distance between consecutive rows of a column (the stride of the
+ * column distribution) and "rowStride" the distance between consecutive columns; portion k starts at
+ * Portions + k*portionSize.  The reference issues one 2-D copy per portion; here all portions are one kernel launch.
+ * Every function exists as _f64 (double) and _f32 (float). */
+int hyd_interleave_f64(int64_t height, int64_t width, const double* A, int64_t colStrideA, int64_t rowStrideA,
+                       double* B, int64_t colStrideB, int64_t rowStrideB, hyd_stream_t stream);
+int hyd_interleave_update_f64(double alpha, int64_t height, int64_t width, const double* A, int64_t colStrideA, int64_t rowStrideA,
+                              double* B, int64_t colStrideB, int64_t rowStrideB, hyd_stream_t stream);
+int hyd_row_strided_pack_f64(int64_t height, int64_t width, int64_t rowAlign, int64_t rowStride,
+                             const double* A, int64_t ALDim, double* BPortions, int64_t portionSize, hyd_stream_t stream);
+int hyd_row_strided_unpack_f64(int64_t height, int64_t width, int64_t rowAlign, int64_t rowStride,
+                               const double* APortions, int64_t portionSize, double* B, int64_t BLDim, hyd_stream_t stream);
+int hyd_partial_row_strided_pack_f64(int64_t height, int64_t width, int64_t rowAlign, int64_t rowStride,
+                                     int64_t rowStrideUnion, int64_t rowStridePart, int64_t rowRankPart, int64_t rowShiftA,
+                                     const double* A, int64_t ALDim, double* BPortions, int64_t portionSize, hyd_stream_t stream);
+int hyd_partial_row_strided_unpack_f64(int64_t height, int64_t width, int64_t rowAlign, int64_t rowStride,
+                                       int64_t rowStrideUnion, int64_t rowStridePart, int64_t rowRankPart, int64_t rowShiftB,
+                                       const double* APortions, int64_t portionSize, double* B, int64_t BLDim, hyd_stream_t stream);
+int hyd_col_strided_pack_f64(int64_t height, int64_t width, int64_t colAlign, int64_t colStride,
+                             const double* A, int64_t ALDim, double* BPortions, int64_t portionSize, hyd_stream_t stream);
+int hyd_col_strided_unpack_f64(int64_t height, int64_t width, int64_t colAlign, int64_t colStride,
+                               const double* APortions, int64_t portionSize, double* B, int64_t BLDim, hyd_stream_t stream);
+int hyd_partial_col_strided_pack_f64(int64_t height, int64_t width, int64_t colAlign, int64_t colStride,
+                                     int64_t colStrideUnion, int64_t colStridePart, int64_t colRankPart, int64_t colShiftA,
+                                     const double* A, int64_t ALDim, double* BPortions, int64_t portionSize, hyd_stream_t stream);
+int hyd_partial_col_strided_unpack_f64(int64_t height, int64_t width, int64_t colAlign, int64_t colStride,
+                                       int64_t colStrideUnion, int64_t colStridePart, int64_t colRankPart, int64_t colShiftB,
+                                       const double* APortions, int64_t portionSize, double* B, int64_t BLDim, hyd_stream_t stream);
+int hyd_strided_pack_f64(int64_t height, int64_t width, int64_t colAlign, int64_t colStride, int64_t rowAlign, int64_t rowStride,
+                         const double* A, int64_t ALDim, double* BPortions, int64_t portionSize, hyd_stream_t stream);
+int hyd_strided_unpack_f64(int64_t height, int64_t width, int64_t colAlign, int64_t colStride, int64_t rowAlign, int64_t rowStride,
+                           const double* APortions, int64_t portionSize, double* B, int64_t BLDim, hyd_stream_t stream);
+
+int hyd_interleave_f32(int64_t height, int64_t width, const float* A, int64_t colStrideA, int64_t rowStrideA,
+                       float* B, int64_t colStrideB, int64_t rowStrideB, hyd_stream_t stream);
+int hyd_interleave_update_f32(float alpha, int64_t height, int64_t width, const float* A, int64_t colStrideA, int64_t rowStrideA,
+                              float* B, int64_t colStrideB, int64_t rowStrideB, hyd_stream_t stream);
+int hyd_row_strided_pack_f32(int64_t height, int64_t width, int64_t rowAlign, int64_t rowStride,
+                             const float* A, int64_t ALDim, float* BPortions, int64_t portionSize, hyd_stream_t stream);
+int hyd_row_strided_unpack_f32(int64_t height, int64_t width, int64_t rowAlign, int64_t rowStride,
+                               const float* APortions, int64_t portionSize, float* B, int64_t BLDim, hyd_stream_t stream);
+int hyd_partial_row_strided_pack_f32(int64_t height, int64_t width, int64_t rowAlign, int64_t rowStride,
+                                     int64_t rowStrideUnion, int64_t rowStridePart, int64_t rowRankPart, int64_t rowShiftA,
+                                     const float* A, int64_t ALDim, float* BPortions, int64_t portionSize, hyd_stream_t stream);
+int hyd_partial_row_strided_unpack_f32(int64_t height, int64_t width, int64_t rowAlign, int64_t rowStride,
+                                       int64_t rowStrideUnion, int64_t rowStridePart, int64_t rowRankPart, int64_t rowShiftB,
+                                       const float* APortions, int64_t portionSize, float* B, int64_t BLDim, hyd_stream_t stream);
+int hyd_col_strided_pack_f32(int64_t height, int64_t width, int64_t colAlign, int64_t colStride,
+                             const float* A, int64_t ALDim, float* BPortions, int64_t portionSize, hyd_stream_t stream);
+int hyd_col_strided_unpack_f32(int64_t height, int64_t width, int64_t colAlign, int64_t colStride,
+                               const float* APortions, int64_t portionSize, float* B, int64_t BLDim, hyd_stream_t stream);
+int hyd_partial_col_strided_pack_f32(int64_t height, int64_t width, int64_t colAlign, int64_t colStride,
+                                     int64_t colStrideUnion, int64_t colStridePart, int64_t colRankPart, int64_t colShiftA,
+                                     const float* A, int64_t ALDim, float* BPortions, int64_t portionSize, hyd_stream_t stream);
+int hyd_partial_col_strided_unpack_f32(int64_t height, int64_t width, int64_t colAlign, int64_t colStride,
+                                       int64_t colStrideUnion, int64_t colStridePart, int64_t colRankPart, int64_t colShiftB,
+                                       const float* APortions, int64_t portionSize, float* B, int64_t BLDim, hyd_stream_t stream);
+int hyd_strided_pack_f32(int64_t height, int64_t width, int64_t colAlign, int64_t colStride, int64_t rowAlign, int64_t rowStride,
+                         const float* A, int64_t ALDim, float* BPortions, int64_t portionSize, hyd_stream_t stream);
+int hyd_strided_unpack_f32(int64_t height, int64_t width, int64_t colAlign, int64_t colStride, int64_t rowAlign, int64_t rowStride,
+                           const float* APortions, int64_t portionSize, float* B, int64_t BLDim, hyd_stream_t stream);
+
 /* ---- index arithmetic (host, no GPU needed) ------------------------------------
  * ref: include/El/core/indexing/impl.hpp:33-66 (Length_, MaxLength_), :229-245 (Mod_, Shift_). */
 int64_t hyd_mod(int64_t a, int64_t b);
@@ -149,6 +216,28 @@ int hyd_view(const hyd_grid* g, const hyd_dm* a, int64_t i, int64_t j, int64_t h
  * (the headers under include/El/blas_like/level1/Copy/).  Arrays have gridHeight*gridWidth entries; entry [rank] is the local part. */
 int hyd_redist_plan(int gridHeight, int gridWidth, int order, int rank, const hyd_dm* src, const hyd_dm* dst, int transpose,
                     int elemSize, int64_t* sendBytes, int64_t* recvBytes);
+
+/* ---- seam S2: collectives on the grid's sub-communicators (device buffers, async on `stream`) ---------------------
+ * ref: mpi::AllGather / AllToAll / ReduceScatter / SendRecv / Broadcast <T, Device::GPU> with a SyncInfo<GPU>
+ *      (src/core/imports/mpi/{AllGather,AllToAll,ReduceScatter,SendRecv,Broadcast}.hpp, include/El/core/imports/mpi.hpp)
+ *      on Grid::MCComm() / MRComm() / VCComm() / VRComm() (include/El/core/Grid.hpp:31-54, src/core/Grid.cpp:133-150).
+ * HYD_COMM_MC = the ranks of my grid COLUMN indexed by grid row (size = Height), HYD_COMM_MR = my grid ROW indexed by
+ * grid column (size = Width), HYD_COMM_VC / VR = all ranks in column-major / row-major order.
+ * Counts are BYTES per member (the typed reference calls multiply by sizeof(T)), except hyd_reducescatter_* which is
+ * typed because it adds: member k ends with the sum of everybody's k-th block of `count` elements, added in ascending
+ * communicator rank (bit-reproducible).  Collective over the GRID: every rank calls, each within its own
+ * sub-communicator, in the same order (as every copy:: primitive of the reference does). */
+enum { HYD_COMM_MC = 0, HYD_COMM_MR = 1, HYD_COMM_VC = 2, HYD_COMM_VR = 3 };
+int hyd_comm_size(const hyd_grid* g, int comm);
+int hyd_comm_rank(const hyd_grid* g, int comm);
+int hyd_comm_world_rank(const hyd_grid* g, int comm, int commRank); /* owning-communicator rank of member commRank */
+int hyd_allgather(hyd_grid* g, int comm, const void* sbuf, int64_t bytesPerMember, void* rbuf, hyd_stream_t stream);
+int hyd_alltoall(hyd_grid* g, int comm, const void* sbuf, int64_t bytesPerMember, void* rbuf, hyd_stream_t stream);
+int hyd_sendrecv(hyd_grid* g, int comm, const void* sbuf, int64_t sendBytes, int to, void* rbuf, int64_t recvBytes, int from,
+                 hyd_stream_t stream);
+int hyd_bcast(hyd_grid* g, int comm, void* buf, int64_t bytes, int root, hyd_stream_t stream);
+int hyd_reducescatter_f64(hyd_grid* g, int comm, const double* sbuf, double* rbuf, int64_t count, hyd_stream_t stream);
+int hyd_reducescatter_f32(hyd_grid* g, int comm, const float* sbuf, float* rbuf, int64_t count, hyd_stream_t stream);
 
 /* ---- seam S1: distributed operations (collective over the grid; async on `stream`) --------- */
 
