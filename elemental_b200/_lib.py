@@ -103,6 +103,15 @@ for _sf, _ft in (("f64", f64), ("f32", f32)):
         _sig(f"hyd_partial_{_n}_strided_unpack_{_sf}", i32, [i64] * 8 + [vp, i64, vp, i64, vp])
     _sig("hyd_strided_pack_" + _sf, i32, [i64] * 6 + [vp, i64, vp, i64, vp])
     _sig("hyd_strided_unpack_" + _sf, i32, [i64] * 6 + [vp, i64, vp, i64, vp])
+# the rest of the GPU BLAS-1 layer (level1.cu)
+for _sf, _ft in (("f64", f64), ("f32", f32)):
+    _sig("hyd_fill_" + _sf, i32, [i64, i64, _ft, vp, i64, vp])
+    _sig("hyd_hadamard_" + _sf, i32, [i64, i64, vp, i64, i64, vp, i64, i64, vp, i64, i64, vp])
+    _sig("hyd_axpy_trans_" + _sf, i32, [i32, i64, i64, _ft, vp, i64, vp, i64, vp])
+    _sig("hyd_copy1d_" + _sf, i32, [i64, vp, i64, vp, i64, vp])
+    _sig("hyd_axpy1d_" + _sf, i32, [i64, _ft, vp, i64, vp, i64, vp])
+    _sig("hyd_scale1d_" + _sf, i32, [i64, _ft, vp, i64, vp])
+    _sig("hyd_axpy_dist_" + _sf, i32, [vp, _ft, dmp, dmp, i32, vp])
 # seam S2: collectives on the grid's sub-communicators
 for _n in ("hyd_comm_size", "hyd_comm_rank"):
     _sig(_n, i32, [vp, i32])

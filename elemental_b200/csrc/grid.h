@@ -34,6 +34,7 @@ struct Grid {
     Workspace panel[4];  // gathered panels (A/B x double buffer) or reduce temporaries
     Workspace host_stage[3];  // device images of host operands (hyd_gemm_host_*)
     Workspace coll_ws;        // receive area of hyd_reducescatter_* (coll.cu)
+    Workspace level1_ws;      // X in Y's distribution for hyd_axpy_dist_* (level1.cu)
     int overlap = -1;    // -1 auto: gather panels under the previous GEMM only when the transport is SM-heavy (staged NCCL); 0 off; 1 on
     int sm_reserve = 4;  // SMs the local GEMM leaves to NCCL / pack kernels while overlapping
     long long launches = 0;

@@ -279,6 +279,52 @@ def TransposeAxpyContract(alpha, A, B, stream=None):
                                                              _stream_ptr(stream)))
 
 
+def Axpy(alpha, X, Y, stream=None):
+    """Y += alpha X between any two distributions (El::Axpy on ElementalMatrix, Axpy.hpp:161-187)."""
+    x, y = X.desc(), Y.desc()
+    check(getattr(lib, "hyd_axpy_dist_" + _sfx(Y.dtype))(Y.grid.h, _scalar(Y.dtype, alpha), C.byref(x), C.byref(y), 0,
+                                                         _stream_ptr(stream)))
+
+
+def TransposeAxpy(alpha, X, Y, stream=None):
+    """Y += alpha X^T (El::TransposeAxpy, TransposeAxpy.hpp)."""
+    x, y = X.desc(), Y.desc()
+    check(getattr(lib, "hyd_axpy_dist_" + _sfx(Y.dtype))(Y.grid.h, _scalar(Y.dtype, alpha), C.byref(x), C.byref(y), 1,
+                                                         _stream_ptr(stream)))
+
+
+def _same_dist(A, B):
+    return (A.cd, A.rd, A.ca, A.ra) == (B.cd, B.rd, B.ca, B.ra)
+
+
+def Hadamard(A, B, Cm, stream=None):
+    """C(i,j) = A(i,j) B(i,j) on identically distributed and aligned matrices (Hadamard.hpp:109-135)."""
+    if (A.m, A.n) != (B.m, B.n):
+        raise HydrogenError("Hadamard product requires equal dimensions")
+    if (A.cd, A.rd) != (B.cd, B.rd) or (B.cd, B.rd) != (Cm.cd, Cm.rd):
+        raise HydrogenError("A, B, and C must share the same distribution")
+    if (A.ca, A.ra) != (B.ca, B.ra):
+        raise HydrogenError("A and B must be aligned")
+    if not _same_dist(A, Cm) or (Cm.m, Cm.n) != (A.m, A.n):
+        raise HydrogenError("Hadamard: C must already be aligned with A and have its size (C.AlignWith / Resize)")
+    check(getattr(lib, "hyd_hadamard_" + _sfx(Cm.dtype))(A.lh, A.lw, _ptr(A.store), 1, A.ld, _ptr(B.store), 1, B.ld,
+                                                        _ptr(Cm.store), 1, Cm.ld, _stream_ptr(stream)))
+
+
+def Fill(A, alpha, stream=None):
+    """Every entry := alpha (El::Fill on the local block, Fill.hpp)."""
+    check(getattr(lib, "hyd_fill_" + _sfx(A.dtype))(A.lh, A.lw, _scalar(A.dtype, alpha), _ptr(A.store), A.ld, _stream_ptr(stream)))
+
+
+def Zero(A, stream=None):
+    Fill(A, 0.0, stream)
+
+
+def Scale(alpha, A, stream=None):
+    """A *= alpha (El::Scale on the local block, Scale.hpp)."""
+    check(getattr(lib, "hyd_scale2d_" + _sfx(A.dtype))(A.lh, A.lw, _scalar(A.dtype, alpha), _ptr(A.store), A.ld, _stream_ptr(stream)))
+
+
 def Gemm(orientA, orientB, alpha, A, B, beta, Cm, alg=GEMM_DEFAULT, stream=None, blocksize=None):
     """C := alpha op(A) op(B) + beta C  (El::Gemm on AbstractDistMatrix)."""
     a, b, c = A.desc(), B.desc(), Cm.desc()

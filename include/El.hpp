@@ -156,6 +156,13 @@ template <> struct Sfx<double> {
     static int copy2d(int64_t m, int64_t n, const double* A, int64_t lda, double* B, int64_t ldb, void* s) { return hyd_copy2d_f64(m, n, A, lda, B, ldb, s); }
     static int axpy2d(int64_t m, int64_t n, double al, const double* A, int64_t lda, double* B, int64_t ldb, void* s) { return hyd_axpy2d_f64(m, n, al, A, lda, B, ldb, s); }
     static int scale2d(int64_t m, int64_t n, double al, double* A, int64_t lda, void* s) { return hyd_scale2d_f64(m, n, al, A, lda, s); }
+    static int fill(int64_t m, int64_t n, double al, double* A, int64_t lda, void* s) { return hyd_fill_f64(m, n, al, A, lda, s); }
+    static int hadamard(int64_t m, int64_t n, const double* X, int64_t csX, int64_t rsX, const double* Y, int64_t csY, int64_t rsY, double* Z, int64_t csZ, int64_t rsZ, void* s) { return hyd_hadamard_f64(m, n, X, csX, rsX, Y, csY, rsY, Z, csZ, rsZ, s); }
+    static int axpy_trans(int tA, int64_t m, int64_t n, double al, const double* A, int64_t lda, double* B, int64_t ldb, void* s) { return hyd_axpy_trans_f64(tA, m, n, al, A, lda, B, ldb, s); }
+    static int copy1d(int64_t n, const double* X, int64_t incx, double* Y, int64_t incy, void* s) { return hyd_copy1d_f64(n, X, incx, Y, incy, s); }
+    static int axpy1d(int64_t n, double al, const double* X, int64_t incx, double* Y, int64_t incy, void* s) { return hyd_axpy1d_f64(n, al, X, incx, Y, incy, s); }
+    static int scale1d(int64_t n, double al, double* X, int64_t incx, void* s) { return hyd_scale1d_f64(n, al, X, incx, s); }
+    static int axpy_dist(hyd_grid* g, double al, const hyd_dm* X, const hyd_dm* Y, int t, void* s) { return hyd_axpy_dist_f64(g, al, X, Y, t, s); }
     static int interleave(int64_t h, int64_t w, const double* A, int64_t csA, int64_t rsA, double* B, int64_t csB, int64_t rsB, void* s) { return hyd_interleave_f64(h, w, A, csA, rsA, B, csB, rsB, s); }
     static int interleave_update(double al, int64_t h, int64_t w, const double* A, int64_t csA, int64_t rsA, double* B, int64_t csB, int64_t rsB, void* s) { return hyd_interleave_update_f64(al, h, w, A, csA, rsA, B, csB, rsB, s); }
     static int row_pack(int64_t h, int64_t w, int64_t al, int64_t st, const double* A, int64_t ld, double* P, int64_t ps, void* s) { return hyd_row_strided_pack_f64(h, w, al, st, A, ld, P, ps, s); }
@@ -178,6 +185,13 @@ template <> struct Sfx<float> {
     static int copy2d(int64_t m, int64_t n, const float* A, int64_t lda, float* B, int64_t ldb, void* s) { return hyd_copy2d_f32(m, n, A, lda, B, ldb, s); }
     static int axpy2d(int64_t m, int64_t n, float al, const float* A, int64_t lda, float* B, int64_t ldb, void* s) { return hyd_axpy2d_f32(m, n, al, A, lda, B, ldb, s); }
     static int scale2d(int64_t m, int64_t n, float al, float* A, int64_t lda, void* s) { return hyd_scale2d_f32(m, n, al, A, lda, s); }
+    static int fill(int64_t m, int64_t n, float al, float* A, int64_t lda, void* s) { return hyd_fill_f32(m, n, al, A, lda, s); }
+    static int hadamard(int64_t m, int64_t n, const float* X, int64_t csX, int64_t rsX, const float* Y, int64_t csY, int64_t rsY, float* Z, int64_t csZ, int64_t rsZ, void* s) { return hyd_hadamard_f32(m, n, X, csX, rsX, Y, csY, rsY, Z, csZ, rsZ, s); }
+    static int axpy_trans(int tA, int64_t m, int64_t n, float al, const float* A, int64_t lda, float* B, int64_t ldb, void* s) { return hyd_axpy_trans_f32(tA, m, n, al, A, lda, B, ldb, s); }
+    static int copy1d(int64_t n, const float* X, int64_t incx, float* Y, int64_t incy, void* s) { return hyd_copy1d_f32(n, X, incx, Y, incy, s); }
+    static int axpy1d(int64_t n, float al, const float* X, int64_t incx, float* Y, int64_t incy, void* s) { return hyd_axpy1d_f32(n, al, X, incx, Y, incy, s); }
+    static int scale1d(int64_t n, float al, float* X, int64_t incx, void* s) { return hyd_scale1d_f32(n, al, X, incx, s); }
+    static int axpy_dist(hyd_grid* g, float al, const hyd_dm* X, const hyd_dm* Y, int t, void* s) { return hyd_axpy_dist_f32(g, al, X, Y, t, s); }
     static int interleave(int64_t h, int64_t w, const float* A, int64_t csA, int64_t rsA, float* B, int64_t csB, int64_t rsB, void* s) { return hyd_interleave_f32(h, w, A, csA, rsA, B, csB, rsB, s); }
     static int interleave_update(float al, int64_t h, int64_t w, const float* A, int64_t csA, int64_t rsA, float* B, int64_t csB, int64_t rsB, void* s) { return hyd_interleave_update_f32(al, h, w, A, csA, rsA, B, csB, rsB, s); }
     static int row_pack(int64_t h, int64_t w, int64_t al, int64_t st, const float* A, int64_t ld, float* P, int64_t ps, void* s) { return hyd_row_strided_pack_f32(h, w, al, st, A, ld, P, ps, s); }
@@ -343,7 +357,48 @@ template <typename T>
 void Scale(Int m, Int n, T alpha, T* A, Int lda, const SyncInfoGPU& si) {
     detail::check(detail::Sfx<T>::scale2d(m, n, alpha, A, lda, si.stream_));
 }
+// B += alpha op(A), B is m x n (GPU_BLAS_impl.hpp:531-541)
+template <typename T>
+void Axpy(Orientation transA, Int m, Int n, T alpha, const T* A, Int lda, T* B, Int ldb, const SyncInfoGPU& si) {
+    detail::check(detail::Sfx<T>::axpy_trans(transA != NORMAL, m, n, alpha, A, lda, B, ldb, si.stream_));
+}
+// two-stride 2-D forms (GPU_BLAS_impl.hpp:543-548,570-588): the lattice kernels behind copy::util / axpy::util
+template <typename T>
+void Copy(Int m, Int n, const T* A, Int rowStrideA, Int lda, T* B, Int rowStrideB, Int ldb, const SyncInfoGPU& si) {
+    detail::check(detail::Sfx<T>::interleave(m, n, A, rowStrideA, lda, B, rowStrideB, ldb, si.stream_));
+}
+template <typename T>
+void Axpy(Int m, Int n, T alpha, const T* A, Int rowStrideA, Int lda, T* B, Int rowStrideB, Int ldb, const SyncInfoGPU& si) {
+    detail::check(detail::Sfx<T>::interleave_update(alpha, m, n, A, rowStrideA, lda, B, rowStrideB, ldb, si.stream_));
+}
+// 1-D forms with increments (GPU_BLAS_impl.hpp:510-518,550-556,590-597)
+template <typename T>
+void Copy(Int size, const T* X, Int incx, T* Y, Int incy, const SyncInfoGPU& si) {
+    detail::check(detail::Sfx<T>::copy1d(size, X, incx, Y, incy, si.stream_));
+}
+template <typename T>
+void Axpy(Int size, T alpha, const T* X, Int incx, T* Y, Int incy, const SyncInfoGPU& si) {
+    detail::check(detail::Sfx<T>::axpy1d(size, alpha, X, incx, Y, incy, si.stream_));
+}
+template <typename T>
+void Scale(Int size, T alpha, T* X, Int incx, const SyncInfoGPU& si) {
+    detail::check(detail::Sfx<T>::scale1d(size, alpha, X, incx, si.stream_));
+}
 }  // namespace gpu_blas
+
+// hydrogen::Fill_GPU_impl / Hadamard_GPU_impl (include/hydrogen/blas/gpu/{Fill,Hadamard}.hpp)
+namespace hydrogen_gpu {
+template <typename T>
+void Fill_GPU_impl(size_t height, size_t width, T alpha, T* buffer, size_t ldim, cudaStream_t stream) {
+    detail::check(detail::Sfx<T>::fill((Int)height, (Int)width, alpha, buffer, (Int)ldim, stream));
+}
+template <typename T>
+void Hadamard_GPU_impl(size_t height, size_t width, const T* X, size_t colStrideX, size_t rowStrideX, const T* Y, size_t colStrideY,
+                       size_t rowStrideY, T* Z, size_t colStrideZ, size_t rowStrideZ, cudaStream_t stream) {
+    detail::check(detail::Sfx<T>::hadamard((Int)height, (Int)width, X, (Int)colStrideX, (Int)rowStrideX, Y, (Int)colStrideY, (Int)rowStrideY,
+                                           Z, (Int)colStrideZ, (Int)rowStrideZ, stream));
+}
+}  // namespace hydrogen_gpu
 
 // ---- copy::util / axpy::util on device buffers (include/El/blas_like/level1/Copy/util.hpp, Axpy/util.hpp): the
 // reference's names and argument order; each call is one kernel launch for all portions ----
@@ -435,8 +490,38 @@ template <typename T>
 void Scale(T alpha, AbstractDistMatrix<T>& A) {
     detail::check(detail::Sfx<T>::scale2d(A.LocalHeight(), A.LocalWidth(), alpha, A.Buffer(), A.LDim(), A.Stream()));
 }
+// every local entry := alpha (Fill.hpp); Zero (Zero.hpp) is Fill(0): also clears NaN / Inf, as the reference's memset does
 template <typename T>
-void Zero(AbstractDistMatrix<T>& A) { Scale(T(0), A); }
+void Fill(AbstractDistMatrix<T>& A, T alpha) {
+    detail::check(detail::Sfx<T>::fill(A.LocalHeight(), A.LocalWidth(), alpha, A.Buffer(), A.LDim(), A.Stream()));
+}
+template <typename T>
+void Zero(AbstractDistMatrix<T>& A) { Fill(A, T(0)); }
+// Y += alpha X between any two distributions (Axpy.hpp:161-187): local if the DistData agree, else X is copied into Y's
+// distribution and alignment first
+template <typename T>
+void Axpy(T alpha, const AbstractDistMatrix<T>& X, AbstractDistMatrix<T>& Y) {
+    detail::check(detail::Sfx<T>::axpy_dist(Y.Grid().handle(), alpha, X.desc(), Y.desc(), 0, Y.Stream()));
+}
+// Y += alpha X^T (TransposeAxpy.hpp); conjugate is a no-op for real T
+template <typename T>
+void TransposeAxpy(T alpha, const AbstractDistMatrix<T>& X, AbstractDistMatrix<T>& Y, bool /*conjugate*/ = false) {
+    detail::check(detail::Sfx<T>::axpy_dist(Y.Grid().handle(), alpha, X.desc(), Y.desc(), 1, Y.Stream()));
+}
+template <typename T>
+void AdjointAxpy(T alpha, const AbstractDistMatrix<T>& X, AbstractDistMatrix<T>& Y) { TransposeAxpy(alpha, X, Y, true); }
+// C(i,j) := A(i,j) B(i,j) (Hadamard.hpp:109-135): same distribution, A and B aligned; C is aligned with A and resized
+template <typename T>
+void Hadamard(const AbstractDistMatrix<T>& A, const AbstractDistMatrix<T>& B, AbstractDistMatrix<T>& C) {
+    if (A.Height() != B.Height() || A.Width() != B.Width()) LogicError("Hadamard product requires equal dimensions");
+    if (A.ColDist() != B.ColDist() || A.RowDist() != B.RowDist() || B.ColDist() != C.ColDist() || B.RowDist() != C.RowDist())
+        LogicError("A, B, and C must share the same distribution");
+    if (A.ColAlign() != B.ColAlign() || A.RowAlign() != B.RowAlign()) LogicError("A and B must be aligned");
+    if (C.ColAlign() != A.ColAlign() || C.RowAlign() != A.RowAlign()) C.Align(A.ColAlign(), A.RowAlign());
+    if (C.Height() != A.Height() || C.Width() != A.Width()) C.Resize(A.Height(), A.Width());
+    detail::check(detail::Sfx<T>::hadamard(A.LocalHeight(), A.LocalWidth(), A.LockedBuffer(), 1, A.LDim(), B.LockedBuffer(), 1, B.LDim(),
+                                           C.Buffer(), 1, C.LDim(), C.Stream()));
+}
 // B := sum of A over the ranks along which A is a partial sum (Contract.hpp:14-98): align with A, zero, AxpyContract
 template <typename T>
 void Contract(const AbstractDistMatrix<T>& A, AbstractDistMatrix<T>& B) {

@@ -65,6 +65,31 @@ int hyd_axpy2d_f32(int64_t m, int64_t n, float alpha, const float* A, int64_t ld
 int hyd_scale2d_f64(int64_t m, int64_t n, double alpha, double* A, int64_t lda, hyd_stream_t stream);
 int hyd_scale2d_f32(int64_t m, int64_t n, float alpha, float* A, int64_t lda, hyd_stream_t stream);
 
+/* A(i,j) := alpha over an m x n block.  ref: hydrogen::Fill_GPU_impl(height, width, alpha, buffer, ldim, stream)
+ *      include/hydrogen/blas/gpu/Fill.hpp:19-21, src/hydrogen/blas/gpu/Fill.cu; callers El::Fill / El::Zero
+ *      (include/El/blas_like/level1/{Fill,Zero}.hpp). */
+int hyd_fill_f64(int64_t m, int64_t n, double alpha, double* A, int64_t lda, hyd_stream_t stream);
+int hyd_fill_f32(int64_t m, int64_t n, float alpha, float* A, int64_t lda, hyd_stream_t stream);
+/* Z(i,j) := X(i,j) * Y(i,j); every operand has its own (colStride, rowStride) as in the reference; Z may be X or Y.
+ * ref: hydrogen::Hadamard_GPU_impl src/hydrogen/blas/gpu/Hadamard.cu:60-112; caller El::Hadamard
+ *      include/El/blas_like/level1/Hadamard.hpp:22-107. */
+int hyd_hadamard_f64(int64_t m, int64_t n, const double* X, int64_t colStrideX, int64_t rowStrideX, const double* Y,
+                     int64_t colStrideY, int64_t rowStrideY, double* Z, int64_t colStrideZ, int64_t rowStrideZ, hyd_stream_t stream);
+int hyd_hadamard_f32(int64_t m, int64_t n, const float* X, int64_t colStrideX, int64_t rowStrideX, const float* Y,
+                     int64_t colStrideY, int64_t rowStrideY, float* Z, int64_t colStrideZ, int64_t rowStrideZ, hyd_stream_t stream);
+/* B += alpha*op(A), B is m x n; transA != 0: A is n x m.  ref: gpu_blas::Axpy(TransposeMode, ...) -> geam(op(A), B)
+ *      include/hydrogen/blas/GPU_BLAS_impl.hpp:108-132,531-541; axpy_2d_transpose_tiled_kernel src/hydrogen/blas/gpu/Axpy.cu:14-68. */
+int hyd_axpy_trans_f64(int transA, int64_t m, int64_t n, double alpha, const double* A, int64_t lda, double* B, int64_t ldb, hyd_stream_t stream);
+int hyd_axpy_trans_f32(int transA, int64_t m, int64_t n, float alpha, const float* A, int64_t lda, float* B, int64_t ldb, hyd_stream_t stream);
+/* 1-D forms with increments.  ref: gpu_blas::Copy / Axpy / Scale (size, X, incx, ...) GPU_BLAS_impl.hpp:510-518,550-556,590-597
+ *      (-> cublas?copy / ?axpy / ?scal). */
+int hyd_copy1d_f64(int64_t n, const double* X, int64_t incx, double* Y, int64_t incy, hyd_stream_t stream);
+int hyd_copy1d_f32(int64_t n, const float* X, int64_t incx, float* Y, int64_t incy, hyd_stream_t stream);
+int hyd_axpy1d_f64(int64_t n, double alpha, const double* X, int64_t incx, double* Y, int64_t incy, hyd_stream_t stream);
+int hyd_axpy1d_f32(int64_t n, float alpha, const float* X, int64_t incx, float* Y, int64_t incy, hyd_stream_t stream);
+int hyd_scale1d_f64(int64_t n, double alpha, double* X, int64_t incx, hyd_stream_t stream);
+int hyd_scale1d_f32(int64_t n, float alpha, float* X, int64_t incx, hyd_stream_t stream);
+
 /* ---- seam S2: the reference's pack / unpack utilities, same argument lists (device buffers) --------------------
  * ref: copy::util::* in include/El/blas_like/level1/Copy/util.hpp -- InterleaveMatrix :122-146 (GPU :244-267),
  *      RowStridedPack/Unpack :148-184 (:269-309), PartialRowStridedPack/Unpack :186-230 (:311-359),
@@ -254,6 +279,13 @@ int hyd_axpy_contract_f64(hyd_grid* g, double alpha, const hyd_dm* src, const hy
                           hyd_stream_t stream);
 int hyd_axpy_contract_f32(hyd_grid* g, float alpha, const hyd_dm* src, const hyd_dm* dst, int transpose,
                           hyd_stream_t stream);
+
+/* Y += alpha*X (transpose = 0) or Y += alpha*X^T (transpose = 1) on distributed matrices of ANY two supported distributions:
+ * equal distribution and alignments -> local axpy; otherwise X is first redistributed into Y's distribution and alignment.
+ * ref: El::Axpy(alpha, ElementalMatrix X, ElementalMatrix Y) include/El/blas_like/level1/Axpy.hpp:161-187;
+ *      El::TransposeAxpy include/El/blas_like/level1/TransposeAxpy.hpp. */
+int hyd_axpy_dist_f64(hyd_grid* g, double alpha, const hyd_dm* X, const hyd_dm* Y, int transpose, hyd_stream_t stream);
+int hyd_axpy_dist_f32(hyd_grid* g, float alpha, const hyd_dm* X, const hyd_dm* Y, int transpose, hyd_stream_t stream);
 
 /* C := alpha op(A) op(B) + beta C.  ref: El::Gemm(orientA,orientB,alpha,A,B,beta,C,alg),
  * include/El/blas_like/level3.hpp:66-84, src/blas_like/level3/Gemm.cpp:278-307; blocksize = El::Blocksize()

@@ -103,6 +103,11 @@ int orc_gemm(int orientA, int orientB, int alg, double alpha, orc_dm* A, orc_dm*
 void orc_dense_gemm_ref(int tA, int tB, int64_t m, int64_t n, int64_t k, double alpha, const void* A, int64_t lda,
                         const void* B, int64_t ldb, double beta, void* C, int64_t ldc, int es);
 
+/* ---- distributed BLAS-1 around Gemm (oracle_level1.c) ---- */
+int orc_axpy(double alpha, const orc_dm* X, orc_dm* Y, int transpose);   /* Axpy.hpp:161-187, TransposeAxpy.hpp:181-210 */
+int orc_hadamard(const orc_dm* A, const orc_dm* B, orc_dm* C);          /* Hadamard.hpp:109-135 */
+void orc_scale(double alpha, orc_dm* A);                                 /* Scale.hpp */
+
 #ifdef __cplusplus
 }
 #endif

@@ -18,6 +18,11 @@ template <typename T> void inst(El::Grid& g) {
     As = A;
     El::Scale(T(2), A);
     El::Zero(A);
+    El::Fill(A, T(3));
+    El::Axpy(T(2), As, A);
+    El::TransposeAxpy(T(2), Bt, A);
+    El::AdjointAxpy(T(2), A, C);
+    El::Hadamard(A, C, C);
     El::SyncInfoGPU si;
     T* p = A.Buffer();
     El::gpu_blas::Gemm(El::NORMAL, El::NORMAL, 2, 2, 2, T(1), p, 2, p, 2, T(0), p, 2, si);
@@ -25,6 +30,14 @@ template <typename T> void inst(El::Grid& g) {
     El::gpu_blas::Copy(El::NORMAL, 2, 2, p, 2, p, 2, si);
     El::gpu_blas::Axpy(2, 2, T(1), p, 2, p, 2, si);
     El::gpu_blas::Scale(2, 2, T(1), p, 2, si);
+    El::gpu_blas::Axpy(El::TRANSPOSE, 2, 2, T(1), p, 2, p, 2, si);
+    El::gpu_blas::Copy(2, 2, p, 1, 2, p, 1, 2, si);
+    El::gpu_blas::Axpy(2, 2, T(1), p, 1, 2, p, 1, 2, si);
+    El::gpu_blas::Copy(4, p, 1, p, 1, si);
+    El::gpu_blas::Axpy(4, T(1), p, 1, p, 1, si);
+    El::gpu_blas::Scale(4, T(1), p, 1, si);
+    El::hydrogen_gpu::Fill_GPU_impl<T>(2, 2, T(1), p, 2, si.stream_);
+    El::hydrogen_gpu::Hadamard_GPU_impl<T>(2, 2, p, 1, 2, p, 1, 2, p, 1, 2, si.stream_);
     El::copy::util::InterleaveMatrix(2, 2, p, 1, 2, p, 1, 2, si);
     El::copy::util::RowStridedPack(2, 2, 0, 1, p, 2, p, 4, si);
     El::copy::util::RowStridedUnpack(2, 2, 0, 1, p, 4, p, 2, si);

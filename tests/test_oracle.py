@@ -227,3 +227,46 @@ def test_gemm_fp32_and_dot_operands():
     O.gemm(0, 1, 4, 2.0, A, B, 3.0, Cm2, 16)
     got2, _ = Cm2.to_global()
     assert np.max(np.abs(got2 - exp)) <= 1e-3
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# distributed BLAS-1 around Gemm (oracle/oracle_level1.c): Axpy / TransposeAxpy / Hadamard / Scale
+# ---------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("r,c", [(1, 1), (2, 2), (2, 4), (3, 2)])
+def test_level1_axpy_matches_dense_definition(r, c):
+    """El::Axpy / TransposeAxpy between any two distributions (Axpy.hpp:161-187, TransposeAxpy.hpp:181-210) is
+    Y_global += alpha X_global(^T): checked after gathering, replicas included, for integer data (exact arithmetic)."""
+    og = O.Grid(r, c, 1)
+    rng = np.random.default_rng(17 * r + c)
+    for (xcd, xrd), (ycd, yrd) in itertools.product(O.PAIRS, [(MC, MR), (STAR, VC), (MR, STAR), (STAR, STAR)]):
+        for transpose in (0, 1):
+            m, n = (37, 22)
+            al = lambda d: int(rng.integers(0, O.lib.orc_dist_stride(og, d)))
+            X = O.DM(og, n if transpose else m, m if transpose else n, xcd, xrd, al(xcd), al(xrd)).fill_index()
+            Y = O.DM(og, m, n, ycd, yrd, al(ycd), al(yrd)).fill_index()
+            Y0, _ = Y.to_global()
+            Y0 = Y0.copy()
+            assert O.lib.orc_axpy(2.0, X.h, Y.h, transpose) == 0
+            Xg, _ = X.to_global()
+            Yg, mism = Y.to_global()
+            assert mism == 0
+            assert np.array_equal(Yg, Y0 + 2.0 * (Xg.T if transpose else Xg))
+    A = O.DM(og, 5, 4, MC, MR)
+    assert O.lib.orc_axpy(1.0, A.h, O.DM(og, 4, 5, MC, MR).h, 0) != 0   # nonconformal
+
+
+def test_level1_hadamard_and_scale():
+    og = O.Grid(2, 2, 1)
+    A = O.DM(og, 33, 21, MC, MR, 1, 0).fill(1)
+    B = O.DM(og, 33, 21, MC, MR, 1, 0).fill(2)
+    Cm = O.DM(og, 33, 21, MC, MR, 1, 0)
+    assert O.lib.orc_hadamard(A.h, B.h, Cm.h) == 0
+    assert np.array_equal(Cm.to_global()[0], A.to_global()[0] * B.to_global()[0])
+    assert O.lib.orc_hadamard(A.h, O.DM(og, 33, 21, MC, MR, 0, 0).h, Cm.h) == 3      # "A and B must be aligned"
+    assert O.lib.orc_hadamard(A.h, O.DM(og, 33, 21, MC, STAR, 1, 0).h, Cm.h) == 2    # "must share the same distribution"
+    assert O.lib.orc_hadamard(A.h, O.DM(og, 30, 21, MC, MR, 1, 0).h, Cm.h) == 1      # "requires equal dimensions"
+    A0 = A.to_global()[0].copy()
+    O.lib.orc_scale(0.3, A.h)
+    assert np.array_equal(A.to_global()[0], 0.3 * A0)
+    O.lib.orc_scale(0.0, A.h)
+    assert not A.to_global()[0].any()
