@@ -53,6 +53,8 @@ def parse():
 def cpu_gemm_tflops(n, grid, nb, steps=1, warmup=0):
     import oracle_lib as O
     blas = O.use_blas(True)
+    if blas:  # torchrun exports OMP_NUM_THREADS=1: the CPU arm uses (and reports) every host core
+        O.lib.orc_blas_threads(os.cpu_count() or 1)
     g = O.Grid(grid[0], grid[1], 1)
     A = O.DM(g, n, n, O.MC, O.MR).fill(1)
     B = O.DM(g, n, n, O.MC, O.MR).fill(2)
@@ -66,6 +68,12 @@ def cpu_gemm_tflops(n, grid, nb, steps=1, warmup=0):
     return 2.0 * n ** 3 / dt / 1e12, dt, blas
 
 
+def cpu_threads(blas):
+    """Threads the CPU arm really ran on: OpenBLAS' own count (1 for the naive loop)."""
+    import oracle_lib as O
+    return (O.lib.orc_blas_threads(0) or (os.cpu_count() or 1)) if blas else 1
+
+
 def pick_cpu_sample(budget_s, grid, nb):
     """Largest n in {2048,4096,8192} whose estimated time fits the budget (cubic extrapolation from 2048)."""
     tf, dt, _ = cpu_gemm_tflops(2048, grid, nb)
@@ -77,9 +85,9 @@ def pick_cpu_sample(budget_s, grid, nb):
 
 
 def cpu_baseline(grid, nb):
-    cores = os.cpu_count() or 1
     n = pick_cpu_sample(20.0, grid, 128)
     tf, dt, blas = cpu_gemm_tflops(n, grid, 128)
+    cores = cpu_threads(blas)
     return {"value": round(tf, 4), "unit": "TFLOP/s", "cores": cores, "kind": "port",
             "sample": f"oracle SUMMA-C NN fp64 m=n=k={n} (workload shape scaled from {M}), blocksize 128 (reference default), "
                       f"{grid[0]}x{grid[1]} simulated grid, {'OpenBLAS dgemm all cores' if blas else 'naive triple loop'}, {dt:.2f} s"}
@@ -93,7 +101,7 @@ def run_reference(args):
     total = max(1, args.steps + args.warmup)
     n = pick_cpu_sample(120.0 / total, grid, 128)
     tf, dt, blas = cpu_gemm_tflops(n, grid, 128, steps=args.steps, warmup=args.warmup)
-    cores = os.cpu_count() or 1
+    cores = cpu_threads(blas)
     sample = (f"oracle SUMMA-C NN fp64 m=n=k={n} per step (bounded sample of the {M}^3 workload), blocksize 128, "
               f"{grid[0]}x{grid[1]} simulated grid in one process, {'OpenBLAS dgemm all cores' if blas else 'naive loop'}")
     line = {"impl": "reference", "metric": "distributed Gemm TFLOP/s (fp64)", "value": round(tf, 4), "unit": "TFLOP/s",

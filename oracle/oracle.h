@@ -95,6 +95,7 @@ void orc_local_transpose(const orc_dm* A, orc_dm* B);       /* Transpose.hpp:99-
 /* ---- GEMM ---- */
 /* optional vendor BLAS (dlopen'ed): path to a library exporting scipy_dgemm_/scipy_sgemm_ or dgemm_/sgemm_ */
 int orc_set_blas(const char* path);
+int orc_blas_threads(int n);   /* set (n > 0) / query the registered BLAS' thread count */
 void orc_local_gemm(int tA, int tB, int64_t m, int64_t n, int64_t k, double alpha, const void* A, int64_t lda,
                     const void* B, int64_t ldb, double beta, void* C, int64_t ldc, int es);
 /* El::Gemm on the simulated grid, following the reference loops (alg: 0 default, 1 A, 2 B, 3 C, 4 Dot) */

@@ -19,6 +19,10 @@ typedef void (*sgemm_fn)(const char*, const char*, const int*, const int*, const
                          const int*, const float*, const int*, const float*, float*, const int*);
 static dgemm_fn g_dgemm = 0;
 static sgemm_fn g_sgemm = 0;
+typedef void (*set_threads_fn)(int);
+typedef int (*get_threads_fn)(void);
+static set_threads_fn g_set_threads = 0;
+static get_threads_fn g_get_threads = 0;
 
 int orc_set_blas(const char* path) {
     if (!path) { g_dgemm = 0; g_sgemm = 0; return 0; }
@@ -28,7 +32,18 @@ int orc_set_blas(const char* path) {
     if (!g_dgemm) g_dgemm = (dgemm_fn)dlsym(h, "dgemm_");
     g_sgemm = (sgemm_fn)dlsym(h, "scipy_sgemm_");
     if (!g_sgemm) g_sgemm = (sgemm_fn)dlsym(h, "sgemm_");
+    g_set_threads = (set_threads_fn)dlsym(h, "scipy_openblas_set_num_threads");
+    if (!g_set_threads) g_set_threads = (set_threads_fn)dlsym(h, "openblas_set_num_threads");
+    g_get_threads = (get_threads_fn)dlsym(h, "scipy_openblas_get_num_threads");
+    if (!g_get_threads) g_get_threads = (get_threads_fn)dlsym(h, "openblas_get_num_threads");
     return (g_dgemm && g_sgemm) ? 0 : -2;
+}
+
+/* Threads the registered BLAS uses (launchers such as torchrun export OMP_NUM_THREADS=1, which OpenBLAS honours at
+ * load time; the timed CPU arm sets the count it reports).  n <= 0 only queries.  Returns the count, 0 if unknown. */
+int orc_blas_threads(int n) {
+    if (n > 0 && g_set_threads) g_set_threads(n);
+    return g_get_threads ? g_get_threads() : 0;
 }
 
 #define NAIVE_GEMM(T, NAME)                                                                                  \

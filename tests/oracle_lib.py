@@ -70,6 +70,7 @@ _sig("orc_axpy", i32, [f64, vp, vp, i32])
 _sig("orc_hadamard", i32, [vp, vp, vp])
 _sig("orc_scale", None, [f64, vp])
 _sig("orc_set_blas", i32, [C.c_char_p])
+_sig("orc_blas_threads", i32, [i32])
 _sig("orc_local_gemm", None, [i32, i32, i64, i64, i64, f64, vp, i64, vp, i64, f64, vp, i64, i32])
 _sig("orc_gemm", i32, [i32, i32, i32, f64, vp, vp, f64, vp, i64])
 _sig("orc_dense_gemm_ref", None, [i32, i32, i64, i64, i64, f64, vp, i64, vp, i64, f64, vp, i64, i32])
