@@ -80,6 +80,7 @@ void orc_partial_col_strided_pack(int64_t h, int64_t w, int64_t colAlign, int64_
 void orc_partial_col_strided_unpack(int64_t h, int64_t w, int64_t colAlign, int64_t colStride, int64_t uni, int64_t part, int64_t rankPart, int64_t shiftB, const void* Ap, int64_t portion, void* B, int64_t ldB, int es); /* :510-533 */
 void orc_strided_pack(int64_t h, int64_t w, int64_t colAlign, int64_t colStride, int64_t rowAlign, int64_t rowStride, const void* A, int64_t ldA, void* Bp, int64_t portion, int es); /* :671-695 */
 void orc_strided_unpack(int64_t h, int64_t w, int64_t colAlign, int64_t colStride, int64_t rowAlign, int64_t rowStride, const void* Ap, int64_t portion, void* B, int64_t ldB, int es); /* :697-722 */
+void orc_interleave_update(double alpha, int64_t h, int64_t w, const void* A, int64_t csA, int64_t rsA, void* B, int64_t csB, int64_t rsB, int es); /* Axpy/util.hpp:23-37 */
 
 /* ---- primitive chains (pack -> simulated collective -> unpack), aligned and unaligned branches.
  * Each returns 0, or -1 if (src,dst) is not the pair the primitive serves. dst alignments are inputs. */

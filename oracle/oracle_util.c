@@ -96,12 +96,25 @@ void orc_strided_unpack(int64_t h, int64_t w, int64_t colAlign, int64_t colStrid
         }
     }
 }
+/* Axpy/util.hpp:23-37: column j of B += alpha * column j of A (blas::Axpy per column = ?axpy: the product and the
+ * sum are each rounded once; this file is built with -ffp-contract=off so no FMA is formed) */
+void orc_interleave_update(double alpha, int64_t h, int64_t w, const void* A, int64_t csA, int64_t rsA, void* B, int64_t csB, int64_t rsB, int es) {
+    for (int64_t j = 0; j < w; ++j)
+        for (int64_t i = 0; i < h; ++i) {
+            if (es == 8) {
+                const double p = alpha * ((const double*)A)[i * csA + j * rsA];
+                ((double*)B)[i * csB + j * rsB] += p;
+            } else {
+                const float p = (float)alpha * ((const float*)A)[i * csA + j * rsA];
+                ((float*)B)[i * csB + j * rsB] += p;
+            }
+        }
+}
 
 /* ---------------- simulated communicators ---------------- */
 typedef struct { int mc, mr; } coord;
 static coord co(orc_grid g, int p) { coord c; orc_grid_coords(g, p, &c.mc, &c.mr); return c; }
 /* the communicator a 1-D distribution lives on: rank within it, size, and world rank of member k of p's comm */
-static int comm_size(orc_grid g, int dist) { return orc_dist_stride(g, dist); }
 static int comm_member(orc_grid g, int dist, int p, int k) {
     coord c = co(g, p);
     switch (dist) {

@@ -85,6 +85,7 @@ for n in ("orc_partial_row_strided_pack", "orc_partial_row_strided_unpack", "orc
 _sig("orc_strided_pack", None, [i64, i64, i64, i64, i64, i64, vp, i64, vp, i64, i32])
 _sig("orc_strided_unpack", None, [i64, i64, i64, i64, i64, i64, vp, i64, vp, i64, i32])
 _sig("orc_interleave", None, [i64, i64, vp, i64, i64, vp, i64, i64, i32])
+_sig("orc_interleave_update", None, [f64, i64, i64, vp, i64, i64, vp, i64, i64, i32])
 
 
 def find_blas():

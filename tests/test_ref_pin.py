@@ -1,0 +1,115 @@
+"""-m "not gpu": the oracle pinned by the REFERENCE's own code.
+
+tests/golden/copy_util.npz holds outputs of the reference's copy::util pack/unpack loops, axpy::util::InterleaveMatrixUpdate
+and indexing functions, produced by compiling those headers from /root/reference in place (oracle/Makefile target `ref`,
+shim oracle/ref/ref_util.cpp; generator tests/golden/make_golden.py).  Here:
+  * the C restatement (oracle/oracle_util.c, oracle_core.c) must reproduce every fixture bit for bit;
+  * where oracle/_ref/libref_util.so exists (this container, or shipped prebuilt to the GPU box), the fixtures must still
+    be what the reference computes, and oracle == reference on fresh random arguments beyond the fixture list.
+"""
+import os
+
+import numpy as np
+import pytest
+
+import golden_cases as G
+import oracle_lib as O
+
+HAVE_REF = os.path.exists(G.REF_LIB)
+needs_ref = pytest.mark.skipif(not HAVE_REF, reason="oracle/_ref/libref_util.so not built (needs /root/reference)")
+
+
+def test_fixture_is_the_declared_case_list():
+    cases, sha, outs, idx_in, idx_out = G.load_golden()
+    assert cases == G.build_cases()
+    assert sha.shape == (len(cases), 32) and len(outs) == len(cases)
+    assert np.array_equal(idx_in, G.indexing_inputs())
+    # every function, both dtypes, empty and ragged shapes are present
+    assert {c[0] for c in cases} == set(G.FNS) and {c[1] for c in cases} == {"f64", "f32"}
+    assert any(c[2][0] == 0 for c in cases) and any(c[2][1] == 0 for c in cases)
+
+
+def test_oracle_restatement_reproduces_reference_pack_unpack_fixtures():
+    n = G.check_against_golden(G.OracleBackend())
+    assert n == len(G.build_cases())
+
+
+def test_oracle_indexing_reproduces_reference_fixtures():
+    _, _, _, idx_in, idx_out = G.load_golden()
+    for (n, rank, align, stride), exp in zip(idx_in.tolist(), idx_out.tolist()):
+        shift = O.lib.orc_shift(rank, align, stride)
+        got = (shift, O.lib.orc_length(n, shift, stride), O.lib.orc_length(n, O.lib.orc_shift(rank, align, stride), stride),
+               O.lib.orc_max_length(n, stride), O.lib.orc_mod(rank - align - stride, stride))
+        assert got == tuple(exp[:5]), (n, rank, align, stride)
+
+
+def test_product_host_indexing_reproduces_reference_fixtures():
+    """hyd_mod/shift/length/max_length are host functions of the C ABI (no GPU needed)."""
+    from elemental_b200 import lib
+    _, _, _, idx_in, idx_out = G.load_golden()
+    for (n, rank, align, stride), exp in zip(idx_in.tolist(), idx_out.tolist()):
+        shift = lib.hyd_shift(rank, align, stride)
+        got = (shift, lib.hyd_length(n, shift, stride), lib.hyd_max_length(n, stride), lib.hyd_mod(rank - align - stride, stride))
+        assert got == (exp[0], exp[1], exp[3], exp[4]), (n, rank, align, stride)
+
+
+@needs_ref
+def test_fixtures_are_what_the_reference_computes():
+    ref = G.RefBackend()
+    assert ref.lib.ref_int_bytes() == 4
+    assert G.check_against_golden(ref) == len(G.build_cases())
+
+
+@needs_ref
+def test_oracle_equals_reference_on_random_arguments():
+    """Beyond the fixture list: 400 random argument sets per family, reference loops vs restatement, bitwise."""
+    ref, orc = G.RefBackend(), G.OracleBackend()
+    rng = np.random.default_rng(99)
+    n = 0
+    for _ in range(400):
+        h, w = int(rng.integers(0, 90)), int(rng.integers(0, 90))
+        dn = "f64" if rng.integers(0, 2) else "f32"
+        kind = "row" if rng.integers(0, 2) else "col"
+        stride = int(rng.integers(1, 10))
+        align = int(rng.integers(0, stride))
+        ld = max(1, h) + int(rng.integers(0, 5))
+        maxl = -(-w // stride) if kind == "row" else -(-h // stride)
+        portion = max(1, (h if kind == "row" else w) * maxl) + int(rng.integers(0, 4))
+        cases = [(kind + "_pack", dn, (h, w, align, stride, ld, portion)), (kind + "_unpack", dn, (h, w, align, stride, ld, portion))]
+        uni, part = int(rng.integers(1, 5)), int(rng.integers(1, 5))
+        st2 = uni * part
+        al2, rp = int(rng.integers(0, st2)), int(rng.integers(0, part))
+        sm = (rp - al2 % part) % part
+        nd = w if kind == "row" else h
+        loc = (nd - sm - 1) // part + 1 if nd > sm else 0
+        lh, lw = (h, loc) if kind == "row" else (loc, w)
+        ld2 = max(1, lh) + int(rng.integers(0, 5))
+        por2 = max(1, (h if kind == "row" else w) * (-(-nd // st2))) + int(rng.integers(0, 4))
+        pp = (h, w, al2, st2, uni, part, rp, sm, ld2, por2, lh, lw)
+        cases += [("p" + kind + "_pack", dn, pp), ("p" + kind + "_unpack", dn, pp)]
+        cs, rs = int(rng.integers(1, 6)), int(rng.integers(1, 6))
+        p2 = (h, w, int(rng.integers(0, cs)), cs, int(rng.integers(0, rs)), rs, ld, max(1, (-(-h // cs)) * (-(-w // rs))) + 1)
+        cases += [("pack2d", dn, p2), ("unpack2d", dn, p2)]
+        if h and w:
+            csA, csB = int(rng.integers(1, 4)), int(rng.integers(1, 4))
+            pi = (h, w, csA, csA * h + int(rng.integers(0, 3)), csB, csB * h + int(rng.integers(0, 3)))
+            cases += [("interleave", dn, pi), ("update", dn, pi + (int(rng.integers(0, len(G.ALPHAS))),))]
+        for (fn, d, p) in cases:
+            assert np.array_equal(ref.run(fn, d, p), orc.run(fn, d, p)), (fn, d, p)
+            n += 1
+    assert n > 3000
+
+
+@needs_ref
+def test_oracle_indexing_equals_reference_exhaustively_on_small_arguments():
+    ref = G.RefBackend().lib
+    for stride in range(1, 13):
+        for align in range(stride):
+            for rank in range(stride):
+                s = ref.ref_shift(rank, align, stride)
+                assert s == O.lib.orc_shift(rank, align, stride)
+                for n in list(range(0, 40)) + [1000, 32768]:
+                    assert ref.ref_length(n, s, stride) == O.lib.orc_length(n, s, stride)
+                    assert ref.ref_max_length(n, stride) == O.lib.orc_max_length(n, stride)
+        for a in range(-30, 30):
+            assert ref.ref_mod(a, stride) == O.lib.orc_mod(a, stride)
