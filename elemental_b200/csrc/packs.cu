@@ -49,6 +49,30 @@ int launch(const std::vector<CopyDesc>& v, cudaStream_t s, const char* who) {
     return 0;
 }
 
+// Row-interleaved unpack (Col / PartialCol / 2-D Strided unpack): the S portions of a call each hold every S-th row of
+// the destination block.  Unpacked one lattice at a time (as the reference does, one copy_2d_kernel per portion), every
+// 32-byte sector of the block is written S times, an S-th at a time; lattice_merge_kernel writes each destination
+// vector once, fetching its elements from the portions that own them.  src_of_residue[r] = portion holding rows
+// r, r+S, ...; cs_of_residue[r] = its leading dimension.
+template <typename T>
+int launch_merge(int S, T* const* src_of_residue, const i64* cs_of_residue, T* dst, i64 d_cs, i64 nr, i64 nc, cudaStream_t s,
+                 const char* who) {
+    if (nr == 0 || nc == 0) return 0;
+    MergeDesc md;
+    md.S = S;
+    for (int r = 0; r < S; ++r) { md.src[r] = src_of_residue[r]; md.s_cs[r] = cs_of_residue[r]; }
+    md.dst = dst;
+    md.d_cs = d_cs;
+    md.nr = nr;
+    md.nc = nc;
+    const i64 V = 16 / (i64)sizeof(T);
+    const i64 want = ((nr + V - 1) / V + 255) / 256 * ((nc + 7) / 8);
+    const unsigned grid = (unsigned)std::max<i64>(1, std::min<i64>(want, (i64)num_sms() * 8));
+    lattice_merge_kernel<T><<<grid, 256, 0, s>>>(md);
+    ++g_launches;
+    return check_cuda(cudaGetLastError(), who);
+}
+
 inline int bad_dims(i64 h, i64 w, const char* who) { return (h < 0 || w < 0) ? set_error("%s: negative dimension", who) : 0; }
 inline int bad_stride(i64 align, i64 stride, const char* who) {
     if (stride <= 0) return set_error("%s: stride must be positive", who);
@@ -121,6 +145,16 @@ int col_strided(bool pack, i64 h, i64 w, i64 colAlign, i64 colStride, T* M, i64 
     if (h == 0 || w == 0) return 0;
     if (ld < h) return set_error("%s: leading dimension too small", who);
     if (portion < w * max_length_(h, colStride)) return set_error("%s: portionSize too small", who);
+    if (!pack && colStride >= 2 && colStride <= kMaxMerge) {
+        T* src[kMaxMerge];
+        i64 cs[kMaxMerge];
+        for (i64 k = 0; k < colStride; ++k) {
+            const i64 colShift = shift_(k, colAlign, colStride);  // portion k owns rows colShift, colShift + colStride, ...
+            src[colShift] = P + k * portion;
+            cs[colShift] = length_(h, colShift, colStride);
+        }
+        return launch_merge<T>((int)colStride, src, cs, M, ld, h, w, s, who);
+    }
     std::vector<CopyDesc> v;
     for (i64 k = 0; k < colStride; ++k) {
         const i64 colShift = shift_(k, colAlign, colStride);
@@ -143,6 +177,19 @@ int partial_col_strided(bool pack, i64 h, i64 w, i64 colAlign, i64 colStride, i6
     const i64 lhM = length_(h, shiftM, part);  // rows the matrix itself holds
     if (ld < lhM) return set_error("%s: leading dimension too small", who);
     if (portion < w * max_length_(h, colStride)) return set_error("%s: portionSize too small", who);
+    if (!pack && uni >= 2 && uni <= kMaxMerge) {
+        T* src[kMaxMerge];
+        i64 cs[kMaxMerge];
+        for (i64 k = 0; k < uni; ++k) {
+            const i64 colShift = shift_(rankPart + k * part, colAlign, colStride);
+            if (mod_(colShift - shiftM, part) != 0) return set_error("%s: shift is not congruent to the partial rank", who);
+            const i64 off = (colShift - shiftM) / part;  // portion k owns local rows off, off + uni, ... (off < uni, distinct)
+            if (off < 0 || off >= uni) return set_error("%s: shift is not congruent to the partial rank", who);
+            src[off] = P + k * portion;
+            cs[off] = length_(h, colShift, colStride);
+        }
+        return launch_merge<T>((int)uni, src, cs, M, ld, lhM, w, s, who);
+    }
     std::vector<CopyDesc> v;
     for (i64 k = 0; k < uni; ++k) {
         const i64 colShift = shift_(rankPart + k * part, colAlign, colStride);
@@ -166,6 +213,21 @@ int strided(bool pack, i64 h, i64 w, i64 colAlign, i64 colStride, i64 rowAlign, 
     if (h == 0 || w == 0) return 0;
     if (ld < h) return set_error("%s: leading dimension too small", who);
     if (portion < max_length_(h, colStride) * max_length_(w, rowStride)) return set_error("%s: portionSize too small", who);
+    if (!pack && colStride >= 2 && colStride <= kMaxMerge) {
+        for (i64 l = 0; l < rowStride; ++l) {  // one merged pass per column class
+            const i64 rowShift = shift_(l, rowAlign, rowStride);
+            const i64 lw = length_(w, rowShift, rowStride);
+            T* src[kMaxMerge];
+            i64 cs[kMaxMerge];
+            for (i64 k = 0; k < colStride; ++k) {
+                const i64 colShift = shift_(k, colAlign, colStride);
+                src[colShift] = P + (k + l * colStride) * portion;
+                cs[colShift] = length_(h, colShift, colStride);
+            }
+            if (launch_merge<T>((int)colStride, src, cs, M + rowShift * ld, rowStride * ld, h, lw, s, who)) return 1;
+        }
+        return 0;
+    }
     std::vector<CopyDesc> v;
     for (i64 l = 0; l < rowStride; ++l) {
         const i64 rowShift = shift_(l, rowAlign, rowStride);
