@@ -6,12 +6,18 @@
  * All P ranks of an r x c grid are simulated inside one process: a distributed matrix is an
  * array of P local column-major buffers.  Collectives are memcpy / rank-ascending sums.
  *
- * Pinning: the reference cannot be built here (needs MPI, LAPACK, Aluminum, NVSHMEM) and
- * ships no golden vectors.  The pins are the reference's own test PROPERTIES:
- *   - tests/core/DistMatrix.cpp:28-76  : B = A for every distribution pair with random alignments,
- *     gather both to [*,*], require bitwise equality  -> tests/test_oracle.py checks every restated
- *     primitive chain against the closed-form ownership definition this way;
- *   - tests/blas_like/BasicGemm.cpp:93-94,108 : |GPU - CPU| <= 1e-10 (fp64) / 1e-3 (fp32), alpha=2, beta=3.
+ * Pinning, strongest first:
+ *   - REFERENCE CODE: indexing (include/El/core/indexing/impl.hpp), every copy::util CPU pack/unpack loop
+ *     (include/El/blas_like/level1/Copy/util.hpp) and axpy::util::InterleaveMatrixUpdate (Axpy/util.hpp) compile
+ *     from where they lie into oracle/_ref/libref_util.so (oracle/Makefile target `ref`, shim oracle/ref/); the
+ *     golden vectors tests/golden/copy_util.npz come from it (tests/golden/make_golden.py) and tests/test_ref_pin.py
+ *     holds oracle_core.c / oracle_util.c to them bit for bit (plus 3000+ random argument sets where _ref exists).
+ *   - The reference as a whole cannot be built here (needs MPI, LAPACK, Aluminum, NVSHMEM) and ships no
+ *     golden vectors, so what only exists above MPI is pinned by the reference's own test PROPERTIES:
+ *       tests/core/DistMatrix.cpp:28-76  : B = A for every distribution pair with random alignments,
+ *         gather both to [*,*], require bitwise equality  -> tests/test_oracle.py checks every restated
+ *         primitive chain against the closed-form ownership definition this way;
+ *       tests/blas_like/BasicGemm.cpp:93-94,108 : |GPU - CPU| <= 1e-10 (fp64) / 1e-3 (fp32), alpha=2, beta=3.
  * The bit pattern of GEMM results is "parity unpinned" (vendor BLAS / cuBLAS / NCCL sum orders
  * are third-party) -- hence the Frobenius tolerance of BASELINE.json.
  */
