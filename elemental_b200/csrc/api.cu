@@ -9,7 +9,8 @@ const char* last_error();
 int probe_peak(int kind, int iters, int ctas_per_sm, double* tflops);
 template <typename T>
 int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A, const DM& B, T beta, const DM& C, i64 blocksize,
-              cudaStream_t s, const void* hostA, i64 hostLdA, const void* hostB, i64 hostLdB);
+              cudaStream_t s, const void* hostA, i64 hostLdA, const void* hostB, i64 hostLdB, void* hostC, i64 hostLdC,
+              int* c_downloaded);
 }  // namespace hyd
 
 struct hyd_world { hyd::World* w; };
@@ -69,8 +70,11 @@ static int gemm_host(hyd_grid* g, int oA, int oB, int alg, T alpha, const hyd_dm
                 return 1;
         }
     }
-    if (hyd::dist_gemm<T>(G, oA, oB, alg, alpha, dev[0], dev[1], beta, dev[2], blocksize, s, A->buf, A->ldim, B->buf, B->ldim)) return 1;
-    if (L[2].lh > 0 && L[2].lw > 0 &&
+    int c_downloaded = 0;  // set when the engine already wrote C's blocks to the host (column-blocked path)
+    if (hyd::dist_gemm<T>(G, oA, oB, alg, alpha, dev[0], dev[1], beta, dev[2], blocksize, s, A->buf, A->ldim, B->buf, B->ldim,
+                          C->buf, C->ldim, &c_downloaded))
+        return 1;
+    if (!c_downloaded && L[2].lh > 0 && L[2].lw > 0 &&
         hyd::check_cuda(cudaMemcpy2DAsync(C->buf, (size_t)C->ldim * sizeof(T), dev[2].buf, (size_t)dev[2].ldim * sizeof(T),
                                           (size_t)L[2].lh * sizeof(T), (size_t)L[2].lw, cudaMemcpyDeviceToHost, s),
                         "hyd_gemm_host: D2H"))
@@ -248,14 +252,14 @@ int hyd_gemm_f64(hyd_grid* g, int oA, int oB, int alg, double alpha, const hyd_d
     const hyd::GridShape& sh = g->g->shape;
     if (check_dm(sh, A, "hyd_gemm(A)") || check_dm(sh, B, "hyd_gemm(B)") || check_dm(sh, C, "hyd_gemm(C)")) return 1;
     return hyd::dist_gemm<double>(*g->g, oA, oB, alg, alpha, to_dm(A), to_dm(B), beta, to_dm(C), blocksize,
-                                  (cudaStream_t)stream, nullptr, 0, nullptr, 0);
+                                  (cudaStream_t)stream, nullptr, 0, nullptr, 0, nullptr, 0, nullptr);
 }
 int hyd_gemm_f32(hyd_grid* g, int oA, int oB, int alg, float alpha, const hyd_dm* A, const hyd_dm* B, float beta,
                  const hyd_dm* C, int64_t blocksize, hyd_stream_t stream) {
     const hyd::GridShape& sh = g->g->shape;
     if (check_dm(sh, A, "hyd_gemm(A)") || check_dm(sh, B, "hyd_gemm(B)") || check_dm(sh, C, "hyd_gemm(C)")) return 1;
     return hyd::dist_gemm<float>(*g->g, oA, oB, alg, alpha, to_dm(A), to_dm(B), beta, to_dm(C), blocksize,
-                                 (cudaStream_t)stream, nullptr, 0, nullptr, 0);
+                                 (cudaStream_t)stream, nullptr, 0, nullptr, 0, nullptr, 0, nullptr);
 }
 
 

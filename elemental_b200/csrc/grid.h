@@ -31,6 +31,8 @@ struct Grid {
     cudaEvent_t ev_unpack_fork = nullptr, ev_unpack_join = nullptr;
     cudaEvent_t ev_chunk[8] = {};                   // chunk q's own part has been packed
     std::vector<cudaEvent_t> upload_ev;  // per-panel H2D completion (hyd_gemm_host_*)
+    cudaStream_t download_stream = nullptr;          // hyd_gemm_host_* with HYD_HOST_CBLOCKS > 1: D2H of finished column blocks of C
+    cudaEvent_t ev_block_done = nullptr, ev_download_done = nullptr;
     Workspace panel[4];  // gathered panels (A/B x double buffer) or reduce temporaries
     Workspace host_stage[3];  // device images of host operands (hyd_gemm_host_*)
     Workspace coll_ws;        // receive area of hyd_reducescatter_* (coll.cu)

@@ -612,6 +612,9 @@ void grid_destroy(Grid* g) {
     if (g->ev_fork) cudaEventDestroy(g->ev_fork);
     if (g->ev_join) cudaEventDestroy(g->ev_join);
     if (g->unpack_stream) cudaStreamDestroy(g->unpack_stream);
+    if (g->download_stream) cudaStreamDestroy(g->download_stream);
+    if (g->ev_block_done) cudaEventDestroy(g->ev_block_done);
+    if (g->ev_download_done) cudaEventDestroy(g->ev_download_done);
     if (g->ev_unpack_fork) cudaEventDestroy(g->ev_unpack_fork);
     if (g->ev_unpack_join) cudaEventDestroy(g->ev_unpack_join);
     for (cudaEvent_t e : g->ev_chunk) if (e) cudaEventDestroy(e);

@@ -77,7 +77,9 @@ int ensure_engine(Grid& g) {
 
 // Host images of A's and B's local blocks (hyd_gemm_host_*): SUMMA-C streams them to the device panel by panel
 // on an upload stream, so the H2D copies hide under the previous panels' GEMMs instead of preceding the whole Gemm.
-struct HostOperands { const void* A; i64 lda; const void* B; i64 ldb; };
+// With a host image of C as well (C, ldc; cblocks > 1; 1x1 grid) the local C is computed column block by column block and
+// each finished block goes back to the host on a download stream under the next block's GEMMs (summa_c_host_blocked).
+struct HostOperands { const void* A; i64 lda; const void* B; i64 ldb; void* C; i64 ldc; int cblocks; };
 
 // upload the slice of a local block that holds global rows/cols [k0, k0+kb) of the k-dimension
 template <typename T>
@@ -200,6 +202,81 @@ int gather_panels_ce(Grid& g, const DM& A, const DM& B, const DM& C, i64 k0, i64
     return g.world->push_wait(slotA, fromA.data(), cs) || g.world->push_wait(slotB, fromB.data(), cs);
 }
 
+// 1x1 grid, host-resident operands, C in `cblocks` column blocks (hyd_gemm_host_* with HYD_HOST_CBLOCKS > 1).
+// Stationary-C keeps every element of C open until the last k-panel, so a whole-C SUMMA can only start the download when
+// all the flops are done (2 GiB = 40 ms at 16384^2 fp64, the gap between `value` and `e2e`).  Block by block instead:
+//   upload stream   : for block j, panel p: [A(:,K_p) if j == 0] and op(B)(K_p, J_j)       (all enqueued up front)
+//   compute stream  : C(:,J_j) = alpha * sum_p A(:,K_p) op(B)(K_p,J_j) + beta C(:,J_j)      (waits per (j,p) upload event)
+//   download stream : C(:,J_j) -> host as soon as block j's last panel is done, under block j+1's GEMMs
+// A is uploaded once (block 0) and re-read from HBM by the later blocks.  Only the first (narrow) panel's upload and the
+// last block's download stay exposed.  The k-sum of every element is grouped exactly as in the unblocked host path.
+template <typename T>
+int summa_c_host_blocked(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, const DM& B, T beta, const DM& C,
+                         const std::vector<i64>& ks, cudaStream_t s, const HostOperands& ho) {
+    const size_t npanels = ks.size() - 1;
+    // column blocks: multiples of 128 columns (GEMM tile width; keeps every block's C and B pointers 16-byte aligned)
+    const i64 nblk_want = std::max<i64>(1, std::min<i64>(ho.cblocks, (n + 511) / 512));
+    const i64 wb = ((n + nblk_want - 1) / nblk_want + 127) / 128 * 128;
+    std::vector<i64> js;
+    for (i64 j0 = 0; j0 < n; j0 += wb) js.push_back(j0);
+    js.push_back(n);
+    const size_t nblk = js.size() - 1;
+    if (!g.download_stream) {
+        if (check_cuda(cudaStreamCreateWithFlags(&g.download_stream, cudaStreamNonBlocking), "download stream")) return 1;
+        cudaEventCreateWithFlags(&g.ev_block_done, cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&g.ev_download_done, cudaEventDisableTiming);
+    }
+    cudaStream_t us = g.comm_stream[1], ds = g.download_stream;
+    while (g.upload_ev.size() < npanels * nblk) {
+        cudaEvent_t e;
+        cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+        g.upload_ev.push_back(e);
+    }
+    // uploads may start once everything enqueued so far on the caller's stream (earlier users of the images) is done
+    if (check_cuda(cudaEventRecord(g.ev_join, s), "upload fork")) return 1;
+    cudaStreamWaitEvent(us, g.ev_join, 0);
+    cudaStreamWaitEvent(ds, g.ev_join, 0);
+    const T* hB = static_cast<const T*>(ho.B);
+    T* dB = static_cast<T*>(B.buf);
+    for (size_t j = 0; j < nblk; ++j) {
+        const i64 j0 = js[j], w = js[j + 1] - js[j];
+        for (size_t p = 0; p < npanels; ++p) {
+            const i64 k0 = ks[p], kb = ks[p + 1] - ks[p];
+            if (j == 0 && upload_k_slice<T>(g.shape, A, g.mc, g.mr, oA != 0, k0, kb, ho.A, ho.lda, us)) return 1;
+            // op(B)(k0:k0+kb, j0:j0+w): B is k x n (oB == 0: rows k0.., columns j0..) or n x k (rows j0.., columns k0..)
+            const i64 r0 = oB ? j0 : k0, nr = oB ? w : kb, c0 = oB ? k0 : j0, nc = oB ? kb : w;
+            if (check_cuda(cudaMemcpy2DAsync(dB + r0 + c0 * B.ldim, (size_t)B.ldim * sizeof(T), hB + r0 + c0 * ho.ldb,
+                                             (size_t)ho.ldb * sizeof(T), (size_t)nr * sizeof(T), (size_t)nc,
+                                             cudaMemcpyHostToDevice, us),
+                           "hyd_gemm_host: H2D block of B"))
+                return 1;
+            cudaEventRecord(g.upload_ev[j * npanels + p], us);
+        }
+    }
+    for (size_t j = 0; j < nblk; ++j) {
+        const i64 j0 = js[j], w = js[j + 1] - js[j];
+        T* c = static_cast<T*>(C.buf) + j0 * C.ldim;
+        for (size_t p = 0; p < npanels; ++p) {
+            const i64 k0 = ks[p], kb = ks[p + 1] - ks[p];
+            cudaStreamWaitEvent(s, g.upload_ev[j * npanels + p], 0);
+            const T* a = static_cast<const T*>(A.buf) + (oA ? k0 : k0 * A.ldim);
+            const T* b = dB + (oB ? j0 + k0 * B.ldim : k0 + j0 * B.ldim);
+            if (lgemm<T>(g, oA, oB, m, w, kb, alpha, a, A.ldim, b, B.ldim, k0 == 0 ? beta : T(1), c, C.ldim, s, 0)) return 1;
+        }
+        // block j is final: download it while block j+1 computes (stream order on ds keeps the blocks in sequence)
+        if (check_cuda(cudaEventRecord(g.ev_block_done, s), "block done")) return 1;
+        cudaStreamWaitEvent(ds, g.ev_block_done, 0);
+        if (check_cuda(cudaMemcpy2DAsync(static_cast<T*>(ho.C) + j0 * ho.ldc, (size_t)ho.ldc * sizeof(T), c,
+                                         (size_t)C.ldim * sizeof(T), (size_t)m * sizeof(T), (size_t)w, cudaMemcpyDeviceToHost, ds),
+                       "hyd_gemm_host: D2H block of C"))
+            return 1;
+    }
+    // the caller's stream is complete only when the last download is
+    if (check_cuda(cudaEventRecord(g.ev_download_done, ds), "download join")) return 1;
+    cudaStreamWaitEvent(s, g.ev_download_done, 0);
+    return 0;
+}
+
 // ---- SUMMA-C (stationary C) -------------------------------------------------
 template <typename T>
 int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, const DM& B, T beta, const DM& C, i64 nb,
@@ -227,6 +304,8 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
         ks.push_back(k);
     }
     const size_t npanels = ks.size() - 1;
+    if (ho && ho->C && ho->cblocks > 1 && sh.size() == 1 && Lc.lh > 0 && Lc.lw >= 1024)
+        return summa_c_host_blocked<T>(g, oA, oB, m, n, k, alpha, A, B, beta, C, ks, s, *ho);
     if (ho) {
         // all uploads are enqueued now, in panel order, on the upload stream; consumers wait per panel
         cudaStream_t us = g.comm_stream[1];
@@ -422,7 +501,8 @@ int read_proxy(Grid& g, TempPool& pool, const DM& a, int cd, int rd, bool colCon
 
 template <typename T>
 int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A0, const DM& B0, T beta, const DM& C0,
-              i64 blocksize, cudaStream_t s, const void* hostA, i64 hostLdA, const void* hostB, i64 hostLdB) {
+              i64 blocksize, cudaStream_t s, const void* hostA, i64 hostLdA, const void* hostB, i64 hostLdB, void* hostC,
+              i64 hostLdC, int* c_downloaded) {
     oA = oA ? 1 : 0;
     oB = oB ? 1 : 0;
     const i64 m = C0.height, n = C0.width;
@@ -444,7 +524,10 @@ int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A0, const DM&
     if (m == 0 || n == 0) return 0;
     // host-resident A/B (hyd_gemm_host_*): SUMMA-C on [MC,MR] operands streams them panel by panel under the
     // GEMMs; every other path uploads both blocks first.
-    HostOperands ho{hostA, hostLdA, hostB, hostLdB};
+    // HYD_HOST_CBLOCKS = n > 1: column-blocked host path on a 1x1 grid (summa_c_host_blocked); default 1 = whole-C download
+    static const int cblocks_env = getenv("HYD_HOST_CBLOCKS") ? std::max(1, atoi(getenv("HYD_HOST_CBLOCKS"))) : 1;
+    HostOperands ho{hostA, hostLdA, hostB, hostLdB, hostC, hostLdC, cblocks_env};
+    if (c_downloaded) *c_downloaded = 0;
     const bool stream_ops = hostA && hostB && alg == 3 && k > 0 && A0.colDist == MC && A0.rowDist == MR &&
                             B0.colDist == MC && B0.rowDist == MR;
     if (hostA && hostB && !stream_ops) {
@@ -477,7 +560,15 @@ int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A0, const DM&
         if (read_proxy<T>(g, pool, B0, MC, MR, false, 0, false, 0, B, s)) return 1;
         if (alg == 1) rc = summa_a<T>(g, oA, oB, m, n, k, alpha, A, B, C, blocksize, s);
         else if (alg == 2) rc = summa_b<T>(g, oA, oB, m, n, k, alpha, A, B, C, blocksize, s);
-        else rc = summa_c<T>(g, oA, oB, m, n, k, alpha, A, B, fuse_beta ? beta : T(1), C, blocksize, s, stream_ops ? &ho : nullptr);
+        else {
+            // the blocked host path writes C's blocks to the host itself; it applies when nothing sits between the caller's
+            // blocks and the engine (no proxies) on a 1x1 grid with a C wide enough to split
+            const bool blocked = stream_ops && hostC && cblocks_env > 1 && g.shape.size() == 1 && C.buf == C0.buf &&
+                                 A.buf == A0.buf && B.buf == B0.buf && Lc0.lh > 0 && Lc0.lw >= 1024 && fuse_beta;
+            if (!blocked) ho.C = nullptr;
+            rc = summa_c<T>(g, oA, oB, m, n, k, alpha, A, B, fuse_beta ? beta : T(1), C, blocksize, s, stream_ops ? &ho : nullptr);
+            if (!rc && blocked && c_downloaded) *c_downloaded = 1;
+        }
     }
     if (rc) return rc;
     if (C.buf != C0.buf) {  // write-back half of the ReadWrite proxy
@@ -487,7 +578,7 @@ int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A0, const DM&
     return 0;
 }
 
-template int dist_gemm<double>(Grid&, int, int, int, double, const DM&, const DM&, double, const DM&, i64, cudaStream_t, const void*, i64, const void*, i64);
-template int dist_gemm<float>(Grid&, int, int, int, float, const DM&, const DM&, float, const DM&, i64, cudaStream_t, const void*, i64, const void*, i64);
+template int dist_gemm<double>(Grid&, int, int, int, double, const DM&, const DM&, double, const DM&, i64, cudaStream_t, const void*, i64, const void*, i64, void*, i64, int*);
+template int dist_gemm<float>(Grid&, int, int, int, float, const DM&, const DM&, float, const DM&, i64, cudaStream_t, const void*, i64, const void*, i64, void*, i64, int*);
 
 }  // namespace hyd

@@ -5,6 +5,7 @@ Tolerances (written here, as BASELINE.json asks): relative Frobenius error <= 1e
 1e-5*sqrt(k) (fp32); and the reference's own bound |x-y| <= 1e-10 / 1e-3 at alpha=2, beta=3
 (tests/blas_like/BasicGemm.cpp:93-94,108)."""
 import itertools
+import os
 
 import numpy as np
 import pytest
@@ -133,6 +134,18 @@ def test_gemm_host_buffers_roundtrip():
         return cm.local_numpy()
     got = H.run_ranks(1, body)[0]
     assert np.abs(got - Cexp.block(0)).max() <= 1e-10
+
+
+@pytest.mark.skipif(os.environ.get("HYD_TEST_EXPERIMENTAL") != "1",
+                    reason="column-blocked host path (HYD_HOST_CBLOCKS > 1) is off by default and was written after round 1's "
+                           "GPU budget was spent; set HYD_TEST_EXPERIMENTAL=1 to run tools/host_blocked_check.py")
+def test_gemm_host_column_blocked_path_is_bit_identical():
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "tools", "host_blocked_check.py")], capture_output=True, text=True,
+                         timeout=900)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
 
 
 def test_gemm_over_staged_transport(monkeypatch):
