@@ -92,6 +92,8 @@ _sig("hyd_gemm_f32", i32, [vp, i32, i32, i32, f32, dmp, dmp, f32, dmp, i64, vp])
 _sig("hyd_gemm_host_f64", i32, [vp, i32, i32, i32, f64, dmp, dmp, f64, dmp, i64, vp])
 _sig("hyd_gemm_host_f32", i32, [vp, i32, i32, i32, f32, dmp, dmp, f32, dmp, i64, vp])
 _sig("hyd_probe_peak", i32, [i32, i32, i32, C.POINTER(f64)])
+_sig("hyd_memcopy2d_async", i32, [vp, i64, vp, i64, i64, i64, i32, i32, vp])
+_sig("hyd_memcopy1d_async", i32, [vp, vp, i64, i32, i32, vp])
 # seam S2: copy::util pack / unpack and axpy::util::InterleaveMatrixUpdate with the reference's argument lists
 for _sf, _ft in (("f64", f64), ("f32", f32)):
     _sig("hyd_interleave_" + _sf, i32, [i64, i64, vp, i64, i64, vp, i64, i64, vp])

@@ -289,6 +289,37 @@ int hyd_scale2d_f32(int64_t m, int64_t n, float alpha, float* A, int64_t lda, hy
     return hyd::scale_local<float>(m, n, alpha, A, lda, (cudaStream_t)s);
 }
 
+static int copy_kind(int kind, cudaMemcpyKind* out, const char* who) {
+    if (kind == 0) *out = cudaMemcpyHostToDevice;
+    else if (kind == 1) *out = cudaMemcpyDeviceToHost;
+    else if (kind == 2) *out = cudaMemcpyDeviceToDevice;
+    else return set_error("%s: kind must be 0 (H2D), 1 (D2H) or 2 (D2D)", who);
+    return 0;
+}
+int hyd_memcopy2d_async(void* dst, int64_t dst_ldim, const void* src, int64_t src_ldim, int64_t height, int64_t width,
+                        int elem_size, int kind, hyd_stream_t stream) {
+    const char* who = "hyd_memcopy2d_async";
+    cudaMemcpyKind k = cudaMemcpyDefault;
+    if (copy_kind(kind, &k, who)) return 1;
+    if (elem_size != 4 && elem_size != 8) return set_error("%s: elem_size must be 4 or 8", who);
+    if (height < 0 || width < 0) return set_error("%s: negative dimension", who);
+    if (height == 0 || width == 0) return 0;
+    if (!dst || !src) return set_error("%s: null buffer", who);
+    if (dst_ldim < height || src_ldim < height) return set_error("%s: leading dimension too small", who);
+    return hyd::check_cuda(cudaMemcpy2DAsync(dst, (size_t)dst_ldim * elem_size, src, (size_t)src_ldim * elem_size,
+                                             (size_t)height * elem_size, (size_t)width, k, (cudaStream_t)stream), who);
+}
+int hyd_memcopy1d_async(void* dst, const void* src, int64_t count, int elem_size, int kind, hyd_stream_t stream) {
+    const char* who = "hyd_memcopy1d_async";
+    cudaMemcpyKind k = cudaMemcpyDefault;
+    if (copy_kind(kind, &k, who)) return 1;
+    if (elem_size != 4 && elem_size != 8) return set_error("%s: elem_size must be 4 or 8", who);
+    if (count < 0) return set_error("%s: negative count", who);
+    if (count == 0) return 0;
+    if (!dst || !src) return set_error("%s: null buffer", who);
+    return hyd::check_cuda(cudaMemcpyAsync(dst, src, (size_t)count * elem_size, k, (cudaStream_t)stream), who);
+}
+
 int hyd_gemm_host_f64(hyd_grid* g, int oA, int oB, int alg, double alpha, const hyd_dm* A, const hyd_dm* B, double beta,
                       const hyd_dm* C, int64_t blocksize, hyd_stream_t stream) {
     return gemm_host<double>(g, oA, oB, alg, alpha, A, B, beta, C, blocksize, (cudaStream_t)stream);

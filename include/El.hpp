@@ -400,6 +400,23 @@ void Hadamard_GPU_impl(size_t height, size_t width, const T* X, size_t colStride
 }
 }  // namespace hydrogen_gpu
 
+// InterDeviceCopy<SrcD,DestD> (include/hydrogen/device/gpu/CUDA.hpp:229-420): the reference's names and argument order
+template <Device SrcD, Device DestD> struct InterDeviceCopy {
+    static constexpr int kind() { return SrcD == Device::CPU ? (DestD == Device::GPU ? 0 : -1) : (DestD == Device::CPU ? 1 : 2); }
+    template <typename T>
+    static void MemCopy1DAsync(T* dest, const T* src, size_t size, cudaStream_t stream = nullptr) {
+        static_assert(kind() >= 0, "host-to-host copies do not go through the device library");
+        detail::check(hyd_memcopy1d_async(dest, src, (Int)size, (int)sizeof(T), kind(), stream));
+    }
+    template <typename T>
+    static void MemCopy2DAsync(T* dest, size_t dest_ldim, const T* src, size_t src_ldim, size_t height, size_t width,
+                               cudaStream_t stream = nullptr) {
+        static_assert(kind() >= 0, "host-to-host copies do not go through the device library");
+        detail::check(hyd_memcopy2d_async(dest, (Int)dest_ldim, src, (Int)src_ldim, (Int)height, (Int)width, (int)sizeof(T), kind(),
+                                          stream));
+    }
+};
+
 // ---- copy::util / axpy::util on device buffers (include/El/blas_like/level1/Copy/util.hpp, Axpy/util.hpp): the
 // reference's names and argument order; each call is one kernel launch for all portions ----
 namespace copy { namespace util {

@@ -304,6 +304,16 @@ int hyd_gemm_host_f64(hyd_grid* g, int orientA, int orientB, int alg, double alp
 int hyd_gemm_host_f32(hyd_grid* g, int orientA, int orientB, int alg, float alpha, const hyd_dm* A, const hyd_dm* B,
                       float beta, const hyd_dm* C, int64_t blocksize, hyd_stream_t stream);
 
+/* Inter-device copies of local blocks: `height` x `width` elements of `elem_size` bytes (4 or 8), column-major
+ * with leading dimensions in elements; kind: 0 = host -> device, 1 = device -> host, 2 = device -> device.  Asynchronous with
+ * respect to the host when the host side is pinned; ordered on `stream`.
+ * ref: InterDeviceCopy<SrcD,DestD>::MemCopy2DAsync / MemCopy1DAsync (include/hydrogen/device/gpu/CUDA.hpp:229-420), callers
+ *      Copy / CopyAsync(Matrix<T,CPU>, Matrix<T,GPU>) and back (include/El/blas_like/level1/Copy.hpp:140-207) and the
+ *      cross-device DistMatrix assignments (src/core/DistMatrix/ElementMatrix/MC_STAR.cpp:304-390). */
+int hyd_memcopy2d_async(void* dst, int64_t dst_ldim, const void* src, int64_t src_ldim, int64_t height, int64_t width,
+                        int elem_size, int kind, hyd_stream_t stream);
+int hyd_memcopy1d_async(void* dst, const void* src, int64_t count, int elem_size, int kind, hyd_stream_t stream);
+
 /* Pipe-peak probe (register-resident loops): kind 0 = FP64 DFMA, 1 = DMMA m8n8k4, 2 = DMMA m16n8k16,
  * 3 = FP32 FFMA.  Writes achieved TFLOP/s.  Measurement aid for the roofline denominator. */
 int hyd_probe_peak(int kind, int iters, int ctas_per_sm, double* tflops);

@@ -28,6 +28,8 @@ template <typename T> void inst(El::Grid& g) {
     El::gpu_blas::Gemm(El::NORMAL, El::NORMAL, 2, 2, 2, T(1), p, 2, p, 2, T(0), p, 2, si);
     El::gpu_blas::Copy(El::TRANSPOSE, 2, 2, p, 2, p, 2, si);
     El::gpu_blas::Copy(El::NORMAL, 2, 2, p, 2, p, 2, si);
+    El::InterDeviceCopy<El::Device::CPU, El::Device::GPU>::MemCopy2DAsync(p, 2, p, 2, 2, 2, si.stream_);
+    El::InterDeviceCopy<El::Device::GPU, El::Device::CPU>::MemCopy1DAsync(p, p, 4, si.stream_);
     El::gpu_blas::Axpy(2, 2, T(1), p, 2, p, 2, si);
     El::gpu_blas::Scale(2, 2, T(1), p, 2, si);
     El::gpu_blas::Axpy(El::TRANSPOSE, 2, 2, T(1), p, 2, p, 2, si);

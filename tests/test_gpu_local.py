@@ -189,3 +189,34 @@ def test_launch_counter_and_probe():
     Cm = torch.zeros((8, 8), dtype=torch.float64, device=DEV)
     check(lib.hyd_scale2d_f64(8, 8, 2.0, C.c_void_p(Cm.data_ptr()), 8, None))
     assert lib.hyd_launch_count() > n0
+
+
+def test_interdevice_copies_roundtrip():
+    """hyd_memcopy{2d,1d}_async = InterDeviceCopy<..>::MemCopy{2D,1D}Async (include/hydrogen/device/gpu/CUDA.hpp:229-420;
+    Copy(Matrix<T,CPU>, Matrix<T,GPU>) and back, Copy.hpp:140-207): block with leading dimensions up, down, device to device;
+    padding of the destination untouched; argument errors."""
+    import ctypes as C
+    from elemental_b200 import lib, check
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for dt, es in ((torch.float64, 8), (torch.float32, 4)):
+        m, n, lda, ldb = 37, 11, 40, 45
+        hA = (torch.arange(lda * n, dtype=dt) % 1000).pin_memory()
+        dB = torch.full((ldb * n,), -5.0, dtype=dt, device="cuda")
+        dC = torch.full((lda * n,), -6.0, dtype=dt, device="cuda")
+        hD = torch.full((ldb * n,), -7.0, dtype=dt).pin_memory()
+        p = lambda t: C.c_void_p(t.data_ptr())
+        check(lib.hyd_memcopy2d_async(p(dB), ldb, p(hA), lda, m, n, es, 0, st))      # host -> device
+        check(lib.hyd_memcopy2d_async(p(dC), lda, p(dB), ldb, m, n, es, 2, st))      # device -> device
+        check(lib.hyd_memcopy2d_async(p(hD), ldb, p(dC), lda, m, n, es, 1, st))      # device -> host
+        torch.cuda.current_stream().synchronize()
+        A2, D2 = hA.view(n, lda), hD.view(n, ldb)
+        assert torch.equal(D2[:, :m], A2[:, :m])
+        assert bool((D2[:, m:] == -7.0).all()) and bool((dB.view(n, ldb)[:, m:] == -5.0).all())
+        h1 = torch.zeros(100, dtype=dt).pin_memory()
+        d1 = torch.arange(100, dtype=dt, device="cuda")
+        check(lib.hyd_memcopy1d_async(p(h1), p(d1), 100, es, 1, st))
+        torch.cuda.current_stream().synchronize()
+        assert torch.equal(h1, d1.cpu())
+        assert lib.hyd_memcopy2d_async(p(dB), m - 1, p(hA), lda, m, n, es, 0, st) != 0       # ldim < height
+        assert lib.hyd_memcopy2d_async(p(dB), ldb, p(hA), lda, m, n, es, 7, st) != 0         # bad kind
+        assert lib.hyd_memcopy2d_async(p(dB), ldb, p(hA), lda, 0, n, es, 0, st) == 0         # empty
