@@ -50,6 +50,8 @@ _sig("hyd_version", i32, [])
 _sig("hyd_launch_count", C.c_longlong, [])
 _sig("hyd_lgemm_f64", i32, [i32, i32, i64, i64, i64, f64, vp, i64, vp, i64, f64, vp, i64, vp])
 _sig("hyd_lgemm_f32", i32, [i32, i32, i64, i64, i64, f32, vp, i64, vp, i64, f32, vp, i64, vp])
+_sig("hyd_lgemm_f16", i32, [i32, i32, i64, i64, i64, f32, vp, i64, vp, i64, f32, vp, i64, vp])
+_sig("hyd_lgemm_bf16", i32, [i32, i32, i64, i64, i64, f32, vp, i64, vp, i64, f32, vp, i64, vp])
 _sig("hyd_transpose_f64", i32, [i64, i64, vp, i64, vp, i64, vp])
 _sig("hyd_transpose_f32", i32, [i64, i64, vp, i64, vp, i64, vp])
 _sig("hyd_copy2d_f64", i32, [i64, i64, vp, i64, vp, i64, vp])

@@ -103,6 +103,16 @@ int hyd_lgemm_f32(int tA, int tB, int64_t m, int64_t n, int64_t k, float alpha, 
     ++hyd::g_launches;
     return hyd::lgemm_f32(tA ? 1 : 0, tB ? 1 : 0, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, (cudaStream_t)stream);
 }
+int hyd_lgemm_f16(int tA, int tB, int64_t m, int64_t n, int64_t k, float alpha, const void* A, int64_t lda, const void* B,
+                  int64_t ldb, float beta, void* C, int64_t ldc, hyd_stream_t stream) {
+    ++hyd::g_launches;
+    return hyd::lgemm_f16(tA ? 1 : 0, tB ? 1 : 0, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, (cudaStream_t)stream);
+}
+int hyd_lgemm_bf16(int tA, int tB, int64_t m, int64_t n, int64_t k, float alpha, const void* A, int64_t lda, const void* B,
+                   int64_t ldb, float beta, void* C, int64_t ldc, hyd_stream_t stream) {
+    ++hyd::g_launches;
+    return hyd::lgemm_bf16(tA ? 1 : 0, tB ? 1 : 0, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, (cudaStream_t)stream);
+}
 int hyd_probe_peak(int kind, int iters, int ctas_per_sm, double* tflops) {
     return hyd::probe_peak(kind, iters, ctas_per_sm, tflops);
 }

@@ -33,5 +33,10 @@ int lgemm_f32_tc(int tA, int tB, long long m, long long n, long long k, float al
 int lgemm_f32(int tA, int tB, long long m, long long n, long long k, float alpha, const float* A,
               long long lda, const float* B, long long ldb, float beta, float* C, long long ldc,
               cudaStream_t s);
+// half-precision operands / result, fp32 accumulation (lgemm_f16_tc.cu; pointers to __half / __nv_bfloat16 storage)
+int lgemm_f16(int tA, int tB, long long m, long long n, long long k, float alpha, const void* A, long long lda, const void* B,
+              long long ldb, float beta, void* C, long long ldc, cudaStream_t s);
+int lgemm_bf16(int tA, int tB, long long m, long long n, long long k, float alpha, const void* A, long long lda, const void* B,
+               long long ldb, float beta, void* C, long long ldc, cudaStream_t s);
 
 }  // namespace hyd

@@ -47,6 +47,16 @@ int hyd_lgemm_f32(int transA, int transB, int64_t m, int64_t n, int64_t k, float
                   const float* A, int64_t lda, const float* B, int64_t ldb, float beta,
                   float* C, int64_t ldc, hyd_stream_t stream);
 
+/* Half-precision operands and result (IEEE fp16 / bfloat16 storage, 2 bytes per element), fp32 accumulation, alpha and beta
+ * in fp32, one rounding to the half type at the store.  SURVEY 8f N3.
+ * ref: Gemm on Matrix<gpu_half_type,Device::GPU> (src/blas_like/level3/Gemm.cpp:460-467) -> cublasHgemm
+ *      (src/core/imports/cublas.cpp:213); bf16 has no counterpart in the reference.
+ * EXPERIMENTAL: added after round 1's last GPU call -- compiles for sm_100a, not yet run on a GPU; not used by hyd_gemm_*. */
+int hyd_lgemm_f16(int transA, int transB, int64_t m, int64_t n, int64_t k, float alpha, const void* A, int64_t lda,
+                  const void* B, int64_t ldb, float beta, void* C, int64_t ldc, hyd_stream_t stream);
+int hyd_lgemm_bf16(int transA, int transB, int64_t m, int64_t n, int64_t k, float alpha, const void* A, int64_t lda,
+                   const void* B, int64_t ldb, float beta, void* C, int64_t ldc, hyd_stream_t stream);
+
 /* B := A^T (A is m x n, B is n x m), bit-exact.
  * ref: gpu_blas::Copy(TRANSPOSE,...) -> cublas?geam(1,A,0,-) include/hydrogen/blas/GPU_BLAS_impl.hpp:152-172,558-567;
  *      caller El::Transpose(Matrix<T,GPU>) include/El/blas_like/level1/Transpose.hpp:161-181. */

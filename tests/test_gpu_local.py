@@ -220,3 +220,41 @@ def test_interdevice_copies_roundtrip():
         assert lib.hyd_memcopy2d_async(p(dB), m - 1, p(hA), lda, m, n, es, 0, st) != 0       # ldim < height
         assert lib.hyd_memcopy2d_async(p(dB), ldb, p(hA), lda, m, n, es, 7, st) != 0         # bad kind
         assert lib.hyd_memcopy2d_async(p(dB), ldb, p(hA), lda, 0, n, es, 0, st) == 0         # empty
+
+
+@pytest.mark.skipif(__import__("os").environ.get("HYD_TEST_EXPERIMENTAL") != "1",
+                    reason="hyd_lgemm_{f16,bf16} (tcgen05 kind::f16, csrc/lgemm_f16_tc.cu) was written after round 1's GPU budget "
+                           "was spent and has not run on a GPU yet; set HYD_TEST_EXPERIMENTAL=1")
+@pytest.mark.parametrize("tdt,name", [(torch.bfloat16, "bf16"), (torch.float16, "f16")])
+def test_lgemm_half(tdt, name):
+    """fp16 / bf16 operands and result, fp32 accumulation: against torch's fp32 product of the same half inputs, rounded once
+    to the half type.  Tolerance: one half-precision ulp of the result plus fp32 accumulation-order noise
+    (|d| <= 2^-8 |c| + 1e-3*sqrt(k)*eps32-scale for bf16, 2^-11 for fp16)."""
+    import ctypes as C
+    fn = getattr(lib, "hyd_lgemm_" + name)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    gen = torch.Generator(device=DEV).manual_seed(77)
+    ulp = 2.0 ** -8 if tdt == torch.bfloat16 else 2.0 ** -11
+    for (m, n, k) in [(128, 128, 64), (256, 384, 192), (1000, 520, 328), (2048, 2048, 1024), (100, 60, 40)]:
+        for tA, tB in itertools.product((0, 1), (0, 1)):
+            for beta in (0.0, 0.5):
+                ar, ac = (k, m) if tA else (m, k)
+                br, bc = (n, k) if tB else (k, n)
+                lda, ldb, ldc = -(-ar // 8) * 8 + 8, -(-br // 8) * 8, m + 2
+                A = ((torch.rand((ac, lda), device=DEV, generator=gen) * 2 - 1)).to(tdt)
+                B = ((torch.rand((bc, ldb), device=DEV, generator=gen) * 2 - 1)).to(tdt)
+                Cm = ((torch.rand((n, ldc), device=DEV, generator=gen) * 2 - 1)).to(tdt)
+                C0 = Cm.clone()
+                check(fn(tA, tB, m, n, k, C.c_float(0.75), C.c_void_p(A.data_ptr()), lda, C.c_void_p(B.data_ptr()), ldb,
+                         C.c_float(beta), C.c_void_p(Cm.data_ptr()), ldc, st))
+                torch.cuda.synchronize()
+                a = A[:, :ar].float().t()    # ar x ac (column-major storage: A[j, i] = element (i, j))
+                b = B[:, :br].float().t()
+                opa = a.t() if tA else a     # m x k
+                opb = b.t() if tB else b     # k x n
+                ref = 0.75 * (opa @ opb) + beta * C0[:, :m].float().t()
+                got = Cm[:, :m].float().t()
+                err = (got - ref).abs()
+                tol = ulp * ref.abs() + 4e-6 * k ** 0.5 + 1e-6
+                assert bool((err <= tol).all()), (name, m, n, k, tA, tB, beta, float(err.max()))
+                assert torch.equal(Cm[:, m:], C0[:, m:])     # ldc padding untouched
