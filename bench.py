@@ -155,6 +155,28 @@ class Clocks:
                 "samples": len(sm), "power_w_max": max(pw) if pw else None}
 
 
+def bind_to_gpu_numa_node(local_rank):
+    """Multi-GPU runs: pin this rank to the CPU cores NVML reports as local to its GPU, so that the pinned host blocks of
+    the end-to-end leg are first-touched on the GPU's own NUMA node and H2D/D2H do not cross the socket link.  Launchers
+    such as torchrun do not bind ranks.  Never fatal; HYD_BENCH_NUMA=0 disables.  (One rank keeps every core at N=1:
+    the CPU baseline leg runs there.)"""
+    if os.environ.get("HYD_BENCH_NUMA", "1") == "0":
+        return False
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * w + b for w, word in enumerate(words) for b in range(64) if (int(word) >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return False
+        os.sched_setaffinity(0, cpus)
+        return True
+    except Exception:  # noqa: BLE001
+        return False
+
+
 # ---------------------------------------------------------------------------------------------
 def run_ours(args):
     import ctypes as C
@@ -170,6 +192,7 @@ def run_ours(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product has no CPU path")
     torch.cuda.set_device(local_rank)
+    numa_bound = bind_to_gpu_numa_node(local_rank) if world_size > 1 else False
     dist = None
     if world_size > 1:
         import torch.distributed as dist
@@ -298,7 +321,7 @@ def run_ours(args):
                 "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": workload_name(n, (r, c)),
                            "blocksize": nb, "alpha": 1.0, "beta": 0.0, "l2": "operands (3 x %.1f GiB per GPU) exceed the 126 MB L2" %
-                           (A.lh * A.lw * 8 / 2 ** 30), "comm": world.kind},
+                           (A.lh * A.lw * 8 / 2 ** 30), "comm": world.kind, "ranks_bound_to_gpu_numa_node": numa_bound},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
                 "frac_of_fp64_peak_all_gpus": round(value / (peak.value * args.gpus), 4)}
         print(json.dumps(line), flush=True)
