@@ -84,6 +84,11 @@ int ref_gpu_finalize() { REF_TRY(GPUManager::Destroy()) }
     int ref_gpu_axpy2d_##sfx(int64_t m, int64_t n, T alpha, const T* A, int64_t lda, T* B, int64_t ldb, void* s) {  \
         REF_TRY(gpu_blas::Axpy((Int)m, (Int)n, alpha, A, (Int)lda, B, (Int)ldb, si(s)))                             \
     }                                                                                                                \
+    /* gpu_blas::Axpy(TransposeMode, m, n, ...): B (m x n) += alpha op(A) -> cublas?geam (GPU_BLAS_impl.hpp:110-132,530-540) */ \
+    int ref_gpu_axpy_trans_##sfx(int trans, int64_t m, int64_t n, T alpha, const T* A, int64_t lda, T* B, int64_t ldb,  \
+                                 void* s) {                                                                          \
+        REF_TRY(gpu_blas::Axpy(tmode(trans), (Int)m, (Int)n, alpha, A, (Int)lda, B, (Int)ldb, si(s)))               \
+    }                                                                                                                \
     int ref_gpu_scale2d_##sfx(int64_t m, int64_t n, T alpha, T* A, int64_t lda, void* s) {                          \
         REF_TRY(gpu_blas::Scale((Int)m, (Int)n, alpha, A, (Int)lda, si(s)))                                         \
     }                                                                                                                \
