@@ -28,11 +28,12 @@ constexpr int BM = 128, BK = 16;
 // Two tile configurations (template parameter WN = consumer warps along n):
 //   WN = 4 : 128 x 128 tile, 8 consumer warps (2 x 4), 6-stage ring, ONE CTA per SM  (setmaxnreg split)
 //   WN = 2 : 128 x  64 tile, 4 consumer warps (2 x 2), 4-stage ring, TWO CTAs per SM -- while one CTA
-//            runs its epilogue (C read-modify-write) the other keeps the DMMA pipe busy.
+//            runs its epilogue (C read-modify-write) the other keeps the DMMA pipe busy (HYD_DGEMM_WN=2; the
+//            setmaxnreg split that makes it spill-free was added after round 1's last GPU call: unmeasured).
 template <int WN> struct Cfg {
     static constexpr int BN = 32 * WN;
     static constexpr int kConsumerWarps = 2 * WN;
-    static constexpr int kThreads = (WN == 4) ? (kConsumerWarps + 4) * 32 : (kConsumerWarps + 1) * 32;
+    static constexpr int kThreads = (kConsumerWarps + 4) * 32;   // + one producer warpgroup (setmaxnreg acts on whole warpgroups)
     static constexpr int kCtasPerSm = (WN == 4) ? 1 : 2;
     static constexpr int kStageBytesA = BM * BK * 8;
     static constexpr int kStageBytesB = BN * BK * 8;
@@ -111,7 +112,7 @@ dgemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
 
     if (warp >= kConsumerWarps) {
         // ===================== TMA producer =====================
-        if (WN == 4) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
         if (warp == kConsumerWarps && lane == 0) {
             tma_prefetch_desc(&mapA);
             tma_prefetch_desc(&mapB);
@@ -149,6 +150,7 @@ dgemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
 
     // ===================== DMMA consumers =====================
     if (WN == 4) asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+    else asm volatile("setmaxnreg.inc.sync.aligned.u32 208;");   // two CTAs of 256 threads per SM: 128 x (208 + 40) registers each
     const int g = lane >> 2, t = lane & 3;
     const int wm = warp & 1, wn = warp >> 1;  // 2 x WN warps, warp tile 64 x 32
     uint32_t offA[4], offB[4];
