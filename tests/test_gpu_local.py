@@ -191,6 +191,8 @@ def test_launch_counter_and_probe():
     assert lib.hyd_launch_count() > n0
 
 
+@pytest.mark.skipif(__import__("os").environ.get("HYD_TEST_EXPERIMENTAL") != "1",
+                    reason="hyd_memcopy{1d,2d}_async were added after round 1's last GPU call; set HYD_TEST_EXPERIMENTAL=1")
 def test_interdevice_copies_roundtrip():
     """hyd_memcopy{2d,1d}_async = InterDeviceCopy<..>::MemCopy{2D,1D}Async (include/hydrogen/device/gpu/CUDA.hpp:229-420;
     Copy(Matrix<T,CPU>, Matrix<T,GPU>) and back, Copy.hpp:140-207): block with leading dimensions up, down, device to device;
