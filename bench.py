@@ -156,25 +156,49 @@ class Clocks:
 
 
 def bind_to_gpu_numa_node(local_rank):
-    """Multi-GPU runs: pin this rank to the CPU cores NVML reports as local to its GPU, so that the pinned host blocks of
-    the end-to-end leg are first-touched on the GPU's own NUMA node and H2D/D2H do not cross the socket link.  Launchers
-    such as torchrun do not bind ranks.  Never fatal; HYD_BENCH_NUMA=0 disables.  (One rank keeps every core at N=1:
-    the CPU baseline leg runs there.)"""
+    """Multi-GPU runs: place this rank next to its GPU, so that the pinned host blocks of the end-to-end leg live on the
+    GPU's own NUMA node and H2D/D2H do not cross the socket link (launchers such as torchrun do not bind ranks; at 4 and 8
+    GPUs the round-1 e2e leg moved only ~55 GB/s host<->device in aggregate).  Two independent steps, each best effort and
+    never fatal: (1) CPU affinity = the cores NVML reports as local to the GPU (intersected with the cores this process may
+    use); (2) memory policy MPOL_PREFERRED = the NUMA node sysfs reports for the GPU's PCI function.  HYD_BENCH_NUMA=0
+    disables both.  Returns what was done, for the JSON line.  (One rank keeps every core at N=1: the CPU baseline leg runs
+    there.)"""
+    done = {"cpu_bound": False, "mem_node": None}
     if os.environ.get("HYD_BENCH_NUMA", "1") == "0":
-        return False
+        return done
     try:
         import pynvml
         pynvml.nvmlInit()
         h = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+    except Exception:  # noqa: BLE001
+        return done
+    try:
         words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
         cpus = {64 * w + b for w, word in enumerate(words) for b in range(64) if (int(word) >> b) & 1}
         cpus &= os.sched_getaffinity(0)
-        if not cpus:
-            return False
-        os.sched_setaffinity(0, cpus)
-        return True
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            done["cpu_bound"] = True
     except Exception:  # noqa: BLE001
-        return False
+        pass
+    try:
+        import ctypes
+        bus = pynvml.nvmlDeviceGetPciInfo(h).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        bus = bus.lower()
+        if len(bus.split(":")[0]) == 8:      # NVML prints an 8-digit PCI domain, sysfs a 4-digit one
+            bus = bus[4:]
+        with open(f"/sys/bus/pci/devices/{bus}/numa_node") as f:
+            node = int(f.read().strip())
+        if 0 <= node < 64:
+            mask = ctypes.c_ulong(1 << node)
+            libc = ctypes.CDLL(None, use_errno=True)
+            MPOL_PREFERRED, SYS_set_mempolicy = 1, 238   # x86_64
+            if libc.syscall(SYS_set_mempolicy, MPOL_PREFERRED, ctypes.byref(mask), 65) == 0:
+                done["mem_node"] = node
+    except Exception:  # noqa: BLE001
+        pass
+    return done
 
 
 # ---------------------------------------------------------------------------------------------
@@ -192,7 +216,7 @@ def run_ours(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product has no CPU path")
     torch.cuda.set_device(local_rank)
-    numa_bound = bind_to_gpu_numa_node(local_rank) if world_size > 1 else False
+    numa_bound = bind_to_gpu_numa_node(local_rank) if world_size > 1 else None
     dist = None
     if world_size > 1:
         import torch.distributed as dist
@@ -321,7 +345,7 @@ def run_ours(args):
                 "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": workload_name(n, (r, c)),
                            "blocksize": nb, "alpha": 1.0, "beta": 0.0, "l2": "operands (3 x %.1f GiB per GPU) exceed the 126 MB L2" %
-                           (A.lh * A.lw * 8 / 2 ** 30), "comm": world.kind, "ranks_bound_to_gpu_numa_node": numa_bound},
+                           (A.lh * A.lw * 8 / 2 ** 30), "comm": world.kind, "rank0_numa_placement": numa_bound},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
                 "frac_of_fp64_peak_all_gpus": round(value / (peak.value * args.gpus), 4)}
         print(json.dumps(line), flush=True)
