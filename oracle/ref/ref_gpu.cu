@@ -10,8 +10,8 @@
 //                                               :363-722 InterleaveMatrix -> copy_2d_kernel per portion)
 //   include/El/blas_like/level1/Axpy/util.hpp   InterleaveMatrixUpdate (GPU) -> axpy_2d kernel
 // TEST / MEASUREMENT INFRASTRUCTURE ONLY: this is "the recompiled reference" the product is compared with on the
-// GPU box -- bit-exact parity of every copy (tests/test_gpu_ref_kernels.py, tools/ref_gpu_check.cpp) and a
-// GPU-vs-GPU baseline (tools/ref_gpu_bench.py).  The product never links or loads it.
+// GPU box -- bit-exact parity of every copy (tests/test_gpu_ref_kernels.py, tools/ref_gpu_check.cpp, tools/ref_gpu_check_level1.cpp) and a
+// GPU-vs-GPU baseline (the timing half of tools/ref_gpu_check.cpp).  The product never links or loads it.
 // One change is forced by the toolkit: cudaPointerAttributes::memoryType (CUDA <= 10) is named ::type since CUDA 11;
 // the Makefile passes -DmemoryType=type (include/hydrogen/device/gpu/CUDA.hpp:128).
 #include <El/hydrogen_config.h>
