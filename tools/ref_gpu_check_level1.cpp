@@ -259,6 +259,78 @@ template <typename T> static void packs() {
     }
 }
 
+// REF_CHECK_SUMMA=1: the headline workload on ONE GPU, reference-built against product.  On a 1x1 grid the reference's
+// SUMMA_NNC (src/blas_like/level3/Gemm/NN.hpp:325-367) degenerates to, per k-panel of width Blocksize():
+//   A1[MC,*] <- A1      RowAllGather with stride 1 = a local Copy                  (Copy/RowAllGather.hpp:35-38)
+//   B1^T[MR,*] <- B1    Transpose: a local cublasDgeam                              (Transpose.hpp:161-181)
+//   C += alpha A1 (B1^T)^T     LocalGemm(NORMAL, TRANSPOSE) -> cublasDgemm          (Gemm.cpp:152-155)
+// after one Scale(beta, C) (Gemm.cpp:287; beta = 0 here, i.e. Zero(C)).  Built here from the recompiled reference layer's own entry points and timed
+// against hyd_gemm_f64 (SUMMA-C) on the same operands; the results must agree within 1e-13*sqrt(k) relative Frobenius.
+static void summa_1x1() {
+    typedef int (*copy_fn)(int, i64, i64, const double*, i64, double*, i64, void*);
+    typedef int (*scale_fn)(i64, i64, double, double*, i64, void*);
+    typedef int (*gemm_fn)(int, int, i64, i64, i64, double, const double*, i64, const double*, i64, double, double*, i64, void*);
+    copy_fn rcopy = sym<copy_fn>("ref_gpu_copy_f64");
+    scale_fn rfill = sym<scale_fn>("ref_gpu_fill_f64");   // Scale(0, C) is Zero(C) = Fill (level1/Scale.hpp), same argument list
+    gemm_fn rgemm = sym<gemm_fn>("ref_gpu_gemm_f64");
+    const i64 n = std::getenv("REF_CHECK_N") ? atoll(std::getenv("REF_CHECK_N")) : 16384;
+    hyd_local_group* grp = nullptr;
+    hyd_world* w = nullptr;
+    hyd_grid* g = nullptr;
+    H(hyd_local_group_create(1, &grp), "local group"); H(hyd_world_create_local(grp, 0, &w), "world"); H(hyd_grid_create(w, 1, 1, &g), "grid");
+    Dev<double> A(n * n), B(n * n), C1(n * n), C2(n * n);
+    {
+        std::vector<double> h(n * n);
+        uint64_t x = 88172645463325252ull;
+        auto next = [&]() { x ^= x << 13; x ^= x >> 7; x ^= x << 17; return (double)(x >> 11) / 9007199254740992.0 * 2.0 - 1.0; };
+        for (auto& v : h) v = next();
+        A.set(h);
+        for (auto& v : h) v = next();
+        B.set(h);
+    }
+    cudaStream_t st;
+    CK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    for (i64 nb : {(i64)128, (i64)1024}) {
+        Dev<double> A1(n * nb), B1t(n * nb);
+        auto reference = [&]() {
+            R(rfill(n, n, 0.0, C1.p, n, st), "Zero");
+            for (i64 k0 = 0; k0 < n; k0 += nb) {
+                const i64 kb = std::min(nb, n - k0);
+                R(rcopy(0, n, kb, A.p + k0 * n, n, A1.p, n, st), "Copy");                 // A(:, k0:k0+kb)
+                R(rcopy(1, n, kb, B.p + k0, n, B1t.p, n, st), "Transpose");              // B(k0:k0+kb, :)^T is n x kb
+                R(rgemm(0, 1, n, n, kb, 1.0, A1.p, n, B1t.p, n, 1.0, C1.p, n, st), "Gemm");
+            }
+        };
+        hyd_dm a{A.p, n, n, n, HYD_MC, HYD_MR, 0, 0, 0, 0}, b{B.p, n, n, n, HYD_MC, HYD_MR, 0, 0, 0, 0}, c{C2.p, n, n, n, HYD_MC, HYD_MR, 0, 0, 0, 0};
+        auto product = [&]() { H(hyd_gemm_f64(g, HYD_NORMAL, HYD_NORMAL, HYD_GEMM_SUMMA_C, 1.0, &a, &b, 0.0, &c, nb, st), "hyd_gemm_f64"); };
+        double ms[2];
+        for (int side = 0; side < 2; ++side) {
+            auto run = [&]() { if (side == 0) reference(); else product(); };
+            run();
+            CK(cudaStreamSynchronize(st));
+            CK(cudaEventRecord(e0, st));
+            for (int i = 0; i < 3; ++i) run();
+            CK(cudaEventRecord(e1, st));
+            CK(cudaEventSynchronize(e1));
+            float t;
+            CK(cudaEventElapsedTime(&t, e0, e1));
+            ms[side] = t / 3;
+        }
+        CK(cudaDeviceSynchronize());
+        auto x = C1.host(), y = C2.host();
+        double num = 0, den = 0;
+        for (size_t i = 0; i < x.size(); ++i) { const double d = x[i] - y[i]; num += d * d; den += x[i] * x[i]; }
+        const double rel = std::sqrt(num / den), tf = 2.0 * n * n * n / 1e12;
+        char d[256];
+        std::snprintf(d, sizeof(d), "n=%lld nb=%lld: reference-built 1x1 SUMMA-C %.2f ms = %.2f TFLOP/s, hyd_gemm_f64 %.2f ms = %.2f TFLOP/s, rel. Frobenius diff %.3g",
+                      (long long)n, (long long)nb, ms[0], tf / ms[0] * 1e3, ms[1], tf / ms[1] * 1e3, rel);
+        report("El::Gemm NN fp64 on a 1x1 grid, reference layer vs product", rel <= 1e-13 * std::sqrt((double)n), d);
+    }
+    hyd_grid_destroy(g); hyd_world_destroy(w); hyd_local_group_destroy(grp);
+}
+
 int main(int argc, char** argv) {
     const char* refpath = std::getenv("REF_GPU_LIB") ? std::getenv("REF_GPU_LIB") : "oracle/_ref/libref_gpu.so";
     g_ref = dlopen(refpath, RTLD_NOW | RTLD_LOCAL);
@@ -269,6 +341,7 @@ int main(int argc, char** argv) {
     packs<float>();          // fp64 families are in tools/ref_gpu_check.cpp
     level1<double>();
     level1<float>();
+    if (std::getenv("REF_CHECK_SUMMA")) summa_1x1();
     const std::string out = "{\"tool\": \"ref_gpu_check_level1\", \"failed_checks\": " + std::to_string(g_fail) + ", \"results\": [\n " + g_json + "\n]}\n";
     std::fputs(out.c_str(), stdout);
     if (argc > 1) { if (FILE* f = std::fopen(argv[1], "w")) { std::fputs(out.c_str(), f); std::fclose(f); } }
