@@ -71,6 +71,9 @@ _sig("hyd_local_group_destroy", i32, [vp])
 _sig("hyd_world_create_local", i32, [vp, i32, C.POINTER(vp)])
 _sig("hyd_world_destroy", i32, [vp])
 _sig("hyd_world_barrier", i32, [vp])
+_sig("hyd_grid_default_height", i32, [i32])
+_sig("hyd_world_size", i32, [vp])
+_sig("hyd_world_rank", i32, [vp])
 _sig("hyd_grid_create", i32, [vp, i32, i32, C.POINTER(vp)])
 _sig("hyd_grid_destroy", i32, [vp])
 for _n in ("hyd_grid_height", "hyd_grid_width", "hyd_grid_size", "hyd_grid_rank", "hyd_grid_row", "hyd_grid_col",

@@ -126,6 +126,15 @@ int hyd_world_create_nccl(const void* id128, int rank, int nranks, hyd_world** o
     *out = new hyd_world{w};
     return 0;
 }
+int hyd_world_size(const hyd_world* w) { return w && w->w ? w->w->size : 0; }
+int hyd_world_rank(const hyd_world* w) { return w && w->w ? w->w->rank : -1; }
+int hyd_grid_default_height(int size) {
+    if (size <= 0) return 0;
+    int h = 1;
+    while ((long long)(h + 1) * (h + 1) <= size) ++h;   // floor(sqrt(size)) without floating point
+    while (size % h != 0) ++h;
+    return h;
+}
 int hyd_local_group_create(int nranks, hyd_local_group** out) {
     if (nranks <= 0 || !out) return set_error("hyd_local_group_create: bad arguments");
     *out = new hyd_local_group{hyd::local_shared_create(nranks)};

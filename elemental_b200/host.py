@@ -120,10 +120,8 @@ class Grid:
     """El::Grid(comm, height, order)."""
 
     def __init__(self, world, height=None, order=COLUMN_MAJOR):
-        if height is None:  # Grid::DefaultHeight, Grid.cpp:58-64: largest divisor <= sqrt(p)
-            height = int(np.floor(np.sqrt(world.size)))
-            while world.size % height:
-                height -= 1
+        if height is None:  # Grid::DefaultHeight, Grid.cpp:58-64: from floor(sqrt(p)) upwards until it divides p
+            height = lib.hyd_grid_default_height(world.size)
         self.world = world
         self.h = C.c_void_p()
         check(lib.hyd_grid_create(world.h, height, order, C.byref(self.h)))

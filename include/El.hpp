@@ -73,6 +73,8 @@ public:
     static Comm Local(hyd_local_group* grp, int rank) { Comm c; detail::check(hyd_world_create_local(grp, rank, &c.w_)); return c; }
     static Comm Self() { Comm c; detail::check(hyd_local_group_create(1, &c.grp_)); detail::check(hyd_world_create_local(c.grp_, 0, &c.w_)); return c; }
     hyd_world* handle() const { return w_; }
+    int Size() const { return hyd_world_size(w_); }
+    int Rank() const { return hyd_world_rank(w_); }
     void Barrier() const { detail::check(hyd_world_barrier(w_)); }
     void Free() { if (w_) hyd_world_destroy(w_); if (grp_) hyd_local_group_destroy(grp_); w_ = nullptr; grp_ = nullptr; }
 private:
@@ -85,6 +87,9 @@ private:
 class Grid {
 public:
     Grid(const mpi::Comm& comm, int height, GridOrder order = COLUMN_MAJOR) { detail::check(hyd_grid_create(comm.handle(), height, order, &g_)); }
+    // Grid(comm, order): height = Grid::DefaultHeight(size) (Grid.cpp:58-64,70-72)
+    explicit Grid(const mpi::Comm& comm, GridOrder order = COLUMN_MAJOR) : Grid(comm, hyd_grid_default_height(comm.Size()), order) {}
+    static int DefaultHeight(int gridSize) { return hyd_grid_default_height(gridSize); }
     ~Grid() { if (g_) hyd_grid_destroy(g_); }
     Grid(const Grid&) = delete;
     Grid& operator=(const Grid&) = delete;

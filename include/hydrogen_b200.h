@@ -212,7 +212,13 @@ int hyd_local_group_destroy(hyd_local_group* grp);
 int hyd_world_create_local(hyd_local_group* grp, int rank, hyd_world** out);
 int hyd_world_destroy(hyd_world* w);
 int hyd_world_barrier(hyd_world* w);
+/* mpi::Size / mpi::Rank of the owning communicator (include/El/core/imports/mpi.hpp) */
+int hyd_world_size(const hyd_world* w);
+int hyd_world_rank(const hyd_world* w);
 
+/* Grid::DefaultHeight (src/core/Grid.cpp:58-64): the grid height El::Grid(comm) picks when none is given --
+ * start at floor(sqrt(size)) and INCREASE until it divides size (8 -> 2x4, 4 -> 2x2, a prime p >= 5 -> p x 1). Host function. */
+int hyd_grid_default_height(int size);
 /* order: 0 = ROW_MAJOR, 1 = COLUMN_MAJOR (types.hpp:409-413); height must divide the world size. */
 int hyd_grid_create(hyd_world* w, int height, int order, hyd_grid** out);
 int hyd_grid_destroy(hyd_grid* g);

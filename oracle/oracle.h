@@ -37,6 +37,7 @@ int64_t orc_length(int64_t n, int64_t shift, int64_t stride);
 int64_t orc_max_length(int64_t n, int64_t stride);
 
 typedef struct { int r, c, col_major; } orc_grid;  /* Grid.cpp:95-150 */
+int orc_grid_default_height(int size);             /* Grid::DefaultHeight, Grid.cpp:58-64 */
 void orc_grid_coords(orc_grid g, int rank, int* mc, int* mr);
 int orc_grid_rank_of(orc_grid g, int mc, int mr);
 int orc_dist_stride(orc_grid g, int dist);

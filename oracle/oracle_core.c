@@ -1,6 +1,7 @@
 /* oracle_core.c -- indexing, grid, simulated distributed matrices, closed-form definitions.
  * TEST INFRASTRUCTURE ONLY (see oracle.h). */
 #include "oracle.h"
+#include <math.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -15,6 +16,12 @@ int64_t orc_max_length(int64_t n, int64_t stride) { return n > 0 ? (n - 1) / str
 
 /* src/core/Grid.cpp:121-148: column-major grids number ranks down the columns (rank == VC rank),
  * row-major grids along the rows (rank == VR rank). */
+/* Grid::DefaultHeight, src/core/Grid.cpp:58-64: int(sqrt(double(gridSize))), then ++ until it divides gridSize */
+int orc_grid_default_height(int size) {
+    int h = (int)sqrt((double)size);
+    while (size % h != 0) ++h;
+    return h;
+}
 void orc_grid_coords(orc_grid g, int rank, int* mc, int* mr) {
     if (g.col_major) { *mc = rank % g.r; *mr = rank / g.r; }
     else             { *mc = rank / g.c; *mr = rank % g.c; }

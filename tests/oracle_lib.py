@@ -48,6 +48,7 @@ _sig("orc_max_length", i64, [i64, i64])
 _sig("orc_dist_stride", i32, [Grid, i32])
 _sig("orc_dist_rank", i32, [Grid, i32, i32, i32])
 _sig("orc_grid_rank_of", i32, [Grid, i32, i32])
+_sig("orc_grid_default_height", i32, [i32])
 _sig("orc_dm_create", vp, [Grid, i64, i64, i32, i32, i32, i32, i32])
 _sig("orc_dm_free", None, [vp])
 _sig("orc_dm_local", vp, [vp, i32])

@@ -97,3 +97,17 @@ def test_redist_plan_is_a_consistent_permutation(r, c):
             D = O.DM(og, dm, dn, dcd, drd, sa[2], sa[3])
             for p in range(P):
                 assert recv[p].sum() == D.lh(p) * D.lw(p) * 8
+
+
+def test_default_grid_height_matches_the_reference_rule():
+    """Grid::DefaultHeight (src/core/Grid.cpp:58-64): floor(sqrt(p)) upwards until it divides p -- NOT the largest divisor
+    below sqrt(p): 8 -> 2 (2x4), 4 -> 2, but 10 -> 5 (5x2) and a prime p >= 5 -> p (p x 1).  Product (host function of the C ABI)
+    against the oracle's restatement and the known answers."""
+    import oracle_lib as O
+    from elemental_b200 import lib
+    known = {1: 1, 2: 1, 3: 1, 4: 2, 5: 5, 6: 2, 7: 7, 8: 2, 9: 3, 10: 5, 12: 3, 16: 4, 24: 4, 64: 8}
+    for p, h in known.items():
+        assert lib.hyd_grid_default_height(p) == h == O.lib.orc_grid_default_height(p), p
+    for p in range(1, 2000):
+        assert lib.hyd_grid_default_height(p) == O.lib.orc_grid_default_height(p), p
+        assert p % lib.hyd_grid_default_height(p) == 0
