@@ -158,6 +158,7 @@ int hyd_world_barrier(hyd_world* w) { return w ? w->w->barrier() : set_error("hy
 int hyd_grid_create(hyd_world* w, int height, int order, hyd_grid** out) {
     if (!w || !out) return set_error("hyd_grid_create: bad arguments");
     const int size = w->w->size;
+    if (height <= 0) height = hyd_grid_default_height(size);   // Grid.cpp:87: height <= 0 ? DefaultHeight(size) : height
     if (height <= 0 || size % height != 0)
         return set_error("Grid height, %d, does not evenly divide grid size, %d", height, size);  // Grid.cpp:98-100
     hyd::Grid* g = new hyd::Grid;

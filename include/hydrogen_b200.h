@@ -219,7 +219,8 @@ int hyd_world_rank(const hyd_world* w);
 /* Grid::DefaultHeight (src/core/Grid.cpp:58-64): the grid height El::Grid(comm) picks when none is given --
  * start at floor(sqrt(size)) and INCREASE until it divides size (8 -> 2x4, 4 -> 2x2, a prime p >= 5 -> p x 1). Host function. */
 int hyd_grid_default_height(int size);
-/* order: 0 = ROW_MAJOR, 1 = COLUMN_MAJOR (types.hpp:409-413); height must divide the world size. */
+/* order: 0 = ROW_MAJOR, 1 = COLUMN_MAJOR (types.hpp:409-413); height must divide the world size; height <= 0 picks
+ * hyd_grid_default_height(size) as the reference does (Grid.cpp:87). */
 int hyd_grid_create(hyd_world* w, int height, int order, hyd_grid** out);
 int hyd_grid_destroy(hyd_grid* g);
 int hyd_grid_height(const hyd_grid* g);
