@@ -215,6 +215,42 @@ template <> struct Sfx<float> {
 // ---- AbstractDistMatrix<T> / DistMatrix<T,U,V,ELEMENT,Device::GPU> (include/El/core/DistMatrix/**) ----
 // Metadata + this rank's local column-major device block.  Shifts follow
 // src/core/DistMatrix/AbstractDistMatrix.cpp:399-430; lengths include/El/core/indexing/impl.hpp:33-66.
+// Distribution algebra (include/El/core/types.hpp:292-337)
+inline Dist Collect(Dist U) { return U == CIRC ? CIRC : STAR; }
+inline Dist Partial(Dist U) { return U == VC ? MC : (U == VR ? MR : U); }
+inline Dist PartialUnionRow(Dist U, Dist V) { return U == VC ? MR : (U == VR ? MC : V); }
+inline Dist PartialUnionCol(Dist U, Dist V) { return PartialUnionRow(V, U); }
+
+namespace detail {
+// ElementalMatrix<T>::AlignColsWith / AlignRowsWith (src/core/DistMatrix/ElementMatrix.cpp:243-300) as a pure function:
+// `mine` is the distribution of the dimension being aligned, `minePartialUnion` its PartialUnion{Col,Row}Dist, `stride` its
+// stride; (dCol, dColAlign, dRow, dRowAlign) the DistData aligned with.  Returns 1 and the new alignment, 0 when the
+// reference leaves the alignment alone, -1 where it raises "Nonsensical alignment" (unless allowMismatch).
+inline int align_dim_with(Dist mine, Dist minePartialUnion, int stride, Dist dCol, int dColAlign, Dist dRow, int dRowAlign, int* out) {
+    if (dCol == mine || dCol == Partial(mine)) { *out = dColAlign; return 1; }
+    if (dRow == mine || dRow == Partial(mine)) { *out = dRowAlign; return 1; }
+    if (dCol == minePartialUnion) { *out = dColAlign % stride; return 1; }
+    if (dRow == minePartialUnion) { *out = dRowAlign % stride; return 1; }
+    if (mine != Collect(mine) && dCol != Collect(mine) && dRow != Collect(mine)) return -1;
+    return 0;
+}
+// The alignment an UNCONSTRAINED destination dimension adopts from the same dimension of the source in B = A:
+// one line of every copy:: primitive (include/El/blas_like/level1/Copy/*.hpp) --
+//   same distribution            Translate.hpp:38-42, RowAllGather.hpp:23, ColAllGather.hpp:36, {Row,Col}Filter.hpp:27-29
+//                                -> the source's alignment
+//   dst = Partial(src) (VC->MC)  PartialColAllGather.hpp:43-44, PartialRowAllGather.hpp:22-23, {Col,Row}AllToAllPromote.hpp:26-27
+//                                -> Mod(srcAlign, dstStride)
+//   src = Partial(dst) (MC->VC)  {Col,Row}AllToAllDemote.hpp:25, Partial{Col,Row}Filter.hpp:29-31  -> the source's alignment
+// Unrelated distributions (MC vs MR, VC vs VR, anything vs STAR) adopt nothing.
+inline bool copy_adopts(Dist src, int srcAlign, Dist dst, int dstStride, int* out) {
+    if (dst == STAR) return false;
+    if (src == dst) { *out = srcAlign; return true; }
+    if (dst == Partial(src)) { *out = srcAlign % dstStride; return true; }
+    if (src == Partial(dst)) { *out = srcAlign; return true; }
+    return false;
+}
+}  // namespace detail
+
 template <typename T>
 class AbstractDistMatrix {
 public:
@@ -243,11 +279,65 @@ public:
     void SetStream(cudaStream_t s) { sync_.stream_ = s; }
     const hyd_dm* desc() const { return &d_; }
 
-    void Align(int colAlign, int rowAlign) { d_.colAlign = colAlign; d_.rowAlign = rowAlign; Resize(d_.height, d_.width); }
-    void AlignWith(const AbstractDistMatrix<T>& A) {  // ElementMatrix.cpp AlignWith: adopt alignments of matching dists
-        if (A.d_.colDist == d_.colDist) d_.colAlign = A.d_.colAlign; else if (A.d_.rowDist == d_.colDist) d_.colAlign = A.d_.rowAlign;
-        if (A.d_.rowDist == d_.rowDist) d_.rowAlign = A.d_.rowAlign; else if (A.d_.colDist == d_.rowDist) d_.rowAlign = A.d_.colAlign;
-        Resize(d_.height, d_.width);
+    // ---- alignment (src/core/DistMatrix/ElementMatrix.cpp:170-370): explicit alignment constrains a dimension; an
+    // unconstrained dimension adopts the source's alignment in B = A (AlignColsAndResize(..., force=false, constrain=false))
+    bool ColConstrained() const { return colConstrained_; }
+    bool RowConstrained() const { return rowConstrained_; }
+    void FreeAlignments() { if (!viewing_) { colConstrained_ = false; rowConstrained_ = false; } }   // AbstractDistMatrix.cpp:93-102
+    Dist PartialColDist() const { return Partial(ColDist()); }
+    Dist PartialRowDist() const { return Partial(RowDist()); }
+    Dist PartialUnionColDist() const { return PartialUnionCol(ColDist(), RowDist()); }
+    Dist PartialUnionRowDist() const { return PartialUnionRow(ColDist(), RowDist()); }
+    void Align(int colAlign, int rowAlign, bool constrain = true) {
+        if (viewing_ && (colAlign != d_.colAlign || rowAlign != d_.rowAlign)) LogicError("Tried to realign a view");
+        if (constrain) { colConstrained_ = true; rowConstrained_ = true; }
+        d_.colAlign = colAlign; d_.rowAlign = rowAlign; Resize(d_.height, d_.width);
+    }
+    void AlignCols(int colAlign, bool constrain = true) {
+        if (viewing_ && colAlign != d_.colAlign) LogicError("Tried to realign a view");
+        if (constrain) colConstrained_ = true;
+        d_.colAlign = colAlign; Resize(d_.height, d_.width);
+    }
+    void AlignRows(int rowAlign, bool constrain = true) {
+        if (viewing_ && rowAlign != d_.rowAlign) LogicError("Tried to realign a view");
+        if (constrain) rowConstrained_ = true;
+        d_.rowAlign = rowAlign; Resize(d_.height, d_.width);
+    }
+    void AlignColsWith(const AbstractDistMatrix<T>& A, bool constrain = true, bool allowMismatch = false) {
+        int a;
+        const int r = detail::align_dim_with(ColDist(), PartialUnionColDist(), ColStride(), A.ColDist(), A.ColAlign(), A.RowDist(), A.RowAlign(), &a);
+        if (r > 0) AlignCols(a, constrain);
+        else if (r < 0 && !allowMismatch) LogicError("Nonsensical alignment");
+    }
+    void AlignRowsWith(const AbstractDistMatrix<T>& A, bool constrain = true, bool allowMismatch = false) {
+        int a;
+        const int r = detail::align_dim_with(RowDist(), PartialUnionRowDist(), RowStride(), A.ColDist(), A.ColAlign(), A.RowDist(), A.RowAlign(), &a);
+        if (r > 0) AlignRows(a, constrain);
+        else if (r < 0 && !allowMismatch) LogicError("Nonsensical alignment");
+    }
+    void AlignWith(const AbstractDistMatrix<T>& A, bool constrain = true, bool allowMismatch = false) {
+        AlignColsWith(A, constrain, allowMismatch); AlignRowsWith(A, constrain, allowMismatch);
+    }
+    void AlignAndResize(int colAlign, int rowAlign, Int height, Int width, bool force = false, bool constrain = false) {
+        if (!viewing_) {
+            if (force || !colConstrained_) d_.colAlign = colAlign;
+            if (force || !rowConstrained_) d_.rowAlign = rowAlign;
+        }
+        if (constrain) { colConstrained_ = true; rowConstrained_ = true; }
+        if (force && (d_.colAlign != colAlign || d_.rowAlign != rowAlign)) LogicError("Could not set alignments");
+        Resize(height, width);
+    }
+    void AlignColsAndResize(int colAlign, Int height, Int width, bool force = false, bool constrain = false) {
+        if (!viewing_ && (force || !colConstrained_)) d_.colAlign = colAlign;
+        if (constrain) colConstrained_ = true;
+        if (force && d_.colAlign != colAlign) LogicError("Could not set col alignment");
+        Resize(height, width);
+    }
+    void AlignRowsAndResize(int rowAlign, Int height, Int width, bool force = false, bool constrain = false) {
+        if (!viewing_ && (force || !rowConstrained_)) d_.rowAlign = rowAlign;
+        if (constrain) rowConstrained_ = true;
+        if (force && d_.rowAlign != rowAlign) LogicError("Could not set row alignment");
+        Resize(height, width);
     }
     void Resize(Int height, Int width) {
         d_.height = height; d_.width = width;
@@ -266,7 +356,9 @@ public:
         d_.ldim = ld;
     }
     void Attach(Int height, Int width, int colAlign, int rowAlign, T* buffer, Int ldim) {
-        Empty(); viewing_ = true; d_.colAlign = colAlign; d_.rowAlign = rowAlign; d_.buf = buffer; d_.ldim = ldim; Resize(height, width);
+        Empty(); viewing_ = true; d_.colAlign = colAlign; d_.rowAlign = rowAlign; d_.buf = buffer; d_.ldim = ldim;
+        colConstrained_ = rowConstrained_ = true;   // ElementMatrix.cpp Attach: a view's alignments are fixed
+        Resize(height, width);
     }
     void Empty() { if (!viewing_ && d_.buf) cudaFree(d_.buf); d_.buf = nullptr; cap_ = 0; viewing_ = false; }
 
@@ -288,19 +380,38 @@ protected:
     Int colShift_ = 0, rowShift_ = 0, lh_ = 0, lw_ = 0;
     size_t cap_ = 0;
     bool viewing_ = false;
+    bool colConstrained_ = false, rowConstrained_ = false;
     SyncInfoGPU sync_;
 };
 
 // B = A between any two supported distributions (DistMatrix::operator= tables,
 // src/core/DistMatrix/ElementMatrix/*.cpp -> copy::* primitives)
+// An unconstrained dimension of B first adopts the alignment of the same dimension of A where the two distributions are
+// related (detail::copy_adopts: the AlignColsAndResize / AlignRowsAndResize line of the reference's copy:: primitive), so a
+// `B = A` into a fresh [MC,*] / [VC,*] / ... matrix lands exactly where the reference puts it, with no realignment traffic.
 template <typename T>
 void Copy(const AbstractDistMatrix<T>& A, AbstractDistMatrix<T>& B) {
-    B.Resize(A.Height(), A.Width());
+    int ca = B.ColAlign(), ra = B.RowAlign(), a;
+    if (!B.ColConstrained() && detail::copy_adopts(A.ColDist(), A.ColAlign(), B.ColDist(), B.ColStride(), &a)) ca = a;
+    if (!B.RowConstrained() && detail::copy_adopts(A.RowDist(), A.RowAlign(), B.RowDist(), B.RowStride(), &a)) ra = a;
+    B.AlignAndResize(ca, ra, A.Height(), A.Width(), false, false);
     detail::check(detail::Sfx<T>::redist(B.Grid().handle(), A.desc(), B.desc(), 0, B.Stream()));
 }
 // B = A^T (Transpose.hpp:318-356); conjugate is a no-op for real T
 template <typename T>
 void Transpose(const AbstractDistMatrix<T>& A, AbstractDistMatrix<T>& B, bool /*conjugate*/ = false) {
+    // Transpose.hpp:191-250: B's column dimension relates to A's ROW dimension and vice versa.  With exactly transposed
+    // distributions and compatible (or free) alignments the reference calls B.Align(A.RowAlign(), A.ColAlign()), which also
+    // constrains B (:202-210); the filter / all-gather branches adopt without constraining.
+    int ca = B.ColAlign(), ra = B.RowAlign(), a;
+    const bool transposed = A.ColDist() == B.RowDist() && A.RowDist() == B.ColDist();
+    if (transposed && (A.ColAlign() == B.RowAlign() || !B.RowConstrained()) && (A.RowAlign() == B.ColAlign() || !B.ColConstrained())) {
+        B.Align(A.RowAlign(), A.ColAlign(), true);
+    } else {
+        if (!B.ColConstrained() && detail::copy_adopts(A.RowDist(), A.RowAlign(), B.ColDist(), B.ColStride(), &a)) ca = a;
+        if (!B.RowConstrained() && detail::copy_adopts(A.ColDist(), A.ColAlign(), B.RowDist(), B.RowStride(), &a)) ra = a;
+        B.AlignAndResize(ca, ra, A.Width(), A.Height(), false, false);
+    }
     B.Resize(A.Width(), A.Height());
     detail::check(detail::Sfx<T>::redist(B.Grid().handle(), A.desc(), B.desc(), 1, B.Stream()));
 }

@@ -31,7 +31,28 @@ def main():
                       ref.lib.ref_max_length(n, stride), ref.lib.ref_mod(rank - align - stride, stride),
                       ref.lib.ref_gcd(max(n, 1), stride))
     G.save_golden(G.GOLDEN, cases, outs, idx_in, idx_out)
+    write_dist_algebra()
     print(f"{len(cases)} cases, {sum(o.size for o in outs)} output elements, {os.path.getsize(G.GOLDEN)} bytes -> {G.GOLDEN}")
+
+
+def write_dist_algebra():
+    """tests/golden/dist_algebra.json: the reference's Collect / Partial / PartialUnion tables and enumerator values
+    (include/El/core/types.hpp, compiled in place by oracle/ref/ref_types.cpp) for tests/test_shim_align.py."""
+    import ctypes
+    import json
+    ref = ctypes.CDLL(os.path.join(ROOT, "oracle", "_ref", "libref_util.so"))
+    names = {"MC": 0, "MD": 1, "MR": 2, "VC": 3, "VR": 4, "STAR": 5, "CIRC": 6, "NORMAL": 10, "TRANSPOSE": 11, "ADJOINT": 12,
+             "ROW_MAJOR": 20, "COLUMN_MAJOR": 21, "ELEMENT": 30, "BLOCK": 31}
+    table = {
+        "enum": {k: ref.ref_enum_value(v) for k, v in names.items()},
+        "collect": [ref.ref_dist_collect(d) for d in range(7)],
+        "partial": [ref.ref_dist_partial(d) for d in range(7)],
+        "partial_union_row": [ref.ref_dist_partial_union_row(u, v) for u in range(7) for v in range(7)],
+        "partial_union_col": [ref.ref_dist_partial_union_col(u, v) for u in range(7) for v in range(7)],
+    }
+    with open(os.path.join(HERE, "dist_algebra.json"), "w") as f:
+        json.dump(table, f, indent=0)
+        f.write("\n")
 
 
 if __name__ == "__main__":
