@@ -243,7 +243,7 @@ inline int align_dim_with(Dist mine, Dist minePartialUnion, int stride, Dist dCo
 //   src = Partial(dst) (MC->VC)  {Col,Row}AllToAllDemote.hpp:25, Partial{Col,Row}Filter.hpp:29-31  -> the source's alignment
 // Unrelated distributions (MC vs MR, VC vs VR, anything vs STAR) adopt nothing.
 inline bool copy_adopts(Dist src, int srcAlign, Dist dst, int dstStride, int* out) {
-    if (dst == STAR) return false;
+    if (dst == STAR || dst == CIRC || src == STAR || src == CIRC) return false;   // stride 1: nothing to align
     if (src == dst) { *out = srcAlign; return true; }
     if (dst == Partial(src)) { *out = srcAlign % dstStride; return true; }
     if (src == Partial(dst)) { *out = srcAlign; return true; }

@@ -38,6 +38,14 @@ int64_t orc_max_length(int64_t n, int64_t stride);
 
 typedef struct { int r, c, col_major; } orc_grid;  /* Grid.cpp:95-150 */
 int orc_grid_default_height(int size);             /* Grid::DefaultHeight, Grid.cpp:58-64 */
+/* distribution algebra (types.hpp:292-337) and the alignment rules (ElementMatrix.cpp:243-300; the copy:: primitives) */
+int orc_dist_collect(int u);
+int orc_dist_partial(int u);
+int orc_dist_partial_union_row(int u, int v);
+int orc_dist_partial_union_col(int u, int v);
+int orc_align_dim_with(int U, int V, int which, int stride, int dataColDist, int dataColAlign, int dataRowDist, int dataRowAlign,
+                       int* align);
+int orc_copy_adopts(int src, int srcAlign, int dst, int dstStride, int* align);
 void orc_grid_coords(orc_grid g, int rank, int* mc, int* mr);
 int orc_grid_rank_of(orc_grid g, int mc, int mr);
 int orc_dist_stride(orc_grid g, int dist);

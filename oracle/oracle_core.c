@@ -22,6 +22,42 @@ int orc_grid_default_height(int size) {
     while (size % h != 0) ++h;
     return h;
 }
+/* Distribution algebra, include/El/core/types.hpp:292-337, written as lookup tables over the Dist enumerators
+ * (MC MD MR VC VR STAR CIRC = 0..6): Collect, Partial, and the partial-union of a [U,V] matrix's row dimension. */
+static const int kCollect[7] = {ORC_STAR, ORC_STAR, ORC_STAR, ORC_STAR, ORC_STAR, ORC_STAR, ORC_CIRC};
+static const int kPartial[7] = {ORC_MC, ORC_MD, ORC_MR, ORC_MC, ORC_MR, ORC_STAR, ORC_CIRC};
+int orc_dist_collect(int u) { return kCollect[u]; }
+int orc_dist_partial(int u) { return kPartial[u]; }
+int orc_dist_partial_union_row(int u, int v) { return u == ORC_VC ? ORC_MR : (u == ORC_VR ? ORC_MC : v); }
+int orc_dist_partial_union_col(int u, int v) { return orc_dist_partial_union_row(v, u); }
+/* ElementalMatrix::AlignColsWith / AlignRowsWith, src/core/DistMatrix/ElementMatrix.cpp:243-300, for one dimension of a
+ * [U,V] matrix: which = 0 aligns the column dimension (distribution U), 1 the row dimension (V).  `stride` is that
+ * dimension's stride.  Returns 1 and *align when the reference calls AlignCols/AlignRows, 0 when it does nothing, -1 where
+ * it raises "Nonsensical alignment". */
+int orc_align_dim_with(int U, int V, int which, int stride, int dataColDist, int dataColAlign, int dataRowDist, int dataRowAlign,
+                       int* align) {
+    const int mine = which == 0 ? U : V;
+    const int part = kPartial[mine];
+    const int uni = which == 0 ? orc_dist_partial_union_col(U, V) : orc_dist_partial_union_row(U, V);
+    const int coll = kCollect[mine];
+    if (dataColDist == mine || dataColDist == part) *align = dataColAlign;
+    else if (dataRowDist == mine || dataRowDist == part) *align = dataRowAlign;
+    else if (dataColDist == uni) *align = dataColAlign % stride;
+    else if (dataRowDist == uni) *align = dataRowAlign % stride;
+    else return (mine != coll && dataColDist != coll && dataRowDist != coll) ? -1 : 0;
+    return 1;
+}
+/* The alignment argument of the copy:: primitive serving one dimension of B = A when that dimension goes src -> dst
+ * (Translate.hpp:38-42, RowAllGather.hpp:23, ColAllGather.hpp:36, {Row,Col}Filter.hpp:27-29: the source's alignment;
+ * Partial{Col,Row}AllGather.hpp:43-44/22-23, {Col,Row}AllToAllPromote.hpp:26-27: Mod(srcAlign, dstStride);
+ * {Col,Row}AllToAllDemote.hpp:25, Partial{Col,Row}Filter.hpp:29-31: the source's alignment).  An unconstrained destination
+ * takes it; returns 0 where no primitive passes one (unrelated distributions, STAR, CIRC). */
+int orc_copy_adopts(int src, int srcAlign, int dst, int dstStride, int* align) {
+    if (dst == ORC_STAR || dst == ORC_CIRC || src == ORC_STAR || src == ORC_CIRC) return 0;
+    if (src == dst || kPartial[dst] == src) { *align = srcAlign; return 1; }
+    if (kPartial[src] == dst) { *align = srcAlign % dstStride; return 1; }
+    return 0;
+}
 void orc_grid_coords(orc_grid g, int rank, int* mc, int* mr) {
     if (g.col_major) { *mc = rank % g.r; *mr = rank / g.r; }
     else             { *mc = rank / g.c; *mr = rank % g.c; }

@@ -49,6 +49,12 @@ _sig("orc_dist_stride", i32, [Grid, i32])
 _sig("orc_dist_rank", i32, [Grid, i32, i32, i32])
 _sig("orc_grid_rank_of", i32, [Grid, i32, i32])
 _sig("orc_grid_default_height", i32, [i32])
+_sig("orc_dist_collect", i32, [i32])
+_sig("orc_dist_partial", i32, [i32])
+_sig("orc_dist_partial_union_row", i32, [i32, i32])
+_sig("orc_dist_partial_union_col", i32, [i32, i32])
+_sig("orc_align_dim_with", i32, [i32] * 8 + [C.POINTER(C.c_int)])
+_sig("orc_copy_adopts", i32, [i32] * 4 + [C.POINTER(C.c_int)])
 _sig("orc_dm_create", vp, [Grid, i64, i64, i32, i32, i32, i32, i32])
 _sig("orc_dm_free", None, [vp])
 _sig("orc_dm_local", vp, [vp, i32])

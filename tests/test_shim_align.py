@@ -151,3 +151,31 @@ def test_copy_adopts_the_alignment_each_primitive_passes(dump):
             assert k == 0, (s, d)
         else:
             assert (k, a) == (1, want), (s, d)
+
+
+def test_alignment_rules_match_the_oracle_restatement(dump):
+    """All 7^4 (matrix distribution, DistData) combinations of AlignWith and all 49 copy pairs: the shim (El.hpp) against
+    the oracle's table-driven restatement (oracle_core.c orc_align_dim_with / orc_copy_adopts)."""
+    import ctypes
+    from oracle_lib import lib as orc
+    for d in range(7):
+        assert dump["collect"][d] == orc.orc_dist_collect(d) and dump["partial"][d] == orc.orc_dist_partial(d)
+    stride = {MC: R, MR: C, VC: R * C, VR: R * C, MD: 6, STAR: 1, CIRC: 1}
+    a = ctypes.c_int(-1)
+    for u in range(7):
+        for v in range(7):
+            assert dump["partial_union_row"][u * 7 + v] == orc.orc_dist_partial_union_row(u, v)
+            assert dump["partial_union_col"][u * 7 + v] == orc.orc_dist_partial_union_col(u, v)
+            for dc in range(7):
+                for dr in range(7):
+                    got = _aw(dump, u, v, dc, dr)
+                    for which, st in ((0, stride[u]), (1, stride[v])):
+                        a.value = -1
+                        k = orc.orc_align_dim_with(u, v, which, st, dc, CA, dr, RA, ctypes.byref(a))
+                        assert (k, a.value if k == 1 else -1) == (got[2 * which], got[2 * which + 1] if k == 1 else -1), (u, v, dc, dr, which)
+    for s in range(7):
+        for d in range(7):
+            a.value = -1
+            k = orc.orc_copy_adopts(s, 5, d, stride[d], ctypes.byref(a))
+            got = dump["copy_adopts"][s * 7 + d]
+            assert (k, a.value if k else -1) == (got[0], got[1] if k else -1), (s, d)
