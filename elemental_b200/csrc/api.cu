@@ -11,6 +11,11 @@ template <typename T>
 int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A, const DM& B, T beta, const DM& C, i64 blocksize,
               cudaStream_t s, const void* hostA, i64 hostLdA, const void* hostB, i64 hostLdB, void* hostC, i64 hostLdC,
               int* c_downloaded);
+template <typename T>
+int dist_trrk(Grid& g, int uplo, int oA, int oB, T alpha, const DM& A, const DM& B, T beta, const DM& C, i64 blocksize,
+              cudaStream_t s);
+template <typename T>
+int dist_trapezoid(Grid& g, int op, int uplo, T alpha, const DM* X, const DM& Y, i64 offset, cudaStream_t s);
 }  // namespace hyd
 
 struct hyd_world { hyd::World* w; };
@@ -308,6 +313,56 @@ int hyd_scale2d_f64(int64_t m, int64_t n, double alpha, double* A, int64_t lda, 
 int hyd_scale2d_f32(int64_t m, int64_t n, float alpha, float* A, int64_t lda, hyd_stream_t s) {
     return hyd::scale_local<float>(m, n, alpha, A, lda, (cudaStream_t)s);
 }
+
+// ---- triangular rank-k updates on the SUMMA-C engine, and the trapezoid level-1 kernels around them ----
+#define HYD_TRRK(SFX, T)                                                                                                        \
+    int hyd_trrk_##SFX(hyd_grid* g, int uplo, int oA, int oB, T alpha, const hyd_dm* A, const hyd_dm* B, T beta, const hyd_dm* C, \
+                       int64_t blocksize, hyd_stream_t stream) {                                                                \
+        const hyd::GridShape& sh = g->g->shape;                                                                                 \
+        if (check_dm(sh, A, "hyd_trrk(A)") || check_dm(sh, B, "hyd_trrk(B)") || check_dm(sh, C, "hyd_trrk(C)")) return 1;         \
+        return hyd::dist_trrk<T>(*g->g, uplo, oA, oB, alpha, to_dm(A), to_dm(B), beta, to_dm(C), blocksize, (cudaStream_t)stream); \
+    }                                                                                                                           \
+    int hyd_syrk_##SFX(hyd_grid* g, int uplo, int orient, T alpha, const hyd_dm* A, T beta, const hyd_dm* C, int64_t blocksize,   \
+                       hyd_stream_t stream) {                                                                                   \
+        const hyd::GridShape& sh = g->g->shape;                                                                                 \
+        if (check_dm(sh, A, "hyd_syrk(A)") || check_dm(sh, C, "hyd_syrk(C)")) return 1;                                         \
+        /* NORMAL: C := alpha A A^T + beta C; TRANSPOSE / ADJOINT (real): C := alpha A^T A + beta C */                         \
+        return hyd::dist_trrk<T>(*g->g, uplo, orient ? 1 : 0, orient ? 0 : 1, alpha, to_dm(A), to_dm(A), beta, to_dm(C),         \
+                                 blocksize, (cudaStream_t)stream);                                                              \
+    }                                                                                                                           \
+    int hyd_scale_trapezoid_##SFX(T alpha, int uplo, int64_t m, int64_t n, T* A, int64_t lda, int64_t offset, hyd_stream_t s) {  \
+        if (uplo != 0 && uplo != 1) return set_error("hyd_scale_trapezoid: uplo must be LOWER (0) or UPPER (1)");               \
+        if (alpha == T(1)) return 0;                                                                                            \
+        return hyd::trapezoid_local<T>(2, uplo, m, n, 0, 1, 0, 1, offset, alpha, nullptr, 0, A, lda, (cudaStream_t)s);            \
+    }                                                                                                                           \
+    int hyd_axpy_trapezoid_##SFX(int uplo, T alpha, int64_t m, int64_t n, const T* X, int64_t ldx, T* Y, int64_t ldy,            \
+                                 int64_t offset, hyd_stream_t s) {                                                              \
+        if (uplo != 0 && uplo != 1) return set_error("hyd_axpy_trapezoid: uplo must be LOWER (0) or UPPER (1)");                \
+        return hyd::trapezoid_local<T>(1, uplo, m, n, 0, 1, 0, 1, offset, alpha, X, ldx, Y, ldy, (cudaStream_t)s);               \
+    }                                                                                                                           \
+    int hyd_make_trapezoidal_##SFX(int uplo, int64_t m, int64_t n, T* A, int64_t lda, int64_t offset, hyd_stream_t s) {          \
+        if (uplo != 0 && uplo != 1) return set_error("hyd_make_trapezoidal: uplo must be LOWER (0) or UPPER (1)");              \
+        return hyd::trapezoid_local<T>(3, uplo, m, n, 0, 1, 0, 1, offset, T(0), nullptr, 0, A, lda, (cudaStream_t)s);            \
+    }                                                                                                                           \
+    int hyd_scale_trapezoid_dist_##SFX(hyd_grid* g, T alpha, int uplo, const hyd_dm* A, int64_t offset, hyd_stream_t s) {        \
+        if (check_dm(g->g->shape, A, "hyd_scale_trapezoid_dist")) return 1;                                                     \
+        if (alpha == T(1)) return 0;                                                                                            \
+        return hyd::dist_trapezoid<T>(*g->g, 2, uplo, alpha, nullptr, to_dm(A), offset, (cudaStream_t)s);                       \
+    }                                                                                                                           \
+    int hyd_axpy_trapezoid_dist_##SFX(hyd_grid* g, int uplo, T alpha, const hyd_dm* X, const hyd_dm* Y, int64_t offset,          \
+                                      hyd_stream_t s) {                                                                         \
+        if (check_dm(g->g->shape, X, "hyd_axpy_trapezoid_dist(X)") || check_dm(g->g->shape, Y, "hyd_axpy_trapezoid_dist(Y)"))    \
+            return 1;                                                                                                           \
+        const hyd::DM x = to_dm(X);                                                                                             \
+        return hyd::dist_trapezoid<T>(*g->g, 1, uplo, alpha, &x, to_dm(Y), offset, (cudaStream_t)s);                            \
+    }                                                                                                                           \
+    int hyd_make_trapezoidal_dist_##SFX(hyd_grid* g, int uplo, const hyd_dm* A, int64_t offset, hyd_stream_t s) {                \
+        if (check_dm(g->g->shape, A, "hyd_make_trapezoidal_dist")) return 1;                                                    \
+        return hyd::dist_trapezoid<T>(*g->g, 3, uplo, T(0), nullptr, to_dm(A), offset, (cudaStream_t)s);                        \
+    }
+HYD_TRRK(f64, double)
+HYD_TRRK(f32, float)
+#undef HYD_TRRK
 
 static int copy_kind(int kind, cudaMemcpyKind* out, const char* who) {
     if (kind == 0) *out = cudaMemcpyHostToDevice;

@@ -149,7 +149,62 @@ int scale_local(i64 m, i64 n, T beta, T* C, i64 ldc, cudaStream_t s) {
     return launch_ew<T, 2>(m, n, beta, nullptr, 0, C, ldc, s, "hyd_scale2d");
 }
 
+// ---------------------------------------------------------------------------
+// Trapezoid kernels: ScaleTrapezoid / AxpyTrapezoid / MakeTrapezoidal on a local block whose element (i,j) is global
+// (gi0 + i*rs, gj0 + j*cs) -- a plain Matrix is gi0 = gj0 = 0, rs = cs = 1; a DistMatrix block passes its shifts and strides
+// (include/El/blas_like/level1/{ScaleTrapezoid,AxpyTrapezoid,MakeTrapezoidal}.hpp).  LOWER holds the entries with
+// gj - gi <= offset, UPPER those with gj - gi >= offset.  OP 1: Y += alpha X inside; 2: Y *= alpha inside (exactly the
+// reference's `*=`, so alpha = 0 keeps NaNs); 3: Y = 0 outside.  Tiles of 256 rows x 4 columns; a tile wholly on the
+// untouched side is skipped before any memory access, so the traffic is that of the trapezoid, not of the block.
+// ---------------------------------------------------------------------------
+template <typename T, int OP>
+__global__ void __launch_bounds__(256) trapezoid_kernel(int upper, i64 m, i64 n, i64 gi0, i64 rs, i64 gj0, i64 cs, i64 offset,
+                                                        T alpha, const T* __restrict__ X, i64 ldx, T* __restrict__ Y, i64 ldy) {
+    constexpr int U = 4;
+    const i64 row_chunks = (m + 255) / 256, col_groups = (n + U - 1) / U;
+    const i64 total = row_chunks * col_groups;
+    for (i64 t = blockIdx.x; t < total; t += gridDim.x) {
+        const i64 rc = t % row_chunks, cg = t / row_chunks;
+        const i64 i0 = rc * 256, i1 = min(m, i0 + 256) - 1, j0 = cg * U, j1 = min(n, j0 + U) - 1;
+        // d = gj - gi over the tile ranges from dmin (last row, first column) to dmax (first row, last column)
+        const i64 dmin = (gj0 + j0 * cs) - (gi0 + i1 * rs), dmax = (gj0 + j1 * cs) - (gi0 + i0 * rs);
+        const bool none_inside = upper ? dmax < offset : dmin > offset;
+        const bool all_inside = upper ? dmin >= offset : dmax <= offset;
+        if (OP == 3 ? all_inside : none_inside) continue;
+        const i64 i = i0 + threadIdx.x;
+        if (i > i1) continue;
+        const i64 gi = gi0 + i * rs;
+#pragma unroll
+        for (int q = 0; q < U; ++q) {
+            const i64 j = j0 + q;
+            if (j > j1) break;
+            const i64 d = (gj0 + j * cs) - gi;
+            const bool inside = upper ? d >= offset : d <= offset;
+            T* y = Y + i + j * ldy;
+            if (OP == 1) { if (inside) *y = *y + alpha * __ldg(X + i + j * ldx); }
+            else if (OP == 2) { if (inside) *y = *y * alpha; }
+            else { if (!inside) *y = T(0); }
+        }
+    }
+}
+
+template <typename T>
+int trapezoid_local(int op, int upper, i64 m, i64 n, i64 gi0, i64 rs, i64 gj0, i64 cs, i64 offset, T alpha, const T* X, i64 ldx,
+                    T* Y, i64 ldy, cudaStream_t s) {
+    if (m < 0 || n < 0) return set_error("trapezoid: negative dimension");
+    if (m == 0 || n == 0) return 0;
+    if (ldy < m || (op == 1 && ldx < m)) return set_error("trapezoid: leading dimension too small");
+    const i64 total = ((m + 255) / 256) * ((n + 3) / 4);
+    const unsigned grid = (unsigned)std::max<i64>(1, std::min<i64>(total, (i64)num_sms() * 8));
+    if (op == 1) trapezoid_kernel<T, 1><<<grid, 256, 0, s>>>(upper, m, n, gi0, rs, gj0, cs, offset, alpha, X, ldx, Y, ldy);
+    else if (op == 2) trapezoid_kernel<T, 2><<<grid, 256, 0, s>>>(upper, m, n, gi0, rs, gj0, cs, offset, alpha, X, ldx, Y, ldy);
+    else trapezoid_kernel<T, 3><<<grid, 256, 0, s>>>(upper, m, n, gi0, rs, gj0, cs, offset, alpha, X, ldx, Y, ldy);
+    ++g_launches;
+    return check_cuda(cudaGetLastError(), "trapezoid_kernel");
+}
+
 #define HYD_INST(T)                                                                             \
+    template int trapezoid_local<T>(int, int, i64, i64, i64, i64, i64, i64, i64, T, const T*, i64, T*, i64, cudaStream_t); \
     template int transpose_local<T>(i64, i64, const T*, i64, T*, i64, cudaStream_t);           \
     template int copy2d_local<T>(i64, i64, const T*, i64, T*, i64, cudaStream_t);              \
     template int axpy2d_local<T>(i64, i64, T, const T*, i64, T*, i64, cudaStream_t);           \

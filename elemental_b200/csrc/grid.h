@@ -37,6 +37,7 @@ struct Grid {
     Workspace host_stage[3];  // device images of host operands (hyd_gemm_host_*)
     Workspace coll_ws;        // receive area of hyd_reducescatter_* (coll.cu)
     Workspace level1_ws;      // X in Y's distribution for hyd_axpy_dist_* (level1.cu)
+    Workspace trrk_ws;        // diagonal-strip products of the trapezoidal local update (summa.cu local_trrk)
     int overlap = -1;    // -1 auto: gather panels under the previous GEMM only when the transport is SM-heavy (staged NCCL); 0 off; 1 on
     int sm_reserve = 4;  // SMs the local GEMM leaves to NCCL / pack kernels while overlapping
     long long launches = 0;
@@ -91,6 +92,10 @@ template <typename T> int transpose_local(i64 m, i64 n, const T* A, i64 lda, T* 
 template <typename T> int copy2d_local(i64 m, i64 n, const T* A, i64 lda, T* B, i64 ldb, cudaStream_t s);
 template <typename T> int axpy2d_local(i64 m, i64 n, T alpha, const T* A, i64 lda, T* B, i64 ldb, cudaStream_t s);
 template <typename T> int scale_local(i64 m, i64 n, T beta, T* C, i64 ldc, cudaStream_t s);
+// op 1: Y += alpha X, 2: Y *= alpha (inside the trapezoid), 3: Y = 0 outside it; local (i,j) is global (gi0+i*rs, gj0+j*cs)
+template <typename T>
+int trapezoid_local(int op, int upper, i64 m, i64 n, i64 gi0, i64 rs, i64 gj0, i64 cs, i64 offset, T alpha, const T* X, i64 ldx,
+                    T* Y, i64 ldy, cudaStream_t s);
 
 extern long long g_launches;  // kernels launched by this library in this process
 

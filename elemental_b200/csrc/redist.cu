@@ -602,6 +602,7 @@ void grid_destroy(Grid* g) {
     for (auto& w : g->host_stage) if (w.buf) cudaFree(w.buf);
     if (g->coll_ws.buf) cudaFree(g->coll_ws.buf);
     if (g->level1_ws.buf) cudaFree(g->level1_ws.buf);
+    if (g->trrk_ws.buf) cudaFree(g->trrk_ws.buf);
     for (auto& v : g->prof_ev) for (cudaEvent_t e : v) cudaEventDestroy(e);
     for (cudaEvent_t e : g->upload_ev) cudaEventDestroy(e);
     for (int i = 0; i < 2; ++i) {

@@ -74,6 +74,66 @@ int ensure_engine(Grid& g) {
     return 0;
 }
 
+// Trapezoidal local update, C_loc(tri) += alpha op(A_loc) op(B_loc): the reference's LocalTrrk
+// (src/blas_like/level3/Trrk/Local.hpp:640-740) without its recursion.  `tri` 0 = LOWER, 1 = UPPER, of the GLOBAL matrix:
+// local (i,j) is global (colShift + i*colStride, rowShift + j*rowStride).  The local block is cut into column blocks of
+// kTrrkBlock local columns.  In each, the rows split three ways by the global diagonal:
+//   * wholly inside the triangle for every column of the block -> one GEMM straight into C (beta = 1);
+//   * wholly outside -> nothing (the flops the triangle saves);
+//   * the strip the diagonal crosses (about kTrrkBlock*rowStride/colStride local rows) -> GEMM into a temporary, then a
+//     masked add (trapezoid_kernel OP 1, alpha = 1: one rounding, like the reference's AxpyTrapezoid of its DTL/DBR temporaries).
+// Row cuts are rounded to 16 bytes outwards so every sub-GEMM keeps TMA-aligned operands.
+constexpr i64 kTrrkBlock = 512;
+template <typename T>
+int local_trrk(Grid& g, int tri, int tA, int tB, const LocalShape& Lc, i64 kb, T alpha, const T* A, i64 lda, const T* B, i64 ldb,
+               T* C, i64 ldc, cudaStream_t s, int sm_reserve) {
+    const i64 q = 16 / (i64)sizeof(T);
+    const i64 r = Lc.colStride, c = Lc.rowStride, lh = Lc.lh, lw = Lc.lw;
+    auto clip = [&](i64 x) { return std::max<i64>(0, std::min<i64>(lh, x)); };
+    auto ceil_div = [](i64 a, i64 b) { return a >= 0 ? (a + b - 1) / b : -((-a) / b); };
+    auto floor_div = [](i64 a, i64 b) { return a >= 0 ? a / b : -((-a + b - 1) / b); };
+    {   // the widest strip any column block can have, reserved once (growing a workspace synchronises the device)
+        const i64 wmax = std::min(kTrrkBlock, lw), thmax = std::min(lh, ((wmax - 1) * c) / r + 2 + 2 * q);
+        if (lw > 0 && ws_reserve(g.trrk_ws, (size_t)(pad_ld(thmax, sizeof(T)) * wmax) * sizeof(T))) return 1;
+    }
+    for (i64 j0 = 0; j0 < lw; j0 += kTrrkBlock) {
+        const i64 w = std::min(kTrrkBlock, lw - j0);
+        const i64 gj_first = Lc.rowShift + j0 * c, gj_last = Lc.rowShift + (j0 + w - 1) * c;
+        i64 d0, d1, t0, t1;   // direct rows [d0,d1), strip rows [t0,t1)
+        if (tri == 0) {       // LOWER: gi >= gj
+            t0 = clip(ceil_div(gj_first - Lc.colShift, r)) / q * q;
+            t1 = std::min(lh, (clip(ceil_div(gj_last - Lc.colShift, r)) + q - 1) / q * q);
+            d0 = t1; d1 = lh;
+        } else {              // UPPER: gi <= gj
+            d0 = 0;
+            d1 = clip(floor_div(gj_first - Lc.colShift, r) + 1) / q * q;
+            t0 = d1;
+            t1 = clip(floor_div(gj_last - Lc.colShift, r) + 1);
+        }
+        const T* Bj = tB ? B + j0 : B + j0 * ldb;
+        T* Cj = C + j0 * ldc;
+        if (d1 > d0) {
+            const T* Ai = tA ? A + d0 * lda : A + d0;
+            if (lgemm<T>(g, tA, tB, d1 - d0, w, kb, alpha, Ai, lda, Bj, ldb, T(1), Cj + d0, ldc, s, sm_reserve)) return 1;
+        }
+        if (t1 > t0) {
+            const i64 th = t1 - t0, ldt = pad_ld(th, sizeof(T));
+            if (ws_reserve(g.trrk_ws, (size_t)(ldt * w) * sizeof(T))) return 1;
+            T* D = reinterpret_cast<T*>(g.trrk_ws.buf);
+            const T* Ai = tA ? A + t0 * lda : A + t0;
+            if (lgemm<T>(g, tA, tB, th, w, kb, alpha, Ai, lda, Bj, ldb, T(0), D, ldt, s, sm_reserve)) return 1;
+            if (trapezoid_local<T>(1, tri, th, w, Lc.colShift + t0 * r, r, gj_first, c, 0, T(1), D, ldt, Cj + t0, ldc, s)) return 1;
+        }
+    }
+    return 0;
+}
+// the local update of SUMMA-C: the whole block (Gemm), or only its part of the global triangle (Trrk / Syrk)
+template <typename T>
+int local_update(Grid& g, int tri, int tA, int tB, const LocalShape& Lc, i64 kb, T alpha, const T* A, i64 lda, const T* B, i64 ldb,
+                 T beta, T* C, i64 ldc, cudaStream_t s, int sm_reserve) {
+    if (tri < 0) return lgemm<T>(g, tA, tB, Lc.lh, Lc.lw, kb, alpha, A, lda, B, ldb, beta, C, ldc, s, sm_reserve);
+    return local_trrk<T>(g, tri, tA, tB, Lc, kb, alpha, A, lda, B, ldb, C, ldc, s, sm_reserve);   // beta applied by the caller
+}
 
 // Host images of A's and B's local blocks (hyd_gemm_host_*): SUMMA-C streams them to the device panel by panel
 // on an upload stream, so the H2D copies hide under the previous panels' GEMMs instead of preceding the whole Gemm.
@@ -280,7 +340,9 @@ int summa_c_host_blocked(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, 
 // ---- SUMMA-C (stationary C) -------------------------------------------------
 template <typename T>
 int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, const DM& B, T beta, const DM& C, i64 nb,
-            cudaStream_t s, const HostOperands* ho) {
+            cudaStream_t s, const HostOperands* ho, int tri = -1) {
+    // tri >= 0 (Trrk / Syrk): only the LOWER (0) / UPPER (1) triangle of C is updated; the caller has already applied beta
+    // to it (ScaleTrapezoid) and passes beta = 1.
     // `beta` is applied by the first panel's update (C = alpha A1 B1^T + beta C) instead of a separate
     // Scale(beta, C) pass (reference Gemm.cpp:287): one full read+write of C saved, and beta == 0 never reads C.
     const GridShape& sh = g.shape;
@@ -331,8 +393,8 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
             if (ho) cudaStreamWaitEvent(s, g.upload_ev[p], 0);
             const T* a = static_cast<const T*>(A.buf) + (oA ? k0 : k0 * A.ldim);
             const T* b = static_cast<const T*>(B.buf) + (oB ? k0 * B.ldim : k0);
-            if (lgemm<T>(g, oA, oB, m, n, kb, alpha, a, A.ldim, b, B.ldim, k0 == 0 ? beta : T(1), static_cast<T*>(C.buf),
-                         C.ldim, s, 0))
+            if (local_update<T>(g, tri, oA, oB, Lc, kb, alpha, a, A.ldim, b, B.ldim, k0 == 0 ? beta : T(1),
+                                static_cast<T*>(C.buf), C.ldim, s, 0))
                 return 1;
         }
         return 0;
@@ -371,9 +433,9 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
             cudaEventRecord(g.ev_panel_ready[buf], cs);
             cudaStreamWaitEvent(s, g.ev_panel_ready[buf], 0);
         }
-        if (lgemm<T>(g, 0, ce ? 0 : 1, Lc.lh, Lc.lw, kb, alpha, static_cast<const T*>(Ap.buf), Ap.ldim,
-                     static_cast<const T*>(Bp.buf), Bp.ldim, k0 == 0 ? beta : T(1), static_cast<T*>(C.buf), C.ldim, s,
-                     (overlap && !ce) ? g.sm_reserve : 0))
+        if (local_update<T>(g, tri, 0, ce ? 0 : 1, Lc, kb, alpha, static_cast<const T*>(Ap.buf), Ap.ldim,
+                            static_cast<const T*>(Bp.buf), Bp.ldim, k0 == 0 ? beta : T(1), static_cast<T*>(C.buf), C.ldim, s,
+                            (overlap && !ce) ? g.sm_reserve : 0))
             return 1;
         if (overlap) cudaEventRecord(g.ev_panel_free[buf], s);
         // tell the panel's writers it has been consumed (ordered after the GEMM that read it)
@@ -578,6 +640,57 @@ int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A0, const DM&
     return 0;
 }
 
+// El::Trrk(uplo, orientA, orientB, alpha, A, B, beta, C) -- src/blas_like/level3/Trrk.cpp:98-115 -> ScaleTrapezoid(beta, uplo, C),
+// then trrk::Trrk{NN,NT,TN,TT} (Trrk/NN.hpp:17-57 ...): the SUMMA-C panel loop with LocalTrrk as the local update.  Here: the same
+// SUMMA-C engine as Gemm (one-hop panel gathers, double buffering, copy-engine / push transports) with local_trrk.
+template <typename T>
+int dist_trrk(Grid& g, int uplo, int oA, int oB, T alpha, const DM& A0, const DM& B0, T beta, const DM& C0, i64 blocksize,
+              cudaStream_t s) {
+    oA = oA ? 1 : 0;
+    oB = oB ? 1 : 0;
+    if (uplo != 0 && uplo != 1) return set_error("hyd_trrk: uplo must be LOWER (0) or UPPER (1)");
+    const i64 n = C0.height;
+    const i64 k = oA ? A0.height : A0.width;
+    const i64 am = oA ? A0.width : A0.height, bk = oB ? B0.width : B0.height, bn = oB ? B0.height : B0.width;
+    if (C0.width != n || am != n || bn != n || bk != k)
+        return set_error("hyd_trrk: nonconformal matrices: op(A) %lldx%lld, op(B) %lldx%lld, C %lldx%lld", am, k, bk, bn, n, C0.width);
+    if (blocksize <= 0) return set_error("hyd_trrk: blocksize must be positive");
+    if (n == 0) return 0;
+    const LocalShape Lc0 = local_shape(g.shape, C0, g.mc, g.mr);
+    if (beta != T(1) && trapezoid_local<T>(2, uplo, Lc0.lh, Lc0.lw, Lc0.colShift, Lc0.colStride, Lc0.rowShift, Lc0.rowStride, 0, beta,
+                                            nullptr, 0, static_cast<T*>(C0.buf), C0.ldim, s))
+        return 1;
+    if (k == 0) return 0;
+    TempPool pool;
+    DM A, B, C;
+    if (read_proxy<T>(g, pool, C0, MC, MR, false, 0, false, 0, C, s)) return 1;
+    if (read_proxy<T>(g, pool, A0, MC, MR, false, 0, false, 0, A, s)) return 1;
+    if (read_proxy<T>(g, pool, B0, MC, MR, false, 0, false, 0, B, s)) return 1;
+    if (summa_c<T>(g, oA, oB, n, n, k, alpha, A, B, T(1), C, blocksize, s, nullptr, uplo)) return 1;
+    if (C.buf != C0.buf && redistribute<T>(g, C, C0, false, 3, s)) return 1;
+    if (!pool.bufs.empty() && check_cuda(cudaStreamSynchronize(s), "proxy sync")) return 1;
+    return 0;
+}
+
+// ScaleTrapezoid / AxpyTrapezoid / MakeTrapezoidal on a DistMatrix in any distribution: the local block with its global
+// index map (ScaleTrapezoid.hpp:47-92, AxpyTrapezoid.hpp, MakeTrapezoidal.hpp).  op as in trapezoid_local.
+template <typename T>
+int dist_trapezoid(Grid& g, int op, int uplo, T alpha, const DM* X, const DM& Y, i64 offset, cudaStream_t s) {
+    if (uplo != 0 && uplo != 1) return set_error("trapezoid: uplo must be LOWER (0) or UPPER (1)");
+    const LocalShape L = local_shape(g.shape, Y, g.mc, g.mr);
+    if (X) {
+        if (X->height != Y.height || X->width != Y.width) return set_error("AxpyTrapezoid: nonconformal matrices");
+        if (X->colDist != Y.colDist || X->rowDist != Y.rowDist || X->colAlign != Y.colAlign || X->rowAlign != Y.rowAlign)
+            return set_error("AxpyTrapezoid: X and Y must share distribution and alignments");
+    }
+    return trapezoid_local<T>(op, uplo, L.lh, L.lw, L.colShift, L.colStride, L.rowShift, L.rowStride, offset, alpha,
+                              X ? static_cast<const T*>(X->buf) : nullptr, X ? X->ldim : 0, static_cast<T*>(Y.buf), Y.ldim, s);
+}
+
+template int dist_trrk<double>(Grid&, int, int, int, double, const DM&, const DM&, double, const DM&, i64, cudaStream_t);
+template int dist_trrk<float>(Grid&, int, int, int, float, const DM&, const DM&, float, const DM&, i64, cudaStream_t);
+template int dist_trapezoid<double>(Grid&, int, int, double, const DM*, const DM&, i64, cudaStream_t);
+template int dist_trapezoid<float>(Grid&, int, int, float, const DM*, const DM&, i64, cudaStream_t);
 template int dist_gemm<double>(Grid&, int, int, int, double, const DM&, const DM&, double, const DM&, i64, cudaStream_t, const void*, i64, const void*, i64, void*, i64, int*);
 template int dist_gemm<float>(Grid&, int, int, int, float, const DM&, const DM&, float, const DM&, i64, cudaStream_t, const void*, i64, const void*, i64, void*, i64, int*);
 

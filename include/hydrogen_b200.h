@@ -313,6 +313,42 @@ int hyd_gemm_f64(hyd_grid* g, int orientA, int orientB, int alg, double alpha, c
 int hyd_gemm_f32(hyd_grid* g, int orientA, int orientB, int alg, float alpha, const hyd_dm* A, const hyd_dm* B,
                  float beta, const hyd_dm* C, int64_t blocksize, hyd_stream_t stream);
 
+/* ---- triangular rank-k updates on the same SUMMA-C engine.  uplo: 0 = LOWER, 1 = UPPER
+ * (El::UpperOrLower, include/El/core/types.hpp:489-493).  Only the `uplo` triangle of the square C is read or written.
+ * ref: El::Trrk(uplo,orientA,orientB,alpha,A,B,beta,C), src/blas_like/level3/Trrk.cpp:98-115 (ScaleTrapezoid, then
+ * trrk::Trrk{NN,NT,TN,TT}: SUMMA-C panels with LocalTrrk, Trrk/Local.hpp:640-740); El::Syrk / El::Herk (real T),
+ * src/blas_like/level3/Syrk.cpp:72-90 -> syrk::{LN,LT,UN,UT} (Syrk/LN.hpp:14-50): orient NORMAL is C := alpha A A^T + beta C,
+ * TRANSPOSE is C := alpha A^T A + beta C.  Any supported distribution for A, B, C (proxies as in hyd_gemm_*). */
+int hyd_trrk_f64(hyd_grid* g, int uplo, int orientA, int orientB, double alpha, const hyd_dm* A, const hyd_dm* B, double beta,
+                 const hyd_dm* C, int64_t blocksize, hyd_stream_t stream);
+int hyd_trrk_f32(hyd_grid* g, int uplo, int orientA, int orientB, float alpha, const hyd_dm* A, const hyd_dm* B, float beta,
+                 const hyd_dm* C, int64_t blocksize, hyd_stream_t stream);
+int hyd_syrk_f64(hyd_grid* g, int uplo, int orient, double alpha, const hyd_dm* A, double beta, const hyd_dm* C,
+                 int64_t blocksize, hyd_stream_t stream);
+int hyd_syrk_f32(hyd_grid* g, int uplo, int orient, float alpha, const hyd_dm* A, float beta, const hyd_dm* C,
+                 int64_t blocksize, hyd_stream_t stream);
+/* Trapezoid level-1 operations.  LOWER holds the entries with j - i <= offset, UPPER those with j - i >= offset.
+ * ref: ScaleTrapezoid(alpha,uplo,A,offset) include/El/blas_like/level1/ScaleTrapezoid.hpp:14-92 (A *= alpha inside);
+ *      AxpyTrapezoid(uplo,alpha,X,Y,offset) AxpyTrapezoid.hpp:14-100 (Y += alpha X inside; X, Y same distribution and
+ *      alignments); MakeTrapezoidal(uplo,A,offset) MakeTrapezoidal.hpp (A = 0 outside).
+ * Local column-major blocks (Matrix<T,GPU>) and DistMatrix forms (any supported distribution). */
+int hyd_scale_trapezoid_f64(double alpha, int uplo, int64_t m, int64_t n, double* A, int64_t lda, int64_t offset, hyd_stream_t stream);
+int hyd_scale_trapezoid_f32(float alpha, int uplo, int64_t m, int64_t n, float* A, int64_t lda, int64_t offset, hyd_stream_t stream);
+int hyd_axpy_trapezoid_f64(int uplo, double alpha, int64_t m, int64_t n, const double* X, int64_t ldx, double* Y, int64_t ldy,
+                           int64_t offset, hyd_stream_t stream);
+int hyd_axpy_trapezoid_f32(int uplo, float alpha, int64_t m, int64_t n, const float* X, int64_t ldx, float* Y, int64_t ldy,
+                           int64_t offset, hyd_stream_t stream);
+int hyd_make_trapezoidal_f64(int uplo, int64_t m, int64_t n, double* A, int64_t lda, int64_t offset, hyd_stream_t stream);
+int hyd_make_trapezoidal_f32(int uplo, int64_t m, int64_t n, float* A, int64_t lda, int64_t offset, hyd_stream_t stream);
+int hyd_scale_trapezoid_dist_f64(hyd_grid* g, double alpha, int uplo, const hyd_dm* A, int64_t offset, hyd_stream_t stream);
+int hyd_scale_trapezoid_dist_f32(hyd_grid* g, float alpha, int uplo, const hyd_dm* A, int64_t offset, hyd_stream_t stream);
+int hyd_axpy_trapezoid_dist_f64(hyd_grid* g, int uplo, double alpha, const hyd_dm* X, const hyd_dm* Y, int64_t offset,
+                                hyd_stream_t stream);
+int hyd_axpy_trapezoid_dist_f32(hyd_grid* g, int uplo, float alpha, const hyd_dm* X, const hyd_dm* Y, int64_t offset,
+                                hyd_stream_t stream);
+int hyd_make_trapezoidal_dist_f64(hyd_grid* g, int uplo, const hyd_dm* A, int64_t offset, hyd_stream_t stream);
+int hyd_make_trapezoidal_dist_f32(hyd_grid* g, int uplo, const hyd_dm* A, int64_t offset, hyd_stream_t stream);
+
 /* Same operation with the local blocks of A, B, C in HOST memory (buf = host pointer; pinned memory makes the copies
  * asynchronous): uploads the blocks, runs hyd_gemm_*, downloads C's block and synchronises `stream`.  This is the call a
  * CPU-resident caller of El::Gemm makes (the reference's inter-device DistMatrix copies: MC_STAR.cpp:304-390, then Gemm). */
