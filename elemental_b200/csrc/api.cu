@@ -244,6 +244,21 @@ int hyd_view(const hyd_grid* g, const hyd_dm* a, int64_t i, int64_t j, int64_t h
     return 0;
 }
 
+int hyd_trrk_plan(int gh, int gw, int order, int rank, const hyd_dm* C, int uplo, int64_t j0, int64_t w, int es, int64_t* cuts) {
+    hyd::GridShape sh;
+    sh.r = gh; sh.c = gw; sh.col_major = order ? 1 : 0;
+    if (gh <= 0 || gw <= 0 || rank < 0 || rank >= gh * gw || !cuts) return set_error("hyd_trrk_plan: bad arguments");
+    if ((uplo != 0 && uplo != 1) || (es != 4 && es != 8)) return set_error("hyd_trrk_plan: bad uplo / element size");
+    if (check_dm(sh, C, "hyd_trrk_plan")) return 1;
+    int mc, mr;
+    sh.coords(rank, mc, mr);
+    const hyd::LocalShape L = hyd::local_shape(sh, to_dm(C), mc, mr);
+    if (j0 < 0 || w <= 0 || j0 + w > L.lw) return set_error("hyd_trrk_plan: column block outside the local block");
+    const hyd::TrrkCuts k = hyd::trrk_cuts(uplo, L, j0, w, 16 / es);
+    cuts[0] = k.d0; cuts[1] = k.d1; cuts[2] = k.t0; cuts[3] = k.t1;
+    return 0;
+}
+
 int hyd_redist_plan(int gh, int gw, int order, int rank, const hyd_dm* src, const hyd_dm* dst, int transpose, int es,
                     int64_t* sendBytes, int64_t* recvBytes) {
     hyd::GridShape sh;

@@ -68,6 +68,32 @@ inline LocalShape local_shape(const GridShape& g, const DM& a, int mc, int mr) {
     return s;
 }
 
+// Row cuts of one column block [j0, j0+w) of a local [MC,MR]-like block for the trapezoidal update (summa.cu local_trrk):
+// rows [d0,d1) lie in the `tri` triangle (0 LOWER: gi >= gj, 1 UPPER: gi <= gj) for EVERY column of the block, rows [t0,t1) are
+// the strip the diagonal may cross (computed into a temporary and added under a mask), every other row is outside for every
+// column.  Cuts between the two ranges are rounded to q rows (16 bytes) towards the strip.
+struct TrrkCuts { i64 d0, d1, t0, t1; };
+inline TrrkCuts trrk_cuts(int tri, const LocalShape& L, i64 j0, i64 w, i64 q) {
+    const i64 r = L.colStride, c = L.rowStride, lh = L.lh;
+    auto clip = [&](i64 x) { return x < 0 ? 0 : (x > lh ? lh : x); };
+    auto ceil_div = [](i64 a, i64 b) { return a >= 0 ? (a + b - 1) / b : -((-a) / b); };
+    auto floor_div = [](i64 a, i64 b) { return a >= 0 ? a / b : -((-a + b - 1) / b); };
+    const i64 gj_first = L.rowShift + j0 * c, gj_last = L.rowShift + (j0 + w - 1) * c;
+    TrrkCuts k;
+    if (tri == 0) {
+        k.t0 = clip(ceil_div(gj_first - L.colShift, r)) / q * q;
+        const i64 up = (clip(ceil_div(gj_last - L.colShift, r)) + q - 1) / q * q;
+        k.t1 = up < lh ? up : lh;
+        k.d0 = k.t1; k.d1 = lh;
+    } else {
+        k.d0 = 0;
+        k.d1 = clip(floor_div(gj_first - L.colShift, r) + 1) / q * q;
+        k.t0 = k.d1;
+        k.t1 = clip(floor_div(gj_last - L.colShift, r) + 1);
+    }
+    return k;
+}
+
 // One arithmetic progression of global indices i = first + t*step, t < count,
 // together with where it sits in the source's and the destination's local index space.
 struct Prog { i64 count = 0, src0 = 0, srcStep = 1, dst0 = 0, dstStep = 1; };

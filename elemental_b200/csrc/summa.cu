@@ -89,27 +89,15 @@ int local_trrk(Grid& g, int tri, int tA, int tB, const LocalShape& Lc, i64 kb, T
                T* C, i64 ldc, cudaStream_t s, int sm_reserve) {
     const i64 q = 16 / (i64)sizeof(T);
     const i64 r = Lc.colStride, c = Lc.rowStride, lh = Lc.lh, lw = Lc.lw;
-    auto clip = [&](i64 x) { return std::max<i64>(0, std::min<i64>(lh, x)); };
-    auto ceil_div = [](i64 a, i64 b) { return a >= 0 ? (a + b - 1) / b : -((-a) / b); };
-    auto floor_div = [](i64 a, i64 b) { return a >= 0 ? a / b : -((-a + b - 1) / b); };
     {   // the widest strip any column block can have, reserved once (growing a workspace synchronises the device)
         const i64 wmax = std::min(kTrrkBlock, lw), thmax = std::min(lh, ((wmax - 1) * c) / r + 2 + 2 * q);
         if (lw > 0 && ws_reserve(g.trrk_ws, (size_t)(pad_ld(thmax, sizeof(T)) * wmax) * sizeof(T))) return 1;
     }
     for (i64 j0 = 0; j0 < lw; j0 += kTrrkBlock) {
         const i64 w = std::min(kTrrkBlock, lw - j0);
-        const i64 gj_first = Lc.rowShift + j0 * c, gj_last = Lc.rowShift + (j0 + w - 1) * c;
-        i64 d0, d1, t0, t1;   // direct rows [d0,d1), strip rows [t0,t1)
-        if (tri == 0) {       // LOWER: gi >= gj
-            t0 = clip(ceil_div(gj_first - Lc.colShift, r)) / q * q;
-            t1 = std::min(lh, (clip(ceil_div(gj_last - Lc.colShift, r)) + q - 1) / q * q);
-            d0 = t1; d1 = lh;
-        } else {              // UPPER: gi <= gj
-            d0 = 0;
-            d1 = clip(floor_div(gj_first - Lc.colShift, r) + 1) / q * q;
-            t0 = d1;
-            t1 = clip(floor_div(gj_last - Lc.colShift, r) + 1);
-        }
+        const TrrkCuts cut = trrk_cuts(tri, Lc, j0, w, q);
+        const i64 d0 = cut.d0, d1 = cut.d1, t0 = cut.t0, t1 = cut.t1;
+        const i64 gj_first = Lc.rowShift + j0 * c;
         const T* Bj = tB ? B + j0 : B + j0 * ldb;
         T* Cj = C + j0 * ldc;
         if (d1 > d0) {

@@ -23,6 +23,7 @@ MC, MD, MR, VC, VR, STAR, CIRC = range(7)
 NORMAL, TRANSPOSE, ADJOINT = 0, 1, 2
 GEMM_DEFAULT, GEMM_SUMMA_A, GEMM_SUMMA_B, GEMM_SUMMA_C, GEMM_SUMMA_DOT, GEMM_CANNON = range(6)
 ROW_MAJOR, COLUMN_MAJOR = 0, 1
+LOWER, UPPER = 0, 1   # El::UpperOrLower, include/El/core/types.hpp:489-493
 
 _blocksize_stack = [128]  # environment.cpp:305-306
 
@@ -331,6 +332,47 @@ def Gemm(orientA, orientB, alpha, A, B, beta, Cm, alg=GEMM_DEFAULT, stream=None,
     fn = getattr(lib, ("hyd_gemm_host_" if host else "hyd_gemm_") + _sfx(Cm.dtype))
     check(fn(Cm.grid.h, orientA, orientB, alg, _scalar(Cm.dtype, alpha), C.byref(a), C.byref(b), _scalar(Cm.dtype, beta),
              C.byref(c), nb, _stream_ptr(stream)))
+
+
+def Trrk(uplo, orientA, orientB, alpha, A, B, beta, Cm, stream=None, blocksize=None):
+    """Triangle `uplo` of C := alpha op(A) op(B) + beta C  (El::Trrk on AbstractDistMatrix, Trrk.cpp:98-115)."""
+    a, b, c = A.desc(), B.desc(), Cm.desc()
+    nb = Blocksize() if blocksize is None else int(blocksize)
+    check(getattr(lib, "hyd_trrk_" + _sfx(Cm.dtype))(Cm.grid.h, uplo, orientA, orientB, _scalar(Cm.dtype, alpha), C.byref(a),
+                                                    C.byref(b), _scalar(Cm.dtype, beta), C.byref(c), nb, _stream_ptr(stream)))
+
+
+def Syrk(uplo, orientation, alpha, A, beta, Cm, conjugate=False, stream=None, blocksize=None):
+    """Triangle `uplo` of C := alpha A A^T + beta C (NORMAL) or alpha A^T A + beta C  (El::Syrk, Syrk.cpp:72-90)."""
+    a, c = A.desc(), Cm.desc()
+    nb = Blocksize() if blocksize is None else int(blocksize)
+    check(getattr(lib, "hyd_syrk_" + _sfx(Cm.dtype))(Cm.grid.h, uplo, orientation, _scalar(Cm.dtype, alpha), C.byref(a),
+                                                    _scalar(Cm.dtype, beta), C.byref(c), nb, _stream_ptr(stream)))
+
+
+def Herk(uplo, orientation, alpha, A, beta, Cm, stream=None, blocksize=None):
+    """El::Herk (Herk.cpp): Syrk with conjugate = true; the same operation for real T."""
+    Syrk(uplo, orientation, alpha, A, beta, Cm, True, stream, blocksize)
+
+
+def ScaleTrapezoid(alpha, uplo, A, offset=0, stream=None):
+    """A *= alpha inside the trapezoid (ScaleTrapezoid.hpp:47-92)."""
+    a = A.desc()
+    check(getattr(lib, "hyd_scale_trapezoid_dist_" + _sfx(A.dtype))(A.grid.h, _scalar(A.dtype, alpha), uplo, C.byref(a), offset,
+                                                                   _stream_ptr(stream)))
+
+
+def AxpyTrapezoid(uplo, alpha, X, Y, offset=0, stream=None):
+    """Y += alpha X inside the trapezoid; X and Y share distribution and alignments (AxpyTrapezoid.hpp:54-100)."""
+    x, y = X.desc(), Y.desc()
+    check(getattr(lib, "hyd_axpy_trapezoid_dist_" + _sfx(Y.dtype))(Y.grid.h, uplo, _scalar(Y.dtype, alpha), C.byref(x), C.byref(y),
+                                                                  offset, _stream_ptr(stream)))
+
+
+def MakeTrapezoidal(uplo, A, offset=0, stream=None):
+    """A := 0 outside the trapezoid (MakeTrapezoidal.hpp:48-90)."""
+    a = A.desc()
+    check(getattr(lib, "hyd_make_trapezoidal_dist_" + _sfx(A.dtype))(A.grid.h, uplo, C.byref(a), offset, _stream_ptr(stream)))
 
 
 def lgemm(tA, tB, m, n, k, alpha, A, lda, B, ldb, beta, Cm, ldc, dtype=np.float64, stream=None):

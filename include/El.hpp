@@ -32,6 +32,7 @@ enum DistWrap { ELEMENT, BLOCK };
 enum class Device { CPU, GPU };
 enum Orientation { NORMAL = HYD_NORMAL, TRANSPOSE = HYD_TRANSPOSE, ADJOINT = HYD_ADJOINT };
 enum GridOrder { ROW_MAJOR = 0, COLUMN_MAJOR = 1 };
+enum UpperOrLower { LOWER = 0, UPPER = 1 };   // include/El/core/types.hpp:489-493
 enum GemmAlgorithm {
     GEMM_DEFAULT = HYD_GEMM_DEFAULT, GEMM_SUMMA_A = HYD_GEMM_SUMMA_A, GEMM_SUMMA_B = HYD_GEMM_SUMMA_B,
     GEMM_SUMMA_C = HYD_GEMM_SUMMA_C, GEMM_SUMMA_DOT = HYD_GEMM_SUMMA_DOT, GEMM_CANNON = HYD_GEMM_CANNON
@@ -168,6 +169,11 @@ template <> struct Sfx<double> {
     static int axpy1d(int64_t n, double al, const double* X, int64_t incx, double* Y, int64_t incy, void* s) { return hyd_axpy1d_f64(n, al, X, incx, Y, incy, s); }
     static int scale1d(int64_t n, double al, double* X, int64_t incx, void* s) { return hyd_scale1d_f64(n, al, X, incx, s); }
     static int axpy_dist(hyd_grid* g, double al, const hyd_dm* X, const hyd_dm* Y, int t, void* s) { return hyd_axpy_dist_f64(g, al, X, Y, t, s); }
+    static int trrk(hyd_grid* g, int ul, int oA, int oB, double al, const hyd_dm* A, const hyd_dm* B, double be, const hyd_dm* C, int64_t nb, void* s) { return hyd_trrk_f64(g, ul, oA, oB, al, A, B, be, C, nb, s); }
+    static int syrk(hyd_grid* g, int ul, int o, double al, const hyd_dm* A, double be, const hyd_dm* C, int64_t nb, void* s) { return hyd_syrk_f64(g, ul, o, al, A, be, C, nb, s); }
+    static int scale_trap(hyd_grid* g, double al, int ul, const hyd_dm* A, int64_t off, void* s) { return hyd_scale_trapezoid_dist_f64(g, al, ul, A, off, s); }
+    static int axpy_trap(hyd_grid* g, int ul, double al, const hyd_dm* X, const hyd_dm* Y, int64_t off, void* s) { return hyd_axpy_trapezoid_dist_f64(g, ul, al, X, Y, off, s); }
+    static int make_trap(hyd_grid* g, int ul, const hyd_dm* A, int64_t off, void* s) { return hyd_make_trapezoidal_dist_f64(g, ul, A, off, s); }
     static int interleave(int64_t h, int64_t w, const double* A, int64_t csA, int64_t rsA, double* B, int64_t csB, int64_t rsB, void* s) { return hyd_interleave_f64(h, w, A, csA, rsA, B, csB, rsB, s); }
     static int interleave_update(double al, int64_t h, int64_t w, const double* A, int64_t csA, int64_t rsA, double* B, int64_t csB, int64_t rsB, void* s) { return hyd_interleave_update_f64(al, h, w, A, csA, rsA, B, csB, rsB, s); }
     static int row_pack(int64_t h, int64_t w, int64_t al, int64_t st, const double* A, int64_t ld, double* P, int64_t ps, void* s) { return hyd_row_strided_pack_f64(h, w, al, st, A, ld, P, ps, s); }
@@ -197,6 +203,11 @@ template <> struct Sfx<float> {
     static int axpy1d(int64_t n, float al, const float* X, int64_t incx, float* Y, int64_t incy, void* s) { return hyd_axpy1d_f32(n, al, X, incx, Y, incy, s); }
     static int scale1d(int64_t n, float al, float* X, int64_t incx, void* s) { return hyd_scale1d_f32(n, al, X, incx, s); }
     static int axpy_dist(hyd_grid* g, float al, const hyd_dm* X, const hyd_dm* Y, int t, void* s) { return hyd_axpy_dist_f32(g, al, X, Y, t, s); }
+    static int trrk(hyd_grid* g, int ul, int oA, int oB, float al, const hyd_dm* A, const hyd_dm* B, float be, const hyd_dm* C, int64_t nb, void* s) { return hyd_trrk_f32(g, ul, oA, oB, al, A, B, be, C, nb, s); }
+    static int syrk(hyd_grid* g, int ul, int o, float al, const hyd_dm* A, float be, const hyd_dm* C, int64_t nb, void* s) { return hyd_syrk_f32(g, ul, o, al, A, be, C, nb, s); }
+    static int scale_trap(hyd_grid* g, float al, int ul, const hyd_dm* A, int64_t off, void* s) { return hyd_scale_trapezoid_dist_f32(g, al, ul, A, off, s); }
+    static int axpy_trap(hyd_grid* g, int ul, float al, const hyd_dm* X, const hyd_dm* Y, int64_t off, void* s) { return hyd_axpy_trapezoid_dist_f32(g, ul, al, X, Y, off, s); }
+    static int make_trap(hyd_grid* g, int ul, const hyd_dm* A, int64_t off, void* s) { return hyd_make_trapezoidal_dist_f32(g, ul, A, off, s); }
     static int interleave(int64_t h, int64_t w, const float* A, int64_t csA, int64_t rsA, float* B, int64_t csB, int64_t rsB, void* s) { return hyd_interleave_f32(h, w, A, csA, rsA, B, csB, rsB, s); }
     static int interleave_update(float al, int64_t h, int64_t w, const float* A, int64_t csA, int64_t rsA, float* B, int64_t csB, int64_t rsB, void* s) { return hyd_interleave_update_f32(al, h, w, A, csA, rsA, B, csB, rsB, s); }
     static int row_pack(int64_t h, int64_t w, int64_t al, int64_t st, const float* A, int64_t ld, float* P, int64_t ps, void* s) { return hyd_row_strided_pack_f32(h, w, al, st, A, ld, P, ps, s); }
@@ -449,6 +460,52 @@ void Gemm(Orientation orientA, Orientation orientB, T alpha, const AbstractDistM
     const Int m = orientA == NORMAL ? A.Height() : A.Width(), n = orientB == NORMAL ? B.Width() : B.Height();
     C.Resize(m, n);
     Gemm(orientA, orientB, alpha, A, B, T(0), C, alg);
+}
+
+// ---- triangular rank-k updates and the trapezoid routines around them ----
+// triangle `uplo` of C := alpha op(A) op(B) + beta C   (src/blas_like/level3/Trrk.cpp:98-115)
+template <typename T>
+void Trrk(UpperOrLower uplo, Orientation orientA, Orientation orientB, T alpha, const AbstractDistMatrix<T>& A,
+          const AbstractDistMatrix<T>& B, T beta, AbstractDistMatrix<T>& C) {
+    detail::check(detail::Sfx<T>::trrk(C.Grid().handle(), uplo, orientA, orientB, alpha, A.desc(), B.desc(), beta, C.desc(), Blocksize(),
+                                       C.Stream()));
+}
+// triangle `uplo` of C := alpha A A^T + beta C (NORMAL) / alpha A^T A + beta C   (src/blas_like/level3/Syrk.cpp:72-90)
+template <typename T>
+void Syrk(UpperOrLower uplo, Orientation orientation, T alpha, const AbstractDistMatrix<T>& A, T beta, AbstractDistMatrix<T>& C,
+          bool /*conjugate*/ = false) {
+    detail::check(detail::Sfx<T>::syrk(C.Grid().handle(), uplo, orientation, alpha, A.desc(), beta, C.desc(), Blocksize(), C.Stream()));
+}
+// C resized to n x n and zeroed first (Syrk.cpp:92-103)
+template <typename T>
+void Syrk(UpperOrLower uplo, Orientation orientation, T alpha, const AbstractDistMatrix<T>& A, AbstractDistMatrix<T>& C,
+          bool conjugate = false) {
+    const Int n = orientation == NORMAL ? A.Height() : A.Width();
+    C.Resize(n, n);
+    detail::check(detail::Sfx<T>::fill(C.LocalHeight(), C.LocalWidth(), T(0), C.Buffer(), C.LDim(), C.Stream()));
+    Syrk(uplo, orientation, alpha, A, T(0), C, conjugate);
+}
+// El::Herk (src/blas_like/level3/Herk.cpp): Syrk with conjugate = true; identical for real T
+template <typename T>
+void Herk(UpperOrLower uplo, Orientation orientation, T alpha, const AbstractDistMatrix<T>& A, T beta, AbstractDistMatrix<T>& C) {
+    Syrk(uplo, orientation, alpha, A, beta, C, true);
+}
+template <typename T>
+void Herk(UpperOrLower uplo, Orientation orientation, T alpha, const AbstractDistMatrix<T>& A, AbstractDistMatrix<T>& C) {
+    Syrk(uplo, orientation, alpha, A, C, true);
+}
+// include/El/blas_like/level1/{ScaleTrapezoid,AxpyTrapezoid,MakeTrapezoidal}.hpp on DistMatrices
+template <typename T>
+void ScaleTrapezoid(T alpha, UpperOrLower uplo, AbstractDistMatrix<T>& A, Int offset = 0) {
+    detail::check(detail::Sfx<T>::scale_trap(A.Grid().handle(), alpha, uplo, A.desc(), offset, A.Stream()));
+}
+template <typename T>
+void AxpyTrapezoid(UpperOrLower uplo, T alpha, const AbstractDistMatrix<T>& X, AbstractDistMatrix<T>& Y, Int offset = 0) {
+    detail::check(detail::Sfx<T>::axpy_trap(Y.Grid().handle(), uplo, alpha, X.desc(), Y.desc(), offset, Y.Stream()));
+}
+template <typename T>
+void MakeTrapezoidal(UpperOrLower uplo, AbstractDistMatrix<T>& A, Int offset = 0) {
+    detail::check(detail::Sfx<T>::make_trap(A.Grid().handle(), uplo, A.desc(), offset, A.Stream()));
 }
 
 // local column-major GEMM on raw device buffers (gpu_blas::Gemm, include/hydrogen/blas/GPU_BLAS_impl.hpp:631-646)

@@ -327,6 +327,11 @@ int hyd_syrk_f64(hyd_grid* g, int uplo, int orient, double alpha, const hyd_dm* 
                  int64_t blocksize, hyd_stream_t stream);
 int hyd_syrk_f32(hyd_grid* g, int uplo, int orient, float alpha, const hyd_dm* A, float beta, const hyd_dm* C,
                  int64_t blocksize, hyd_stream_t stream);
+/* Host-only introspection of the trapezoidal local update (no device call; used by the CPU tests): for local columns
+ * [j0, j0+w) of rank `rank`'s block of C on a gh x gw grid, cuts = {d0, d1, t0, t1}: local rows [d0,d1) are updated by a GEMM
+ * straight into C (inside the triangle for every column), rows [t0,t1) through the masked temporary, all others not at all. */
+int hyd_trrk_plan(int gh, int gw, int order, int rank, const hyd_dm* C, int uplo, int64_t j0, int64_t w, int elem_size,
+                  int64_t* cuts);
 /* Trapezoid level-1 operations.  LOWER holds the entries with j - i <= offset, UPPER those with j - i >= offset.
  * ref: ScaleTrapezoid(alpha,uplo,A,offset) include/El/blas_like/level1/ScaleTrapezoid.hpp:14-92 (A *= alpha inside);
  *      AxpyTrapezoid(uplo,alpha,X,Y,offset) AxpyTrapezoid.hpp:14-100 (Y += alpha X inside; X, Y same distribution and

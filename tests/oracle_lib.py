@@ -80,6 +80,12 @@ _sig("orc_set_blas", i32, [C.c_char_p])
 _sig("orc_blas_threads", i32, [i32])
 _sig("orc_local_gemm", None, [i32, i32, i64, i64, i64, f64, vp, i64, vp, i64, f64, vp, i64, i32])
 _sig("orc_gemm", i32, [i32, i32, i32, f64, vp, vp, f64, vp, i64])
+_sig("orc_scale_trapezoid", None, [f64, i32, vp, i64])
+_sig("orc_axpy_trapezoid", i32, [i32, f64, vp, vp, i64])
+_sig("orc_make_trapezoidal", None, [i32, vp, i64])
+_sig("orc_set_local_trrk_blocksize", None, [i32])
+_sig("orc_trrk", i32, [i32, i32, i32, f64, vp, vp, f64, vp, i64])
+_sig("orc_syrk", i32, [i32, i32, f64, vp, f64, vp, i64])
 _sig("orc_dense_gemm_ref", None, [i32, i32, i64, i64, i64, f64, vp, i64, vp, i64, f64, vp, i64, i32])
 # pack/unpack
 _P = [i64, i64, i64, i64, vp, i64, vp, i64, i32]

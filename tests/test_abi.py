@@ -111,3 +111,48 @@ def test_default_grid_height_matches_the_reference_rule():
     for p in range(1, 2000):
         assert lib.hyd_grid_default_height(p) == O.lib.orc_grid_default_height(p), p
         assert p % lib.hyd_grid_default_height(p) == 0
+
+
+@pytest.mark.parametrize("r,c", [(1, 1), (2, 2), (2, 4), (4, 2), (3, 2), (1, 8)])
+def test_trrk_row_cuts_cover_exactly_the_triangle(r, c):
+    """The trapezoidal local update of hyd_trrk_* / hyd_syrk_* (csrc/summa.cu local_trrk) splits each column block of the local
+    C into rows updated directly, rows updated under a mask, and rows left alone.  For random sizes, alignments and column
+    blocks: direct rows are inside the triangle for every column, untouched rows outside for every column, the two ranges
+    are disjoint and ordered, and cuts between them fall on 16-byte row multiples."""
+    rng = np.random.default_rng(r * 31 + c)
+    P = r * c
+    for _ in range(60):
+        n = int(rng.integers(1, 700))
+        ca, ra = int(rng.integers(0, r)), int(rng.integers(0, c))
+        d = hyd_dm(None, 1, n, n, O.MC, O.MR, ca, ra, 0, 0)
+        for p in range(P):
+            cs, rs, lh, lw = (C.c_int64() for _ in range(4))
+            assert lib.hyd_local_shape_of(r, c, 1, p, C.byref(d), C.byref(cs), C.byref(rs), C.byref(lh), C.byref(lw)) == 0
+            if lw.value == 0:
+                continue
+            gi = cs.value + np.arange(lh.value) * r
+            for es, uplo in ((8, 0), (8, 1), (4, 0), (4, 1)):
+                q = 16 // es
+                j0 = int(rng.integers(0, lw.value))
+                w = int(rng.integers(1, lw.value - j0 + 1))
+                cuts = (C.c_int64 * 4)()
+                assert lib.hyd_trrk_plan(r, c, 1, p, C.byref(d), uplo, j0, w, es, cuts) == 0
+                d0, d1, t0, t1 = cuts
+                gj = rs.value + (j0 + np.arange(w)) * c
+                inside = (gi[:, None] >= gj[None, :]) if uplo == 0 else (gi[:, None] <= gj[None, :])
+                assert 0 <= d0 <= d1 <= lh.value and 0 <= t0 <= t1 <= lh.value
+                assert d1 <= t0 or t1 <= d0
+                touched = np.zeros(lh.value, bool)
+                touched[d0:d1] = True
+                assert inside[d0:d1].all()
+                touched[t0:t1] = True
+                assert not inside[~touched].any()
+                boundary = t1 if uplo == 0 else d1          # the cut the two ranges share
+                assert boundary % q == 0 or boundary == lh.value
+                assert (t0 if uplo == 0 else d0) % q == 0   # first updated row: keeps the operand pointers 16-byte aligned
+                # the strip is never wider than the workspace local_trrk reserves
+                assert t1 - t0 <= min(lh.value, ((w - 1) * c) // r + 2 + 2 * q)
+    cuts = (C.c_int64 * 4)()
+    d = hyd_dm(None, 1, 8, 8, O.MC, O.MR, 0, 0, 0, 0)
+    assert lib.hyd_trrk_plan(1, 1, 1, 0, C.byref(d), 2, 0, 4, 8, cuts) != 0
+    assert lib.hyd_trrk_plan(1, 1, 1, 0, C.byref(d), 0, 6, 4, 8, cuts) != 0

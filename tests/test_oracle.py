@@ -270,3 +270,103 @@ def test_level1_hadamard_and_scale():
     assert np.array_equal(A.to_global()[0], 0.3 * A0)
     O.lib.orc_scale(0.0, A.h)
     assert not A.to_global()[0].any()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Trrk / Syrk and the trapezoid routines (oracle/oracle_level3.c)
+# ---------------------------------------------------------------------------------------------------------------
+def _tri_mask(n, uplo, offset=0, m=None):
+    m = n if m is None else m
+    i, j = np.meshgrid(np.arange(m), np.arange(n), indexing="ij")
+    return (j - i <= offset) if uplo == 0 else (j - i >= offset)
+
+
+@pytest.mark.parametrize("r,c", [(1, 1), (2, 2), (2, 4), (3, 2)])
+def test_trapezoid_routines_match_dense_definition(r, c):
+    """ScaleTrapezoid / AxpyTrapezoid / MakeTrapezoidal with offsets, on rectangular matrices in several distributions
+    and random alignments: LOWER holds j - i <= offset, UPPER j - i >= offset (ScaleTrapezoid.hpp:22-42)."""
+    g = Grid(r, c, 1)
+    rng = np.random.default_rng(100 + r * 7 + c)
+    for (m, n), (cd, rd), uplo, offset in itertools.product([(37, 37), (23, 41), (50, 19)], [(MC, MR), (VC, STAR), (STAR, VR), (MR, MC)],
+                                                            (0, 1), (-3, 0, 2)):
+        ca, ra = rand_align(rng, g, cd), rand_align(rng, g, rd)
+        mask = _tri_mask(n, uplo, offset, m)
+        A = DM(g, m, n, cd, rd, ca, ra).fill(5)
+        G0, _ = A.to_global()
+        lib.orc_scale_trapezoid(-1.5, uplo, A.h, offset)
+        G1, mism = A.to_global()
+        assert mism == 0 and np.array_equal(G1, np.where(mask, G0 * -1.5, G0))
+        X = DM(g, m, n, cd, rd, ca, ra).fill(6)
+        GX, _ = X.to_global()
+        assert lib.orc_axpy_trapezoid(uplo, 0.75, X.h, A.h, offset) == 0
+        G2, mism = A.to_global()
+        assert mism == 0 and np.array_equal(G2, np.where(mask, G1 + 0.75 * GX, G1))
+        lib.orc_make_trapezoidal(uplo, A.h, offset)
+        G3, mism = A.to_global()
+        assert mism == 0 and np.array_equal(G3, np.where(mask, G2, 0.0))
+    Y = DM(g, 9, 9, MC, MR, 0, 0)
+    assert lib.orc_axpy_trapezoid(0, 1.0, DM(g, 9, 8, MC, MR, 0, 0).h, Y.h, 0) == -1
+
+
+@pytest.mark.parametrize("use_blas", [False, True])
+@pytest.mark.parametrize("r,c", [(1, 1), (2, 2), (2, 4), (3, 2)])
+def test_trrk_and_syrk_vs_dense(r, c, use_blas):
+    """tests/blas_like/Syrk.cpp restated (alpha, beta, alignments, LocalTrrkBlocksize) with a stronger check than its printed
+    associativity residual: the `uplo` triangle equals the dense long-double product to 1e-10, and every entry on the other
+    side of the diagonal keeps its bits."""
+    if use_blas and not O.use_blas(True):
+        pytest.skip("no vendor BLAS found")
+    if not use_blas:
+        O.use_blas(False)
+    g = Grid(r, c, 1)
+    rng = np.random.default_rng(200 + r * 7 + c)
+    n, k = 150, 45
+    for nb_local in (8, 64):
+        lib.orc_set_local_trrk_blocksize(nb_local)
+        for uplo, oA, oB in itertools.product((0, 1), (0, 1), (0, 1)):
+            am, an = (k, n) if oA else (n, k)
+            bm, bn = (n, k) if oB else (k, n)
+            A = DM(g, am, an, MC, MR, rand_align(rng, g, MC), rand_align(rng, g, MR)).fill(1)
+            B = DM(g, bm, bn, MC, MR, rand_align(rng, g, MC), rand_align(rng, g, MR)).fill(2)
+            Cm = DM(g, n, n, MC, MR, rand_align(rng, g, MC), rand_align(rng, g, MR)).fill(3)
+            GA, _ = A.to_global(); GB, _ = B.to_global(); GC, _ = Cm.to_global()
+            exp = np.asfortranarray(GC.copy())
+            lib.orc_dense_gemm_ref(oA, oB, n, n, k, 2.0, GA.ctypes.data, am, GB.ctypes.data, bm, 3.0, exp.ctypes.data, n, 8)
+            assert lib.orc_trrk(uplo, oA, oB, 2.0, A.h, B.h, 3.0, Cm.h, 16) == 0
+            got, mism = Cm.to_global()
+            mask = _tri_mask(n, uplo)
+            assert mism == 0
+            assert np.max(np.abs(got - exp)[mask]) <= 1e-10, (uplo, oA, oB)
+            assert np.array_equal(got[~mask], GC[~mask]), (uplo, oA, oB)
+        for uplo, orient in itertools.product((0, 1), (0, 1)):
+            am, an = (k, n) if orient else (n, k)
+            A = DM(g, am, an, MC, MR, rand_align(rng, g, MC), rand_align(rng, g, MR)).fill(1)
+            Cm = DM(g, n, n, MC, MR, rand_align(rng, g, MC), rand_align(rng, g, MR)).fill(3)
+            GA, _ = A.to_global(); GC, _ = Cm.to_global()
+            exp = np.asfortranarray(GC.copy())
+            lib.orc_dense_gemm_ref(orient, 1 - orient, n, n, k, 2.0, GA.ctypes.data, am, GA.ctypes.data, am, 3.0, exp.ctypes.data, n, 8)
+            assert lib.orc_syrk(uplo, orient, 2.0, A.h, 3.0, Cm.h, 16) == 0
+            got, mism = Cm.to_global()
+            mask = _tri_mask(n, uplo)
+            assert mism == 0
+            assert np.max(np.abs(got - exp)[mask]) <= 1e-10, (uplo, orient)
+            assert np.array_equal(got[~mask], GC[~mask]), (uplo, orient)
+    lib.orc_set_local_trrk_blocksize(64)
+    O.use_blas(False)
+
+
+def test_trrk_operand_proxies_and_fp32():
+    """Operands and C in other distributions go through the [MC,MR] proxies (Trrk/NN.hpp:36-41); fp32 bound 1e-3."""
+    g = Grid(2, 2, 1)
+    n, k = 64, 30
+    A = DM(g, n, k, VC, STAR, 1, 0, np.float32).fill(1)
+    B = DM(g, k, n, STAR, VR, 0, 2, np.float32).fill(2)
+    Cm = DM(g, n, n, MR, MC, 1, 1, np.float32).fill(3)
+    GA, _ = A.to_global(); GB, _ = B.to_global(); GC, _ = Cm.to_global()
+    exp = np.asfortranarray(GC.copy())
+    lib.orc_dense_gemm_ref(0, 0, n, n, k, 2.0, GA.ctypes.data, n, GB.ctypes.data, k, 3.0, exp.ctypes.data, n, 4)
+    assert lib.orc_trrk(1, 0, 0, 2.0, A.h, B.h, 3.0, Cm.h, 8) == 0
+    got, mism = Cm.to_global()
+    mask = _tri_mask(n, 1)
+    assert mism == 0 and np.max(np.abs(got - exp)[mask]) <= 1e-3 and np.array_equal(got[~mask], GC[~mask])
+    assert lib.orc_trrk(0, 0, 0, 1.0, A.h, B.h, 1.0, DM(g, n, n + 1, MC, MR, 0, 0, np.float32).h, 8) == -1
