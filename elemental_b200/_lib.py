@@ -96,6 +96,7 @@ _sig("hyd_gemm_f64", i32, [vp, i32, i32, i32, f64, dmp, dmp, f64, dmp, i64, vp])
 _sig("hyd_gemm_f32", i32, [vp, i32, i32, i32, f32, dmp, dmp, f32, dmp, i64, vp])
 for _sfx, _ft in (("f64", f64), ("f32", f32)):
     _sig("hyd_trrk_" + _sfx, i32, [vp, i32, i32, i32, _ft, dmp, dmp, _ft, dmp, i64, vp])
+    _sig("hyd_symm_" + _sfx, i32, [vp, i32, i32, _ft, dmp, dmp, _ft, dmp, i64, vp])
     _sig("hyd_syrk_" + _sfx, i32, [vp, i32, i32, _ft, dmp, _ft, dmp, i64, vp])
     _sig("hyd_scale_trapezoid_" + _sfx, i32, [_ft, i32, i64, i64, vp, i64, i64, vp])
     _sig("hyd_axpy_trapezoid_" + _sfx, i32, [i32, _ft, i64, i64, vp, i64, vp, i64, i64, vp])
@@ -103,6 +104,7 @@ for _sfx, _ft in (("f64", f64), ("f32", f32)):
     _sig("hyd_scale_trapezoid_dist_" + _sfx, i32, [vp, _ft, i32, dmp, i64, vp])
     _sig("hyd_axpy_trapezoid_dist_" + _sfx, i32, [vp, i32, _ft, dmp, dmp, i64, vp])
     _sig("hyd_make_trapezoidal_dist_" + _sfx, i32, [vp, i32, dmp, i64, vp])
+    _sig("hyd_make_symmetric_dist_" + _sfx, i32, [vp, i32, dmp, vp])
 _sig("hyd_trrk_plan", i32, [i32, i32, i32, i32, dmp, i32, i64, i64, i32, C.POINTER(i64)])
 _sig("hyd_gemm_host_f64", i32, [vp, i32, i32, i32, f64, dmp, dmp, f64, dmp, i64, vp])
 _sig("hyd_gemm_host_f32", i32, [vp, i32, i32, i32, f32, dmp, dmp, f32, dmp, i64, vp])

@@ -15,6 +15,10 @@ template <typename T>
 int dist_trrk(Grid& g, int uplo, int oA, int oB, T alpha, const DM& A, const DM& B, T beta, const DM& C, i64 blocksize,
               cudaStream_t s);
 template <typename T>
+int dist_make_symmetric(Grid& g, int uplo, const DM& A, cudaStream_t s);
+template <typename T>
+int dist_symm(Grid& g, int side, int uplo, T alpha, const DM& A, const DM& B, T beta, const DM& C, i64 blocksize, cudaStream_t s);
+template <typename T>
 int dist_trapezoid(Grid& g, int op, int uplo, T alpha, const DM* X, const DM& Y, i64 offset, cudaStream_t s);
 }  // namespace hyd
 
@@ -370,6 +374,16 @@ int hyd_scale2d_f32(int64_t m, int64_t n, float alpha, float* A, int64_t lda, hy
             return 1;                                                                                                           \
         const hyd::DM x = to_dm(X);                                                                                             \
         return hyd::dist_trapezoid<T>(*g->g, 1, uplo, alpha, &x, to_dm(Y), offset, (cudaStream_t)s);                            \
+    }                                                                                                                           \
+    int hyd_symm_##SFX(hyd_grid* g, int side, int uplo, T alpha, const hyd_dm* A, const hyd_dm* B, T beta, const hyd_dm* C,        \
+                       int64_t blocksize, hyd_stream_t stream) {                                                                \
+        const hyd::GridShape& sh = g->g->shape;                                                                                 \
+        if (check_dm(sh, A, "hyd_symm(A)") || check_dm(sh, B, "hyd_symm(B)") || check_dm(sh, C, "hyd_symm(C)")) return 1;         \
+        return hyd::dist_symm<T>(*g->g, side, uplo, alpha, to_dm(A), to_dm(B), beta, to_dm(C), blocksize, (cudaStream_t)stream);  \
+    }                                                                                                                           \
+    int hyd_make_symmetric_dist_##SFX(hyd_grid* g, int uplo, const hyd_dm* A, hyd_stream_t s) {                                  \
+        if (check_dm(g->g->shape, A, "hyd_make_symmetric_dist")) return 1;                                                      \
+        return hyd::dist_make_symmetric<T>(*g->g, uplo, to_dm(A), (cudaStream_t)s);                                             \
     }                                                                                                                           \
     int hyd_make_trapezoidal_dist_##SFX(hyd_grid* g, int uplo, const hyd_dm* A, int64_t offset, hyd_stream_t s) {                \
         if (check_dm(g->g->shape, A, "hyd_make_trapezoidal_dist")) return 1;                                                    \

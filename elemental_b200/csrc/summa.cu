@@ -675,6 +675,72 @@ int dist_trapezoid(Grid& g, int op, int uplo, T alpha, const DM* X, const DM& Y,
                               X ? static_cast<const T*>(X->buf) : nullptr, X ? X->ldim : 0, static_cast<T*>(Y.buf), Y.ldim, s);
 }
 
+// MakeSymmetric(uplo, A) on a DistMatrix (include/El/blas_like/level1/MakeSymmetric.hpp:52-68): MakeTrapezoidal(uplo, A);
+// ATrans = A^T; AxpyTrapezoid(the other triangle, 1, ATrans, A, +-1).  ATrans takes A's distribution and alignments, so the
+// transpose is one redistribution and the add is local.
+template <typename T>
+int dist_make_symmetric(Grid& g, int uplo, const DM& A, cudaStream_t s) {
+    if (uplo != 0 && uplo != 1) return set_error("hyd_make_symmetric: uplo must be LOWER (0) or UPPER (1)");
+    if (A.height != A.width) return set_error("hyd_make_symmetric: cannot make non-square matrix symmetric");
+    if (A.height == 0) return 0;
+    const LocalShape L = local_shape(g.shape, A, g.mc, g.mr);
+    if (trapezoid_local<T>(3, uplo, L.lh, L.lw, L.colShift, L.colStride, L.rowShift, L.rowStride, 0, T(0), nullptr, 0,
+                           static_cast<T*>(A.buf), A.ldim, s))
+        return 1;
+    TempPool pool;
+    DM At = A;
+    At.ldim = pad_ld(L.lh, sizeof(T));
+    void* p = nullptr;
+    if (check_cuda(cudaMalloc(&p, (size_t)(At.ldim * std::max<i64>(L.lw, 1)) * sizeof(T)), "MakeSymmetric cudaMalloc")) return 1;
+    pool.bufs.push_back(p);
+    At.buf = p;
+    if (redistribute<T>(g, A, At, true, 3, s)) return 1;
+    if (trapezoid_local<T>(1, 1 - uplo, L.lh, L.lw, L.colShift, L.colStride, L.rowShift, L.rowStride, uplo == 0 ? 1 : -1, T(1),
+                           static_cast<const T*>(At.buf), At.ldim, static_cast<T*>(A.buf), A.ldim, s))
+        return 1;
+    return check_cuda(cudaStreamSynchronize(s), "MakeSymmetric sync");
+}
+// El::Symm(side, uplo, alpha, A, B, beta, C) -- src/blas_like/level3/Symm.cpp:56-80 (C *= beta; symm::{LL,LU,RL,RU}): C := alpha A B +
+// beta C (LEFT) or alpha B A + beta C (RIGHT) with A symmetric and only its `uplo` triangle read.  The reference reads the
+// triangle twice per panel (once as is, once transposed, each under MakeTrapezoidal: Symm/LL.hpp:153-214); here the
+// symmetric completion of A is built once (one transposing redistribution + two trapezoid passes over m^2 entries, against
+// 2 m^2 n flops) and the product is the Gemm engine's -- same flops as the reference, every SUMMA variant and transport
+// available.  A itself is never written.
+template <typename T>
+int dist_symm(Grid& g, int side, int uplo, T alpha, const DM& A0, const DM& B0, T beta, const DM& C0, i64 blocksize, cudaStream_t s) {
+    if (side != 0 && side != 1) return set_error("hyd_symm: side must be LEFT (0) or RIGHT (1)");
+    if (uplo != 0 && uplo != 1) return set_error("hyd_symm: uplo must be LOWER (0) or UPPER (1)");
+    const i64 m = C0.height, n = C0.width, na = side == 0 ? m : n;
+    if (A0.height != na || A0.width != na || B0.height != m || B0.width != n)
+        return set_error("hyd_symm: nonconformal matrices: A %lldx%lld, B %lldx%lld, C %lldx%lld", A0.height, A0.width, B0.height,
+                         B0.width, m, n);
+    TempPool pool;
+    DM Ah;
+    Ah.height = na; Ah.width = na; Ah.colDist = MC; Ah.rowDist = MR;
+    const bool mcmr = A0.colDist == MC && A0.rowDist == MR;
+    Ah.colAlign = mcmr ? A0.colAlign : 0;
+    Ah.rowAlign = mcmr ? A0.rowAlign : 0;
+    const LocalShape L = local_shape(g.shape, Ah, g.mc, g.mr);
+    Ah.ldim = pad_ld(L.lh, sizeof(T));
+    void* p = nullptr;
+    if (check_cuda(cudaMalloc(&p, (size_t)(Ah.ldim * std::max<i64>(L.lw, 1)) * sizeof(T)), "Symm cudaMalloc")) return 1;
+    pool.bufs.push_back(p);
+    Ah.buf = p;
+    if (na > 0) {
+        if (redistribute<T>(g, A0, Ah, false, 3, s)) return 1;
+        if (dist_make_symmetric<T>(g, uplo, Ah, s)) return 1;
+    }
+    const int rc = side == 0 ? dist_gemm<T>(g, 0, 0, 0, alpha, Ah, B0, beta, C0, blocksize, s, nullptr, 0, nullptr, 0, nullptr, 0, nullptr)
+                             : dist_gemm<T>(g, 0, 0, 0, alpha, B0, Ah, beta, C0, blocksize, s, nullptr, 0, nullptr, 0, nullptr, 0, nullptr);
+    if (rc) return rc;
+    return check_cuda(cudaStreamSynchronize(s), "Symm sync");
+}
+template int dist_symm<double>(Grid&, int, int, double, const DM&, const DM&, double, const DM&, i64, cudaStream_t);
+template int dist_symm<float>(Grid&, int, int, float, const DM&, const DM&, float, const DM&, i64, cudaStream_t);
+
+template int dist_make_symmetric<double>(Grid&, int, const DM&, cudaStream_t);
+template int dist_make_symmetric<float>(Grid&, int, const DM&, cudaStream_t);
+
 template int dist_trrk<double>(Grid&, int, int, int, double, const DM&, const DM&, double, const DM&, i64, cudaStream_t);
 template int dist_trrk<float>(Grid&, int, int, int, float, const DM&, const DM&, float, const DM&, i64, cudaStream_t);
 template int dist_trapezoid<double>(Grid&, int, int, double, const DM*, const DM&, i64, cudaStream_t);

@@ -24,6 +24,7 @@ NORMAL, TRANSPOSE, ADJOINT = 0, 1, 2
 GEMM_DEFAULT, GEMM_SUMMA_A, GEMM_SUMMA_B, GEMM_SUMMA_C, GEMM_SUMMA_DOT, GEMM_CANNON = range(6)
 ROW_MAJOR, COLUMN_MAJOR = 0, 1
 LOWER, UPPER = 0, 1   # El::UpperOrLower, include/El/core/types.hpp:489-493
+LEFT, RIGHT = 0, 1    # El::LeftOrRight, types.hpp:417-424
 
 _blocksize_stack = [128]  # environment.cpp:305-306
 
@@ -373,6 +374,25 @@ def MakeTrapezoidal(uplo, A, offset=0, stream=None):
     """A := 0 outside the trapezoid (MakeTrapezoidal.hpp:48-90)."""
     a = A.desc()
     check(getattr(lib, "hyd_make_trapezoidal_dist_" + _sfx(A.dtype))(A.grid.h, uplo, C.byref(a), offset, _stream_ptr(stream)))
+
+
+def Symm(side, uplo, alpha, A, B, beta, Cm, conjugate=False, stream=None, blocksize=None):
+    """C := alpha A B + beta C (LEFT) / alpha B A + beta C (RIGHT), A symmetric, only its `uplo` triangle read (Symm.cpp:56-80)."""
+    a, b, c = A.desc(), B.desc(), Cm.desc()
+    nb = Blocksize() if blocksize is None else int(blocksize)
+    check(getattr(lib, "hyd_symm_" + _sfx(Cm.dtype))(Cm.grid.h, side, uplo, _scalar(Cm.dtype, alpha), C.byref(a), C.byref(b),
+                                                    _scalar(Cm.dtype, beta), C.byref(c), nb, _stream_ptr(stream)))
+
+
+def Hemm(side, uplo, alpha, A, B, beta, Cm, stream=None, blocksize=None):
+    """El::Hemm (Hemm.cpp): Symm with conjugate = true; the same operation for real T."""
+    Symm(side, uplo, alpha, A, B, beta, Cm, True, stream, blocksize)
+
+
+def MakeSymmetric(uplo, A, conjugate=False, stream=None):
+    """A := symmetric completion of its `uplo` triangle (MakeSymmetric.hpp:52-68)."""
+    a = A.desc()
+    check(getattr(lib, "hyd_make_symmetric_dist_" + _sfx(A.dtype))(A.grid.h, uplo, C.byref(a), _stream_ptr(stream)))
 
 
 def lgemm(tA, tB, m, n, k, alpha, A, lda, B, ldb, beta, Cm, ldc, dtype=np.float64, stream=None):

@@ -33,6 +33,7 @@ enum class Device { CPU, GPU };
 enum Orientation { NORMAL = HYD_NORMAL, TRANSPOSE = HYD_TRANSPOSE, ADJOINT = HYD_ADJOINT };
 enum GridOrder { ROW_MAJOR = 0, COLUMN_MAJOR = 1 };
 enum UpperOrLower { LOWER = 0, UPPER = 1 };   // include/El/core/types.hpp:489-493
+enum LeftOrRight { LEFT = 0, RIGHT = 1 };     // types.hpp:417-424
 enum GemmAlgorithm {
     GEMM_DEFAULT = HYD_GEMM_DEFAULT, GEMM_SUMMA_A = HYD_GEMM_SUMMA_A, GEMM_SUMMA_B = HYD_GEMM_SUMMA_B,
     GEMM_SUMMA_C = HYD_GEMM_SUMMA_C, GEMM_SUMMA_DOT = HYD_GEMM_SUMMA_DOT, GEMM_CANNON = HYD_GEMM_CANNON
@@ -174,6 +175,8 @@ template <> struct Sfx<double> {
     static int scale_trap(hyd_grid* g, double al, int ul, const hyd_dm* A, int64_t off, void* s) { return hyd_scale_trapezoid_dist_f64(g, al, ul, A, off, s); }
     static int axpy_trap(hyd_grid* g, int ul, double al, const hyd_dm* X, const hyd_dm* Y, int64_t off, void* s) { return hyd_axpy_trapezoid_dist_f64(g, ul, al, X, Y, off, s); }
     static int make_trap(hyd_grid* g, int ul, const hyd_dm* A, int64_t off, void* s) { return hyd_make_trapezoidal_dist_f64(g, ul, A, off, s); }
+    static int make_symm(hyd_grid* g, int ul, const hyd_dm* A, void* s) { return hyd_make_symmetric_dist_f64(g, ul, A, s); }
+    static int symm(hyd_grid* g, int sd, int ul, double al, const hyd_dm* A, const hyd_dm* B, double be, const hyd_dm* C, int64_t nb, void* s) { return hyd_symm_f64(g, sd, ul, al, A, B, be, C, nb, s); }
     static int interleave(int64_t h, int64_t w, const double* A, int64_t csA, int64_t rsA, double* B, int64_t csB, int64_t rsB, void* s) { return hyd_interleave_f64(h, w, A, csA, rsA, B, csB, rsB, s); }
     static int interleave_update(double al, int64_t h, int64_t w, const double* A, int64_t csA, int64_t rsA, double* B, int64_t csB, int64_t rsB, void* s) { return hyd_interleave_update_f64(al, h, w, A, csA, rsA, B, csB, rsB, s); }
     static int row_pack(int64_t h, int64_t w, int64_t al, int64_t st, const double* A, int64_t ld, double* P, int64_t ps, void* s) { return hyd_row_strided_pack_f64(h, w, al, st, A, ld, P, ps, s); }
@@ -208,6 +211,8 @@ template <> struct Sfx<float> {
     static int scale_trap(hyd_grid* g, float al, int ul, const hyd_dm* A, int64_t off, void* s) { return hyd_scale_trapezoid_dist_f32(g, al, ul, A, off, s); }
     static int axpy_trap(hyd_grid* g, int ul, float al, const hyd_dm* X, const hyd_dm* Y, int64_t off, void* s) { return hyd_axpy_trapezoid_dist_f32(g, ul, al, X, Y, off, s); }
     static int make_trap(hyd_grid* g, int ul, const hyd_dm* A, int64_t off, void* s) { return hyd_make_trapezoidal_dist_f32(g, ul, A, off, s); }
+    static int make_symm(hyd_grid* g, int ul, const hyd_dm* A, void* s) { return hyd_make_symmetric_dist_f32(g, ul, A, s); }
+    static int symm(hyd_grid* g, int sd, int ul, float al, const hyd_dm* A, const hyd_dm* B, float be, const hyd_dm* C, int64_t nb, void* s) { return hyd_symm_f32(g, sd, ul, al, A, B, be, C, nb, s); }
     static int interleave(int64_t h, int64_t w, const float* A, int64_t csA, int64_t rsA, float* B, int64_t csB, int64_t rsB, void* s) { return hyd_interleave_f32(h, w, A, csA, rsA, B, csB, rsB, s); }
     static int interleave_update(float al, int64_t h, int64_t w, const float* A, int64_t csA, int64_t rsA, float* B, int64_t csB, int64_t rsB, void* s) { return hyd_interleave_update_f32(al, h, w, A, csA, rsA, B, csB, rsB, s); }
     static int row_pack(int64_t h, int64_t w, int64_t al, int64_t st, const float* A, int64_t ld, float* P, int64_t ps, void* s) { return hyd_row_strided_pack_f32(h, w, al, st, A, ld, P, ps, s); }
@@ -506,6 +511,24 @@ void AxpyTrapezoid(UpperOrLower uplo, T alpha, const AbstractDistMatrix<T>& X, A
 template <typename T>
 void MakeTrapezoidal(UpperOrLower uplo, AbstractDistMatrix<T>& A, Int offset = 0) {
     detail::check(detail::Sfx<T>::make_trap(A.Grid().handle(), uplo, A.desc(), offset, A.Stream()));
+}
+
+template <typename T>
+void MakeSymmetric(UpperOrLower uplo, AbstractDistMatrix<T>& A, bool /*conjugate*/ = false) {   // MakeSymmetric.hpp:52-68
+    detail::check(detail::Sfx<T>::make_symm(A.Grid().handle(), uplo, A.desc(), A.Stream()));
+}
+template <typename T>
+void MakeHermitian(UpperOrLower uplo, AbstractDistMatrix<T>& A) { MakeSymmetric(uplo, A, true); }
+// C := alpha A B + beta C (LEFT) / alpha B A + beta C (RIGHT), A symmetric, `uplo` triangle read   (Symm.cpp:56-80)
+template <typename T>
+void Symm(LeftOrRight side, UpperOrLower uplo, T alpha, const AbstractDistMatrix<T>& A, const AbstractDistMatrix<T>& B, T beta,
+          AbstractDistMatrix<T>& C, bool /*conjugate*/ = false) {
+    detail::check(detail::Sfx<T>::symm(C.Grid().handle(), side, uplo, alpha, A.desc(), B.desc(), beta, C.desc(), Blocksize(), C.Stream()));
+}
+template <typename T>
+void Hemm(LeftOrRight side, UpperOrLower uplo, T alpha, const AbstractDistMatrix<T>& A, const AbstractDistMatrix<T>& B, T beta,
+          AbstractDistMatrix<T>& C) {   // src/blas_like/level3/Hemm.cpp
+    Symm(side, uplo, alpha, A, B, beta, C, true);
 }
 
 // local column-major GEMM on raw device buffers (gpu_blas::Gemm, include/hydrogen/blas/GPU_BLAS_impl.hpp:631-646)

@@ -327,6 +327,13 @@ int hyd_syrk_f64(hyd_grid* g, int uplo, int orient, double alpha, const hyd_dm* 
                  int64_t blocksize, hyd_stream_t stream);
 int hyd_syrk_f32(hyd_grid* g, int uplo, int orient, float alpha, const hyd_dm* A, float beta, const hyd_dm* C,
                  int64_t blocksize, hyd_stream_t stream);
+/* C := alpha A B + beta C (side 0 = LEFT, A m x m) or alpha B A + beta C (side 1 = RIGHT, A n x n), A symmetric with only its
+ * `uplo` triangle read (El::LeftOrRight, types.hpp:417-424).  ref: El::Symm / El::Hemm (real T) on AbstractDistMatrix,
+ * src/blas_like/level3/Symm.cpp:56-80 -> symm::{LL,LU,RL,RU} (Symm/LL.hpp:153-229 ...).  Synchronises `stream`. */
+int hyd_symm_f64(hyd_grid* g, int side, int uplo, double alpha, const hyd_dm* A, const hyd_dm* B, double beta, const hyd_dm* C,
+                 int64_t blocksize, hyd_stream_t stream);
+int hyd_symm_f32(hyd_grid* g, int side, int uplo, float alpha, const hyd_dm* A, const hyd_dm* B, float beta, const hyd_dm* C,
+                 int64_t blocksize, hyd_stream_t stream);
 /* Host-only introspection of the trapezoidal local update (no device call; used by the CPU tests): for local columns
  * [j0, j0+w) of rank `rank`'s block of C on a gh x gw grid, cuts = {d0, d1, t0, t1}: local rows [d0,d1) are updated by a GEMM
  * straight into C (inside the triangle for every column), rows [t0,t1) through the masked temporary, all others not at all. */
@@ -353,6 +360,11 @@ int hyd_axpy_trapezoid_dist_f32(hyd_grid* g, int uplo, float alpha, const hyd_dm
                                 hyd_stream_t stream);
 int hyd_make_trapezoidal_dist_f64(hyd_grid* g, int uplo, const hyd_dm* A, int64_t offset, hyd_stream_t stream);
 int hyd_make_trapezoidal_dist_f32(hyd_grid* g, int uplo, const hyd_dm* A, int64_t offset, hyd_stream_t stream);
+/* A := the symmetric matrix whose `uplo` triangle is A's.  ref: MakeSymmetric(uplo, A) / MakeHermitian (real T) on
+ * ElementalMatrix, include/El/blas_like/level1/MakeSymmetric.hpp:52-68 (MakeTrapezoidal, Transpose, AxpyTrapezoid of the
+ * strictly other triangle).  Synchronises `stream` (a temporary holds A^T). */
+int hyd_make_symmetric_dist_f64(hyd_grid* g, int uplo, const hyd_dm* A, hyd_stream_t stream);
+int hyd_make_symmetric_dist_f32(hyd_grid* g, int uplo, const hyd_dm* A, hyd_stream_t stream);
 
 /* Same operation with the local blocks of A, B, C in HOST memory (buf = host pointer; pinned memory makes the copies
  * asynchronous): uploads the blocks, runs hyd_gemm_*, downloads C's block and synchronises `stream`.  This is the call a

@@ -129,9 +129,12 @@ void orc_scale(double alpha, orc_dm* A);                                 /* Scal
 void orc_scale_trapezoid(double alpha, int uplo, orc_dm* A, int64_t offset);                      /* ScaleTrapezoid.hpp:47-92 */
 int orc_axpy_trapezoid(int uplo, double alpha, const orc_dm* X, orc_dm* Y, int64_t offset);       /* AxpyTrapezoid.hpp:54-100 */
 void orc_make_trapezoidal(int uplo, orc_dm* A, int64_t offset);                                   /* MakeTrapezoidal.hpp:48-90 */
+int orc_make_symmetric(int uplo, orc_dm* A);                                                      /* MakeSymmetric.hpp:52-68 */
 void orc_set_local_trrk_blocksize(int b);                                                         /* blocksizes.cpp:82-83 */
 int orc_trrk(int uplo, int orientA, int orientB, double alpha, orc_dm* A, orc_dm* B, double beta, orc_dm* C, int64_t blocksize); /* Trrk.cpp:98-115 */
 int orc_syrk(int uplo, int orient, double alpha, orc_dm* A, double beta, orc_dm* C, int64_t blocksize);                           /* Syrk.cpp:72-90 */
+
+int orc_symm(int side, int uplo, double alpha, orc_dm* A, orc_dm* B, double beta, orc_dm* C, int64_t blocksize);   /* Symm.cpp:56-80; side 0 LEFT, 1 RIGHT */
 
 #ifdef __cplusplus
 }

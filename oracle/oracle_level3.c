@@ -205,3 +205,82 @@ int orc_syrk(int uplo, int orient, double alpha, orc_dm* A0, double beta, orc_dm
     if (A != A0) orc_dm_free(A);
     return 0;
 }
+
+/* MakeSymmetric on an ElementalMatrix, MakeSymmetric.hpp:52-68: MakeTrapezoidal(uplo, A); ATrans = A^T (same distribution);
+ * AxpyTrapezoid(UPPER, 1, ATrans, A, 1) for LOWER / AxpyTrapezoid(LOWER, 1, ATrans, A, -1) for UPPER */
+int orc_make_symmetric(int uplo, orc_dm* A) {
+    if (A->m != A->n) return -1;
+    orc_make_trapezoidal(uplo, A, 0);
+    orc_dm* At = orc_dm_create(A->g, A->m, A->n, A->colDist, A->rowDist, A->colAlign, A->rowAlign, A->es);
+    orc_redist_closed(A, At, 1);
+    const int rc = uplo == 0 ? orc_axpy_trapezoid(1, 1.0, At, A, 1) : orc_axpy_trapezoid(0, 1.0, At, A, -1);
+    orc_dm_free(At);
+    return rc;
+}
+
+/* El::Symm on DistMatrices, src/blas_like/level3/Symm.cpp:56-80: C *= beta, then symm::{LL,LU,RL,RU}.  side: 0 LEFT (C += alpha
+ * A B, A m x m), 1 RIGHT (C += alpha B A, A n x n); only the `uplo` triangle of A is read.  Restated: the stationary-C
+ * variants Symm/LL.hpp:153-214 (LLC), LU.hpp (LUC), RL.hpp (RLC), RU.hpp (RUC).  The reference routes tall problems to the
+ * stationary-A variants (LL.hpp:226-229) and a one-column B to Symv (Symm.cpp:62-66); those differ from the C variants only
+ * in the grouping of the sums, and GEMM-class results are compared by tolerance. */
+int orc_symm(int side, int uplo, double alpha, orc_dm* A0, orc_dm* B0, double beta, orc_dm* C0, int64_t bsize) {
+    const orc_grid g = C0->g; const int es = C0->es;
+    const int64_t m = C0->m, n = C0->n, na = side == 0 ? m : n;
+    if (A0->m != na || A0->n != na || B0->m != m || B0->n != n) return -1;
+    orc_scale(beta, C0);
+    orc_dm *A = mcmr_proxy(A0), *B = mcmr_proxy(B0), *C = mcmr_proxy(C0);
+    for (int64_t k = 0; k < na; k += bsize) {
+        const int64_t nb = imin(bsize, na - k);
+        if (side == 0) {
+            orc_dm* B1 = orc_dm_view(B, k, 0, nb, n);
+            orc_dm* Bt = TMP(n, nb, ORC_MR, ORC_STAR, C->rowAlign, 0);            /* B1^T[MR,*] aligned with C */
+            orc_redist_closed(B1, Bt, 1);
+            orc_dm *CT = orc_dm_view(C, 0, 0, k + nb, n), *CB = orc_dm_view(C, k, 0, m - k, n);
+            if (uplo == 0) {      /* LLC: AB1[MC,*] lower trapezoid -> CB;  A1L[*,MC] strictly-left part -> CT */
+                orc_dm *A1L = orc_dm_view(A, k, 0, nb, k + nb), *AB1 = orc_dm_view(A, k, k, m - k, nb);
+                orc_dm *P = TMP(m - k, nb, ORC_MC, ORC_STAR, CB->colAlign, 0), *Q = TMP(nb, k + nb, ORC_STAR, ORC_MC, 0, CT->colAlign);
+                orc_redist_closed(AB1, P, 0); orc_redist_closed(A1L, Q, 0);
+                orc_make_trapezoidal(0, P, 0); orc_make_trapezoidal(0, Q, k - 1);
+                local_gemm_all(0, 1, alpha, P, Bt, 1.0, CB);
+                local_gemm_all(1, 1, alpha, Q, Bt, 1.0, CT);
+                orc_dm_free(P); orc_dm_free(Q); orc_dm_free(A1L); orc_dm_free(AB1);
+            } else {              /* LUC: AT1[MC,*] upper trapezoid (offset -k) -> CT;  A1R[*,MC] strictly-right part -> CB */
+                orc_dm *A1R = orc_dm_view(A, k, k, nb, m - k), *AT1 = orc_dm_view(A, 0, k, k + nb, nb);
+                orc_dm *P = TMP(k + nb, nb, ORC_MC, ORC_STAR, CT->colAlign, 0), *Q = TMP(nb, m - k, ORC_STAR, ORC_MC, 0, CB->colAlign);
+                orc_redist_closed(AT1, P, 0); orc_redist_closed(A1R, Q, 0);
+                orc_make_trapezoidal(1, P, -k); orc_make_trapezoidal(1, Q, 1);
+                local_gemm_all(0, 1, alpha, P, Bt, 1.0, CT);
+                local_gemm_all(1, 1, alpha, Q, Bt, 1.0, CB);
+                orc_dm_free(P); orc_dm_free(Q); orc_dm_free(A1R); orc_dm_free(AT1);
+            }
+            orc_dm_free(CT); orc_dm_free(CB); orc_dm_free(Bt); orc_dm_free(B1);
+        } else {
+            orc_dm* B1 = orc_dm_view(B, 0, k, m, nb);
+            orc_dm* Bm = TMP(m, nb, ORC_MC, ORC_STAR, C->colAlign, 0);            /* B1[MC,*] aligned with C */
+            orc_redist_closed(B1, Bm, 0);
+            orc_dm *CL = orc_dm_view(C, 0, 0, m, k + nb), *CR = orc_dm_view(C, 0, k, m, n - k);
+            if (uplo == 0) {      /* RLC: A1L^T[MR,*] upper (offset -k) -> CL;  AB1^T[*,MR] strictly-upper -> CR */
+                orc_dm *A1L = orc_dm_view(A, k, 0, nb, k + nb), *AB1 = orc_dm_view(A, k, k, n - k, nb);
+                orc_dm *P = TMP(k + nb, nb, ORC_MR, ORC_STAR, CL->rowAlign, 0), *Q = TMP(nb, n - k, ORC_STAR, ORC_MR, 0, CR->rowAlign);
+                orc_redist_closed(A1L, P, 1); orc_redist_closed(AB1, Q, 1);
+                orc_make_trapezoidal(1, P, -k); orc_make_trapezoidal(1, Q, 1);
+                local_gemm_all(0, 1, alpha, Bm, P, 1.0, CL);
+                local_gemm_all(0, 0, alpha, Bm, Q, 1.0, CR);
+                orc_dm_free(P); orc_dm_free(Q); orc_dm_free(A1L); orc_dm_free(AB1);
+            } else {              /* RUC: A1R^T[MR,*] lower -> CR;  AT1^T[*,MR] strictly-lower (offset k-1) -> CL */
+                orc_dm *A1R = orc_dm_view(A, k, k, nb, n - k), *AT1 = orc_dm_view(A, 0, k, k + nb, nb);
+                orc_dm *P = TMP(n - k, nb, ORC_MR, ORC_STAR, CR->rowAlign, 0), *Q = TMP(nb, k + nb, ORC_STAR, ORC_MR, 0, CL->rowAlign);
+                orc_redist_closed(A1R, P, 1); orc_redist_closed(AT1, Q, 1);
+                orc_make_trapezoidal(0, P, 0); orc_make_trapezoidal(0, Q, k - 1);
+                local_gemm_all(0, 1, alpha, Bm, P, 1.0, CR);
+                local_gemm_all(0, 0, alpha, Bm, Q, 1.0, CL);
+                orc_dm_free(P); orc_dm_free(Q); orc_dm_free(A1R); orc_dm_free(AT1);
+            }
+            orc_dm_free(CL); orc_dm_free(CR); orc_dm_free(Bm); orc_dm_free(B1);
+        }
+    }
+    if (C != C0) { orc_redist_closed(C, C0, 0); orc_dm_free(C); }
+    if (A != A0) orc_dm_free(A);
+    if (B != B0) orc_dm_free(B);
+    return 0;
+}

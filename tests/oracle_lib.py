@@ -83,6 +83,8 @@ _sig("orc_gemm", i32, [i32, i32, i32, f64, vp, vp, f64, vp, i64])
 _sig("orc_scale_trapezoid", None, [f64, i32, vp, i64])
 _sig("orc_axpy_trapezoid", i32, [i32, f64, vp, vp, i64])
 _sig("orc_make_trapezoidal", None, [i32, vp, i64])
+_sig("orc_make_symmetric", i32, [i32, vp])
+_sig("orc_symm", i32, [i32, i32, f64, vp, vp, f64, vp, i64])
 _sig("orc_set_local_trrk_blocksize", None, [i32])
 _sig("orc_trrk", i32, [i32, i32, i32, f64, vp, vp, f64, vp, i64])
 _sig("orc_syrk", i32, [i32, i32, f64, vp, f64, vp, i64])

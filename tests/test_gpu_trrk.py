@@ -172,3 +172,78 @@ def test_trapezoid_routines_bit_exact(r, c, dtype):
             s1, s2, s3, pad_ok = out[p][i]
             assert pad_ok
             assert np.array_equal(s1, Y1.block(p)) and np.array_equal(s2, Y2.block(p)) and np.array_equal(s3, Y3.block(p)), (i, p)
+
+
+@pytest.mark.parametrize("r,c", [(1, 1), (2, 2), (2, 4), (3, 2)])
+def test_make_symmetric_bit_exact(r, c):
+    og = O.Grid(r, c, 1)
+    rng = np.random.default_rng(13 * r + c)
+    cases = []
+    for n, d, uplo, dtype in itertools.product((1, 300, 1111), [(MC, MR), (VC, STAR), (STAR, VR), (MR, MC)], (0, 1), (np.float64, np.float32)):
+        ca, ra = U.rand_align(rng, og, d[0]), U.rand_align(rng, og, d[1])
+        A0 = O.DM(og, n, n, d[0], d[1], ca, ra, dtype).fill(7)
+        A1 = O.DM(og, n, n, d[0], d[1], ca, ra, dtype).fill(7)
+        assert O.lib.orc_make_symmetric(uplo, A1.h) == 0
+        cases.append((uplo, A0, A1))
+
+    def body(grid):
+        res = []
+        for uplo, A0, A1 in cases:
+            a = U.to_rank(grid, A0, ldim_extra=1)
+            H.MakeSymmetric(uplo, a)
+            res.append((U.block_of(a), U.padding_untouched(a)))
+        return res
+
+    out = H.run_ranks(r * c, body, height=r)
+    for i, (uplo, A0, A1) in enumerate(cases):
+        for p in range(r * c):
+            got, pad_ok = out[p][i]
+            assert pad_ok and np.array_equal(got, A1.block(p)), (i, p)
+
+
+@pytest.mark.parametrize("r,c", [(1, 1), (2, 2), (2, 4), (3, 2)])
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_symm_hemm_all_sides(r, c, dtype):
+    """Symm / Hemm against the oracle's restated stationary-C loops (Symm/{LL,LU,RL,RU}.hpp): Gemm tolerances; A (whose other
+    triangle holds unrelated values) is left untouched."""
+    og = O.Grid(r, c, 1)
+    rng = np.random.default_rng(19 * r + c)
+    m, n, nb = 157, 123, 32
+    cases = []
+    O.use_blas(True)
+    try:
+        for side, uplo in itertools.product((H.LEFT, H.RIGHT), (H.LOWER, H.UPPER)):
+            na = m if side == H.LEFT else n
+            dA = (MC, MR) if (side + uplo) % 2 == 0 else (VC, STAR)          # half of the cases through the [MC,MR] copy of a proxy
+            mk = lambda h, w, d, seed: O.DM(og, h, w, d[0], d[1], U.rand_align(rng, og, d[0]), U.rand_align(rng, og, d[1]), dtype).fill(seed)
+            A, B, Cm = mk(na, na, dA, 1), mk(m, n, (MC, MR), 2), mk(m, n, (MC, MR), 3)
+            Cin = O.DM(og, m, n, MC, MR, Cm.ca, Cm.ra, dtype).fill(3)
+            assert O.lib.orc_symm(side, uplo, 2.0, A.h, B.h, 3.0, Cm.h, nb) == 0
+            cases.append((side, uplo, A, B, Cin, Cm))
+    finally:
+        O.use_blas(False)
+
+    def body(grid):
+        res = []
+        for i, (side, uplo, A, B, Cin, Cexp) in enumerate(cases):
+            a, b, cm = U.to_rank(grid, A), U.to_rank(grid, B), U.to_rank(grid, Cin, ldim_extra=2)
+            (H.Symm if i % 2 == 0 else H.Hemm)(side, uplo, 2.0, a, b, 3.0, cm, blocksize=nb)
+            res.append((U.block_of(cm), U.padding_untouched(cm), U.block_of(a)))
+        return res
+
+    out = H.run_ranks(r * c, body, height=r)
+    tol_rel = 1e-13 if dtype == np.float64 else 1e-5
+    tol_abs = 1e-10 if dtype == np.float64 else 1e-3
+    for i, (side, uplo, A, B, Cin, Cexp) in enumerate(cases):
+        k = m if side == H.LEFT else n
+        num = den = 0.0
+        for p in range(r * c):
+            got, pad_ok, a_after = out[p][i]
+            exp = Cexp.block(p)
+            assert pad_ok and np.array_equal(a_after, A.block(p))
+            d = got.astype(np.float64) - exp.astype(np.float64)
+            num += float((d * d).sum())
+            den += float((exp.astype(np.float64) ** 2).sum())
+            if d.size:
+                assert np.abs(d).max() <= tol_abs, (side, uplo, p, np.abs(d).max())
+        assert (num / max(den, 1e-300)) ** 0.5 <= tol_rel * max(1.0, k) ** 0.5, (side, uplo)

@@ -370,3 +370,48 @@ def test_trrk_operand_proxies_and_fp32():
     mask = _tri_mask(n, 1)
     assert mism == 0 and np.max(np.abs(got - exp)[mask]) <= 1e-3 and np.array_equal(got[~mask], GC[~mask])
     assert lib.orc_trrk(0, 0, 0, 1.0, A.h, B.h, 1.0, DM(g, n, n + 1, MC, MR, 0, 0, np.float32).h, 8) == -1
+
+
+@pytest.mark.parametrize("r,c", [(1, 1), (2, 2), (2, 4), (3, 2)])
+def test_make_symmetric_matches_the_local_definition(r, c):
+    """The DistMatrix form (MakeTrapezoidal + Transpose + AxpyTrapezoid, MakeSymmetric.hpp:52-68) against the Matrix form
+    (:14-50: copy the triangle across the diagonal), bit for bit."""
+    g = Grid(r, c, 1)
+    rng = np.random.default_rng(300 + r * 7 + c)
+    for n, (cd, rd), uplo in itertools.product((1, 37, 130), [(MC, MR), (VC, STAR), (STAR, VR), (MR, MC), (STAR, STAR)], (0, 1)):
+        A = DM(g, n, n, cd, rd, rand_align(rng, g, cd), rand_align(rng, g, rd)).fill(7)
+        G0, _ = A.to_global()
+        assert lib.orc_make_symmetric(uplo, A.h) == 0
+        G1, mism = A.to_global()
+        T = np.tril(G0) if uplo == 0 else np.triu(G0)
+        exp = T + T.T - np.diag(np.diag(G0))
+        assert mism == 0 and np.array_equal(G1, exp)
+    assert lib.orc_make_symmetric(0, DM(g, 4, 5, MC, MR, 0, 0).h) == -1
+
+
+@pytest.mark.parametrize("r,c", [(1, 1), (2, 2), (2, 4), (3, 2)])
+def test_symm_vs_dense(r, c):
+    """Symm (stationary-C variants, Symm/{LL,LU,RL,RU}.hpp) against the dense product with the symmetric completion of the
+    `uplo` triangle of A: the other triangle of A is garbage and must not influence C.  Bound 1e-10 as for Gemm."""
+    g = Grid(r, c, 1)
+    rng = np.random.default_rng(400 + r * 7 + c)
+    m, n = 57, 43
+    for side, uplo in itertools.product((0, 1), (0, 1)):
+        na = m if side == 0 else n
+        A = DM(g, na, na, MC, MR, rand_align(rng, g, MC), rand_align(rng, g, MR)).fill(1)
+        B = DM(g, m, n, MC, MR, rand_align(rng, g, MC), rand_align(rng, g, MR)).fill(2)
+        Cm = DM(g, m, n, MC, MR, rand_align(rng, g, MC), rand_align(rng, g, MR)).fill(3)
+        GA, _ = A.to_global(); GB, _ = B.to_global(); GC, _ = Cm.to_global()
+        T = np.tril(GA) if uplo == 0 else np.triu(GA)
+        S = np.asfortranarray(T + T.T - np.diag(np.diag(GA)))
+        exp = np.asfortranarray(GC.copy())
+        if side == 0:
+            lib.orc_dense_gemm_ref(0, 0, m, n, m, 2.0, S.ctypes.data, m, GB.ctypes.data, m, 3.0, exp.ctypes.data, m, 8)
+        else:
+            lib.orc_dense_gemm_ref(0, 0, m, n, n, 2.0, GB.ctypes.data, m, S.ctypes.data, n, 3.0, exp.ctypes.data, m, 8)
+        assert lib.orc_symm(side, uplo, 2.0, A.h, B.h, 3.0, Cm.h, 16) == 0
+        got, mism = Cm.to_global()
+        assert mism == 0 and np.max(np.abs(got - exp)) <= 1e-10, (side, uplo, np.max(np.abs(got - exp)))
+        GA2, _ = A.to_global()
+        assert np.array_equal(GA, GA2)
+    assert lib.orc_symm(0, 0, 1.0, DM(g, 5, 5, MC, MR, 0, 0).h, DM(g, 6, 4, MC, MR, 0, 0).h, 0.0, DM(g, 6, 4, MC, MR, 0, 0).h, 8) == -1
