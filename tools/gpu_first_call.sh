@@ -14,5 +14,6 @@ timeout 120 tools/ref_gpu_check gpurun_out/ref_gpu_check.json 2> gpurun_out/ref_
 HYD_DGEMM_WN=2 timeout 120 tools/ref_gpu_check gpurun_out/ref_gpu_check_wn2.json 2> gpurun_out/ref_gpu_check_wn2.err; echo "ref_gpu_check (HYD_DGEMM_WN=2) rc=$?"
 REF_CHECK_SUMMA=1 timeout 240 tools/ref_gpu_check_level1 gpurun_out/ref_gpu_check_level1.json 2> gpurun_out/ref_gpu_check_level1.err; echo "ref_gpu_check_level1 rc=$?" | tee -a gpurun_out/ref_gpu_check_level1.err
 HBC_N=16384 HBC_NB=1024 HBC_TIME=1 timeout 300 python tools/host_blocked_check.py > gpurun_out/host_blocked_check.json 2> gpurun_out/host_blocked_check.err; echo "host_blocked rc=$?"
+timeout 240 python tools/syrk_bench.py > gpurun_out/syrk_bench.json 2> gpurun_out/syrk_bench.err; echo "syrk_bench rc=$?"
 timeout 300 python bench.py --steps 5 --warmup 3 > gpurun_out/bench_1gpu.json 2> gpurun_out/bench_1gpu.err; echo "bench rc=$?"
 tail -3 gpurun_out/pytest_gpu.log gpurun_out/pytest_experimental.log gpurun_out/pytest_trrk.log gpurun_out/ref_gpu_check.err gpurun_out/host_blocked_check.json
