@@ -11,6 +11,11 @@ template <typename T>
 int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A, const DM& B, T beta, const DM& C, i64 blocksize,
               cudaStream_t s, const void* hostA, i64 hostLdA, const void* hostB, i64 hostLdB, void* hostC, i64 hostLdC,
               int* c_downloaded);
+int dist_gemm_half(Grid& g, int bf16, int oA, int oB, int alg, float alpha, const DM& A, const DM& B, float beta, const DM& C,
+                   i64 blocksize, cudaStream_t s);
+struct h16;
+template <typename T>
+int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot, cudaStream_t s);
 template <typename T>
 int dist_trrk(Grid& g, int uplo, int oA, int oB, T alpha, const DM& A, const DM& B, T beta, const DM& C, i64 blocksize,
               cudaStream_t s);
@@ -331,6 +336,25 @@ int hyd_scale2d_f64(int64_t m, int64_t n, double alpha, double* A, int64_t lda, 
 }
 int hyd_scale2d_f32(int64_t m, int64_t n, float alpha, float* A, int64_t lda, hyd_stream_t s) {
     return hyd::scale_local<float>(m, n, alpha, A, lda, (cudaStream_t)s);
+}
+
+// ---- half-precision storage (fp16 / bf16), fp32 accumulation: SUMMA-C and the 2-byte redistributions ----
+int hyd_gemm_f16(hyd_grid* g, int oA, int oB, int alg, float alpha, const hyd_dm* A, const hyd_dm* B, float beta, const hyd_dm* C,
+                 int64_t blocksize, hyd_stream_t stream) {
+    const hyd::GridShape& sh = g->g->shape;
+    if (check_dm(sh, A, "hyd_gemm_f16(A)") || check_dm(sh, B, "hyd_gemm_f16(B)") || check_dm(sh, C, "hyd_gemm_f16(C)")) return 1;
+    return hyd::dist_gemm_half(*g->g, 0, oA, oB, alg, alpha, to_dm(A), to_dm(B), beta, to_dm(C), blocksize, (cudaStream_t)stream);
+}
+int hyd_gemm_bf16(hyd_grid* g, int oA, int oB, int alg, float alpha, const hyd_dm* A, const hyd_dm* B, float beta, const hyd_dm* C,
+                  int64_t blocksize, hyd_stream_t stream) {
+    const hyd::GridShape& sh = g->g->shape;
+    if (check_dm(sh, A, "hyd_gemm_bf16(A)") || check_dm(sh, B, "hyd_gemm_bf16(B)") || check_dm(sh, C, "hyd_gemm_bf16(C)")) return 1;
+    return hyd::dist_gemm_half(*g->g, 1, oA, oB, alg, alpha, to_dm(A), to_dm(B), beta, to_dm(C), blocksize, (cudaStream_t)stream);
+}
+int hyd_redist_b16(hyd_grid* g, const hyd_dm* src, const hyd_dm* dst, int transpose, hyd_stream_t stream) {
+    const hyd::GridShape& sh = g->g->shape;
+    if (check_dm(sh, src, "hyd_redist_b16(src)") || check_dm(sh, dst, "hyd_redist_b16(dst)")) return 1;
+    return hyd::redistribute<hyd::h16>(*g->g, to_dm(src), to_dm(dst), transpose != 0, 3, (cudaStream_t)stream);
 }
 
 // ---- triangular rank-k updates on the SUMMA-C engine, and the trapezoid level-1 kernels around them ----

@@ -49,6 +49,11 @@ struct ReduceBatch {
 template <typename T> struct Vec16;
 template <> struct Vec16<double> { typedef double2 type; static constexpr int N = 2; };
 template <> struct Vec16<float> { typedef float4 type; static constexpr int N = 4; };
+// 2-byte elements moved as opaque bits (fp16 / bf16 storage: SURVEY 8f N3); copies and merges only, no arithmetic
+struct h16 { unsigned short v; };
+template <> struct Vec16<h16> { typedef uint4 type; static constexpr int N = 8; };
+template <typename T> __device__ __forceinline__ T ldg_scalar(const T* p) { return __ldg(p); }
+template <> __device__ __forceinline__ h16 ldg_scalar<h16>(const h16* p) { h16 r; r.v = __ldg(&p->v); return r; }
 
 // Paths, by the four strides: (1) both sides contiguous along a: 16-byte vector copy; (2) destination contiguous
 // along a, source closer to contiguous along b (a transposing pack): (32 V) x 32 tile through shared memory,
@@ -158,7 +163,7 @@ __global__ void __launch_bounds__(256) lattice_copy_kernel(const __grid_constant
                 for (int q = 0; q < 4; ++q)
                     if (b0 + q < nc) {
 #pragma unroll
-                        for (int e = 0; e < V; ++e) v[q][e] = __ldg(s + (av * V + e) * D.s_rs + (b0 + q) * D.s_cs);
+                        for (int e = 0; e < V; ++e) v[q][e] = ldg_scalar(s + (av * V + e) * D.s_rs + (b0 + q) * D.s_cs);
                     }
 #pragma unroll
                 for (int q = 0; q < 4; ++q)
@@ -273,7 +278,7 @@ __global__ void __launch_bounds__(256) lattice_merge_kernel(const __grid_constan
         for (int q = 0; q < CP; ++q)
             if (b0 + q < nc) {
 #pragma unroll
-                for (int e = 0; e < V; ++e) v[q][e] = __ldg(p[e] + (b0 + q) * cs[e]);
+                for (int e = 0; e < V; ++e) v[q][e] = ldg_scalar(p[e] + (b0 + q) * cs[e]);
             }
 #pragma unroll
         for (int q = 0; q < CP; ++q)

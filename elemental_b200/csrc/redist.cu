@@ -589,6 +589,7 @@ int reduce_into(Grid& g, T alpha, const DM& src, const DM& dst, bool transpose, 
 
 template int redistribute<double>(Grid&, const DM&, const DM&, bool, int, cudaStream_t);
 template int redistribute<float>(Grid&, const DM&, const DM&, bool, int, cudaStream_t);
+template int redistribute<h16>(Grid&, const DM&, const DM&, bool, int, cudaStream_t);
 template int redistribute_direct<double>(Grid&, const DM&, DM&, bool, int, i64, cudaStream_t);
 template int redistribute_direct<float>(Grid&, const DM&, DM&, bool, int, i64, cudaStream_t);
 template int reduce_into<double>(Grid&, double, const DM&, const DM&, bool, int, cudaStream_t);

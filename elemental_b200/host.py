@@ -184,7 +184,8 @@ class Grid:
             self.h = None
 
 
-_TORCH = {np.dtype(np.float64): torch.float64, np.dtype(np.float32): torch.float32}
+_TORCH = {np.dtype(np.float64): torch.float64, np.dtype(np.float32): torch.float32, np.dtype(np.float16): torch.float16}
+BF16 = "bfloat16"   # dtype tag for bf16 storage (numpy has no such type: host-side arrays of a bf16 matrix are float32)
 
 
 class DistMatrix:
@@ -194,8 +195,10 @@ class DistMatrix:
                  device="cuda", ldim=None, pinned=False):
         self.grid, self.m, self.n = grid, int(height), int(width)
         self.cd, self.rd, self.ca, self.ra = colDist, rowDist, int(colAlign), int(rowAlign)
-        self.dtype = np.dtype(dtype)
-        self.es = self.dtype.itemsize
+        self.bf16 = isinstance(dtype, str) and dtype == BF16
+        self.dtype = np.dtype(np.float32) if self.bf16 else np.dtype(dtype)
+        self.tdtype = torch.bfloat16 if self.bf16 else _TORCH[self.dtype]
+        self.es = 2 if self.bf16 else self.dtype.itemsize
         meta = hyd_dm(None, 1, self.m, self.n, colDist, rowDist, self.ca, self.ra, 0, 0)
         cs, rs, lh, lw = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64()
         check(lib.hyd_local_shape(grid.h, C.byref(meta), C.byref(cs), C.byref(rs), C.byref(lh), C.byref(lw)))
@@ -205,7 +208,7 @@ class DistMatrix:
         if self.ld < max(self.lh, 1):
             raise HydrogenError("DistMatrix: ldim smaller than the local height")
         # torch (lw, ld) row-major == column-major (ld, lw)
-        kw = dict(dtype=_TORCH[self.dtype], device=device)
+        kw = dict(dtype=self.tdtype, device=device)
         if device == "cpu" and pinned:
             kw["pin_memory"] = True
         self.store = torch.zeros((max(self.lw, 1), self.ld), **kw)
@@ -240,7 +243,8 @@ class DistMatrix:
         return self
 
     def local_numpy(self):
-        return self.store[: self.lw, : self.lh].t().cpu().numpy()
+        blk = self.store[: self.lw, : self.lh].t().cpu()
+        return (blk.float() if self.bf16 else blk).numpy()
 
     def scatter_into_global(self, G):
         if self.lh and self.lw:
@@ -255,16 +259,22 @@ def _scalar(dtype, v):
     return C.c_double(v) if np.dtype(dtype) == np.float64 else C.c_float(v)
 
 
+def _redist_fn(A, B):
+    if A.es != B.es or A.bf16 != B.bf16:
+        raise HydrogenError("Copy / Transpose: element types differ")
+    return lib.hyd_redist_b16 if A.es == 2 else getattr(lib, "hyd_redist_" + _sfx(A.dtype))
+
+
 def Copy(A, B, stream=None):
     """B = A between any two supported distributions (DistMatrix::operator=)."""
     a, b = A.desc(), B.desc()
-    check(getattr(lib, "hyd_redist_" + _sfx(A.dtype))(A.grid.h, C.byref(a), C.byref(b), 0, _stream_ptr(stream)))
+    check(_redist_fn(A, B)(A.grid.h, C.byref(a), C.byref(b), 0, _stream_ptr(stream)))
 
 
 def Transpose(A, B, stream=None):
     """B = A^T (El::Transpose(A, B), Transpose.hpp:318-356)."""
     a, b = A.desc(), B.desc()
-    check(getattr(lib, "hyd_redist_" + _sfx(A.dtype))(A.grid.h, C.byref(a), C.byref(b), 1, _stream_ptr(stream)))
+    check(_redist_fn(A, B)(A.grid.h, C.byref(a), C.byref(b), 1, _stream_ptr(stream)))
 
 
 def AxpyContract(alpha, A, B, stream=None):
@@ -329,6 +339,13 @@ def Gemm(orientA, orientB, alpha, A, B, beta, Cm, alg=GEMM_DEFAULT, stream=None,
     """C := alpha op(A) op(B) + beta C  (El::Gemm on AbstractDistMatrix)."""
     a, b, c = A.desc(), B.desc(), Cm.desc()
     nb = Blocksize() if blocksize is None else int(blocksize)
+    if Cm.es == 2:   # fp16 / bf16 storage, fp32 accumulation and scalars (SURVEY 8f N3)
+        if (A.es, A.bf16, B.es, B.bf16) != (2, Cm.bf16, 2, Cm.bf16):
+            raise HydrogenError("Gemm: A, B and C must share the half-precision storage type")
+        fn = lib.hyd_gemm_bf16 if Cm.bf16 else lib.hyd_gemm_f16
+        check(fn(Cm.grid.h, orientA, orientB, alg, C.c_float(alpha), C.byref(a), C.byref(b), C.c_float(beta), C.byref(c), nb,
+                 _stream_ptr(stream)))
+        return
     host = Cm.store.device.type == "cpu"
     fn = getattr(lib, ("hyd_gemm_host_" if host else "hyd_gemm_") + _sfx(Cm.dtype))
     check(fn(Cm.grid.h, orientA, orientB, alg, _scalar(Cm.dtype, alpha), C.byref(a), C.byref(b), _scalar(Cm.dtype, beta),

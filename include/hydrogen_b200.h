@@ -366,6 +366,18 @@ int hyd_make_trapezoidal_dist_f32(hyd_grid* g, int uplo, const hyd_dm* A, int64_
 int hyd_make_symmetric_dist_f64(hyd_grid* g, int uplo, const hyd_dm* A, hyd_stream_t stream);
 int hyd_make_symmetric_dist_f32(hyd_grid* g, int uplo, const hyd_dm* A, hyd_stream_t stream);
 
+/* ---- fp16 / bf16 storage, fp32 accumulation.  EXPERIMENTAL: not yet run on a GPU. ----
+ * El::Gemm on DistMatrix<gpu_half_type,...,Device::GPU> (Gemm.cpp:278-307 with cublasHgemm as the local product, Gemm.cpp:460-467);
+ * bf16 has no counterpart in the reference.  Stationary-C only (alg = GEMM_DEFAULT or GEMM_SUMMA_C); C is rounded to its
+ * storage type once per k-panel, as in the reference's loop.  Any supported distribution for A, B, C. */
+int hyd_gemm_f16(hyd_grid* g, int orientA, int orientB, int alg, float alpha, const hyd_dm* A, const hyd_dm* B, float beta,
+                 const hyd_dm* C, int64_t blocksize, hyd_stream_t stream);
+int hyd_gemm_bf16(hyd_grid* g, int orientA, int orientB, int alg, float alpha, const hyd_dm* A, const hyd_dm* B, float beta,
+                  const hyd_dm* C, int64_t blocksize, hyd_stream_t stream);
+/* dst := src (or src^T) for 2-byte elements of any kind (fp16, bf16: bits are moved, never interpreted), bit-exact.
+ * ref: DistMatrix<gpu_half_type,U,V>::operator= tables as for hyd_redist_f64. */
+int hyd_redist_b16(hyd_grid* g, const hyd_dm* src, const hyd_dm* dst, int transpose, hyd_stream_t stream);
+
 /* Same operation with the local blocks of A, B, C in HOST memory (buf = host pointer; pinned memory makes the copies
  * asynchronous): uploads the blocks, runs hyd_gemm_*, downloads C's block and synchronises `stream`.  This is the call a
  * CPU-resident caller of El::Gemm makes (the reference's inter-device DistMatrix copies: MC_STAR.cpp:304-390, then Gemm). */

@@ -1,0 +1,133 @@
+"""-m gpu: fp16 / bf16 storage with fp32 accumulation: hyd_redist_b16 (2-byte elements through the one-hop
+redistribution engine, bit-exact) and hyd_gemm_{f16,bf16} (stationary-C SUMMA, tcgen05 kind::f16 local product).
+
+Reference: El::Gemm on DistMatrix<gpu_half_type,...,Device::GPU> (Gemm.cpp:278-307, local product cublasHgemm,
+Gemm.cpp:460-467): C lives in half precision, so every k-panel's update rounds it once.  The checker restates exactly that
+in numpy: per panel C = round(alpha * A1 B1 + beta' * C) with the product in float64.  Tolerance: one unit in the last
+place of the storage type (2^-10 relative for fp16, 2^-7 for bf16) on every entry -- the device accumulates in fp32, so a
+result that sits next to a rounding boundary may land on the neighbouring value -- and at least 98 % of the entries equal
+bit for bit.
+
+Written after this round's GPU budget was spent: gated by HYD_TEST_EXPERIMENTAL=1 until it has run on a B200 once."""
+import itertools
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import oracle_lib as O
+from oracle_lib import MC, MR, VC, VR, STAR
+from elemental_b200 import host as H
+import gpu_util as U
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(os.environ.get("HYD_TEST_EXPERIMENTAL") != "1", reason="not yet run on a GPU; set HYD_TEST_EXPERIMENTAL=1")]
+
+
+@pytest.mark.parametrize("r,c", [(1, 1), (2, 2), (2, 4), (3, 2)])
+def test_redist_b16_every_pair_bit_exact(r, c):
+    """tests/core/DistMatrix.cpp:28-76 for 2-byte elements: B = A and B = A^T for every distribution pair, random alignments;
+    the 16-bit patterns (every value incl. NaN patterns) must arrive unchanged.  The oracle moves them as float32 integers."""
+    og = O.Grid(r, c, 1)
+    rng = np.random.default_rng(23 * r + c)
+    pairs = [(MC, MR), (MR, MC), (MC, STAR), (STAR, MR), (MR, STAR), (STAR, MC), (VC, STAR), (STAR, VC), (VR, STAR), (STAR, VR), (STAR, STAR)]
+    cases = []
+    for (s, d), (m, n), tr in itertools.product(itertools.product(pairs, pairs), [(57, 44), (130, 131)], (0, 1)):
+        if rng.random() > 0.35:
+            continue
+        A = O.DM(og, m, n, s[0], s[1], U.rand_align(rng, og, s[0]), U.rand_align(rng, og, s[1]), np.float32)
+        A.from_global(rng.integers(0, 65536, size=(m, n)).astype(np.float32))
+        B = O.DM(og, n if tr else m, m if tr else n, d[0], d[1], U.rand_align(rng, og, d[0]), U.rand_align(rng, og, d[1]), np.float32)
+        O.lib.orc_redist_closed(A.h, B.h, tr)
+        cases.append((tr, A, B))
+
+    def load(grid, X):
+        p = grid.Rank()
+        d = H.DistMatrix(grid, X.m, X.n, X.cd, X.rd, np.float16, X.ca, X.ra)
+        if d.lh and d.lw:
+            bits = torch.from_numpy(np.ascontiguousarray(X.block(p).T).astype(np.uint16).view(np.int16))
+            d.store.view(torch.int16)[: d.lw, : d.lh].copy_(bits)
+        return d
+
+    def body(grid):
+        res = []
+        for tr, A, B in cases:
+            a, b = load(grid, A), H.DistMatrix(grid, B.m, B.n, B.cd, B.rd, np.float16, B.ca, B.ra)
+            (H.Transpose if tr else H.Copy)(a, b)
+            torch.cuda.synchronize()
+            res.append(b.store.view(torch.int16)[: b.lw, : b.lh].t().cpu().numpy().view(np.uint16))
+        return res
+
+    out = H.run_ranks(r * c, body, height=r)
+    for i, (tr, A, B) in enumerate(cases):
+        for p in range(r * c):
+            assert np.array_equal(out[p][i], B.block(p).astype(np.uint16)), (i, p, tr)
+
+
+def _round(x, kind):
+    t = torch.from_numpy(np.asarray(x, dtype=np.float64))
+    return t.to(torch.float16 if kind == "f16" else torch.bfloat16).to(torch.float64).numpy()
+
+
+@pytest.mark.parametrize("r,c", [(1, 1), (2, 2), (2, 4), (3, 2)])
+@pytest.mark.parametrize("kind", ["f16", "bf16"])
+def test_gemm_half_summa_c(r, c, kind):
+    rng = np.random.default_rng(29 * r + c)
+    dt = np.float16 if kind == "f16" else H.BF16
+    cases = []
+    for (oA, oB), (m, n, k, nb) in itertools.product(itertools.product((0, 1), (0, 1)), [(300, 260, 200, 64), (129, 385, 96, 128)]):
+        GA = _round(rng.uniform(-1, 1, size=(k, m) if oA else (m, k)), kind)
+        GB = _round(rng.uniform(-1, 1, size=(n, k) if oB else (k, n)), kind)
+        GC = _round(rng.uniform(-1, 1, size=(m, n)), kind)
+        opA, opB = (GA.T if oA else GA), (GB.T if oB else GB)
+        exp = GC.copy()
+        for k0 in range(0, k, nb):          # the reference's panel loop: C is rounded to its storage type after every panel
+            exp = _round(2.0 * (opA[:, k0:k0 + nb] @ opB[k0:k0 + nb, :]) + (3.0 if k0 == 0 else 1.0) * exp, kind)
+        al = [int(rng.integers(0, s)) for s in (r, c, r, c, r, c)]
+        cases.append((oA, oB, nb, GA, GB, GC, exp, al))
+    # operands in other distributions go through the [MC,MR] proxies
+    m, n, k, nb = 140, 150, 130, 32
+    GA, GB, GC = (_round(rng.uniform(-1, 1, size=s), kind) for s in ((m, k), (k, n), (m, n)))
+    exp = GC.copy()
+    for k0 in range(0, k, nb):
+        exp = _round(2.0 * (GA[:, k0:k0 + nb] @ GB[k0:k0 + nb, :]) + (3.0 if k0 == 0 else 1.0) * exp, kind)
+
+    def body(grid):
+        res = []
+        for oA, oB, nb_, A_, B_, C_, _, al in cases:
+            a = H.DistMatrix(grid, *A_.shape, MC, MR, dt, al[0], al[1]).set_from_global(A_)
+            b = H.DistMatrix(grid, *B_.shape, MC, MR, dt, al[2], al[3]).set_from_global(B_)
+            cm = H.DistMatrix(grid, *C_.shape, MC, MR, dt, al[4], al[5]).set_from_global(C_)
+            H.Gemm(oA, oB, 2.0, a, b, 3.0, cm, H.GEMM_SUMMA_C, blocksize=nb_)
+            torch.cuda.synchronize()
+            res.append((cm.colShift, cm.rowShift, cm.local_numpy().astype(np.float64)))
+        a = H.DistMatrix(grid, m, k, VC, STAR, dt).set_from_global(GA)
+        b = H.DistMatrix(grid, k, n, STAR, VR, dt).set_from_global(GB)
+        cm = H.DistMatrix(grid, m, n, MR, MC, dt).set_from_global(GC)
+        H.Gemm(0, 0, 2.0, a, b, 3.0, cm, H.GEMM_DEFAULT, blocksize=nb)
+        torch.cuda.synchronize()
+        res.append((cm.colShift, cm.rowShift, cm.ColStride(), cm.RowStride(), cm.local_numpy().astype(np.float64)))
+        with pytest.raises(H.HydrogenError, match="SUMMA_C"):
+            H.Gemm(0, 0, 1.0, a, b, 0.0, cm, H.GEMM_SUMMA_A)
+        return res
+
+    out = H.run_ranks(r * c, body, height=r)
+    ulp = 2.0 ** -10 if kind == "f16" else 2.0 ** -7
+
+    def check(got, want, tag):
+        d = np.abs(got - want)
+        assert (d <= ulp * np.maximum(np.abs(want), 2.0 ** -14)).all(), (tag, d.max())
+        assert (d == 0).mean() >= 0.98, (tag, (d == 0).mean())
+
+    for i, (oA, oB, nb_, A_, B_, C_, want, al) in enumerate(cases):
+        got = np.full_like(want, np.nan)
+        for p in range(r * c):
+            cs, rs, blk = out[p][i]
+            got[cs::r, rs::c] = blk
+        check(got, want, (i, oA, oB))
+    got = np.full_like(exp, np.nan)
+    for p in range(r * c):
+        cs, rs, cst, rst, blk = out[p][-1]
+        got[cs::cst, rs::rst] = blk
+    check(got, exp, "proxies")
