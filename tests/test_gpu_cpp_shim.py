@@ -15,3 +15,15 @@ def test_basicgemm_cpp_driver():
     for args in (["1", "1", "257", "128"], ["4", "2", "300", "96"]):
         out = subprocess.run([exe] + args, capture_output=True, text=True, timeout=120)
         assert out.returncode == 0 and "PASSED" in out.stdout, out.stdout + out.stderr
+
+
+@pytest.mark.skipif(os.environ.get("HYD_TEST_EXPERIMENTAL") != "1", reason="not yet run on a GPU; set HYD_TEST_EXPERIMENTAL=1")
+def test_basicsyrk_cpp_driver():
+    """examples/BasicSyrk.cpp: tests/blas_like/Syrk.cpp restated against the shim (Align, MakeSymmetric, Syrk, both triangles
+    and orientations) plus the shim's alignment rules (adoption in B = A, AlignWith)."""
+    exe = os.path.join(ROOT, "examples", "BasicSyrk")
+    if not os.path.exists(exe):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "examples")])
+    for args in (["1", "1", "257", "128", "64"], ["4", "2", "300", "200", "64"], ["6", "3", "1301", "96", "32"]):
+        out = subprocess.run([exe] + args, capture_output=True, text=True, timeout=180)
+        assert out.returncode == 0 and "PASSED" in out.stdout, out.stdout + out.stderr

@@ -6,8 +6,8 @@
 mkdir -p gpurun_out
 nvidia-smi -L > gpurun_out/smi.txt 2>&1
 timeout 240 python -m pytest tests -m gpu -q --durations=5 > gpurun_out/pytest_gpu.log 2>&1; echo "suite rc=$?" | tee -a gpurun_out/pytest_gpu.log
-HYD_TEST_EXPERIMENTAL=1 timeout 300 python -m pytest tests/test_gpu_local.py tests/test_gpu_gemm.py -m gpu -q \
-    -k "half or column_blocked or interdevice" > gpurun_out/pytest_experimental.log 2>&1; echo "experimental rc=$?" | tee -a gpurun_out/pytest_experimental.log
+HYD_TEST_EXPERIMENTAL=1 timeout 300 python -m pytest tests/test_gpu_local.py tests/test_gpu_gemm.py tests/test_gpu_cpp_shim.py -m gpu -q \
+    -k "half or column_blocked or interdevice or basicsyrk" > gpurun_out/pytest_experimental.log 2>&1; echo "experimental rc=$?" | tee -a gpurun_out/pytest_experimental.log
 HYD_TEST_EXPERIMENTAL=1 timeout 420 python -m pytest tests/test_gpu_trrk.py -m gpu -q --durations=5 > gpurun_out/pytest_trrk.log 2>&1; echo "trrk rc=$?" | tee -a gpurun_out/pytest_trrk.log
 HYD_TEST_EXPERIMENTAL=1 timeout 300 python -m pytest tests/test_gpu_half.py -m gpu -q --durations=5 > gpurun_out/pytest_half.log 2>&1; echo "half rc=$?" | tee -a gpurun_out/pytest_half.log
 timeout 120 tools/ref_gpu_check gpurun_out/ref_gpu_check.json 2> gpurun_out/ref_gpu_check.err; echo "ref_gpu_check rc=$?" | tee -a gpurun_out/ref_gpu_check.err
