@@ -68,6 +68,29 @@ static int run(int P, int height, El::Int n, El::Int k, El::Int nb, double tol, 
                     El::DistMatrix<T, El::MR, El::STAR> X_MR_STAR(grid);
                     X_MR_STAR.AlignWith(C);
                     if (X_MR_STAR.ColAlign() != C.RowAlign() || !X_MR_STAR.ColConstrained()) failed[rank] = 1;
+                    if (variant == 0) {
+                        // Device::CPU matrices (pinned host blocks): cross-device assignment both ways is a copy of the local
+                        // block (MC_STAR.cpp:304-390), and Gemm on three of them goes through hyd_gemm_host_*
+                        El::DistMatrix<T, El::MC, El::MR, El::ELEMENT, El::Device::CPU> Ah(grid), Gh(grid);
+                        El::DistMatrix<T, El::MC, El::MR> A2(grid), Gd(grid);
+                        Ah.SetStream(st); Gh.SetStream(st); A2.SetStream(st); Gd.SetStream(st);
+                        Ah = A;
+                        A2 = Ah;
+                        cudaStreamSynchronize(st);
+                        if (Ah.ColAlign() != A.ColAlign() || Ah.RowAlign() != A.RowAlign() || A2.ColAlign() != A.ColAlign()) failed[rank] = 1;
+                        for (El::Int j = 0; j < Ah.LocalWidth(); ++j)
+                            for (El::Int i = 0; i < Ah.LocalHeight(); ++i)
+                                if (Ah.LockedBuffer()[i + j * Ah.LDim()] != uni<T>(1, Ah.GlobalRow(i) + Ah.GlobalCol(j) * am)) failed[rank] = 1;
+                        El::Gemm(El::NORMAL, El::TRANSPOSE, T(1), A2, A2, Gd);
+                        El::Gemm(El::NORMAL, El::TRANSPOSE, T(1), Ah, Ah, Gh);      // returns synchronised, result in host memory
+                        std::vector<T> gd((size_t)Gd.LocalHeight() * Gd.LocalWidth());
+                        Gd.GetLocalToHost(gd.data(), Gd.LocalHeight());
+                        if (Gh.LocalHeight() != Gd.LocalHeight() || Gh.LocalWidth() != Gd.LocalWidth()) failed[rank] = 1;
+                        for (El::Int j = 0; j < Gd.LocalWidth(); ++j)
+                            for (El::Int i = 0; i < Gd.LocalHeight(); ++i)
+                                worst[rank] = std::fmax(worst[rank], std::fabs((double)gd[i + j * Gd.LocalHeight()] -
+                                                                               (double)Gh.LockedBuffer()[i + j * Gh.LDim()]));
+                    }
                     El::Syrk(uplo, orient, T(2), A, T(3), C);
                     std::vector<T> got((size_t)C.LocalHeight() * C.LocalWidth());
                     C.GetLocalToHost(got.data(), C.LocalHeight());

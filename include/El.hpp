@@ -158,6 +158,7 @@ template <> struct Sfx<double> {
     static int redist(hyd_grid* g, const hyd_dm* a, const hyd_dm* b, int t, void* s) { return hyd_redist_f64(g, a, b, t, s); }
     static int contract(hyd_grid* g, double al, const hyd_dm* a, const hyd_dm* b, int t, void* s) { return hyd_axpy_contract_f64(g, al, a, b, t, s); }
     static int gemm(hyd_grid* g, int oA, int oB, int alg, double al, const hyd_dm* A, const hyd_dm* B, double be, const hyd_dm* C, int64_t nb, void* s) { return hyd_gemm_f64(g, oA, oB, alg, al, A, B, be, C, nb, s); }
+    static int gemm_host(hyd_grid* g, int oA, int oB, int alg, double al, const hyd_dm* A, const hyd_dm* B, double be, const hyd_dm* C, int64_t nb, void* s) { return hyd_gemm_host_f64(g, oA, oB, alg, al, A, B, be, C, nb, s); }
     static int lgemm(int tA, int tB, int64_t m, int64_t n, int64_t k, double al, const double* A, int64_t lda, const double* B, int64_t ldb, double be, double* C, int64_t ldc, void* s) { return hyd_lgemm_f64(tA, tB, m, n, k, al, A, lda, B, ldb, be, C, ldc, s); }
     static int transpose(int64_t m, int64_t n, const double* A, int64_t lda, double* B, int64_t ldb, void* s) { return hyd_transpose_f64(m, n, A, lda, B, ldb, s); }
     static int copy2d(int64_t m, int64_t n, const double* A, int64_t lda, double* B, int64_t ldb, void* s) { return hyd_copy2d_f64(m, n, A, lda, B, ldb, s); }
@@ -194,6 +195,7 @@ template <> struct Sfx<float> {
     static int redist(hyd_grid* g, const hyd_dm* a, const hyd_dm* b, int t, void* s) { return hyd_redist_f32(g, a, b, t, s); }
     static int contract(hyd_grid* g, float al, const hyd_dm* a, const hyd_dm* b, int t, void* s) { return hyd_axpy_contract_f32(g, al, a, b, t, s); }
     static int gemm(hyd_grid* g, int oA, int oB, int alg, float al, const hyd_dm* A, const hyd_dm* B, float be, const hyd_dm* C, int64_t nb, void* s) { return hyd_gemm_f32(g, oA, oB, alg, al, A, B, be, C, nb, s); }
+    static int gemm_host(hyd_grid* g, int oA, int oB, int alg, float al, const hyd_dm* A, const hyd_dm* B, float be, const hyd_dm* C, int64_t nb, void* s) { return hyd_gemm_host_f32(g, oA, oB, alg, al, A, B, be, C, nb, s); }
     static int lgemm(int tA, int tB, int64_t m, int64_t n, int64_t k, float al, const float* A, int64_t lda, const float* B, int64_t ldb, float be, float* C, int64_t ldc, void* s) { return hyd_lgemm_f32(tA, tB, m, n, k, al, A, lda, B, ldb, be, C, ldc, s); }
     static int transpose(int64_t m, int64_t n, const float* A, int64_t lda, float* B, int64_t ldb, void* s) { return hyd_transpose_f32(m, n, A, lda, B, ldb, s); }
     static int copy2d(int64_t m, int64_t n, const float* A, int64_t lda, float* B, int64_t ldb, void* s) { return hyd_copy2d_f32(m, n, A, lda, B, ldb, s); }
@@ -365,30 +367,34 @@ public:
         const Int ld = lh > 0 ? (lh + q - 1) / q * q : q;  // 16-byte columns: TMA-friendly
         const size_t need = (size_t)ld * (size_t)(lw > 0 ? lw : 1) * sizeof(T);
         if (need > cap_) {
-            if (d_.buf) detail::check_cuda(cudaFree(d_.buf), "cudaFree");
-            detail::check_cuda(cudaMalloc(&d_.buf, need), "cudaMalloc");
+            release();
+            // Device::CPU blocks are pinned host memory (the reference pins through its host memory pool, src/core/MemoryPool):
+            // copies to and from the GPU are then asynchronous and hyd_gemm_host_* can stream them under the GEMMs
+            if (dev_ == Device::GPU) detail::check_cuda(cudaMalloc(&d_.buf, need), "cudaMalloc");
+            else detail::check_cuda(cudaMallocHost(&d_.buf, need), "cudaMallocHost");
             cap_ = need;
         }
         d_.ldim = ld;
     }
+    Device GetLocalDevice() const { return dev_; }
     void Attach(Int height, Int width, int colAlign, int rowAlign, T* buffer, Int ldim) {
         Empty(); viewing_ = true; d_.colAlign = colAlign; d_.rowAlign = rowAlign; d_.buf = buffer; d_.ldim = ldim;
         colConstrained_ = rowConstrained_ = true;   // ElementMatrix.cpp Attach: a view's alignments are fixed
         Resize(height, width);
     }
-    void Empty() { if (!viewing_ && d_.buf) cudaFree(d_.buf); d_.buf = nullptr; cap_ = 0; viewing_ = false; }
+    void Empty() { if (!viewing_) release(); d_.buf = nullptr; cap_ = 0; viewing_ = false; }
 
     // host <-> device helpers for tests and drivers (the reference's inter-device Copy, MC_STAR.cpp:304-390)
     void SetLocalFromHost(const T* host, Int ldh) {
-        if (lh_ && lw_) detail::check_cuda(cudaMemcpy2DAsync(d_.buf, d_.ldim * sizeof(T), host, ldh * sizeof(T), lh_ * sizeof(T), lw_, cudaMemcpyHostToDevice, sync_.stream_), "H2D");
+        if (lh_ && lw_) detail::check_cuda(cudaMemcpy2DAsync(d_.buf, d_.ldim * sizeof(T), host, ldh * sizeof(T), lh_ * sizeof(T), lw_, cudaMemcpyDefault, sync_.stream_), "H2D");
     }
     void GetLocalToHost(T* host, Int ldh) const {
-        if (lh_ && lw_) detail::check_cuda(cudaMemcpy2DAsync(host, ldh * sizeof(T), d_.buf, d_.ldim * sizeof(T), lh_ * sizeof(T), lw_, cudaMemcpyDeviceToHost, sync_.stream_), "D2H");
+        if (lh_ && lw_) detail::check_cuda(cudaMemcpy2DAsync(host, ldh * sizeof(T), d_.buf, d_.ldim * sizeof(T), lh_ * sizeof(T), lw_, cudaMemcpyDefault, sync_.stream_), "D2H");
         detail::check_cuda(cudaStreamSynchronize(sync_.stream_), "sync");
     }
 
 protected:
-    AbstractDistMatrix(const El::Grid& g, int cd, int rd) : grid_(&g) {
+    AbstractDistMatrix(const El::Grid& g, int cd, int rd, Device dev = Device::GPU) : grid_(&g), dev_(dev) {
         d_.buf = nullptr; d_.ldim = 1; d_.height = d_.width = 0; d_.colDist = cd; d_.rowDist = rd; d_.colAlign = d_.rowAlign = 0; d_.root = 0; d_.reserved = 0;
     }
     const El::Grid* grid_;
@@ -397,8 +403,22 @@ protected:
     size_t cap_ = 0;
     bool viewing_ = false;
     bool colConstrained_ = false, rowConstrained_ = false;
+    Device dev_ = Device::GPU;
     SyncInfoGPU sync_;
+    void release() {
+        if (!d_.buf) return;
+        if (dev_ == Device::GPU) cudaFree(d_.buf); else cudaFreeHost(d_.buf);
+        d_.buf = nullptr;
+    }
 };
+
+namespace detail {
+// every operation except assignment and Gemm-on-host-blocks needs its operands on the GPU: there is no CPU path to fall back to
+template <typename T>
+inline void require_gpu(const AbstractDistMatrix<T>& A, const char* who) {
+    if (A.GetLocalDevice() != Device::GPU) LogicError(std::string(who) + ": Device::CPU matrix; this library computes on the GPU only (assign it to a Device::GPU matrix)");
+}
+}  // namespace detail
 
 // B = A between any two supported distributions (DistMatrix::operator= tables,
 // src/core/DistMatrix/ElementMatrix/*.cpp -> copy::* primitives)
@@ -411,11 +431,26 @@ void Copy(const AbstractDistMatrix<T>& A, AbstractDistMatrix<T>& B) {
     if (!B.ColConstrained() && detail::copy_adopts(A.ColDist(), A.ColAlign(), B.ColDist(), B.ColStride(), &a)) ca = a;
     if (!B.RowConstrained() && detail::copy_adopts(A.RowDist(), A.RowAlign(), B.RowDist(), B.RowStride(), &a)) ra = a;
     B.AlignAndResize(ca, ra, A.Height(), A.Width(), false, false);
+    if (A.GetLocalDevice() != Device::GPU || B.GetLocalDevice() != Device::GPU) {
+        // Cross-device assignment (the INSTGPU instantiations, src/core/DistMatrix/ElementMatrix/MC_STAR.cpp:304-390 ->
+        // Copy(Matrix<T,CPU>, Matrix<T,GPU>), Copy.hpp:140-207): same distribution and alignments, so it is a 2-D copy of the
+        // local block.  Redistributions run on the GPU only: there is no CPU path in this library.
+        if (A.GetLocalDevice() == Device::CPU && B.GetLocalDevice() == Device::CPU)
+            LogicError("B = A between two Device::CPU matrices: this library has no CPU path; assign to a Device::GPU matrix");
+        if (A.ColDist() != B.ColDist() || A.RowDist() != B.RowDist() || A.ColAlign() != B.ColAlign() || A.RowAlign() != B.RowAlign())
+            LogicError("cross-device B = A needs equal distributions and alignments; redistribute on the GPU side");
+        const int kind = A.GetLocalDevice() == Device::CPU ? 0 : 1;
+        detail::check(hyd_memcopy2d_async(B.desc()->buf, B.LDim(), A.desc()->buf, A.LDim(), A.LocalHeight(), A.LocalWidth(),
+                                          (int)sizeof(T), kind, B.Stream()));
+        return;
+    }
     detail::check(detail::Sfx<T>::redist(B.Grid().handle(), A.desc(), B.desc(), 0, B.Stream()));
 }
 // B = A^T (Transpose.hpp:318-356); conjugate is a no-op for real T
 template <typename T>
 void Transpose(const AbstractDistMatrix<T>& A, AbstractDistMatrix<T>& B, bool /*conjugate*/ = false) {
+    detail::require_gpu(A, "Transpose");
+    detail::require_gpu(B, "Transpose");
     // Transpose.hpp:191-250: B's column dimension relates to A's ROW dimension and vice versa.  With exactly transposed
     // distributions and compatible (or free) alignments the reference calls B.Align(A.RowAlign(), A.ColAlign()), which also
     // constrains B (:202-210); the filter / all-gather branches adopt without constraining.
@@ -433,21 +468,27 @@ void Transpose(const AbstractDistMatrix<T>& A, AbstractDistMatrix<T>& B, bool /*
 }
 template <typename T>
 void AxpyContract(T alpha, const AbstractDistMatrix<T>& A, AbstractDistMatrix<T>& B) {  // AxpyContract.hpp:483-544
+    detail::require_gpu(A, "AxpyContract");
+    detail::require_gpu(B, "AxpyContract");
     detail::check(detail::Sfx<T>::contract(B.Grid().handle(), alpha, A.desc(), B.desc(), 0, B.Stream()));
 }
 template <typename T>
 void TransposeAxpyContract(T alpha, const AbstractDistMatrix<T>& A, AbstractDistMatrix<T>& B, bool = false) {  // TransposeAxpyContract.hpp:14-48
+    detail::require_gpu(A, "TransposeAxpyContract");
+    detail::require_gpu(B, "TransposeAxpyContract");
     detail::check(detail::Sfx<T>::contract(B.Grid().handle(), alpha, A.desc(), B.desc(), 1, B.Stream()));
 }
 
 template <typename T, Dist U = MC, Dist V = MR, DistWrap W = ELEMENT, Device D = Device::GPU>
 class DistMatrix : public AbstractDistMatrix<T> {
-    static_assert(W == ELEMENT && D == Device::GPU, "only ELEMENT-wrapped GPU matrices are on the Gemm path");
+    static_assert(W == ELEMENT, "only ELEMENT-wrapped matrices are on the Gemm path");
 public:
-    explicit DistMatrix(const El::Grid& g) : AbstractDistMatrix<T>(g, U, V) { this->Resize(0, 0); }
-    DistMatrix(Int height, Int width, const El::Grid& g) : AbstractDistMatrix<T>(g, U, V) { this->Resize(height, width); }
-    template <Dist U2, Dist V2>
-    DistMatrix& operator=(const DistMatrix<T, U2, V2, W, D>& A) { Copy<T>(A, *this); return *this; }
+    // Device::CPU matrices hold their block in pinned host memory: they can be filled, assigned to / from a Device::GPU
+    // matrix of the same distribution, and passed to Gemm (all three on the CPU: hyd_gemm_host_*); nothing computes on the CPU
+    explicit DistMatrix(const El::Grid& g) : AbstractDistMatrix<T>(g, U, V, D) { this->Resize(0, 0); }
+    DistMatrix(Int height, Int width, const El::Grid& g) : AbstractDistMatrix<T>(g, U, V, D) { this->Resize(height, width); }
+    template <Dist U2, Dist V2, Device D2>
+    DistMatrix& operator=(const DistMatrix<T, U2, V2, W, D2>& A) { Copy<T>(A, *this); return *this; }
     DistMatrix& operator=(const DistMatrix& A) { Copy<T>(A, *this); return *this; }
 };
 
@@ -455,6 +496,15 @@ public:
 template <typename T>
 void Gemm(Orientation orientA, Orientation orientB, T alpha, const AbstractDistMatrix<T>& A, const AbstractDistMatrix<T>& B,
           T beta, AbstractDistMatrix<T>& C, GemmAlgorithm alg = GEMM_DEFAULT) {
+    const int ncpu = (A.GetLocalDevice() == Device::CPU) + (B.GetLocalDevice() == Device::CPU) + (C.GetLocalDevice() == Device::CPU);
+    if (ncpu == 3) {
+        // all three blocks in (pinned) host memory: the library uploads them panel by panel under the GEMMs and brings C back
+        // (what a CPU-resident caller of the reference does with three cross-device assignments around Gemm); returns synchronised
+        detail::check(detail::Sfx<T>::gemm_host(C.Grid().handle(), orientA, orientB, alg, alpha, A.desc(), B.desc(), beta, C.desc(),
+                                                Blocksize(), C.Stream()));
+        return;
+    }
+    if (ncpu != 0) LogicError("Gemm: A, B and C must live on the same device");
     detail::check(detail::Sfx<T>::gemm(C.Grid().handle(), orientA, orientB, alg, alpha, A.desc(), B.desc(), beta, C.desc(),
                                        Blocksize(), C.Stream()));
 }
@@ -472,6 +522,9 @@ void Gemm(Orientation orientA, Orientation orientB, T alpha, const AbstractDistM
 template <typename T>
 void Trrk(UpperOrLower uplo, Orientation orientA, Orientation orientB, T alpha, const AbstractDistMatrix<T>& A,
           const AbstractDistMatrix<T>& B, T beta, AbstractDistMatrix<T>& C) {
+    detail::require_gpu(A, "Trrk");
+    detail::require_gpu(B, "Trrk");
+    detail::require_gpu(C, "Trrk");
     detail::check(detail::Sfx<T>::trrk(C.Grid().handle(), uplo, orientA, orientB, alpha, A.desc(), B.desc(), beta, C.desc(), Blocksize(),
                                        C.Stream()));
 }
@@ -479,6 +532,8 @@ void Trrk(UpperOrLower uplo, Orientation orientA, Orientation orientB, T alpha, 
 template <typename T>
 void Syrk(UpperOrLower uplo, Orientation orientation, T alpha, const AbstractDistMatrix<T>& A, T beta, AbstractDistMatrix<T>& C,
           bool /*conjugate*/ = false) {
+    detail::require_gpu(A, "Syrk");
+    detail::require_gpu(C, "Syrk");
     detail::check(detail::Sfx<T>::syrk(C.Grid().handle(), uplo, orientation, alpha, A.desc(), beta, C.desc(), Blocksize(), C.Stream()));
 }
 // C resized to n x n and zeroed first (Syrk.cpp:92-103)
@@ -502,19 +557,24 @@ void Herk(UpperOrLower uplo, Orientation orientation, T alpha, const AbstractDis
 // include/El/blas_like/level1/{ScaleTrapezoid,AxpyTrapezoid,MakeTrapezoidal}.hpp on DistMatrices
 template <typename T>
 void ScaleTrapezoid(T alpha, UpperOrLower uplo, AbstractDistMatrix<T>& A, Int offset = 0) {
+    detail::require_gpu(A, "ScaleTrapezoid");
     detail::check(detail::Sfx<T>::scale_trap(A.Grid().handle(), alpha, uplo, A.desc(), offset, A.Stream()));
 }
 template <typename T>
 void AxpyTrapezoid(UpperOrLower uplo, T alpha, const AbstractDistMatrix<T>& X, AbstractDistMatrix<T>& Y, Int offset = 0) {
+    detail::require_gpu(X, "AxpyTrapezoid");
+    detail::require_gpu(Y, "AxpyTrapezoid");
     detail::check(detail::Sfx<T>::axpy_trap(Y.Grid().handle(), uplo, alpha, X.desc(), Y.desc(), offset, Y.Stream()));
 }
 template <typename T>
 void MakeTrapezoidal(UpperOrLower uplo, AbstractDistMatrix<T>& A, Int offset = 0) {
+    detail::require_gpu(A, "MakeTrapezoidal");
     detail::check(detail::Sfx<T>::make_trap(A.Grid().handle(), uplo, A.desc(), offset, A.Stream()));
 }
 
 template <typename T>
 void MakeSymmetric(UpperOrLower uplo, AbstractDistMatrix<T>& A, bool /*conjugate*/ = false) {   // MakeSymmetric.hpp:52-68
+    detail::require_gpu(A, "MakeSymmetric");
     detail::check(detail::Sfx<T>::make_symm(A.Grid().handle(), uplo, A.desc(), A.Stream()));
 }
 template <typename T>
@@ -523,6 +583,9 @@ void MakeHermitian(UpperOrLower uplo, AbstractDistMatrix<T>& A) { MakeSymmetric(
 template <typename T>
 void Symm(LeftOrRight side, UpperOrLower uplo, T alpha, const AbstractDistMatrix<T>& A, const AbstractDistMatrix<T>& B, T beta,
           AbstractDistMatrix<T>& C, bool /*conjugate*/ = false) {
+    detail::require_gpu(A, "Symm");
+    detail::require_gpu(B, "Symm");
+    detail::require_gpu(C, "Symm");
     detail::check(detail::Sfx<T>::symm(C.Grid().handle(), side, uplo, alpha, A.desc(), B.desc(), beta, C.desc(), Blocksize(), C.Stream()));
 }
 template <typename T>
