@@ -17,4 +17,5 @@ REF_CHECK_SUMMA=1 timeout 240 tools/ref_gpu_check_level1 gpurun_out/ref_gpu_chec
 HBC_N=16384 HBC_NB=1024 HBC_TIME=1 timeout 300 python tools/host_blocked_check.py > gpurun_out/host_blocked_check.json 2> gpurun_out/host_blocked_check.err; echo "host_blocked rc=$?"
 timeout 240 python tools/syrk_bench.py > gpurun_out/syrk_bench.json 2> gpurun_out/syrk_bench.err; echo "syrk_bench rc=$?"
 timeout 300 python bench.py --steps 5 --warmup 3 > gpurun_out/bench_1gpu.json 2> gpurun_out/bench_1gpu.err; echo "bench rc=$?"
-tail -3 gpurun_out/pytest_gpu.log gpurun_out/pytest_experimental.log gpurun_out/pytest_trrk.log gpurun_out/pytest_half.log gpurun_out/ref_gpu_check.err gpurun_out/host_blocked_check.json
+
+python tools/summarize_first_call.py gpurun_out > gpurun_out/SUMMARY.json 2>&1; cat gpurun_out/SUMMARY.json
