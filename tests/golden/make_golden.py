@@ -32,7 +32,16 @@ def main():
                       ref.lib.ref_gcd(max(n, 1), stride))
     G.save_golden(G.GOLDEN, cases, outs, idx_in, idx_out)
     write_dist_algebra()
+    write_trapezoid()
     print(f"{len(cases)} cases, {sum(o.size for o in outs)} output elements, {os.path.getsize(G.GOLDEN)} bytes -> {G.GOLDEN}")
+
+
+def write_trapezoid():
+    """tests/golden/trapezoid.json: SHA-256 of what the reference's ScaleTrapezoid / AxpyTrapezoid / MakeTrapezoidal loops
+    (compiled in place by oracle/ref/ref_trapezoid.cpp) produce for every case of tests/trapezoid_cases.py."""
+    import trapezoid_cases as T
+    ref = T.RefBackend()
+    T.save_golden([T.digest(ref.run(c)) for c in T.build_cases()])
 
 
 def write_dist_algebra():

@@ -247,3 +247,39 @@ def test_symm_hemm_all_sides(r, c, dtype):
             if d.size:
                 assert np.abs(d).max() <= tol_abs, (side, uplo, p, np.abs(d).max())
         assert (num / max(den, 1e-300)) ** 0.5 <= tol_rel * max(1.0, k) ** 0.5, (side, uplo)
+
+
+def test_trapezoid_kernels_reproduce_reference_fixtures():
+    """hyd_{scale,axpy}_trapezoid_* / hyd_make_trapezoidal_* (the Matrix<T,GPU> forms) against tests/golden/trapezoid.json: digests of
+    what the REFERENCE's own ScaleTrapezoid / AxpyTrapezoid / MakeTrapezoidal loops produce (compiled in place,
+    oracle/ref/ref_trapezoid.cpp).  The 1x1-grid cases of tests/trapezoid_cases.py; alpha = +-2^k, so bit-exact."""
+    import ctypes as C
+    import torch
+    import trapezoid_cases as T
+    from elemental_b200 import lib, check
+
+    class Cuda:
+        def run(self, case):
+            Y, X = T.inputs(case)
+            m, n = Y.shape
+            ld = max(m, 1) + case["pad"]
+            tdt = torch.float64 if case["dt"] == "f64" else torch.float32
+            y = torch.full((max(n, 1), ld), 7.0, dtype=tdt, device="cuda")      # (n, ld) row-major == column-major ld x n
+            x = torch.zeros((max(n, 1), max(m, 1)), dtype=tdt, device="cuda")
+            if m and n:
+                y[:n, :m].copy_(torch.from_numpy(np.ascontiguousarray(Y.T)))
+                x[:n, :m].copy_(torch.from_numpy(np.ascontiguousarray(X.T)))
+            sc = (C.c_double if case["dt"] == "f64" else C.c_float)(case["alpha"])
+            yp, xp = C.c_void_p(y.data_ptr()), C.c_void_p(x.data_ptr())
+            if case["op"] == "scale":
+                check(getattr(lib, "hyd_scale_trapezoid_" + case["dt"])(sc, case["uplo"], m, n, yp, ld, case["offset"], None))
+            elif case["op"] == "axpy":
+                check(getattr(lib, "hyd_axpy_trapezoid_" + case["dt"])(case["uplo"], sc, m, n, xp, max(m, 1), yp, ld, case["offset"], None))
+            else:
+                check(getattr(lib, "hyd_make_trapezoidal_" + case["dt"])(case["uplo"], m, n, yp, ld, case["offset"], None))
+            torch.cuda.synchronize()
+            assert bool((y[:, m:] == 7.0).all().item())
+            return [y[:n, :m].t().cpu().numpy()]
+
+    n = T.check_against_golden(Cuda(), select=lambda c: c["r"] * c["c"] == 1)
+    assert n == 60

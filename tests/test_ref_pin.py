@@ -113,3 +113,16 @@ def test_oracle_indexing_equals_reference_exhaustively_on_small_arguments():
                     assert ref.ref_max_length(n, stride) == O.lib.orc_max_length(n, stride)
         for a in range(-30, 30):
             assert ref.ref_mod(a, stride) == O.lib.orc_mod(a, stride)
+
+
+# ---- trapezoid level-1 routines (ScaleTrapezoid / AxpyTrapezoid / MakeTrapezoidal): tests/trapezoid_cases.py ----
+def test_oracle_trapezoid_routines_reproduce_reference_fixtures():
+    """oracle/oracle_level3.c against digests of the reference's own loops (tests/golden/trapezoid.json)."""
+    import trapezoid_cases as T
+    assert T.check_against_golden(T.OracleBackend()) == len(T.build_cases())
+
+
+@needs_ref
+def test_trapezoid_fixtures_are_what_the_reference_computes():
+    import trapezoid_cases as T
+    assert T.check_against_golden(T.RefBackend()) == len(T.build_cases())
