@@ -116,6 +116,9 @@ void orc_local_gemm(int tA, int tB, int64_t m, int64_t n, int64_t k, double alph
                     const void* B, int64_t ldb, double beta, void* C, int64_t ldc, int es);
 /* El::Gemm on the simulated grid, following the reference loops (alg: 0 default, 1 A, 2 B, 3 C, 4 Dot) */
 int orc_gemm(int orientA, int orientB, int alg, double alpha, orc_dm* A, orc_dm* B, double beta, orc_dm* C, int64_t blocksize);
+/* DistMatrixReadProxy<T,T,U,V> (Proxy.hpp:174-260): X itself if it already is [U,V] with the constrained alignments, else a new
+ * matrix assigned from X whose unconstrained dimensions adopt alignments as in B = A (orc_copy_adopts); caller frees if != X */
+orc_dm* orc_read_proxy(orc_dm* X, int U, int V, int colCon, int colAlign, int rowCon, int rowAlign);
 /* dense check: C := alpha op(A) op(B) + beta C on global column-major arrays (long-double accumulation) */
 void orc_dense_gemm_ref(int tA, int tB, int64_t m, int64_t n, int64_t k, double alpha, const void* A, int64_t lda,
                         const void* B, int64_t ldb, double beta, void* C, int64_t ldc, int es);

@@ -118,6 +118,21 @@ static void scale_all(double beta, orc_dm* C) {
 }
 static int64_t imin(int64_t a, int64_t b) { return a < b ? a : b; }
 #define TMP(m, n, cd, rd, ca, ra) orc_dm_create(g, m, n, cd, rd, ca, ra, es)
+/* DistMatrixReadProxy<T,T,U,V> of X (Proxy.hpp:174-260): X itself when it is already [U,V] (and has the constrained
+ * alignments), else a fresh [U,V] matrix assigned from X -- whose unconstrained dimensions adopt the alignment the copy::
+ * primitive passes (orc_copy_adopts: e.g. an [MC,MR] operand read as [VC,*] keeps its MC alignment, ColAllToAllDemote.hpp:25).
+ * Found by compiling the reference's own SUMMA_*Dot loops (oracle/ref/ref_summa.cpp): with alignment 0 instead, the k-slices
+ * land on other ranks and the partial sums group differently (last-bit differences). */
+orc_dm* orc_read_proxy(orc_dm* X, int U, int V, int colCon, int ca, int rowCon, int ra) {
+    if (X->colDist == U && X->rowDist == V && (!colCon || X->colAlign == ca) && (!rowCon || X->rowAlign == ra)) return X;
+    const orc_grid g = X->g;
+    int a = 0;
+    if (!colCon) ca = orc_copy_adopts(X->colDist, X->colAlign, U, orc_dist_stride(g, U), &a) ? a : 0;
+    if (!rowCon) ra = orc_copy_adopts(X->rowDist, X->rowAlign, V, orc_dist_stride(g, V), &a) ? a : 0;
+    orc_dm* P = orc_dm_create(g, X->m, X->n, U, V, ca, ra, X->es);
+    orc_redist_closed(X, P, 0);
+    return P;
+}
 
 /* ---- stationary C: NN.hpp:325-367, NT.hpp:178-221, TN.hpp:178-217, TT.hpp:195-240 ---- */
 static void summa_c(int oA, int oB, double alpha, orc_dm* A, orc_dm* B, orc_dm* C, int64_t bsize) {
@@ -215,12 +230,9 @@ static void summa_dot(int oA, int oB, double alpha, orc_dm* A0, orc_dm* B0, orc_
     const orc_grid g = C->g; const int es = C->es;
     const int64_t m = C->m, n = C->n;
     /* read proxies: A -> [*,VC] (N) / [VC,*] (T); B -> [VC,*] (N) / [*,VC] (T) aligned to A */
-    orc_dm* A = oA ? TMP(A0->m, A0->n, ORC_VC, ORC_STAR, (A0->colDist == ORC_VC ? A0->colAlign : 0), 0)
-                   : TMP(A0->m, A0->n, ORC_STAR, ORC_VC, 0, (A0->rowDist == ORC_VC ? A0->rowAlign : 0));
-    orc_redist_closed(A0, A, 0);
-    const int kal = oA ? A->colAlign : A->rowAlign;
-    orc_dm* B = oB ? TMP(B0->m, B0->n, ORC_STAR, ORC_VC, 0, kal) : TMP(B0->m, B0->n, ORC_VC, ORC_STAR, kal, 0);
-    orc_redist_closed(B0, B, 0);
+    orc_dm* A = oA ? orc_read_proxy(A0, ORC_VC, ORC_STAR, 0, 0, 0, 0) : orc_read_proxy(A0, ORC_STAR, ORC_VC, 0, 0, 0, 0);
+    const int kal = oA ? A->colAlign : A->rowAlign;     /* BCtrl.{row,col}Constrain = true, align = A's (TT.hpp:304-307 ...) */
+    orc_dm* B = oB ? orc_read_proxy(B0, ORC_STAR, ORC_VC, 0, 0, 1, kal) : orc_read_proxy(B0, ORC_VC, ORC_STAR, 1, kal, 0, 0);
     for (int64_t kO = 0; kO < m; kO += blockSize) {
         const int64_t nbO = imin(blockSize, m - kO);
         orc_dm* A1 = oA ? orc_dm_view(A, 0, kO, A->m, nbO) : orc_dm_view(A, kO, 0, nbO, A->n);
@@ -235,7 +247,8 @@ static void summa_dot(int oA, int oB, double alpha, orc_dm* A0, orc_dm* B0, orc_
         }
         orc_dm_free(A1);
     }
-    orc_dm_free(A); orc_dm_free(B);
+    if (A != A0) orc_dm_free(A);
+    if (B != B0) orc_dm_free(B);
 }
 
 int orc_gemm(int oA, int oB, int alg, double alpha, orc_dm* A0, orc_dm* B0, double beta, orc_dm* C0, int64_t bsize) {
@@ -252,12 +265,11 @@ int orc_gemm(int oA, int oB, int alg, double alpha, orc_dm* A0, orc_dm* B0, doub
     }
     /* ReadWrite proxy of C to [MC,MR] (Proxy.hpp:694-795) */
     orc_dm* C = C0;
-    if (!(C0->colDist == ORC_MC && C0->rowDist == ORC_MR)) { C = TMP(m, n, ORC_MC, ORC_MR, 0, 0); orc_redist_closed(C0, C, 0); }
+    (void)es; (void)g;
+    C = orc_read_proxy(C0, ORC_MC, ORC_MR, 0, 0, 0, 0);
     if (alg == 4) summa_dot(oA, oB, alpha, A0, B0, C, 2000);
     else {
-        orc_dm *A = A0, *B = B0;
-        if (!(A0->colDist == ORC_MC && A0->rowDist == ORC_MR)) { A = TMP(A0->m, A0->n, ORC_MC, ORC_MR, 0, 0); orc_redist_closed(A0, A, 0); }
-        if (!(B0->colDist == ORC_MC && B0->rowDist == ORC_MR)) { B = TMP(B0->m, B0->n, ORC_MC, ORC_MR, 0, 0); orc_redist_closed(B0, B, 0); }
+        orc_dm *A = orc_read_proxy(A0, ORC_MC, ORC_MR, 0, 0, 0, 0), *B = orc_read_proxy(B0, ORC_MC, ORC_MR, 0, 0, 0, 0);
         if (alg == 1) summa_a(oA, oB, alpha, A, B, C, bsize);
         else if (alg == 2) summa_b(oA, oB, alpha, A, B, C, bsize);
         else if (alg == 3) summa_c(oA, oB, alpha, A, B, C, bsize);

@@ -142,12 +142,7 @@ static void local_trrk(int uplo, int tA, int tB, double alpha, orc_dm* A, orc_dm
 }
 
 #define TMP(m, n, cd, rd, ca, ra) orc_dm_create(g, m, n, cd, rd, ca, ra, es)
-static orc_dm* mcmr_proxy(orc_dm* X) {   /* DistMatrixReadProxy<T,T,MC,MR>, Proxy.hpp:174-260 */
-    if (X->colDist == ORC_MC && X->rowDist == ORC_MR) return X;
-    orc_dm* P = orc_dm_create(X->g, X->m, X->n, ORC_MC, ORC_MR, 0, 0, X->es);
-    orc_redist_closed(X, P, 0);
-    return P;
-}
+static orc_dm* mcmr_proxy(orc_dm* X) { return orc_read_proxy(X, ORC_MC, ORC_MR, 0, 0, 0, 0); }   /* DistMatrixReadProxy<T,T,MC,MR> */
 
 /* El::Trrk on DistMatrices, Trrk.cpp:98-115 */
 int orc_trrk(int uplo, int oA, int oB, double alpha, orc_dm* A0, orc_dm* B0, double beta, orc_dm* C0, int64_t bsize) {
