@@ -33,6 +33,7 @@ def main():
     G.save_golden(G.GOLDEN, cases, outs, idx_in, idx_out)
     write_dist_algebra()
     write_trapezoid()
+    write_summa()
     print(f"{len(cases)} cases, {sum(o.size for o in outs)} output elements, {os.path.getsize(G.GOLDEN)} bytes -> {G.GOLDEN}")
 
 
@@ -42,6 +43,14 @@ def write_trapezoid():
     import trapezoid_cases as T
     ref = T.RefBackend()
     T.save_golden([T.digest(ref.run(c)) for c in T.build_cases()])
+
+
+def write_summa():
+    """tests/golden/summa.json: SHA-256 of C after the reference's own SUMMA_{NT,TN,TT} / Trrk loop code (compiled in place over
+    stand-in matrix classes, oracle/ref/ref_summa.cpp) for every case of tests/summa_cases.py."""
+    import summa_cases as S
+    ref = S.RefBackend()
+    S.save_golden([ref.run(c) for c in S.build_cases()])
 
 
 def write_dist_algebra():

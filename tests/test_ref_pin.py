@@ -126,3 +126,19 @@ def test_oracle_trapezoid_routines_reproduce_reference_fixtures():
 def test_trapezoid_fixtures_are_what_the_reference_computes():
     import trapezoid_cases as T
     assert T.check_against_golden(T.RefBackend()) == len(T.build_cases())
+
+
+# ---- SUMMA / Trrk loops: tests/summa_cases.py ----
+def test_oracle_summa_and_trrk_reproduce_the_reference_loop_code():
+    """oracle_gemm.c (SUMMA NT/TN/TT x A/B/C/Dot/default, operands in four distribution sets, random alignments, four grids) and
+    oracle_level3.c (Trrk, every orientation and triangle, both LocalTrrk branches) against digests of what the reference's own
+    loop headers compute over stand-in matrix classes (tests/golden/summa.json): bit for bit."""
+    import summa_cases as S
+    assert S.check_against_golden(S.OracleBackend()) == len(S.build_cases())
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(os.path.dirname(G.REF_LIB), "libref_summa.so")),
+                    reason="oracle/_ref/libref_summa.so not built (needs /root/reference)")
+def test_summa_fixtures_are_what_the_reference_loops_compute():
+    import summa_cases as S
+    assert S.check_against_golden(S.RefBackend(), select=lambda i, c: i % 3 == 0) > 200
