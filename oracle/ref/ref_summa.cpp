@@ -259,6 +259,8 @@ void LocalAxpyTrapezoid(UpperOrLower uplo, T alpha, const AbstractDistMatrix<T>&
 }
 template <typename T, typename S>
 void ScaleTrapezoid(S alpha, UpperOrLower uplo, AbstractDistMatrix<T>& A, Int offset = 0) { orc_scale_trapezoid((double)alpha, (int)uplo, A.h, offset); }
+template <typename T>
+void MakeTrapezoidal(UpperOrLower uplo, AbstractDistMatrix<T>& A, Int offset = 0) { orc_make_trapezoidal((int)uplo, A.h, offset); }
 template <typename T, Device D = Device::CPU> class Matrix;   /* the Matrix kernels of Trrk/Local.hpp are parsed, never instantiated */
 }  // namespace El
 
@@ -272,6 +274,14 @@ template <typename T, Device D = Device::CPU> class Matrix;   /* the Matrix kern
 #include <blas_like/level3/Trrk/NT.hpp>
 #include <blas_like/level3/Trrk/TN.hpp>
 #include <blas_like/level3/Trrk/TT.hpp>
+#include <blas_like/level3/Syrk/LN.hpp>
+#include <blas_like/level3/Syrk/LT.hpp>
+#include <blas_like/level3/Syrk/UN.hpp>
+#include <blas_like/level3/Syrk/UT.hpp>
+#include <blas_like/level3/Symm/LL.hpp>
+#include <blas_like/level3/Symm/LU.hpp>
+#include <blas_like/level3/Symm/RL.hpp>
+#include <blas_like/level3/Symm/RU.hpp>
 
 namespace {
 /* a caller's matrix (any distribution, decided at run time) as the AbstractDistMatrix the loops take */
@@ -314,7 +324,52 @@ int trrk(int uplo, int oA, int oB, double alpha, orc_dm* A, orc_dm* B, double be
 }
 }  // namespace
 
+namespace {
+template <typename T>
+int syrk(int uplo, int orientation, double alpha, orc_dm* A, double beta, orc_dm* C) {
+    using namespace El;
+    El::Grid g(C->g);
+    Wrapped<T> a(g, A), c(g, C);
+    const UpperOrLower ul = uplo ? UPPER : LOWER;
+    ScaleTrapezoid(T(beta), ul, c);                       /* El::Syrk on AbstractDistMatrix, Syrk.cpp:72-90 */
+    /* the stationary-C loops; syrk::LN ... also route k > 10 n to their Dot variants (LN.hpp:152-159), which need the Matrix-level
+     * Syrk and are not instantiated here */
+    if (ul == LOWER && orientation == 0) syrk::LN_C(T(alpha), a, c, false);
+    else if (ul == LOWER) syrk::LT_C(T(alpha), a, c, false);
+    else if (orientation == 0) syrk::UN_C(T(alpha), a, c, false);
+    else syrk::UT_C(T(alpha), a, c, false);
+    return 0;
+}
+template <typename T>
+int symm(int side, int uplo, double alpha, orc_dm* A, orc_dm* B, double beta, orc_dm* C) {
+    using namespace El;
+    El::Grid g(C->g);
+    Wrapped<T> a(g, A), b(g, B), c(g, C);
+    orc_scale(beta, C);                                   /* El::Symm on AbstractDistMatrix, Symm.cpp:56-80: C *= beta */
+    /* the stationary-C loops; symm::LL ... also route tall problems to their stationary-A variants (LL.hpp:226-229) */
+    if (side == 0 && uplo == 0) symm::LLC(T(alpha), a, b, c, false);
+    else if (side == 0) symm::LUC(T(alpha), a, b, c, false);
+    else if (uplo == 0) symm::RLC(T(alpha), a, b, c, false);
+    else symm::RUC(T(alpha), a, b, c, false);
+    return 0;
+}
+}  // namespace
+
 extern "C" {
+int ref_summa_syrk(int uplo, int orientation, double alpha, orc_dm* A, double beta, orc_dm* C) {
+    try {
+        return C->es == 8 ? syrk<double>(uplo, orientation, alpha, A, beta, C) : syrk<float>(uplo, orientation, alpha, A, beta, C);
+    } catch (const std::exception&) {
+        return -1;
+    }
+}
+int ref_summa_symm(int side, int uplo, double alpha, orc_dm* A, orc_dm* B, double beta, orc_dm* C) {
+    try {
+        return C->es == 8 ? symm<double>(side, uplo, alpha, A, B, beta, C) : symm<float>(side, uplo, alpha, A, B, beta, C);
+    } catch (const std::exception&) {
+        return -1;
+    }
+}
 void ref_summa_set_blocksize(int nb) { El::g_blocksize = nb; }
 void ref_summa_set_local_trrk_blocksize(int nb) { El::g_local_trrk_blocksize = nb; }
 /* El::Gemm(orientA, orientB, alpha, A, B, beta, C, alg) on the simulated grid through the reference's SUMMA_{NT,TN,TT} code.

@@ -1,6 +1,7 @@
 """Case list and backends that pin the oracle's SUMMA / Trrk restatement (oracle/oracle_gemm.c, oracle_level3.c) to the
 REFERENCE's own loop code: src/blas_like/level3/Gemm/{NT,TN,TT}.hpp and Trrk/{Local,NN,NT,TN,TT}.hpp compiled in place over
-stand-in matrix classes on the simulated grid (oracle/ref/ref_summa.cpp -> oracle/_ref/libref_summa.so).
+stand-in matrix classes on the simulated grid (oracle/ref/ref_summa.cpp -> oracle/_ref/libref_summa.so); likewise the stationary-C
+loops of Syrk/{LN,LT,UN,UT}.hpp and Symm/{LL,LU,RL,RU}.hpp.
 
 tests/golden/make_golden.py runs every case through the reference's loops and stores the SHA-256 of the resulting global C
 in tests/golden/summa.json; tests/test_ref_pin.py requires the oracle to reproduce every digest (always), and the reference
@@ -45,6 +46,13 @@ def build_cases():
         # Trrk: all four orientations, both triangles, both branches of LocalTrrk (kernel / recursion)
         for uplo, oA, oB, ds, (n, k, nb, nbl) in itertools.product((0, 1), (0, 1), (0, 1), DISTS[:3], [(150, 45, 16, 8), (97, 70, 32, 64)]):
             cases.append(dict(op="trrk", r=r, c=c, oA=oA, oB=oB, alg=3, ds=ds, m=n, n=n, k=k, nb=nb, nbl=nbl, dt="f64", al=aligns(g, ds), uplo=uplo))
+        # Syrk (stationary-C loops Syrk/{LN,LT,UN,UT}.hpp; oA = orientation) and Symm (Symm/{LL,LU,RL,RU}.hpp *C; oA = side)
+        for uplo, orient, ds, (n, k, nb, nbl) in itertools.product((0, 1), (0, 1), DISTS[:3], [(150, 45, 16, 8), (97, 70, 32, 64)]):
+            cases.append(dict(op="syrk", r=r, c=c, oA=orient, oB=1 - orient, alg=3, ds=ds, m=n, n=n, k=k, nb=nb, nbl=nbl, dt="f64",
+                              al=aligns(g, ds), uplo=uplo))
+        for side, uplo, ds, (m, n, nb) in itertools.product((0, 1), (0, 1), DISTS[:3], [(57, 43, 16), (30, 71, 32)]):
+            cases.append(dict(op="symm", r=r, c=c, oA=side, oB=0, alg=3, ds=ds, m=m, n=n, k=(m if side == 0 else n), nb=nb, nbl=64,
+                              dt="f64", al=aligns(g, ds), uplo=uplo))
     return cases
 
 
@@ -55,6 +63,8 @@ def _operands(case):
     (dA, dB, dC), al = case["ds"], case["al"]
     am, an = (k, m) if oA else (m, k)
     bm, bn = (n, k) if oB else (k, n)
+    if case["op"] == "symm":      # A is the symmetric k x k matrix (k = m for LEFT, n for RIGHT), B is m x n
+        am, an, bm, bn = k, k, m, n
     return (O.DM(g, am, an, dA[0], dA[1], al[0], al[1], dt).fill(1), O.DM(g, bm, bn, dB[0], dB[1], al[2], al[3], dt).fill(2),
             O.DM(g, m, n, dC[0], dC[1], al[4], al[5], dt).fill(3))
 
@@ -73,8 +83,12 @@ class OracleBackend:
         try:
             if case["op"] == "gemm":
                 rc = O.lib.orc_gemm(case["oA"], case["oB"], case["alg"], 2.0, A.h, B.h, 3.0, Cm.h, case["nb"])
-            else:
+            elif case["op"] == "trrk":
                 rc = O.lib.orc_trrk(case["uplo"], case["oA"], case["oB"], 2.0, A.h, B.h, 3.0, Cm.h, case["nb"])
+            elif case["op"] == "syrk":
+                rc = O.lib.orc_syrk(case["uplo"], case["oA"], 2.0, A.h, 3.0, Cm.h, case["nb"])
+            else:
+                rc = O.lib.orc_symm(case["oA"], case["uplo"], 2.0, A.h, B.h, 3.0, Cm.h, case["nb"])
         finally:
             O.lib.orc_set_local_trrk_blocksize(64)
         assert rc == 0, rc
@@ -88,6 +102,10 @@ class RefBackend:
         for fn in (self.lib.ref_summa_gemm, self.lib.ref_summa_trrk):
             fn.restype = C.c_int
             fn.argtypes = [C.c_int] * 3 + [C.c_double, C.c_void_p, C.c_void_p, C.c_double, C.c_void_p]
+        self.lib.ref_summa_syrk.restype = C.c_int
+        self.lib.ref_summa_syrk.argtypes = [C.c_int] * 2 + [C.c_double, C.c_void_p, C.c_double, C.c_void_p]
+        self.lib.ref_summa_symm.restype = C.c_int
+        self.lib.ref_summa_symm.argtypes = [C.c_int] * 2 + [C.c_double, C.c_void_p, C.c_void_p, C.c_double, C.c_void_p]
 
     def run(self, case):
         O.use_blas(False)
@@ -96,8 +114,12 @@ class RefBackend:
         self.lib.ref_summa_set_local_trrk_blocksize(case["nbl"])
         if case["op"] == "gemm":
             rc = self.lib.ref_summa_gemm(case["oA"], case["oB"], case["alg"], 2.0, A.h, B.h, 3.0, Cm.h)
-        else:
+        elif case["op"] == "trrk":
             rc = self.lib.ref_summa_trrk(case["uplo"], case["oA"], case["oB"], 2.0, A.h, B.h, 3.0, Cm.h)
+        elif case["op"] == "syrk":
+            rc = self.lib.ref_summa_syrk(case["uplo"], case["oA"], 2.0, A.h, 3.0, Cm.h)
+        else:
+            rc = self.lib.ref_summa_symm(case["oA"], case["uplo"], 2.0, A.h, B.h, 3.0, Cm.h)
         assert rc == 0, rc
         return digest(Cm)
 
