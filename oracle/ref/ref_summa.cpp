@@ -1,11 +1,13 @@
 /* TEST INFRASTRUCTURE ONLY -- see oracle/oracle.h.
  *
  * The reference's own SUMMA loop code, compiled from where it lies, over stand-in matrix classes:
- *   src/blas_like/level3/Gemm/NT.hpp, TN.hpp, TT.hpp   SUMMA_{NT,TN,TT}{A,B,C,Dot} and the SUMMA_{NT,TN,TT} dispatchers with the
- *                                                      GEMM_DEFAULT heuristic (12 of the 16 variants)
+ *   src/blas_like/level3/Gemm/{NN,NT,TN,TT}.hpp        SUMMA_{NN,NT,TN,TT}{A,B,C,Dot} and the SUMMA_{NN,NT,TN,TT} dispatchers with
+ *                                                      the GEMM_DEFAULT heuristic: all 16 variants
  *   src/blas_like/level3/Trrk/{Local,NN,NT,TN,TT}.hpp  LocalTrrk (recursion + kernels) and the distributed Trrk loops
- * (Gemm/NN.hpp cannot be used: this fork's copy includes NVSHMEM headers, MPI calls and CUDA events unconditionally,
- * NN.hpp:12-13,130,176,372-682.)
+ *   src/blas_like/level3/Syrk/{LN,LT,UN,UT}.hpp, Symm/{LL,LU,RL,RU}.hpp   their stationary-C loops
+ * (This fork's Gemm/NN.hpp also holds a CPU Cannon_NN and timed / NVSHMEM overloads of SUMMA_NNC with MPI calls, CUDA events
+ * and NVSHMEM headers at file scope, NN.hpp:12-13,20-103,370-710: those parts are only parsed -- over empty stand-in headers in
+ * oracle/ref/config and a few declared-but-never-called names -- never instantiated.)
  *
  * Those headers are templates over El::DistMatrix / DistMatrixReadProxy / LocalGemm / Transpose / AxpyContract ...; the full
  * class hierarchy needs MPI and cannot be built here.  Below is a minimal stand-in of exactly the interface the loops use,
@@ -23,6 +25,7 @@
 #include <type_traits>
 #include <utility>
 
+struct CUstream_st;
 namespace El {
 typedef int Int;
 using std::string;
@@ -52,13 +55,30 @@ static Int g_blocksize = 128, g_local_trrk_blocksize = 64;
 inline Int Blocksize() { return g_blocksize; }
 template <typename T> inline Int LocalTrrkBlocksize() { return g_local_trrk_blocksize; }
 
+/* names only the fork-specific parts of Gemm/NN.hpp mention (its Cannon_NN and the timed / NVSHMEM overloads of SUMMA_NNC,
+ * NN.hpp:20-103,370-710): declared so that the file parses, never instantiated or called */
+template <Device D> struct SyncInfo {};
+inline Int Mod(Int a, Int b) { const Int r = a % b; return r < 0 ? r + b : r; }
+namespace mpi {
+struct Comm { int GetMPIComm() const { return 0; } };
+template <typename... Args> inline void SendRecv(Args&&...) {}
+}  // namespace mpi
+
 class Grid {
 public:
     explicit Grid(orc_grid g) : g_(g) {}
     Int Height() const { return g_.r; }
     Int Width() const { return g_.c; }
     Int Size() const { return g_.r * g_.c; }
+    /* every rank is simulated at once: there is no "this rank".  SUMMA_NNA_impl reads these into unused locals (NN.hpp:147-152) */
+    Int Row() const { return 0; }
+    Int Col() const { return 0; }
+    Int Rank() const { return 0; }
+    const mpi::Comm& RowComm() const { return comm_; }
+    const mpi::Comm& ColComm() const { return comm_; }
+    const mpi::Comm& Comm() const { return comm_; }
     orc_grid g_;
+    mpi::Comm comm_;
 };
 
 /* index ranges: A(ALL, IR(k,k+nb)), C(indOuter, indInner), IR(half,END) */
@@ -70,10 +90,19 @@ template <typename I> struct Range {
 inline Range<Int> IR(Int b, Int e) { return Range<Int>(b, e); }
 static const Range<Int> ALL(0, END);
 
+/* SUMMA_NNA_impl of this fork fetches a CUDA stream from B's local matrix when B is on the GPU (NN.hpp:130-132); the branch is
+ * never taken here (GetLocalDevice() is CPU), the types only have to exist */
+template <typename T> class AbstractMatrix {};
+template <typename T, Device D = Device::CPU> class Matrix : public AbstractMatrix<T> {
+public:
+    struct ::CUstream_st* Stream() const { return nullptr; }   /* cudaStream_t */
+};
+
 template <typename T>
 class AbstractDistMatrix {
 public:
     virtual ~AbstractDistMatrix() { release(); }
+    const AbstractMatrix<T>& LockedMatrix() const { static const Matrix<T, Device::GPU> none; return none; }
     Int Height() const { return h ? (Int)h->m : 0; }
     Int Width() const { return h ? (Int)h->n : 0; }
     Int ColAlign() const { return ca; }
@@ -261,11 +290,19 @@ template <typename T, typename S>
 void ScaleTrapezoid(S alpha, UpperOrLower uplo, AbstractDistMatrix<T>& A, Int offset = 0) { orc_scale_trapezoid((double)alpha, (int)uplo, A.h, offset); }
 template <typename T>
 void MakeTrapezoidal(UpperOrLower uplo, AbstractDistMatrix<T>& A, Int offset = 0) { orc_make_trapezoidal((int)uplo, A.h, offset); }
-template <typename T, Device D = Device::CPU> class Matrix;   /* the Matrix kernels of Trrk/Local.hpp are parsed, never instantiated */
 }  // namespace El
+
+typedef int MPI_Comm;
+inline int MPI_Comm_rank(MPI_Comm, int*) { return 0; }
+inline int MPI_Barrier(MPI_Comm) { return 0; }
 
 #define EL_DEBUG_CSE
 #define EL_DEBUG_ONLY(x)
+#define AUTO_PROFILE_REGION(...)   /* the reference's profiling hook (NN.hpp:251,800): nothing to profile here */
+#include <cstdio>
+#include <vector>
+#include <cuda_runtime.h>   /* cudaStream_t / cudaEvent_t in the never-instantiated timed overloads of NN.hpp */
+#include <blas_like/level3/Gemm/NN.hpp>
 #include <blas_like/level3/Gemm/NT.hpp>
 #include <blas_like/level3/Gemm/TN.hpp>
 #include <blas_like/level3/Gemm/TT.hpp>
@@ -302,8 +339,8 @@ int summa(int oA, int oB, int alg, double alpha, orc_dm* A, orc_dm* B, double be
     Wrapped<T> a(g, A), b(g, B), c(g, C);
     const Orientation orA = orient(oA), orB = orient(oB);
     orc_scale(beta, C);                                   /* El::Gemm, Gemm.cpp:287: C *= beta, then the orientation switch :288-306 */
-    if (orA == NORMAL && orB == NORMAL) return -3;        /* Gemm/NN.hpp is not compilable here (see the header comment) */
-    if (orA == NORMAL) gemm::SUMMA_NT(orB, T(alpha), a, b, c, (GemmAlgorithm)alg);
+    if (orA == NORMAL && orB == NORMAL) gemm::SUMMA_NN(T(alpha), a, b, c, (GemmAlgorithm)alg);
+    else if (orA == NORMAL) gemm::SUMMA_NT(orB, T(alpha), a, b, c, (GemmAlgorithm)alg);
     else if (orB == NORMAL) gemm::SUMMA_TN(orA, T(alpha), a, b, c, (GemmAlgorithm)alg);
     else gemm::SUMMA_TT(orA, orB, T(alpha), a, b, c, (GemmAlgorithm)alg);
     return 0;
@@ -373,7 +410,7 @@ int ref_summa_symm(int side, int uplo, double alpha, orc_dm* A, orc_dm* B, doubl
 void ref_summa_set_blocksize(int nb) { El::g_blocksize = nb; }
 void ref_summa_set_local_trrk_blocksize(int nb) { El::g_local_trrk_blocksize = nb; }
 /* El::Gemm(orientA, orientB, alpha, A, B, beta, C, alg) on the simulated grid through the reference's SUMMA_{NT,TN,TT} code.
- * Returns 0, -3 for NN, -1 if the reference raised LogicError. */
+ * Returns 0, or -1 if the reference raised LogicError. */
 int ref_summa_gemm(int oA, int oB, int alg, double alpha, orc_dm* A, orc_dm* B, double beta, orc_dm* C) {
     try {
         return C->es == 8 ? summa<double>(oA, oB, alg, alpha, A, B, beta, C) : summa<float>(oA, oB, alg, alpha, A, B, beta, C);

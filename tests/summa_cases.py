@@ -1,5 +1,5 @@
 """Case list and backends that pin the oracle's SUMMA / Trrk restatement (oracle/oracle_gemm.c, oracle_level3.c) to the
-REFERENCE's own loop code: src/blas_like/level3/Gemm/{NT,TN,TT}.hpp and Trrk/{Local,NN,NT,TN,TT}.hpp compiled in place over
+REFERENCE's own loop code: src/blas_like/level3/Gemm/{NN,NT,TN,TT}.hpp and Trrk/{Local,NN,NT,TN,TT}.hpp compiled in place over
 stand-in matrix classes on the simulated grid (oracle/ref/ref_summa.cpp -> oracle/_ref/libref_summa.so); likewise the stationary-C
 loops of Syrk/{LN,LT,UN,UT}.hpp and Symm/{LL,LU,RL,RU}.hpp.
 
@@ -36,11 +36,11 @@ def build_cases():
 
     for (r, c) in GRIDS:
         g = O.Grid(r, c, 1)
-        # Gemm: NT / TN / TT (the reference's NN.hpp cannot be compiled here) x SUMMA A / B / C / Dot / GEMM_DEFAULT
-        for (oA, oB), alg, ds, (m, n, k, nb), dt in itertools.product([(0, 1), (1, 0), (1, 1)], (1, 2, 3, 4, 0), DISTS,
+        # Gemm: NN / NT / TN / TT x SUMMA A / B / C / Dot / GEMM_DEFAULT
+        for (oA, oB), alg, ds, (m, n, k, nb), dt in itertools.product([(0, 0), (0, 1), (1, 0), (1, 1)], (1, 2, 3, 4, 0), DISTS,
                                                                        [(45, 38, 52, 16), (7, 60, 130, 32)], ("f64",)):
             cases.append(dict(op="gemm", r=r, c=c, oA=oA, oB=oB, alg=alg, ds=ds, m=m, n=n, k=k, nb=nb, nbl=64, dt=dt, al=aligns(g, ds), uplo=0))
-        for (oA, oB), alg in itertools.product([(0, 1), (1, 0), (1, 1)], (3, 4)):
+        for (oA, oB), alg in itertools.product([(0, 0), (0, 1), (1, 0), (1, 1)], (3, 4)):
             cases.append(dict(op="gemm", r=r, c=c, oA=oA, oB=oB, alg=alg, ds=DISTS[0], m=33, n=29, k=41, nb=8, nbl=64, dt="f32",
                               al=aligns(g, DISTS[0]), uplo=0))
         # Trrk: all four orientations, both triangles, both branches of LocalTrrk (kernel / recursion)

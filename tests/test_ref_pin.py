@@ -130,7 +130,7 @@ def test_trapezoid_fixtures_are_what_the_reference_computes():
 
 # ---- SUMMA / Trrk loops: tests/summa_cases.py ----
 def test_oracle_summa_and_trrk_reproduce_the_reference_loop_code():
-    """oracle_gemm.c (SUMMA NT/TN/TT x A/B/C/Dot/default, operands in four distribution sets, random alignments, four grids) and
+    """oracle_gemm.c (SUMMA NN/NT/TN/TT x A/B/C/Dot/default, operands in four distribution sets, random alignments, four grids) and
     oracle_level3.c (Trrk, every orientation and triangle, both LocalTrrk branches) against digests of what the reference's own
     loop headers compute over stand-in matrix classes (tests/golden/summa.json): bit for bit."""
     import summa_cases as S
