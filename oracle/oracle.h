@@ -12,6 +12,13 @@
  *     from where they lie into oracle/_ref/libref_util.so (oracle/Makefile target `ref`, shim oracle/ref/); the
  *     golden vectors tests/golden/copy_util.npz come from it (tests/golden/make_golden.py) and tests/test_ref_pin.py
  *     holds oracle_core.c / oracle_util.c to them bit for bit (plus 3000+ random argument sets where _ref exists).
+ *   - REFERENCE CODE, one level up: the SUMMA loop headers themselves (src/blas_like/level3/Gemm/{NN,NT,TN,TT}.hpp, all 16
+ *     variants and the GEMM_DEFAULT heuristic; Trrk/{Local,NN,NT,TN,TT}.hpp; the stationary-C loops of Syrk/ and Symm/) and the
+ *     trapezoid level-1 headers compile from where they lie over stand-in matrix classes on this library's simulated grid
+ *     (oracle/ref/ref_summa.cpp, ref_trapezoid.cpp -> oracle/_ref/libref_summa.so, libref_util.so); oracle_gemm.c and
+ *     oracle_level3.c reproduce their results bit for bit on the cases of tests/summa_cases.py / trapezoid_cases.py
+ *     (digests in tests/golden/summa.json, trapezoid.json).  That pins the order of operations, temporaries, alignment
+ *     targets and panel ranges of the restatement -- not the rounding of the third-party local product.
  *   - The reference as a whole cannot be built here (needs MPI, LAPACK, Aluminum, NVSHMEM) and ships no
  *     golden vectors, so what only exists above MPI is pinned by the reference's own test PROPERTIES:
  *       tests/core/DistMatrix.cpp:28-76  : B = A for every distribution pair with random alignments,
