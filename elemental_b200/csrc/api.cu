@@ -253,6 +253,11 @@ int hyd_view(const hyd_grid* g, const hyd_dm* a, int64_t i, int64_t j, int64_t h
     return 0;
 }
 
+int hyd_adopted_align(int gh, int gw, int srcDist, int srcAlign, int dstDist) {
+    hyd::GridShape sh;
+    sh.r = gh; sh.c = gw;
+    return hyd::adopted_align(sh, srcDist, srcAlign, dstDist);
+}
 int hyd_trrk_plan(int gh, int gw, int order, int rank, const hyd_dm* C, int uplo, int64_t j0, int64_t w, int es, int64_t* cuts) {
     hyd::GridShape sh;
     sh.r = gh; sh.c = gw; sh.col_major = order ? 1 : 0;

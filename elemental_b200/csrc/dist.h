@@ -48,6 +48,17 @@ inline bool pair_supported(int u, int v) {
     return (u == MC && v == MR) || (u == MR && v == MC);
 }
 
+// Partial(U) (types.hpp:299-307) and the alignment an unconstrained dimension adopts in B = A when it goes src -> dst: the
+// alignment argument of the reference's copy:: primitive for that pair (Copy/Translate.hpp:38-42, RowAllGather.hpp:23,
+// Partial{Col,Row}AllGather.hpp, {Col,Row}AllToAll{Promote,Demote}.hpp, *Filter.hpp); 0 where no primitive passes one.
+inline int partial_dist(int d) { return d == VC ? MC : (d == VR ? MR : d); }
+inline int adopted_align(const GridShape& g, int src, int srcAlign, int dst) {
+    if (dst == STAR || dst == CIRC || src == STAR || src == CIRC) return 0;
+    if (src == dst || partial_dist(dst) == src) return srcAlign;
+    if (partial_dist(src) == dst) return srcAlign % g.stride(dst);
+    return 0;
+}
+
 // Metadata of one distributed matrix (the POD the C ABI passes, include/hydrogen_b200.h hyd_dm).
 struct DM {
     void* buf = nullptr;

@@ -536,8 +536,10 @@ int read_proxy(Grid& g, TempPool& pool, const DM& a, int cd, int rd, bool colCon
     if (ok) { out = a; return 0; }
     out = DM();
     out.height = a.height; out.width = a.width; out.colDist = cd; out.rowDist = rd;
-    out.colAlign = colCon ? ca : (cd == a.colDist ? a.colAlign : 0);
-    out.rowAlign = rowCon ? ra : (rd == a.rowDist ? a.rowAlign : 0);
+    // an unconstrained dimension adopts the source's alignment where the distributions are related, as the reference's proxy
+    // does through B = A (an [MC,MR] operand read as [VC,*] keeps its MC alignment): fewer peers in the redistribution
+    out.colAlign = colCon ? ca : adopted_align(g.shape, a.colDist, a.colAlign, cd);
+    out.rowAlign = rowCon ? ra : adopted_align(g.shape, a.rowDist, a.rowAlign, rd);
     const LocalShape L = local_shape(g.shape, out, g.mc, g.mr);
     out.ldim = pad_ld(L.lh, sizeof(T));
     void* p = nullptr;

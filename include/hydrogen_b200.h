@@ -334,6 +334,10 @@ int hyd_symm_f64(hyd_grid* g, int side, int uplo, double alpha, const hyd_dm* A,
                  int64_t blocksize, hyd_stream_t stream);
 int hyd_symm_f32(hyd_grid* g, int side, int uplo, float alpha, const hyd_dm* A, const hyd_dm* B, float beta, const hyd_dm* C,
                  int64_t blocksize, hyd_stream_t stream);
+/* Host-only: the alignment an unconstrained dimension distributed `dstDist` adopts in B = A from the same dimension of A
+ * (distributed `srcDist`, aligned `srcAlign`) on a gh x gw grid -- the alignment argument of the reference's copy:: primitive for
+ * the pair (the headers under include/El/blas_like/level1/Copy/); 0 where none applies.  The library's read proxies use it. */
+int hyd_adopted_align(int gh, int gw, int srcDist, int srcAlign, int dstDist);
 /* Host-only introspection of the trapezoidal local update (no device call; used by the CPU tests): for local columns
  * [j0, j0+w) of rank `rank`'s block of C on a gh x gw grid, cuts = {d0, d1, t0, t1}: local rows [d0,d1) are updated by a GEMM
  * straight into C (inside the triangle for every column), rows [t0,t1) through the masked temporary, all others not at all. */

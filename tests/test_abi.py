@@ -156,3 +156,16 @@ def test_trrk_row_cuts_cover_exactly_the_triangle(r, c):
     d = hyd_dm(None, 1, 8, 8, O.MC, O.MR, 0, 0, 0, 0)
     assert lib.hyd_trrk_plan(1, 1, 1, 0, C.byref(d), 2, 0, 4, 8, cuts) != 0
     assert lib.hyd_trrk_plan(1, 1, 1, 0, C.byref(d), 0, 6, 4, 8, cuts) != 0
+
+
+def test_proxy_alignment_adoption_matches_the_oracle_rule():
+    """hyd_adopted_align (used by the library's read proxies) against oracle_core.c's orc_copy_adopts, itself exercised by the
+    reference's own SUMMA loops in tests/test_ref_pin.py: every distribution pair, several grids and alignments."""
+    for r, c in [(1, 1), (2, 2), (2, 3), (4, 2), (1, 8)]:
+        og = O.Grid(r, c, 1)
+        for src in range(7):
+            for dst in range(7):
+                for a in range(max(1, O.lib.orc_dist_stride(og, src))):
+                    out = C.c_int(0)
+                    k = O.lib.orc_copy_adopts(src, a, dst, O.lib.orc_dist_stride(og, dst), C.byref(out))
+                    assert lib.hyd_adopted_align(r, c, src, a, dst) == (out.value if k else 0), (r, c, src, dst, a)
