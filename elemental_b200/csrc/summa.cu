@@ -654,6 +654,25 @@ int dist_trrk(Grid& g, int uplo, int oA, int oB, T alpha, const DM& A0, const DM
     TempPool pool;
     DM A, B, C;
     if (read_proxy<T>(g, pool, C0, MC, MR, false, 0, false, 0, C, s)) return 1;
+    if ((double)k > 10.0 * (double)n) {
+        // A long inner dimension against a small C: panel-by-panel SUMMA-C would gather k/nb thin panels for little work each.
+        // The reference's Syrk switches to its Dot variant here (Syrk/LN.hpp:152-159, weightAwayFromDot = 10: operands as
+        // [*,VC] / [VC,*], local products, one reduction); so does this: the Gemm engine's Dot variant computes the full n x n
+        // product into a temporary aligned with C (2x the triangle's flops on a small matrix), and only the triangle is added.
+        const LocalShape Lc = local_shape(g.shape, C, g.mc, g.mr);
+        DM Z = C;
+        Z.ldim = pad_ld(Lc.lh, sizeof(T));
+        void* z = nullptr;
+        if (check_cuda(cudaMalloc(&z, (size_t)(Z.ldim * std::max<i64>(Lc.lw, 1)) * sizeof(T)), "Trrk (Dot) cudaMalloc")) return 1;
+        pool.bufs.push_back(z);
+        Z.buf = z;
+        if (dist_gemm<T>(g, oA, oB, 4, alpha, A0, B0, T(0), Z, blocksize, s, nullptr, 0, nullptr, 0, nullptr, 0, nullptr)) return 1;
+        if (trapezoid_local<T>(1, uplo, Lc.lh, Lc.lw, Lc.colShift, Lc.colStride, Lc.rowShift, Lc.rowStride, 0, T(1),
+                               static_cast<const T*>(Z.buf), Z.ldim, static_cast<T*>(C.buf), C.ldim, s))
+            return 1;
+        if (C.buf != C0.buf && redistribute<T>(g, C, C0, false, 3, s)) return 1;
+        return check_cuda(cudaStreamSynchronize(s), "Trrk (Dot) sync");
+    }
     if (read_proxy<T>(g, pool, A0, MC, MR, false, 0, false, 0, A, s)) return 1;
     if (read_proxy<T>(g, pool, B0, MC, MR, false, 0, false, 0, B, s)) return 1;
     if (summa_c<T>(g, oA, oB, n, n, k, alpha, A, B, T(1), C, blocksize, s, nullptr, uplo)) return 1;

@@ -122,6 +122,10 @@ def test_trrk_proxies_degenerate_and_errors():
         _case(r, c, np.float32, "syrk", 0, 1, 0, 40, 33, 16, rng, dists=((STAR, VC), None, (VR, STAR))),
         _case(r, c, np.float32, "trrk", 0, 0, 1, 1, 5, 4, rng),
         _case(r, c, np.float32, "trrk", 1, 1, 1, 9, 1, 4, rng, alpha=1.0, beta=0.0),
+        # k > 10 n: routed through the Dot variant of the Gemm engine (Syrk/LN.hpp:152-159)
+        _case(r, c, np.float32, "syrk", 0, 0, 0, 24, 400, 64, rng),
+        _case(r, c, np.float32, "syrk", 1, 1, 0, 31, 333, 64, rng, dists=((VC, STAR), None, (MC, MR))),
+        _case(r, c, np.float32, "trrk", 1, 1, 0, 24, 400, 64, rng),
     ]
     _run(r, c, cases, np.float32)
 
