@@ -50,6 +50,29 @@ def parse():
 # ---------------------------------------------------------------------------------------------
 # CPU arm: the oracle's restated SUMMA loops + OpenBLAS (the reference's CPU path: Gemm.cpp:83-101)
 # ---------------------------------------------------------------------------------------------
+_REF_SUMMA = None
+
+
+def ref_summa_lib():
+    """oracle/_ref/libref_summa.so: the reference's own SUMMA loop headers (src/blas_like/level3/Gemm/NN.hpp ...) compiled in
+    place over the oracle's simulated grid (oracle/ref/ref_summa.cpp).  None when it was not built (no /root/reference at build
+    time): the CPU arm then runs the oracle's restatement of the same loops."""
+    global _REF_SUMMA
+    if _REF_SUMMA is None:
+        _REF_SUMMA = False
+        path = os.path.join(ROOT, "oracle", "_ref", "libref_summa.so")
+        if os.path.exists(path):
+            try:
+                import ctypes as C
+                lib = C.CDLL(path)
+                lib.ref_summa_gemm.restype = C.c_int
+                lib.ref_summa_gemm.argtypes = [C.c_int] * 3 + [C.c_double, C.c_void_p, C.c_void_p, C.c_double, C.c_void_p]
+                _REF_SUMMA = lib
+            except OSError:
+                pass
+    return _REF_SUMMA or None
+
+
 def cpu_gemm_tflops(n, grid, nb, steps=1, warmup=0):
     import oracle_lib as O
     blas = O.use_blas(True)
@@ -59,13 +82,30 @@ def cpu_gemm_tflops(n, grid, nb, steps=1, warmup=0):
     A = O.DM(g, n, n, O.MC, O.MR).fill(1)
     B = O.DM(g, n, n, O.MC, O.MR).fill(2)
     Cm = O.DM(g, n, n, O.MC, O.MR).fill(3)
+    ref = ref_summa_lib()
+    if ref is not None:
+        ref.ref_summa_set_blocksize(nb)
+
+    def step():
+        if ref is not None:   # El::Gemm(NORMAL, NORMAL, 1, A, B, 0, C, GEMM_SUMMA_C) through the reference's SUMMA_NNC loop
+            assert ref.ref_summa_gemm(0, 0, 3, 1.0, A.h, B.h, 0.0, Cm.h) == 0
+        else:
+            O.gemm(0, 0, 3, 1.0, A, B, 0.0, Cm, nb)
+
     for _ in range(warmup):
-        O.gemm(0, 0, 3, 1.0, A, B, 0.0, Cm, nb)
+        step()
     t0 = time.perf_counter()
     for _ in range(steps):
-        O.gemm(0, 0, 3, 1.0, A, B, 0.0, Cm, nb)
+        step()
     dt = (time.perf_counter() - t0) / steps
     return 2.0 * n ** 3 / dt / 1e12, dt, blas
+
+
+def cpu_kind():
+    """("reference" | "port", what ran): the reference's loop code when oracle/_ref/libref_summa.so is there, else the restatement."""
+    if ref_summa_lib() is not None:
+        return "reference", "the reference's SUMMA_NNC loop (src/blas_like/level3/Gemm/NN.hpp:324-367, compiled in place over the oracle's simulated grid)"
+    return "port", "oracle SUMMA-C (restated loop)"
 
 
 def cpu_threads(blas):
@@ -88,8 +128,9 @@ def cpu_baseline(grid, nb):
     n = pick_cpu_sample(20.0, grid, 128)
     tf, dt, blas = cpu_gemm_tflops(n, grid, 128)
     cores = cpu_threads(blas)
-    return {"value": round(tf, 4), "unit": "TFLOP/s", "cores": cores, "kind": "port",
-            "sample": f"oracle SUMMA-C NN fp64 m=n=k={n} (workload shape scaled from {M}), blocksize 128 (reference default), "
+    kind, what = cpu_kind()
+    return {"value": round(tf, 4), "unit": "TFLOP/s", "cores": cores, "kind": kind,
+            "sample": f"{what} NN fp64 m=n=k={n} (workload shape scaled from {M}), blocksize 128 (reference default), "
                       f"{grid[0]}x{grid[1]} simulated grid, {'OpenBLAS dgemm all cores' if blas else 'naive triple loop'}, {dt:.2f} s"}
 
 
@@ -102,13 +143,14 @@ def run_reference(args):
     n = pick_cpu_sample(120.0 / total, grid, 128)
     tf, dt, blas = cpu_gemm_tflops(n, grid, 128, steps=args.steps, warmup=args.warmup)
     cores = cpu_threads(blas)
-    sample = (f"oracle SUMMA-C NN fp64 m=n=k={n} per step (bounded sample of the {M}^3 workload), blocksize 128, "
+    kind, what = cpu_kind()
+    sample = (f"{what} NN fp64 m=n=k={n} per step (bounded sample of the {M}^3 workload), blocksize 128, "
               f"{grid[0]}x{grid[1]} simulated grid in one process, {'OpenBLAS dgemm all cores' if blas else 'naive loop'}")
     line = {"impl": "reference", "metric": "distributed Gemm TFLOP/s (fp64)", "value": round(tf, 4), "unit": "TFLOP/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt * 1e3, 3),
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(args.size, grid), "sample_n": n},
-            "cpu_baseline": {"value": round(tf, 4), "unit": "TFLOP/s", "cores": cores, "kind": "port", "sample": sample},
+            "cpu_baseline": {"value": round(tf, 4), "unit": "TFLOP/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": round(tf, 4), "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
