@@ -105,6 +105,7 @@ for _sfx, _ft in (("f64", f64), ("f32", f32)):
     _sig("hyd_axpy_trapezoid_dist_" + _sfx, i32, [vp, i32, _ft, dmp, dmp, i64, vp])
     _sig("hyd_make_trapezoidal_dist_" + _sfx, i32, [vp, i32, dmp, i64, vp])
     _sig("hyd_make_symmetric_dist_" + _sfx, i32, [vp, i32, dmp, vp])
+_sig("hyd_gemm_default_alg", i32, [i64, i64, i64])
 _sig("hyd_adopted_align", i32, [i32, i32, i32, i32, i32])
 _sig("hyd_trrk_plan", i32, [i32, i32, i32, i32, dmp, i32, i64, i64, i32, C.POINTER(i64)])
 _sig("hyd_gemm_f16", i32, [vp, i32, i32, i32, f32, dmp, dmp, f32, dmp, i64, vp])

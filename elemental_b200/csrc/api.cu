@@ -253,6 +253,7 @@ int hyd_view(const hyd_grid* g, const hyd_dm* a, int64_t i, int64_t j, int64_t h
     return 0;
 }
 
+int hyd_gemm_default_alg(int64_t m, int64_t n, int64_t k) { return hyd::gemm_default_alg(m, n, k); }
 int hyd_adopted_align(int gh, int gw, int srcDist, int srcAlign, int dstDist) {
     hyd::GridShape sh;
     sh.r = gh; sh.c = gw;

@@ -59,6 +59,15 @@ inline int adopted_align(const GridShape& g, int src, int srcAlign, int dst) {
     return 0;
 }
 
+// GEMM_DEFAULT: which SUMMA variant El::Gemm picks from the shape (Gemm/NN.hpp:903-925, identical in NT/TN/TT.hpp):
+// 1 = A, 2 = B, 3 = C, 4 = Dot (the GemmAlgorithm enumerators).
+inline int gemm_default_alg(i64 m, i64 n, i64 k) {
+    if (10.0 * (double)m <= (double)k && 10.0 * (double)n <= (double)k) return 4;
+    if (m <= n && 2.0 * (double)m <= (double)k) return 2;
+    if (n <= m && 2.0 * (double)n <= (double)k) return 1;
+    return 3;
+}
+
 // Metadata of one distributed matrix (the POD the C ABI passes, include/hydrogen_b200.h hyd_dm).
 struct DM {
     void* buf = nullptr;

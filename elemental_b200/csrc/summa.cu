@@ -565,12 +565,7 @@ int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A0, const DM&
     if (blocksize <= 0) return set_error("hyd_gemm: blocksize must be positive");
     if (alg == 5) return set_error("hyd_gemm: GEMM_CANNON is CPU-only in the reference (NN.hpp:20-103) and not provided");
     if (alg < 0 || alg > 5) return set_error("hyd_gemm: unsupported Gemm option");
-    if (alg == 0) {  // GEMM_DEFAULT heuristic, NN.hpp:910-925 (identical in NT/TN/TT)
-        if (10.0 * m <= k && 10.0 * n <= k) alg = 4;
-        else if (m <= n && 2.0 * m <= k) alg = 2;
-        else if (n <= m && 2.0 * n <= k) alg = 1;
-        else alg = 3;
-    }
+    if (alg == 0) alg = gemm_default_alg(m, n, k);   // GEMM_DEFAULT heuristic, NN.hpp:910-925 (identical in NT/TN/TT)
     TempPool pool;
     const LocalShape Lc0 = local_shape(g.shape, C0, g.mc, g.mr);
     if (m == 0 || n == 0) return 0;

@@ -334,6 +334,9 @@ int hyd_symm_f64(hyd_grid* g, int side, int uplo, double alpha, const hyd_dm* A,
                  int64_t blocksize, hyd_stream_t stream);
 int hyd_symm_f32(hyd_grid* g, int side, int uplo, float alpha, const hyd_dm* A, const hyd_dm* B, float beta, const hyd_dm* C,
                  int64_t blocksize, hyd_stream_t stream);
+/* Host-only: the SUMMA variant GEMM_DEFAULT selects for an m x n result with inner dimension k (1 A, 2 B, 3 C, 4 Dot).
+ * ref: the switch in gemm::SUMMA_NN / NT / TN / TT, src/blas_like/level3/Gemm/NN.hpp:903-925. */
+int hyd_gemm_default_alg(int64_t m, int64_t n, int64_t k);
 /* Host-only: the alignment an unconstrained dimension distributed `dstDist` adopts in B = A from the same dimension of A
  * (distributed `srcDist`, aligned `srcAlign`) on a gh x gw grid -- the alignment argument of the reference's copy:: primitive for
  * the pair (the headers under include/El/blas_like/level1/Copy/); 0 where none applies.  The library's read proxies use it. */

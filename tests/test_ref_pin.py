@@ -7,6 +7,7 @@ shim oracle/ref/ref_util.cpp; generator tests/golden/make_golden.py).  Here:
   * where oracle/_ref/libref_util.so exists (this container, or shipped prebuilt to the GPU box), the fixtures must still
     be what the reference computes, and oracle == reference on fresh random arguments beyond the fixture list.
 """
+import itertools
 import os
 
 import numpy as np
@@ -142,3 +143,25 @@ def test_oracle_summa_and_trrk_reproduce_the_reference_loop_code():
 def test_summa_fixtures_are_what_the_reference_loops_compute():
     import summa_cases as S
     assert S.check_against_golden(S.RefBackend(), select=lambda i, c: i % 3 == 0) > 200
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(os.path.dirname(G.REF_LIB), "libref_summa.so")),
+                    reason="oracle/_ref/libref_summa.so not built (needs /root/reference)")
+def test_product_default_algorithm_is_the_one_the_reference_dispatcher_picks():
+    """GEMM_DEFAULT: run the reference's own dispatchers (gemm::SUMMA_NN/NT/TN/TT, compiled in place) with alg = GEMM_DEFAULT and with
+    each explicit variant; the variants differ in the last bits, so the digest tells which one the dispatcher took.  The
+    product's host-side choice (hyd_gemm_default_alg, used by hyd_gemm_*) must be that one."""
+    import summa_cases as S
+    from elemental_b200 import lib
+    ref = S.RefBackend()
+    shapes = [(8, 8, 90), (8, 40, 90), (40, 8, 90), (12, 30, 30), (30, 12, 30), (40, 40, 40), (9, 9, 89), (9, 9, 91), (20, 40, 39),
+              (20, 40, 40), (40, 20, 40), (30, 30, 59), (30, 30, 60)]
+    checked = 0
+    for (m, n, k), (oA, oB) in itertools.product(shapes, [(0, 0), (0, 1), (1, 0), (1, 1)]):
+        base = dict(op="gemm", r=2, c=2, oA=oA, oB=oB, ds=S.DISTS[0], m=m, n=n, k=k, nb=8, nbl=64, dt="f64", al=[1, 0, 0, 1, 1, 1], uplo=0)
+        by_alg = {alg: ref.run(dict(base, alg=alg)) for alg in (1, 2, 3, 4)}
+        picked = [alg for alg, dg in by_alg.items() if dg == ref.run(dict(base, alg=0))]
+        assert picked, (m, n, k)
+        assert lib.hyd_gemm_default_alg(m, n, k) in picked, (m, n, k, oA, oB, picked)
+        checked += len(picked) == 1               # the digest singles out one variant: the pick is unambiguous
+    assert checked >= 16      # Dot and C are singled out; A and B produce the same bits (one local product per element, same reduce order)
