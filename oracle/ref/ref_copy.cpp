@@ -22,6 +22,21 @@
 #include <vector>
 
 namespace El {
+/* distribution algebra (types.hpp:292-337): the oracle's tables, themselves pinned to types.hpp by oracle/ref/ref_types.cpp */
+inline Dist Collect(Dist U) { return (Dist)orc_dist_collect(U); }
+inline Dist Partial(Dist U) { return (Dist)orc_dist_partial(U); }
+inline Dist PartialUnionRow(Dist U, Dist V) { return (Dist)orc_dist_partial_union_row(U, V); }
+inline Dist PartialUnionCol(Dist U, Dist V) { return (Dist)orc_dist_partial_union_col(U, V); }
+
+template <Dist U> constexpr Dist Collect() { return U == CIRC ? CIRC : STAR; }
+template <Dist U> constexpr Dist Partial() { return U == VC ? MC : (U == VR ? MR : U); }
+template <Dist U, Dist V> constexpr Dist PartialUnionRow() { return U == VC ? MR : (U == VR ? MC : V); }
+template <Dist U, Dist V> constexpr Dist PartialUnionCol() { return PartialUnionRow<V, U>(); }
+template <Dist U, Dist V> constexpr Dist ProductDist() {   /* types.hpp:343-356 */
+    return U == STAR ? V : (V == STAR ? U : ((U == MC && V == MR) ? VC : ((U == MR && V == MC) ? VR : CIRC)));
+}
+template <Dist U, Dist V> constexpr Dist ProductDistPartner() { return (U == CIRC && V == CIRC) ? CIRC : STAR; }
+template <typename T, Device D> struct IsDeviceValidType : std::true_type {};
 
 /* ---- SPMD runtime ---- */
 struct Barrier {
@@ -36,12 +51,16 @@ struct Barrier {
     std::condition_variable cv;
     int n, count = 0, gen = 0;
 };
-struct CommShared {              /* one communicator instance: its members share a barrier and a pointer board */
-    explicit CommShared(int n) : bar(n), board(n, nullptr), size(n) {}
+struct CommShared {              /* one communicator instance: its members share a barrier, a pointer board and mailboxes */
+    explicit CommShared(int n) : bar(n), board(n, nullptr), box((size_t)n * n, nullptr), size(n) {}
     Barrier bar;
     std::vector<const void*> board;
+    std::vector<const void*> box;    /* box[from*size + to]: a message in flight (point-to-point) */
+    std::mutex m;
+    std::condition_variable cv;
     int size;
 };
+enum class Collective { SENDRECV };
 
 namespace mpi {
 const int MIN_COLL_MSG = 1;                                  /* include/El/core/imports/mpi.hpp:181-185 */
@@ -68,15 +87,26 @@ void AllToAll(const T* sbuf, int sc, T* rbuf, int rc, const Comm& c, SyncInfo<D>
         std::memcpy(rbuf + (size_t)q * rc, static_cast<const T*>(c.sh->board[q]) + (size_t)c.rank * sc, (size_t)sc * sizeof(T));
     c.sh->bar.wait();
 }
+/* point-to-point (not every member of the communicator takes part: Exchange.hpp:36-41): post to the partner's mailbox, take
+ * what the other partner posted, and keep the send buffer alive until it has been taken */
 template <typename T, Device D>
 void SendRecv(const T* sbuf, int sc, int to, T* rbuf, int rc, int from, const Comm& c, SyncInfo<D> const&) {
-    (void)to;
-    c.sh->board[c.rank] = sbuf;
-    c.sh->bar.wait();
-    std::memcpy(rbuf, c.sh->board[from], (size_t)rc * sizeof(T));
-    c.sh->bar.wait();
     (void)sc;
+    CommShared& s = *c.sh;
+    std::unique_lock<std::mutex> lk(s.m);
+    const size_t out = (size_t)c.rank * s.size + to, in = (size_t)from * s.size + c.rank;
+    s.cv.wait(lk, [&] { return s.box[out] == nullptr; });
+    s.box[out] = sbuf ? static_cast<const void*>(sbuf) : static_cast<const void*>(&s);   /* an empty message still has to be seen */
+    s.cv.notify_all();
+    s.cv.wait(lk, [&] { return s.box[in] != nullptr; });
+    if (rc > 0) std::memcpy(rbuf, s.box[in], (size_t)rc * sizeof(T));
+    s.box[in] = nullptr;
+    s.cv.notify_all();
+    s.cv.wait(lk, [&] { return s.box[out] == nullptr; });
 }
+inline int Rank(const Comm& c) { return c.rank; }
+inline int Size(const Comm& c) { return c.Size(); }
+template <typename T, Collective C, Device D> inline void EnsureComm(const Comm&, SyncInfo<D> const&) {}
 template <typename T, Device D>
 void Broadcast(T* buf, int count, int root, const Comm& c, SyncInfo<D> const&) {
     if (c.rank == root) c.sh->board[root] = buf;
@@ -90,7 +120,9 @@ inline bool CongruentToCommSelf(const mpi::Comm& c) { return c.Size() == 1; }
 template <typename T, Device D>
 class simple_buffer {            /* include/hydrogen/utils/SimpleBuffer.hpp */
 public:
+    simple_buffer() {}
     simple_buffer(size_t n, SyncInfo<D> const&) : v_(n) {}
+    void allocate(size_t n) { v_.assign(n, T()); }
     T* data() { return v_.data(); }
 private:
     std::vector<T> v_;
@@ -165,6 +197,8 @@ public:
     Int LDim() const { return (Int)h()->ld[p_]; }
     T* Buffer() { return static_cast<T*>(h()->loc[p_]); }
     const T* LockedBuffer() const { return static_cast<const T*>(h()->loc[p_]); }
+    const T* LockedBuffer(Int iLoc, Int jLoc) const { return LockedBuffer() + iLoc + (size_t)jLoc * LDim(); }
+    T* Buffer(Int iLoc, Int jLoc) { return Buffer() + iLoc + (size_t)jLoc * LDim(); }
     El::Matrix<T, Device::CPU> Matrix() { return El::Matrix<T, Device::CPU>(LocalHeight(), LocalWidth(), Buffer(), LDim()); }
     El::Matrix<T, Device::CPU> LockedMatrix() const {
         return El::Matrix<T, Device::CPU>(LocalHeight(), LocalWidth(), const_cast<T*>(LockedBuffer()), LDim());
@@ -187,8 +221,32 @@ public:
     mpi::Comm ColComm() const { return comm_of(h()->colDist); }
     mpi::Comm RowComm() const { return comm_of(h()->rowDist); }
     mpi::Comm CrossComm() const { return comm_of(STAR); }
-    mpi::Comm PartialColComm() const { return comm_of(h()->colDist == VC ? MC : (h()->colDist == VR ? MR : h()->colDist)); }
-    mpi::Comm PartialRowComm() const { return comm_of(h()->rowDist == VC ? MC : (h()->rowDist == VR ? MR : h()->rowDist)); }
+    /* per-distribution definitions at the bottom of src/core/DistMatrix/ElementMatrix/<dist>.cpp (e.g. VR_STAR.cpp:159-247):
+     * Partial(VC) = MC, Partial(VR) = MR; the partial UNION of VC is the MR communicator, of VR the MC one, of anything else
+     * COMM_SELF (stride 1, rank 0); DistComm is the communicator of the product distribution */
+    static int part(int d) { return d == VC ? MC : (d == VR ? MR : d); }
+    static int puni(int d) { return d == VC ? MR : (d == VR ? MC : STAR); }
+    int prod() const {
+        const int U = h()->colDist, V = h()->rowDist;
+        return U == STAR ? V : (V == STAR ? U : ((U == MC && V == MR) ? VC : ((U == MR && V == MC) ? VR : STAR)));
+    }
+    int rank_in(int d) const { return orc_dist_rank(w_->g, d, mc_, mr_); }
+    int size_of(int d) const { return orc_dist_stride(w_->g, d); }
+    mpi::Comm PartialColComm() const { return comm_of(part(h()->colDist)); }
+    mpi::Comm PartialRowComm() const { return comm_of(part(h()->rowDist)); }
+    mpi::Comm PartialUnionColComm() const { return comm_of(puni(h()->colDist)); }
+    mpi::Comm PartialUnionRowComm() const { return comm_of(puni(h()->rowDist)); }
+    mpi::Comm DistComm() const { return comm_of(prod()); }
+    Int PartialColStride() const { return size_of(part(h()->colDist)); }
+    Int PartialRowStride() const { return size_of(part(h()->rowDist)); }
+    Int PartialUnionColStride() const { return size_of(puni(h()->colDist)); }
+    Int PartialUnionRowStride() const { return size_of(puni(h()->rowDist)); }
+    Int PartialColRank() const { return rank_in(part(h()->colDist)); }
+    Int PartialRowRank() const { return rank_in(part(h()->rowDist)); }
+    Int PartialUnionColRank() const { return rank_in(puni(h()->colDist)); }
+    Int PartialUnionRowRank() const { return rank_in(puni(h()->rowDist)); }
+    Int DistSize() const { return size_of(prod()); }
+    Int DistRank() const { return rank_in(prod()); }
     /* collective: every rank calls it with the same arguments; one of them re-creates the shared storage */
     void realign(int ca, int ra, Int m, Int n) {
         w_->all.wait();
@@ -214,6 +272,12 @@ private:
     int p_, mc_ = 0, mr_ = 0;
     GridView grid_;
 };
+/* the typed form some primitives take (PartialColAllGather, the AllToAll promotions / demotions, Exchange ...) */
+template <typename T, Dist U, Dist V, DistWrap W, Device D>
+class DistMatrix : public ElementalMatrix<T> {
+public:
+    using ElementalMatrix<T>::ElementalMatrix;
+};
 template <typename T>
 inline void Broadcast(ElementalMatrix<T>&, const mpi::Comm&, int) {}   /* cross-communicator broadcast: [o,o] / MD only */
 /* names only the BlockMatrix overloads in the same headers mention: declared so that the files parse, never instantiated */
@@ -227,6 +291,18 @@ template <typename... A> inline void SendRecv(const A&...) {}
 
 #define EL_DEBUG_CSE
 #include <El/blas_like/level1/Copy/RowAllGather.hpp>
+#include <El/blas_like/level1/Copy/ColAllGather.hpp>
+#include <El/blas_like/level1/Copy/PartialColAllGather.hpp>
+#include <El/blas_like/level1/Copy/PartialRowAllGather.hpp>
+#include <El/blas_like/level1/Copy/ColAllToAllDemote.hpp>
+#include <El/blas_like/level1/Copy/RowAllToAllDemote.hpp>
+#include <El/blas_like/level1/Copy/ColAllToAllPromote.hpp>
+#include <El/blas_like/level1/Copy/RowAllToAllPromote.hpp>
+#include <El/blas_like/level1/Copy/Exchange.hpp>
+#include <El/blas_like/level1/Copy/ColFilter.hpp>
+#include <El/blas_like/level1/Copy/RowFilter.hpp>
+#include <El/blas_like/level1/Copy/PartialColFilter.hpp>
+#include <El/blas_like/level1/Copy/PartialRowFilter.hpp>
 
 namespace {
 using namespace El;
@@ -245,18 +321,74 @@ void spmd(orc_dm* A, orc_dm** B, int colCon, int rowCon, F body) {
         });
     for (auto& t : th) t.join();
 }
+/* the typed primitives: build DistMatrix<T,U,V> handles for the (source, destination) pair at hand */
+#define TYPED(SU, SV, DU, DV, CALL)                                                                                         \
+    if (A->colDist == SU && A->rowDist == SV && (*B)->colDist == DU && (*B)->rowDist == DV) {                                \
+        World w(A->g);                                                                                                      \
+        std::vector<std::thread> th;                                                                                        \
+        orc_dm* a_slot = A;                                                                                                 \
+        for (int p = 0; p < w.P; ++p)                                                                                       \
+            th.emplace_back([&, p] {                                                                                        \
+                DistMatrix<T, SU, SV, ELEMENT, Device::CPU> a(&w, &a_slot, p);                                              \
+                DistMatrix<T, DU, DV, ELEMENT, Device::CPU> b(&w, B, p);                                                    \
+                b.colCon = colCon != 0;                                                                                     \
+                b.rowCon = rowCon != 0;                                                                                     \
+                CALL;                                                                                                       \
+            });                                                                                                             \
+        for (auto& t : th) t.join();                                                                                        \
+        return 0;                                                                                                           \
+    }
+
 template <typename T>
 int run(int prim, orc_dm* A, orc_dm** B, int colCon, int rowCon) {
+    typedef ElementalMatrix<T> EM;
+    constexpr Device CPU = Device::CPU;
     switch (prim) {
-        case 0: spmd<T>(A, B, colCon, rowCon, [](ElementalMatrix<T>& a, ElementalMatrix<T>& b) { copy::RowAllGather(a, b); }); return 0;
+        case 0: spmd<T>(A, B, colCon, rowCon, [](EM& a, EM& b) { copy::RowAllGather(a, b); }); return 0;
+        case 1: spmd<T>(A, B, colCon, rowCon, [](EM& a, EM& b) { copy::ColAllGather(a, b); }); return 0;
+        case 2:
+            TYPED(VC, STAR, MC, STAR, copy::PartialColAllGather(a, b))
+            TYPED(VR, STAR, MR, STAR, copy::PartialColAllGather(a, b))
+            return -2;
+        case 3: spmd<T>(A, B, colCon, rowCon, [](EM& a, EM& b) { copy::PartialRowAllGather(a, b); }); return 0;
+        case 4:
+            TYPED(MC, MR, VC, STAR, (copy::ColAllToAllDemote<T, VC, STAR, CPU>(a, b)))
+            TYPED(MR, MC, VR, STAR, (copy::ColAllToAllDemote<T, VR, STAR, CPU>(a, b)))
+            return -2;
+        case 5:
+            TYPED(MC, MR, STAR, VR, (copy::RowAllToAllDemote<T, STAR, VR, CPU>(a, b)))
+            TYPED(MR, MC, STAR, VC, (copy::RowAllToAllDemote<T, STAR, VC, CPU>(a, b)))
+            return -2;
+        case 6:
+            TYPED(VC, STAR, MC, MR, copy::ColAllToAllPromote(a, b))
+            TYPED(VR, STAR, MR, MC, copy::ColAllToAllPromote(a, b))
+            return -2;
+        case 7:
+            TYPED(STAR, VR, MC, MR, copy::RowAllToAllPromote(a, b))
+            TYPED(STAR, VC, MR, MC, copy::RowAllToAllPromote(a, b))
+            return -2;
+        case 8:
+            TYPED(VC, STAR, VR, STAR, (copy::ColwiseVectorExchange<T, MC, MR, CPU>(a, b)))
+            TYPED(VR, STAR, VC, STAR, (copy::ColwiseVectorExchange<T, MR, MC, CPU>(a, b)))
+            return -2;
+        case 9:
+            TYPED(STAR, VC, STAR, VR, (copy::RowwiseVectorExchange<T, MC, MR, CPU>(a, b)))
+            TYPED(STAR, VR, STAR, VC, (copy::RowwiseVectorExchange<T, MR, MC, CPU>(a, b)))
+            return -2;
+        case 10: spmd<T>(A, B, colCon, rowCon, [](EM& a, EM& b) { copy::ColFilter(a, b); }); return 0;
+        case 11: spmd<T>(A, B, colCon, rowCon, [](EM& a, EM& b) { copy::RowFilter(a, b); }); return 0;
+        case 12: spmd<T>(A, B, colCon, rowCon, [](EM& a, EM& b) { copy::PartialColFilter(a, b); }); return 0;
+        case 13: spmd<T>(A, B, colCon, rowCon, [](EM& a, EM& b) { copy::PartialRowFilter(a, b); }); return 0;
     }
     return -1;
 }
 }  // namespace
 
-/* B = A through the reference's copy:: primitive `prim` (0 RowAllGather ...).  *B is the destination as the caller set it up
+/* B = A through the reference's copy:: primitive `prim` (0 RowAllGather, 1 ColAllGather, 2 PartialColAllGather, 3 PartialRowAllGather, 4 ColAllToAllDemote,
+ * 5 RowAllToAllDemote, 6 ColAllToAllPromote, 7 RowAllToAllPromote, 8 ColwiseVectorExchange, 9 RowwiseVectorExchange, 10 ColFilter,
+ * 11 RowFilter, 12 PartialColFilter, 13 PartialRowFilter).  *B is the destination as the caller set it up
  * (distribution, alignments, any size); colCon / rowCon say whether its alignments are constrained (else the primitive may
- * re-align it, in which case *B is replaced).  Returns 0, or -1 for an unknown primitive. */
+ * re-align it, in which case *B is replaced).  Returns 0, -1 for an unknown primitive, -2 if the primitive does not serve the pair. */
 extern "C" int ref_copy_primitive(int prim, orc_dm* A, orc_dm** B, int colCon, int rowCon) {
     return A->es == 8 ? run<double>(prim, A, B, colCon, rowCon) : run<float>(prim, A, B, colCon, rowCon);
 }

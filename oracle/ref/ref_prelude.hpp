@@ -53,7 +53,7 @@ enum Dist { MC, MD, MR, VC, VR, STAR, CIRC };       // include/El/core/types.hpp
 enum DistWrap { ELEMENT, BLOCK };
 template <typename T> class ElementalMatrix;
 template <typename T, Device D = Device::CPU> class Matrix;
-template <typename T, Dist U, Dist V, DistWrap W, Device D> class DistMatrix;
+template <typename T, Dist U = MC, Dist V = MR, DistWrap W = ELEMENT, Device D = Device::CPU> class DistMatrix;
 
 template <typename C> using EnableIf = typename std::enable_if<C::value>::type;
 template <typename C> using DisableIf = typename std::enable_if<!C::value>::type;
