@@ -19,6 +19,10 @@
  *     oracle_level3.c reproduce their results bit for bit on the cases of tests/summa_cases.py / trapezoid_cases.py
  *     (digests in tests/golden/summa.json, trapezoid.json).  That pins the order of operations, temporaries, alignment
  *     targets and panel ranges of the restatement -- not the rounding of the third-party local product.
+ *   - REFERENCE CODE under the definition itself: the copy:: redistribution primitives (Copy/RowAllGather.hpp ... Exchange.hpp,
+ *     *Filter.hpp: fourteen entry points) run SPMD, one thread per simulated rank, over stand-ins (oracle/ref/ref_copy.cpp ->
+ *     oracle/_ref/libref_copy.so) and realise exactly orc_redist_closed's ownership definition, aligned or not; their alignment
+ *     adoption is orc_copy_adopts (tests/test_ref_pin.py).
  *   - The reference as a whole cannot be built here (needs MPI, LAPACK, Aluminum, NVSHMEM) and ships no
  *     golden vectors, so what only exists above MPI is pinned by the reference's own test PROPERTIES:
  *       tests/core/DistMatrix.cpp:28-76  : B = A for every distribution pair with random alignments,

@@ -278,8 +278,13 @@ class DistMatrix : public ElementalMatrix<T> {
 public:
     using ElementalMatrix<T>::ElementalMatrix;
 };
+/* El::Broadcast(A, comm, root) (include/El/blas_like/level1/Broadcast.hpp): the root's local matrix to every member, which all
+ * hold a block of the same shape; column by column here */
 template <typename T>
-inline void Broadcast(ElementalMatrix<T>&, const mpi::Comm&, int) {}   /* cross-communicator broadcast: [o,o] / MD only */
+inline void Broadcast(ElementalMatrix<T>& B, const mpi::Comm& comm, int root) {
+    if (comm.Size() == 1) return;
+    for (Int j = 0; j < B.LocalWidth(); ++j) mpi::Broadcast(B.Buffer(0, j), (int)B.LocalHeight(), root, comm, SyncInfo<Device::CPU>{});
+}
 /* names only the BlockMatrix overloads in the same headers mention: declared so that the files parse, never instantiated */
 using std::vector;
 template <typename T> class BlockMatrix;

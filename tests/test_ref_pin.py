@@ -165,3 +165,73 @@ def test_product_default_algorithm_is_the_one_the_reference_dispatcher_picks():
         assert lib.hyd_gemm_default_alg(m, n, k) in picked, (m, n, k, oA, oB, picked)
         checked += len(picked) == 1               # the digest singles out one variant: the pick is unambiguous
     assert checked >= 16      # Dot and C are singled out; A and B produce the same bits (one local product per element, same reduce order)
+
+
+# ---- the copy:: redistribution primitives, run SPMD through the reference's own headers (oracle/ref/ref_copy.cpp) ----
+_COPY_LIB = os.path.join(os.path.dirname(G.REF_LIB), "libref_copy.so")
+_PRIMS = {
+    0: ("RowAllGather", [((O.MC, O.MR), (O.MC, O.STAR)), ((O.MR, O.MC), (O.MR, O.STAR)), ((O.STAR, O.VC), (O.STAR, O.STAR)),
+                         ((O.STAR, O.MR), (O.STAR, O.STAR)), ((O.VC, O.STAR), (O.VC, O.STAR))]),
+    1: ("ColAllGather", [((O.MC, O.MR), (O.STAR, O.MR)), ((O.MR, O.MC), (O.STAR, O.MC)), ((O.VC, O.STAR), (O.STAR, O.STAR)),
+                         ((O.MR, O.STAR), (O.STAR, O.STAR))]),
+    2: ("PartialColAllGather", [((O.VC, O.STAR), (O.MC, O.STAR)), ((O.VR, O.STAR), (O.MR, O.STAR))]),
+    3: ("PartialRowAllGather", [((O.STAR, O.VC), (O.STAR, O.MC)), ((O.STAR, O.VR), (O.STAR, O.MR))]),
+    4: ("ColAllToAllDemote", [((O.MC, O.MR), (O.VC, O.STAR)), ((O.MR, O.MC), (O.VR, O.STAR))]),
+    5: ("RowAllToAllDemote", [((O.MC, O.MR), (O.STAR, O.VR)), ((O.MR, O.MC), (O.STAR, O.VC))]),
+    6: ("ColAllToAllPromote", [((O.VC, O.STAR), (O.MC, O.MR)), ((O.VR, O.STAR), (O.MR, O.MC))]),
+    7: ("RowAllToAllPromote", [((O.STAR, O.VR), (O.MC, O.MR)), ((O.STAR, O.VC), (O.MR, O.MC))]),
+    8: ("ColwiseVectorExchange", [((O.VC, O.STAR), (O.VR, O.STAR)), ((O.VR, O.STAR), (O.VC, O.STAR))]),
+    9: ("RowwiseVectorExchange", [((O.STAR, O.VC), (O.STAR, O.VR)), ((O.STAR, O.VR), (O.STAR, O.VC))]),
+    10: ("ColFilter", [((O.STAR, O.MR), (O.MC, O.MR)), ((O.STAR, O.MC), (O.MR, O.MC)), ((O.STAR, O.STAR), (O.VC, O.STAR))]),
+    11: ("RowFilter", [((O.MC, O.STAR), (O.MC, O.MR)), ((O.MR, O.STAR), (O.MR, O.MC)), ((O.STAR, O.STAR), (O.STAR, O.VR))]),
+    12: ("PartialColFilter", [((O.MC, O.STAR), (O.VC, O.STAR)), ((O.MR, O.STAR), (O.VR, O.STAR))]),
+    13: ("PartialRowFilter", [((O.STAR, O.MC), (O.STAR, O.VC)), ((O.STAR, O.MR), (O.STAR, O.VR))]),
+}
+
+
+@pytest.mark.skipif(not os.path.exists(_COPY_LIB), reason="oracle/_ref/libref_copy.so not built (needs /root/reference)")
+@pytest.mark.parametrize("prim", sorted(_PRIMS))
+def test_reference_copy_primitives_realise_the_closed_form_definition(prim):
+    """The oracle (and through it every parity test) defines B = A by the ownership formulas (orc_redist_closed).  Here the
+    reference's own copy:: primitive -- pack loops, collectives, the unaligned SendRecv branches, the width/height-1 broadcast
+    branches -- runs SPMD, one thread per simulated rank, and must produce exactly that: every rank's block of B holds the
+    entries of A the formulas give it (gather to [*,*] bitwise equal, replicas consistent), for constrained (possibly
+    unaligned) and unconstrained destinations.  With an unconstrained destination the alignments it ends with must be the ones
+    orc_copy_adopts predicts -- the rule the shim, the library's read proxies and the oracle's proxies share."""
+    import ctypes as C
+    ref = C.CDLL(_COPY_LIB)
+    ref.ref_copy_primitive.restype = C.c_int
+    ref.ref_copy_primitive.argtypes = [C.c_int, C.c_void_p, C.POINTER(C.c_void_p), C.c_int, C.c_int]
+    create = O.lib.orc_dm_create
+    create.restype = C.c_void_p
+
+    class Head(C.Structure):
+        _fields_ = [("g", O.Grid), ("colDist", C.c_int), ("rowDist", C.c_int), ("colAlign", C.c_int), ("rowAlign", C.c_int)]
+
+    rng = np.random.default_rng(500 + prim)
+    name, pairs = _PRIMS[prim]
+    n = 0
+    for (r, c) in [(1, 1), (2, 2), (2, 3), (4, 2)]:
+        g = O.Grid(r, c, 1)
+        al = lambda d: int(rng.integers(0, O.lib.orc_dist_stride(g, d)))
+        for (s, d), (m, w), con in itertools.product(pairs, [(1, 1), (7, 5), (50, 3), (33, 1), (1, 29), (40, 41)], (0, 1)):
+            A = O.DM(g, m, w, s[0], s[1], al(s[0]), al(s[1])).fill(1)
+            b0 = (al(d[0]), al(d[1]))
+            slot = C.c_void_p(create(g, 3, 2, d[0], d[1], b0[0], b0[1], 8))
+            assert ref.ref_copy_primitive(prim, A.h, C.byref(slot), con, con) == 0, name
+            head = Head.from_address(slot.value)
+            got_align = (head.colAlign, head.rowAlign)
+            B = O.DM(g, m, w, d[0], d[1], got_align[0], got_align[1], handle=slot.value)
+            GB, mism = B.to_global()
+            GA, _ = A.to_global()
+            assert mism == 0 and np.array_equal(GB, GA), (name, (r, c), s, d, (m, w), con)
+            if con:
+                assert got_align == b0
+            else:
+                exp = []
+                for sd, sa, dd, init in ((s[0], A.ca, d[0], b0[0]), (s[1], A.ra, d[1], b0[1])):
+                    a = C.c_int(0)
+                    exp.append(a.value if O.lib.orc_copy_adopts(sd, sa, dd, O.lib.orc_dist_stride(g, dd), C.byref(a)) else init)
+                assert got_align == tuple(exp), (name, (r, c), s, d, got_align, exp)
+            n += 1
+    assert n >= 96
