@@ -13,11 +13,13 @@
 #include <El/core/indexing/decl.hpp>
 #include <El/core/indexing/impl.hpp>
 #include <El/blas_like/level1/Copy/util.hpp>
+#include <El/blas_like/level1/Axpy/util.hpp>
 
 #include "../oracle.h"
 #include <condition_variable>
 #include <cstring>
 #include <mutex>
+#include <stdexcept>
 #include <thread>
 #include <vector>
 
@@ -37,6 +39,7 @@ template <Dist U, Dist V> constexpr Dist ProductDist() {   /* types.hpp:343-356 
 }
 template <Dist U, Dist V> constexpr Dist ProductDistPartner() { return (U == CIRC && V == CIRC) ? CIRC : STAR; }
 template <typename T, Device D> struct IsDeviceValidType : std::true_type {};
+template <typename T> struct TypeTraits { static T One() { return T(1); } static T Zero() { return T(0); } };
 
 /* ---- SPMD runtime ---- */
 struct Barrier {
@@ -104,6 +107,37 @@ void SendRecv(const T* sbuf, int sc, int to, T* rbuf, int rc, int from, const Co
     s.cv.notify_all();
     s.cv.wait(lk, [&] { return s.box[out] == nullptr; });
 }
+/* reductions: member q's portion k summed over q in ASCENDING communicator rank (MPI leaves the order open; the oracle's
+ * orc_axpy_contract_closed fixes it the same way).  In-place form (buf holds size*rc entries, the result lands at its front),
+ * two-buffer form, and Reduce to a root. */
+template <typename T>
+inline void reduce_from_board(const Comm& c, T* out, size_t offset, int count) {
+    for (int i = 0; i < count; ++i) {
+        T sum = static_cast<const T*>(c.sh->board[0])[offset + i];
+        for (int q = 1; q < c.sh->size; ++q) sum += static_cast<const T*>(c.sh->board[q])[offset + i];
+        out[i] = sum;
+    }
+}
+template <typename T, Device D>
+void ReduceScatter(const T* sbuf, T* rbuf, int rc, const Comm& c, SyncInfo<D> const&) {
+    c.sh->board[c.rank] = sbuf;
+    c.sh->bar.wait();
+    reduce_from_board(c, rbuf, (size_t)c.rank * rc, rc);
+    c.sh->bar.wait();
+}
+template <typename T, Device D>
+void ReduceScatter(T* buf, int rc, const Comm& c, SyncInfo<D> const& si) {
+    std::vector<T> tmp((size_t)(rc > 0 ? rc : 1));
+    ReduceScatter(static_cast<const T*>(buf), tmp.data(), rc, c, si);   /* the barrier inside orders the overwrite below */
+    std::memcpy(buf, tmp.data(), (size_t)rc * sizeof(T));
+}
+template <typename T, Device D>
+void Reduce(const T* sbuf, T* rbuf, int count, int root, const Comm& c, SyncInfo<D> const&) {
+    c.sh->board[c.rank] = sbuf;
+    c.sh->bar.wait();
+    if (c.rank == root) reduce_from_board(c, rbuf, 0, count);
+    c.sh->bar.wait();
+}
 inline int Rank(const Comm& c) { return c.rank; }
 inline int Size(const Comm& c) { return c.Size(); }
 template <typename T, Collective C, Device D> inline void EnsureComm(const Comm&, SyncInfo<D> const&) {}
@@ -122,6 +156,7 @@ class simple_buffer {            /* include/hydrogen/utils/SimpleBuffer.hpp */
 public:
     simple_buffer() {}
     simple_buffer(size_t n, SyncInfo<D> const&) : v_(n) {}
+    simple_buffer(size_t n, T const& value, SyncInfo<D> const&) : v_(n, value) {}
     void allocate(size_t n) { v_.assign(n, T()); }
     T* data() { return v_.data(); }
 private:
@@ -170,7 +205,11 @@ private:
 template <typename T, Device D>
 inline SyncInfo<D> SyncInfoFromMatrix(const Matrix<T, D>&) { return SyncInfo<D>{}; }
 template <typename T, Device D>
-inline void Copy(const Matrix<T, D>& A, Matrix<T, D> B) { B = A; }   /* B is a handle onto the block */
+inline void Copy(const Matrix<T, D>& A, Matrix<T, D> B) { B = A; }
+template <typename T, Device D>
+inline void Zero(Matrix<T, D> A) {
+    for (Int j = 0; j < A.Width(); ++j) std::memset(static_cast<void*>(A.Buffer() + (size_t)j * A.LDim()), 0, (size_t)A.Height() * sizeof(T));
+}   /* B is a handle onto the block */
 
 template <typename T>
 class ElementalMatrix {
@@ -308,6 +347,19 @@ template <typename... A> inline void SendRecv(const A&...) {}
 #include <El/blas_like/level1/Copy/RowFilter.hpp>
 #include <El/blas_like/level1/Copy/PartialColFilter.hpp>
 #include <El/blas_like/level1/Copy/PartialRowFilter.hpp>
+namespace El {
+/* same-distribution Axpy (AxpyContract's first branch): Y += alpha X on the local blocks, through the reference's own loop */
+template <typename T>
+inline void Axpy(T alpha, const ElementalMatrix<T>& X, ElementalMatrix<T>& Y) {
+    axpy::util::InterleaveMatrixUpdate(alpha, X.LocalHeight(), X.LocalWidth(), X.LockedBuffer(), Int(1), X.LDim(), Y.Buffer(), Int(1), Y.LDim(),
+                                       SyncInfo<Device::CPU>{});
+}
+}  // namespace El
+/* no explicit-instantiation declarations at the end of the header: the routines are instantiated here, from its definitions */
+#define PROTO_INT(T)
+#define PROTO_REAL(T)
+#define PROTO_COMPLEX(T)
+#include <El/blas_like/level1/AxpyContract.hpp>
 
 namespace {
 using namespace El;
@@ -317,14 +369,17 @@ void spmd(orc_dm* A, orc_dm** B, int colCon, int rowCon, F body) {
     World w(A->g);
     std::vector<std::thread> th;
     orc_dm* a_slot = A;
+    std::vector<int> threw(w.P, 0);
     for (int p = 0; p < w.P; ++p)
         th.emplace_back([&, p] {
             ElementalMatrix<T> a(&w, &a_slot, p), b(&w, B, p);
             b.colCon = colCon != 0;
             b.rowCon = rowCon != 0;
-            body(a, b);
+            /* the reference raises its LogicErrors on every rank alike, before any communication: no rank is left waiting */
+            try { body(a, b); } catch (const std::exception&) { threw[p] = 1; }
         });
     for (auto& t : th) t.join();
+    for (int p = 0; p < w.P; ++p) if (threw[p]) throw std::logic_error("the reference raised LogicError");
 }
 /* the typed primitives: build DistMatrix<T,U,V> handles for the (source, destination) pair at hand */
 #define TYPED(SU, SV, DU, DV, CALL)                                                                                         \
@@ -388,6 +443,18 @@ int run(int prim, orc_dm* A, orc_dm** B, int colCon, int rowCon) {
     return -1;
 }
 }  // namespace
+
+/* B += alpha * (sum of A over the ranks along which it is replicated / partially summed): El::AxpyContract(alpha, A, B),
+ * include/El/blas_like/level1/AxpyContract.hpp:484-544, through the reference's own scatter routines */
+extern "C" int ref_axpy_contract(double alpha, orc_dm* A, orc_dm** B) {
+    try {
+        if (A->es == 8) spmd<double>(A, B, 1, 1, [alpha](ElementalMatrix<double>& a, ElementalMatrix<double>& b) { AxpyContract(alpha, a, b); });
+        else spmd<float>(A, B, 1, 1, [alpha](ElementalMatrix<float>& a, ElementalMatrix<float>& b) { AxpyContract((float)alpha, a, b); });
+    } catch (const std::exception&) {
+        return -1;
+    }
+    return 0;
+}
 
 /* B = A through the reference's copy:: primitive `prim` (0 RowAllGather, 1 ColAllGather, 2 PartialColAllGather, 3 PartialRowAllGather, 4 ColAllToAllDemote,
  * 5 RowAllToAllDemote, 6 ColAllToAllPromote, 7 RowAllToAllPromote, 8 ColwiseVectorExchange, 9 RowwiseVectorExchange, 10 ColFilter,

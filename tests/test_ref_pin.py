@@ -235,3 +235,59 @@ def test_reference_copy_primitives_realise_the_closed_form_definition(prim):
                 assert got_align == tuple(exp), (name, (r, c), s, d, got_align, exp)
             n += 1
     assert n >= 96
+
+
+@pytest.mark.skipif(not os.path.exists(_COPY_LIB), reason="oracle/_ref/libref_copy.so not built (needs /root/reference)")
+def test_reference_axpy_contract_realises_the_closed_form_definition():
+    """B += alpha * (sum of A over the ranks it is replicated / partially summed along): the reference's own scatter routines
+    (AxpyContract.hpp: PartialColScatter, PartialRowScatter, ColScatter, RowScatter, Scatter), run SPMD over the stand-ins, against
+    orc_axpy_contract_closed -- the definition behind SUMMA-A/B/Dot in the oracle.  Every rank's contribution is a different
+    small-integer block, so all sums are exact and the comparison is bitwise whatever order a reduction takes.  Only cases the
+    reference implements: its partial scatters exist for aligned operands only ("Unaligned PartialColScatter not implemented"),
+    and the unaligned branch of its ColScatter packs B's local width out of A (AxpyContract.hpp:232-240), which overruns the
+    buffers when the two differ; the library takes any alignment (tests/test_gpu_redist.py::test_axpy_contract)."""
+    import ctypes as C
+    ref = C.CDLL(_COPY_LIB)
+    ref.ref_axpy_contract.restype = C.c_int
+    ref.ref_axpy_contract.argtypes = [C.c_double, C.c_void_p, C.POINTER(C.c_void_p)]
+    create = O.lib.orc_dm_create
+    create.restype = C.c_void_p
+    MC, MR, VC, VR, STAR = O.MC, O.MR, O.VC, O.VR, O.STAR
+    pairs = [((MC, MR), (MC, MR)), ((MC, STAR), (VC, STAR)), ((MR, STAR), (VR, STAR)), ((STAR, MC), (STAR, VC)), ((STAR, MR), (STAR, VR)),
+             ((STAR, MR), (MC, MR)), ((STAR, MC), (MR, MC)), ((STAR, STAR), (VC, STAR)), ((MC, STAR), (MC, MR)), ((MR, STAR), (MR, MC)),
+             ((STAR, STAR), (MC, MR)), ((STAR, STAR), (MR, MC)), ((STAR, STAR), (STAR, VR))]
+    part = {VC: MC, VR: MR}
+    rng = np.random.default_rng(600)
+    n = 0
+    for (r, c) in [(1, 1), (2, 2), (2, 3), (4, 2)]:
+        g = O.Grid(r, c, 1)
+        al = lambda d: int(rng.integers(0, O.lib.orc_dist_stride(g, d)))
+        for (s, d), (m, w), trial in itertools.product(pairs, [(1, 1), (7, 5), (50, 3), (33, 1), (1, 29), (40, 41)], (0, 1)):
+            sa, da = [al(s[0]), al(s[1])], [al(d[0]), al(d[1])]
+            for i in range(2):
+                if s[i] == d[i] and (trial == 0 or s == d or (i == 1 and s[0] == STAR and d[0] != STAR)):
+                    sa[i] = da[i]
+                if part.get(d[i]) == s[i] and s[i] != d[i]:
+                    sa[i] = da[i] % O.lib.orc_dist_stride(g, s[i])
+
+            def operand():
+                A = O.DM(g, m, w, s[0], s[1], sa[0], sa[1])
+                for p in range(r * c):
+                    blk = A.block(p)
+                    if blk.size:
+                        blk[...] = np.random.default_rng(1000 + p).integers(-8, 9, size=blk.shape)
+                return A
+
+            B0 = np.random.default_rng(7).integers(-8, 9, size=(m, w)).astype(np.float64)
+            A, B1 = operand(), O.DM(g, m, w, d[0], d[1], da[0], da[1]).from_global(B0)
+            O.lib.orc_axpy_contract_closed(2.0, A.h, B1.h, 0)
+            G1, m1 = B1.to_global()
+            G1 = G1.copy()
+            A = operand()
+            slot = C.c_void_p(create(g, m, w, d[0], d[1], da[0], da[1], 8))
+            B2 = O.DM(g, m, w, d[0], d[1], da[0], da[1], handle=slot.value).from_global(B0)
+            assert ref.ref_axpy_contract(2.0, A.h, C.byref(slot)) == 0, (s, d, sa, da)
+            G2, m2 = B2.to_global()
+            assert m1 == 0 and m2 == 0 and np.array_equal(G1, G2), ((r, c), s, d, (m, w), sa, da)
+            n += 1
+    assert n == 624
