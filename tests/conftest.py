@@ -15,3 +15,12 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
     config.addinivalue_line("markers", "multigpu: needs >= 2 CUDA devices")
+
+
+def pytest_sessionstart(session):
+    """Test-side convenience only (the product itself fails loudly without its library): on a fresh checkout build
+    elemental_b200/libhydrogen_b200.so before collection, as __graft_entry__.build() would.  nvcc cross-compiles without a GPU."""
+    import subprocess
+    lib = os.path.join(ROOT, "elemental_b200", "libhydrogen_b200.so")
+    if not os.path.exists(lib):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "elemental_b200", "csrc"), "-j8", "-s"])
