@@ -1,7 +1,7 @@
 /* TEST INFRASTRUCTURE ONLY -- see oracle/oracle.h.
  *
  * The reference's redistribution primitives, compiled from where they lie and run SPMD -- one thread per simulated rank --
- * over stand-in classes: include/El/blas_like/level1/Copy/{RowAllGather,ColAllGather,...}.hpp.  The per-portion loops they
+ * over stand-in classes: include/El/blas_like/level1/Copy/{RowAllGather,ColAllGather,...,Translate}.hpp and AxpyContract.hpp.  The per-portion loops they
  * call are the reference's own (Copy/util.hpp, already used by oracle/ref/ref_util.cpp); the stand-ins supply what sits
  * below and around them: an ElementalMatrix view of one rank's block of an orc_dm, and mpi::AllGather / SendRecv /
  * Broadcast / AllToAll over thread barriers with the data order MPI defines (portions in communicator-rank order).
@@ -138,6 +138,15 @@ void Reduce(const T* sbuf, T* rbuf, int count, int root, const Comm& c, SyncInfo
     if (c.rank == root) reduce_from_board(c, rbuf, 0, count);
     c.sh->bar.wait();
 }
+/* in-place exchange (Copy/Translate.hpp:93-95): send buf to `to`, overwrite it with what `from` sends */
+template <typename T, Device D>
+void SendRecv(T* buf, int count, int to, int from, const Comm& c, SyncInfo<D> const& si) {
+    std::vector<T> tmp(buf, buf + count);
+    SendRecv(static_cast<const T*>(tmp.data()), count, to, buf, count, from, c, si);
+}
+/* only reached when the roots of A and B differ, which never happens here (every matrix has root 0) */
+template <typename T, Device D> void Send(const T*, int, int, const Comm&, SyncInfo<D> const&) { throw std::logic_error("mpi::Send: not simulated"); }
+template <typename T, Device D> void Recv(T*, int, int, const Comm&, SyncInfo<D> const&) { throw std::logic_error("mpi::Recv: not simulated"); }
 inline int Rank(const Comm& c) { return c.rank; }
 inline int Size(const Comm& c) { return c.Size(); }
 template <typename T, Collective C, Device D> inline void EnsureComm(const Comm&, SyncInfo<D> const&) {}
@@ -182,8 +191,11 @@ struct World {                   /* shared by all rank threads of one call */
 struct GridView {
     bool InGrid() const { return true; }
     int Rank() const { return rank; }
+    bool operator!=(const GridView&) const { return false; }   /* one grid per call */
     int rank = 0;
 };
+typedef GridView Grid;
+template <typename M, Device D> inline void SetSyncInfo(M&, SyncInfo<D> const&) {}
 
 template <typename T, Device D>
 class Matrix {                   /* the local block */
@@ -243,6 +255,14 @@ public:
         return El::Matrix<T, Device::CPU>(LocalHeight(), LocalWidth(), const_cast<T*>(LockedBuffer()), LDim());
     }
     bool Participating() const { return true; }
+    bool ColConstrained() const { return colCon; }
+    bool RowConstrained() const { return rowCon; }
+    bool RootConstrained() const { return true; }
+    void SetGrid(const GridView&) {}
+    void SetRoot(int) {}
+    Int CrossRank() const { return 0; }
+    void AlignCols(Int ca, bool = true) { realign(ca, RowAlign(), Height(), Width()); }
+    void AlignRows(Int ra, bool = true) { realign(ColAlign(), ra, Height(), Width()); }
     const GridView& Grid() const { return grid_; }
     int Root() const { return 0; }
     Device GetLocalDevice() const { return Device::CPU; }
@@ -347,6 +367,10 @@ template <typename... A> inline void SendRecv(const A&...) {}
 #include <El/blas_like/level1/Copy/RowFilter.hpp>
 #include <El/blas_like/level1/Copy/PartialColFilter.hpp>
 #include <El/blas_like/level1/Copy/PartialRowFilter.hpp>
+namespace El { namespace copy {
+template <typename A, typename B> inline void TranslateBetweenGrids(const A&, B&) { throw std::logic_error("TranslateBetweenGrids: one grid only"); }
+} }
+#include <El/blas_like/level1/Copy/Translate.hpp>
 namespace El {
 /* same-distribution Axpy (AxpyContract's first branch): Y += alpha X on the local blocks, through the reference's own loop */
 template <typename T>
@@ -439,6 +463,19 @@ int run(int prim, orc_dm* A, orc_dm** B, int colCon, int rowCon) {
         case 11: spmd<T>(A, B, colCon, rowCon, [](EM& a, EM& b) { copy::RowFilter(a, b); }); return 0;
         case 12: spmd<T>(A, B, colCon, rowCon, [](EM& a, EM& b) { copy::PartialColFilter(a, b); }); return 0;
         case 13: spmd<T>(A, B, colCon, rowCon, [](EM& a, EM& b) { copy::PartialRowFilter(a, b); }); return 0;
+        case 14:
+            TYPED(MC, MR, MC, MR, copy::Translate(a, b))
+            TYPED(MR, MC, MR, MC, copy::Translate(a, b))
+            TYPED(MC, STAR, MC, STAR, copy::Translate(a, b))
+            TYPED(STAR, MR, STAR, MR, copy::Translate(a, b))
+            TYPED(MR, STAR, MR, STAR, copy::Translate(a, b))
+            TYPED(STAR, MC, STAR, MC, copy::Translate(a, b))
+            TYPED(VC, STAR, VC, STAR, copy::Translate(a, b))
+            TYPED(STAR, VC, STAR, VC, copy::Translate(a, b))
+            TYPED(VR, STAR, VR, STAR, copy::Translate(a, b))
+            TYPED(STAR, VR, STAR, VR, copy::Translate(a, b))
+            TYPED(STAR, STAR, STAR, STAR, copy::Translate(a, b))
+            return -2;
     }
     return -1;
 }
@@ -458,7 +495,7 @@ extern "C" int ref_axpy_contract(double alpha, orc_dm* A, orc_dm** B) {
 
 /* B = A through the reference's copy:: primitive `prim` (0 RowAllGather, 1 ColAllGather, 2 PartialColAllGather, 3 PartialRowAllGather, 4 ColAllToAllDemote,
  * 5 RowAllToAllDemote, 6 ColAllToAllPromote, 7 RowAllToAllPromote, 8 ColwiseVectorExchange, 9 RowwiseVectorExchange, 10 ColFilter,
- * 11 RowFilter, 12 PartialColFilter, 13 PartialRowFilter).  *B is the destination as the caller set it up
+ * 11 RowFilter, 12 PartialColFilter, 13 PartialRowFilter, 14 Translate).  *B is the destination as the caller set it up
  * (distribution, alignments, any size); colCon / rowCon say whether its alignments are constrained (else the primitive may
  * re-align it, in which case *B is replaced).  Returns 0, -1 for an unknown primitive, -2 if the primitive does not serve the pair. */
 extern "C" int ref_copy_primitive(int prim, orc_dm* A, orc_dm** B, int colCon, int rowCon) {

@@ -186,6 +186,7 @@ _PRIMS = {
     11: ("RowFilter", [((O.MC, O.STAR), (O.MC, O.MR)), ((O.MR, O.STAR), (O.MR, O.MC)), ((O.STAR, O.STAR), (O.STAR, O.VR))]),
     12: ("PartialColFilter", [((O.MC, O.STAR), (O.VC, O.STAR)), ((O.MR, O.STAR), (O.VR, O.STAR))]),
     13: ("PartialRowFilter", [((O.STAR, O.MC), (O.STAR, O.VC)), ((O.STAR, O.MR), (O.STAR, O.VR))]),
+    14: ("Translate", [((u, v), (u, v)) for (u, v) in O.PAIRS]),
 }
 
 
