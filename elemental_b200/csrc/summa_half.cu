@@ -31,7 +31,9 @@ struct Pool {
 int proxy_mcmr(Grid& g, Pool& pool, const DM& a, DM& out, cudaStream_t s) {
     if (a.colDist == MC && a.rowDist == MR) { out = a; return 0; }
     out = DM();
-    out.height = a.height; out.width = a.width; out.colDist = MC; out.rowDist = MR; out.colAlign = 0; out.rowAlign = 0;
+    out.height = a.height; out.width = a.width; out.colDist = MC; out.rowDist = MR;
+    out.colAlign = adopted_align(g.shape, a.colDist, a.colAlign, MC);   // as the reference's proxies do through B = A
+    out.rowAlign = adopted_align(g.shape, a.rowDist, a.rowAlign, MR);
     const LocalShape L = local_shape(g.shape, out, g.mc, g.mr);
     out.ldim = pad8(L.lh);
     void* p = nullptr;
