@@ -169,3 +169,11 @@ def test_proxy_alignment_adoption_matches_the_oracle_rule():
                     out = C.c_int(0)
                     k = O.lib.orc_copy_adopts(src, a, dst, O.lib.orc_dist_stride(og, dst), C.byref(out))
                     assert lib.hyd_adopted_align(r, c, src, a, dst) == (out.value if k else 0), (r, c, src, dst, a)
+
+
+def test_abi_header_is_plain_c():
+    """The drop-in boundary is a C ABI: include/hydrogen_b200.h must compile as C99 on its own (what a cgo / JNI / ctypes binding
+    generator sees), with no C++ or CUDA types in any signature."""
+    import subprocess
+    hdr = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "hydrogen_b200.h")
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Werror", "-fsyntax-only", "-x", "c", hdr])
