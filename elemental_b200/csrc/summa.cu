@@ -366,10 +366,18 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
         }
         if (check_cuda(cudaEventRecord(g.ev_join, s), "upload fork")) return 1;
         cudaStreamWaitEvent(us, g.ev_join, 0);
+        // Experiment knob (default off; DESIGN.md section 8, multi-GPU e2e): HYD_HOST_WHOLE = 1 uploads the operand whose
+        // k-dimension runs along its ROWS (B for NN) as ONE contiguous block before the first panel instead of npanels
+        // row-sliced 2-D copies (4 KiB rows at 8 GPUs, 1 KiB for the narrow first panel); = 2 does so for both operands.
+        static const int whole = getenv("HYD_HOST_WHOLE") ? atoi(getenv("HYD_HOST_WHOLE")) : 0;
+        const bool a_rows = oA != 0, b_rows = oB == 0;
+        const bool wholeA = whole >= 2 || (whole == 1 && a_rows), wholeB = whole >= 2 || (whole == 1 && b_rows);
+        if (wholeA && upload_k_slice<T>(sh, A, g.mc, g.mr, a_rows, 0, k, ho->A, ho->lda, us)) return 1;
+        if (wholeB && upload_k_slice<T>(sh, B, g.mc, g.mr, b_rows, 0, k, ho->B, ho->ldb, us)) return 1;
         for (size_t p = 0; p < npanels; ++p) {
             const i64 k0 = ks[p], kb = ks[p + 1] - ks[p];
-            if (upload_k_slice<T>(sh, A, g.mc, g.mr, oA != 0, k0, kb, ho->A, ho->lda, us)) return 1;
-            if (upload_k_slice<T>(sh, B, g.mc, g.mr, oB == 0, k0, kb, ho->B, ho->ldb, us)) return 1;
+            if (!wholeA && upload_k_slice<T>(sh, A, g.mc, g.mr, a_rows, k0, kb, ho->A, ho->lda, us)) return 1;
+            if (!wholeB && upload_k_slice<T>(sh, B, g.mc, g.mr, b_rows, k0, kb, ho->B, ho->ldb, us)) return 1;
             cudaEventRecord(g.upload_ev[p], us);
         }
     }
