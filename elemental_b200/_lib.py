@@ -48,6 +48,12 @@ def _sig(name, res, args):
 _sig("hyd_last_error", C.c_char_p, [])
 _sig("hyd_version", i32, [])
 _sig("hyd_launch_count", C.c_longlong, [])
+_sig("hyd_alloc_count", C.c_longlong, [])
+_sig("hyd_sync_count", C.c_longlong, [])
+_sig("hyd_multisync_begin", i32, [vp, C.POINTER(vp), i32])
+_sig("hyd_multisync_end", i32, [vp, C.POINTER(vp), i32])
+_sig("hyd_grid_set_host_blocks", i32, [vp, i32])
+_sig("hyd_host_block_plan", i32, [i64, i64, i64, f64, f64, i32, C.POINTER(i64)])
 _sig("hyd_lgemm_f64", i32, [i32, i32, i64, i64, i64, f64, vp, i64, vp, i64, f64, vp, i64, vp])
 _sig("hyd_lgemm_f32", i32, [i32, i32, i64, i64, i64, f32, vp, i64, vp, i64, f32, vp, i64, vp])
 _sig("hyd_lgemm_f16", i32, [i32, i32, i64, i64, i64, f32, vp, i64, vp, i64, f32, vp, i64, vp])
@@ -74,6 +80,7 @@ _sig("hyd_world_barrier", i32, [vp])
 _sig("hyd_grid_default_height", i32, [i32])
 _sig("hyd_world_size", i32, [vp])
 _sig("hyd_world_rank", i32, [vp])
+_sig("hyd_world_kind", C.c_char_p, [vp])
 _sig("hyd_grid_create", i32, [vp, i32, i32, C.POINTER(vp)])
 _sig("hyd_grid_destroy", i32, [vp])
 for _n in ("hyd_grid_height", "hyd_grid_width", "hyd_grid_size", "hyd_grid_rank", "hyd_grid_row", "hyd_grid_col",

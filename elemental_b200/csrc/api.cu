@@ -3,14 +3,15 @@
 #include "grid.h"
 #include "hyd_internal.h"
 #include <string.h>
+#include <stdlib.h>
+#include <algorithm>
 
 namespace hyd {
 const char* last_error();
 int probe_peak(int kind, int iters, int ctas_per_sm, double* tflops);
 template <typename T>
 int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A, const DM& B, T beta, const DM& C, i64 blocksize,
-              cudaStream_t s, const void* hostA, i64 hostLdA, const void* hostB, i64 hostLdB, void* hostC, i64 hostLdC,
-              int* c_downloaded);
+              cudaStream_t s, HostImages* host);
 int dist_gemm_half(Grid& g, int bf16, int oA, int oB, int alg, float alpha, const DM& A, const DM& B, float beta, const DM& C,
                    i64 blocksize, cudaStream_t s);
 struct h16;
@@ -84,22 +85,23 @@ static int gemm_host(hyd_grid* g, int oA, int oB, int alg, T alpha, const hyd_dm
                 return 1;
         }
     }
-    int c_downloaded = 0;  // set when the engine already wrote C's blocks to the host (column-blocked path)
-    if (hyd::dist_gemm<T>(G, oA, oB, alg, alpha, dev[0], dev[1], beta, dev[2], blocksize, s, A->buf, A->ldim, B->buf, B->ldim,
-                          C->buf, C->ldim, &c_downloaded))
-        return 1;
-    if (!c_downloaded && L[2].lh > 0 && L[2].lw > 0 &&
+    // c_downloaded: set when the engine already wrote C's blocks to the host (column-blocked path)
+    hyd::HostImages hi{A->buf, A->ldim, B->buf, B->ldim, C->buf, C->ldim, 0};
+    if (hyd::dist_gemm<T>(G, oA, oB, alg, alpha, dev[0], dev[1], beta, dev[2], blocksize, s, &hi)) return 1;
+    if (!hi.c_downloaded && L[2].lh > 0 && L[2].lw > 0 &&
         hyd::check_cuda(cudaMemcpy2DAsync(C->buf, (size_t)C->ldim * sizeof(T), dev[2].buf, (size_t)dev[2].ldim * sizeof(T),
                                           (size_t)L[2].lh * sizeof(T), (size_t)L[2].lw, cudaMemcpyDeviceToHost, s),
                         "hyd_gemm_host: D2H"))
         return 1;
-    return hyd::check_cuda(cudaStreamSynchronize(s), "hyd_gemm_host: sync");
+    return hyd::check_cuda(hyd::stream_sync(s), "hyd_gemm_host: sync");
 }
 extern "C" {
 
 const char* hyd_last_error(void) { return hyd::last_error(); }
 int hyd_version(void) { return 100; }
-long long hyd_launch_count(void) { return hyd::g_launches; }
+long long hyd_launch_count(void) { return hyd::g_launches.load(); }
+long long hyd_alloc_count(void) { return hyd::g_allocs.load(); }
+long long hyd_sync_count(void) { return hyd::g_syncs.load(); }
 
 int64_t hyd_mod(int64_t a, int64_t b) { return hyd::mod_(a, b); }
 int64_t hyd_shift(int64_t rank, int64_t align, int64_t stride) { return hyd::shift_(rank, align, stride); }
@@ -140,6 +142,7 @@ int hyd_world_create_nccl(const void* id128, int rank, int nranks, hyd_world** o
     *out = new hyd_world{w};
     return 0;
 }
+const char* hyd_world_kind(const hyd_world* w) { return w && w->w ? w->w->kind() : "none"; }
 int hyd_world_size(const hyd_world* w) { return w && w->w ? w->w->size : 0; }
 int hyd_world_rank(const hyd_world* w) { return w && w->w ? w->w->rank : -1; }
 int hyd_grid_default_height(int size) {
@@ -182,6 +185,7 @@ int hyd_grid_create(hyd_world* w, int height, int order, hyd_grid** out) {
     g->shape.col_major = order ? 1 : 0;
     g->rank = w->w->rank;
     g->shape.coords(g->rank, g->mc, g->mr);
+    if (const char* e = getenv("HYD_HOST_CBLOCKS")) g->host_cblocks = std::max(1, std::min(8, atoi(e)));
     *out = new hyd_grid{g};
     return 0;
 }
@@ -200,6 +204,11 @@ int hyd_grid_vr_rank(const hyd_grid* g) { return g->g->vr(); }
 int hyd_grid_set_overlap(hyd_grid* g, int overlap, int sm_reserve) {
     g->g->overlap = overlap;
     if (sm_reserve >= 0) g->g->sm_reserve = sm_reserve;
+    return 0;
+}
+int hyd_grid_set_host_blocks(hyd_grid* g, int max_blocks) {
+    if (!g || max_blocks < 1) return set_error("hyd_grid_set_host_blocks: bad arguments");
+    g->g->host_cblocks = max_blocks > 8 ? 8 : max_blocks;
     return 0;
 }
 int hyd_grid_profile(hyd_grid* g, int enable) {
@@ -259,6 +268,13 @@ int hyd_adopted_align(int gh, int gw, int srcDist, int srcAlign, int dstDist) {
     sh.r = gh; sh.c = gw;
     return hyd::adopted_align(sh, srcDist, srcAlign, dstDist);
 }
+int hyd_host_block_plan(int64_t tm, int64_t tn, int64_t sms, double lambda, double mu, int max_blocks, int64_t* cuts) {
+    if (!cuts || max_blocks < 1) return 0;
+    hyd::i64 c[9];
+    const int nb = hyd::host_col_cuts(tm, tn, sms, lambda, mu, max_blocks, c);
+    for (int i = 0; i <= nb; ++i) cuts[i] = c[i];
+    return nb;
+}
 int hyd_trrk_plan(int gh, int gw, int order, int rank, const hyd_dm* C, int uplo, int64_t j0, int64_t w, int es, int64_t* cuts) {
     hyd::GridShape sh;
     sh.r = gh; sh.c = gw; sh.col_major = order ? 1 : 0;
@@ -307,14 +323,14 @@ int hyd_gemm_f64(hyd_grid* g, int oA, int oB, int alg, double alpha, const hyd_d
     const hyd::GridShape& sh = g->g->shape;
     if (check_dm(sh, A, "hyd_gemm(A)") || check_dm(sh, B, "hyd_gemm(B)") || check_dm(sh, C, "hyd_gemm(C)")) return 1;
     return hyd::dist_gemm<double>(*g->g, oA, oB, alg, alpha, to_dm(A), to_dm(B), beta, to_dm(C), blocksize,
-                                  (cudaStream_t)stream, nullptr, 0, nullptr, 0, nullptr, 0, nullptr);
+                                  (cudaStream_t)stream, nullptr);
 }
 int hyd_gemm_f32(hyd_grid* g, int oA, int oB, int alg, float alpha, const hyd_dm* A, const hyd_dm* B, float beta,
                  const hyd_dm* C, int64_t blocksize, hyd_stream_t stream) {
     const hyd::GridShape& sh = g->g->shape;
     if (check_dm(sh, A, "hyd_gemm(A)") || check_dm(sh, B, "hyd_gemm(B)") || check_dm(sh, C, "hyd_gemm(C)")) return 1;
     return hyd::dist_gemm<float>(*g->g, oA, oB, alg, alpha, to_dm(A), to_dm(B), beta, to_dm(C), blocksize,
-                                 (cudaStream_t)stream, nullptr, 0, nullptr, 0, nullptr, 0, nullptr);
+                                 (cudaStream_t)stream, nullptr);
 }
 
 
@@ -422,6 +438,54 @@ int hyd_redist_b16(hyd_grid* g, const hyd_dm* src, const hyd_dm* dst, int transp
 HYD_TRRK(f64, double)
 HYD_TRRK(f32, float)
 #undef HYD_TRRK
+
+// MakeMultiSync(master, others...) (include/hydrogen/SyncInfo.hpp:136-186): at entry the master stream waits for everything
+// enqueued so far on the other streams; at exit the other streams wait for the master.  Events come from a small per-thread
+// cache (never destroyed while recorded work may be pending; cudaEventDisableTiming).
+static cudaEvent_t multisync_event(int i) {
+    static thread_local cudaEvent_t ev[16] = {};
+    static thread_local int dev_of[16];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    i &= 15;
+    if (ev[i] && dev_of[i] != dev) { cudaEventDestroy(ev[i]); ev[i] = nullptr; }
+    if (!ev[i]) { cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming); dev_of[i] = dev; }
+    return ev[i];
+}
+int hyd_multisync_begin(hyd_stream_t master, const hyd_stream_t* others, int n) {
+    if (n < 0 || (n > 0 && !others)) return set_error("hyd_multisync_begin: bad arguments");
+    cudaStream_t m = (cudaStream_t)master;
+    for (int i = 0; i < n; ++i) {
+        cudaStream_t o = (cudaStream_t)others[i];
+        if (o == m) continue;
+        bool seen = false;
+        for (int j = 0; j < i; ++j) seen = seen || others[j] == others[i];
+        if (seen) continue;
+        cudaEvent_t e = multisync_event(i);
+        if (hyd::check_cuda(cudaEventRecord(e, o), "hyd_multisync_begin: record") ||
+            hyd::check_cuda(cudaStreamWaitEvent(m, e, 0), "hyd_multisync_begin: wait"))
+            return 1;
+    }
+    return 0;
+}
+int hyd_multisync_end(hyd_stream_t master, const hyd_stream_t* others, int n) {
+    if (n < 0 || (n > 0 && !others)) return set_error("hyd_multisync_end: bad arguments");
+    cudaStream_t m = (cudaStream_t)master;
+    bool any = false;
+    for (int i = 0; i < n; ++i) any = any || (cudaStream_t)others[i] != m;
+    if (!any) return 0;
+    cudaEvent_t e = multisync_event(15);
+    if (hyd::check_cuda(cudaEventRecord(e, m), "hyd_multisync_end: record")) return 1;
+    for (int i = 0; i < n; ++i) {
+        cudaStream_t o = (cudaStream_t)others[i];
+        if (o == m) continue;
+        bool seen = false;
+        for (int j = 0; j < i; ++j) seen = seen || others[j] == others[i];
+        if (seen) continue;
+        if (hyd::check_cuda(cudaStreamWaitEvent(o, e, 0), "hyd_multisync_end: wait")) return 1;
+    }
+    return 0;
+}
 
 static int copy_kind(int kind, cudaMemcpyKind* out, const char* who) {
     if (kind == 0) *out = cudaMemcpyHostToDevice;

@@ -98,8 +98,8 @@ struct NcclWorld : World {
         HandleMsg mine;
         memset(&mine, 0, sizeof(mine));
         void* p = nullptr;
-        mine.ok = (cudaMalloc(&p, bytes) == cudaSuccess) && (cudaMemset(p, 0, bytes) == cudaSuccess) &&
-                  (cudaIpcGetMemHandle(&mine.h, p) == cudaSuccess) && (cudaDeviceSynchronize() == cudaSuccess);
+        mine.ok = (dev_malloc(&p, bytes) == cudaSuccess) && (cudaMemset(p, 0, bytes) == cudaSuccess) &&
+                  (cudaIpcGetMemHandle(&mine.h, p) == cudaSuccess) && (device_sync() == cudaSuccess);
         std::vector<HandleMsg> all;
         if (gather_handles(mine, all)) return 1;
         bool ok = true;
@@ -152,7 +152,7 @@ struct NcclWorld : World {
         if (bytes <= pc.region_cap[slot]) return 0;
         // every rank takes this branch together (same `bytes`, same history): drain all work that may still
         // touch the old mappings, everywhere, before they go away
-        if (check_cuda(cudaDeviceSynchronize(), "shared_reserve sync")) return 1;
+        if (check_cuda(device_sync(), "shared_reserve sync")) return 1;
         if (barrier()) return 1;
         release_region(slot);
         const size_t cap = push_grow(bytes);
@@ -188,7 +188,7 @@ struct NcclWorld : World {
         static thread_local int* scratch = nullptr;
         if (!scratch && check_cuda(cudaMalloc(&scratch, 4), "barrier scratch")) return 1;
         if (check_nccl(nccl::ncclAllReduce(scratch, scratch, 1, ncclInt, ncclSum, comm, 0), "ncclAllReduce")) return 1;
-        return check_cuda(cudaStreamSynchronize(0), "barrier sync");
+        return check_cuda(stream_sync(0), "barrier sync");
     }
 };
 
@@ -324,14 +324,14 @@ struct LocalWorld : World {
     int shared_reserve(int slot, size_t bytes) override {
         if (ctrl_linked && bytes <= pc.region_cap[slot]) return 0;
         // same decision on every rank-thread (same `bytes`, same history)
-        cudaDeviceSynchronize();
+        device_sync();
         pthread_barrier_wait(&sh->bar);
         int rc = 0;
         if (bytes > pc.region_cap[slot]) {
             if (pc.region_local[slot]) cudaFree(pc.region_local[slot]);
             const size_t cap = push_grow(bytes);
             void* p = nullptr;
-            rc = check_cuda(cudaMalloc(&p, cap), "push region");
+            rc = check_cuda(dev_malloc(&p, cap), "push region");
             pc.region_local[slot] = (char*)p;
             pc.region_cap[slot] = rc ? 0 : cap;
             sh->region[slot][rank] = (char*)p;

@@ -114,6 +114,47 @@ inline TrrkCuts trrk_cuts(int tri, const LocalShape& L, i64 j0, i64 w, i64 q) {
     return k;
 }
 
+// Column blocks of the local C for the host-resident stationary-C Gemm (summa.cu): C is computed block by block so that a
+// finished block downloads under the next block's GEMMs.  Cuts are in 128-column tiles of the LOCAL block (tm x tn tiles).
+// Every block's GEMMs run ceil(tm*w/sms) waves of the persistent kernel, so the cuts are chosen (dynamic programme, <= 8
+// blocks) to minimise   sum_j ceil(tm*w_j/sms)  +  lambda*w_last  +  mu*(blocks-1)
+// -- total waves, the exposed download of the last block (lambda = download time of one tile column in waves) and a small
+// per-block cost (the A panels are gathered again for every block).  Example: tm = tn = 128, 148 SMs -> 37|37|37|17:
+// 128*37 = 32*148 exactly, no wave is lost against the unblocked run.  Returns the cuts 0 = t_0 < ... < t_nblk = tn.
+inline int host_col_cuts(i64 tm, i64 tn, i64 sms, double lambda, double mu, int max_blocks, i64* cuts /*[max_blocks+1]*/) {
+    if (tn <= 0 || tm <= 0 || sms <= 0 || max_blocks < 1) { cuts[0] = 0; cuts[1] = tn > 0 ? tn : 0; return 1; }
+    if (max_blocks > 8) max_blocks = 8;
+    if (tn > 4096) tn = 4096;
+    auto waves = [&](i64 w) { return (double)((tm * w + sms - 1) / sms); };
+    const double INF = 1e300;
+    // best[b][t]: least cost of covering tiles [0, t) with exactly b blocks (no last-block term); from[b][t]: start of block b
+    static thread_local double best[9][4097];
+    static thread_local int from[9][4097];
+    for (int b = 0; b <= max_blocks; ++b) for (i64 t = 0; t <= tn; ++t) best[b][t] = INF;
+    best[0][0] = 0;
+    for (int b = 1; b <= max_blocks; ++b)
+        for (i64 t = b; t <= tn; ++t)
+            for (i64 u = b - 1; u < t; ++u) {
+                if (best[b - 1][u] >= INF) continue;
+                const double c = best[b - 1][u] + waves(t - u) + (b > 1 ? mu : 0.0);
+                if (c < best[b][t]) { best[b][t] = c; from[b][t] = (int)u; }
+            }
+    int nb = 1;
+    i64 ulast = 0;
+    double bc = INF;
+    for (int b = 1; b <= max_blocks && b <= tn; ++b)     // the last block [u, tn) also pays for its exposed download
+        for (i64 u = b - 1; u < tn; ++u) {
+            if (best[b - 1][u] >= INF) continue;
+            const double c = best[b - 1][u] + waves(tn - u) + (b > 1 ? mu : 0.0) + lambda * (double)(tn - u);
+            if (c < bc - 1e-9) { bc = c; nb = b; ulast = u; }
+        }
+    cuts[nb] = tn;
+    i64 t = ulast;
+    cuts[nb - 1] = t;
+    for (int b = nb - 1; b >= 1; --b) { t = from[b][t]; cuts[b - 1] = t; }
+    return nb;
+}
+
 // One arithmetic progression of global indices i = first + t*step, t < count,
 // together with where it sits in the source's and the destination's local index space.
 struct Prog { i64 count = 0, src0 = 0, srcStep = 1, dst0 = 0, dstStep = 1; };

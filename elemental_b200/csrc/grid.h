@@ -5,6 +5,7 @@
 #pragma once
 #include "comm.h"
 #include "dist.h"
+#include "hyd_internal.h"
 #include <cuda_runtime.h>
 #include <vector>
 
@@ -17,6 +18,15 @@ struct Workspace {
     size_t cap = 0;
 };
 
+// One pooled temporary (the reference's simple_buffer<T,D> on the CUB pool: include/hydrogen/utils/SimpleBuffer.hpp,
+// src/core/imports/cub.cpp): persistent device memory plus the event that marks its last use, so that a later borrower
+// on another stream is ordered behind it without any host synchronisation.
+struct PoolBuf {
+    Workspace w;
+    cudaEvent_t released = nullptr;
+    cudaStream_t last = nullptr;
+};
+
 struct Grid {
     World* world = nullptr;
     bool owns_world = false;
@@ -27,6 +37,7 @@ struct Grid {
     cudaStream_t comm_stream[2] = {nullptr, nullptr};
     cudaEvent_t ev_panel_ready[2] = {nullptr, nullptr}, ev_panel_free[2] = {nullptr, nullptr};
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaEvent_t ev_pipe[8] = {};                    // SUMMA-A/B/Dot pipeline: {in ready, in free, out ready, out free} x 2 buffers
     cudaStream_t unpack_stream = nullptr;           // chunk-pipelined redistributions: unpack of chunk q under the push of q+1
     cudaEvent_t ev_unpack_fork = nullptr, ev_unpack_join = nullptr;
     cudaEvent_t ev_chunk[8] = {};                   // chunk q's own part has been packed
@@ -38,8 +49,11 @@ struct Grid {
     Workspace coll_ws;        // receive area of hyd_reducescatter_* (coll.cu)
     Workspace level1_ws;      // X in Y's distribution for hyd_axpy_dist_* (level1.cu)
     Workspace trrk_ws;        // diagonal-strip products of the trapezoidal local update (summa.cu local_trrk)
+    std::vector<PoolBuf> pool;  // stack of pooled temporaries (proxies, Trrk / Symm intermediates): see TempScope
+    size_t pool_top = 0;
     int overlap = -1;    // -1 auto: gather panels under the previous GEMM only when the transport is SM-heavy (staged NCCL); 0 off; 1 on
     int sm_reserve = 4;  // SMs the local GEMM leaves to NCCL / pack kernels while overlapping
+    int host_cblocks = 8; // hyd_gemm_host_*: most column blocks of C (1 = one download after the last panel); hyd_grid_set_host_blocks
     long long launches = 0;
     // optional per-kernel timing (bench.py's roofline leg): CUDA event pairs around each launch of a kind
     enum { PROF_LGEMM = 0, PROF_REDIST = 1, PROF_REDUCE = 2, PROF_PACK = 3, PROF_UNPACK = 4, PROF_KINDS = 5 };
@@ -69,6 +83,36 @@ struct ProfScope {
 };
 void grid_destroy(Grid* g);
 
+// hyd_gemm_host_*: this rank's HOST images of the local blocks (pinned or pageable).  A NULL pointer is legal for an empty
+// local block.  c_downloaded is set when the engine has already written C's blocks back to the host itself.
+struct HostImages { const void* A; i64 lda; const void* B; i64 ldb; void* C; i64 ldc; int c_downloaded; };
+
+// Borrow temporaries from the grid's pool for the duration of one operation (proxies of non-[MC,MR] operands, the symmetric
+// completion in Symm, ...).  Nested operations stack: an inner scope takes the buffers above the outer one's.  Nothing is
+// allocated once the pool has seen the largest shape, and nothing blocks the host: a buffer handed back records an event on
+// the borrowing stream, and the next borrower waits for it on ITS stream only if that is a different one.
+struct TempScope {
+    Grid& g; cudaStream_t s; size_t base;
+    TempScope(Grid& g_, cudaStream_t s_) : g(g_), s(s_), base(g_.pool_top) {}
+    void* take(size_t bytes) {
+        if (g.pool_top == g.pool.size()) g.pool.emplace_back();
+        PoolBuf& b = g.pool[g.pool_top];
+        if (b.released && b.last != s) cudaStreamWaitEvent(s, b.released, 0);
+        if (ws_reserve(b.w, bytes ? bytes : 16)) return nullptr;
+        ++g.pool_top;
+        return b.w.buf;
+    }
+    ~TempScope() {
+        for (size_t i = base; i < g.pool_top; ++i) {
+            PoolBuf& b = g.pool[i];
+            if (!b.released) cudaEventCreateWithFlags(&b.released, cudaEventDisableTiming);
+            cudaEventRecord(b.released, s);
+            b.last = s;
+        }
+        g.pool_top = base;
+    }
+};
+
 // dst := src (or src^T), any pair of supported element distributions / alignments.
 template <typename T>
 int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot, cudaStream_t s);
@@ -97,6 +141,5 @@ template <typename T>
 int trapezoid_local(int op, int upper, i64 m, i64 n, i64 gi0, i64 rs, i64 gj0, i64 cs, i64 offset, T alpha, const T* X, i64 ldx,
                     T* Y, i64 ldy, cudaStream_t s);
 
-extern long long g_launches;  // kernels launched by this library in this process
 
 }  // namespace hyd

@@ -25,19 +25,19 @@
 
 namespace hyd {
 
-long long g_launches = 0;
+std::atomic<long long> g_launches{0}, g_allocs{0}, g_syncs{0};
 
 int ws_reserve(Workspace& w, size_t bytes) {
     if (bytes <= w.cap) return 0;
     if (w.buf) {
-        if (check_cuda(cudaDeviceSynchronize(), "workspace sync")) return 1;
+        if (check_cuda(device_sync(), "workspace sync")) return 1;
         cudaFree(w.buf);
         w.buf = nullptr;
         w.cap = 0;
     }
     size_t cap = std::max(bytes + bytes / 4, (size_t)1 << 20);
     cap = (cap + 255) & ~(size_t)255;
-    if (check_cuda(cudaMalloc(&w.buf, cap), "workspace cudaMalloc")) return 1;
+    if (check_cuda(dev_malloc((void**)&w.buf, cap), "workspace cudaMalloc")) return 1;
     w.cap = cap;
     return 0;
 }
@@ -187,6 +187,7 @@ int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot
     const GridShape& sh = g.shape;
     if (check_pair(sh, src, dst, transpose, "hyd_redist")) return 1;
     if (src.height == 0 || src.width == 0) return 0;
+    NvtxRange nvtx(transpose ? "Transpose" : "Copy");
     ProfScope prof(g, Grid::PROF_REDIST, s);
     const int P = sh.size(), me = g.rank;
     bool mcFree, mrFree;
@@ -461,6 +462,7 @@ int reduce_into(Grid& g, T alpha, const DM& src, const DM& dst, bool transpose, 
     const GridShape& sh = g.shape;
     if (check_pair(sh, src, dst, transpose, "hyd_axpy_contract")) return 1;
     if (src.height == 0 || src.width == 0) return 0;
+    NvtxRange nvtx("AxpyContract");
     ProfScope prof(g, Grid::PROF_REDUCE, s);
     const int P = sh.size();
     bool mcFree, mrFree;
@@ -604,6 +606,10 @@ void grid_destroy(Grid* g) {
     if (g->coll_ws.buf) cudaFree(g->coll_ws.buf);
     if (g->level1_ws.buf) cudaFree(g->level1_ws.buf);
     if (g->trrk_ws.buf) cudaFree(g->trrk_ws.buf);
+    for (auto& b : g->pool) {
+        if (b.w.buf) cudaFree(b.w.buf);
+        if (b.released) cudaEventDestroy(b.released);
+    }
     for (auto& v : g->prof_ev) for (cudaEvent_t e : v) cudaEventDestroy(e);
     for (cudaEvent_t e : g->upload_ev) cudaEventDestroy(e);
     for (int i = 0; i < 2; ++i) {
@@ -612,6 +618,7 @@ void grid_destroy(Grid* g) {
         if (g->ev_panel_free[i]) cudaEventDestroy(g->ev_panel_free[i]);
     }
     if (g->ev_fork) cudaEventDestroy(g->ev_fork);
+    for (cudaEvent_t e : g->ev_pipe) if (e) cudaEventDestroy(e);
     if (g->ev_join) cudaEventDestroy(g->ev_join);
     if (g->unpack_stream) cudaStreamDestroy(g->unpack_stream);
     if (g->download_stream) cudaStreamDestroy(g->download_stream);

@@ -36,6 +36,7 @@ template <typename T>
 int lgemm(Grid& g, int tA, int tB, i64 m, i64 n, i64 k, T alpha, const T* A, i64 lda, const T* B, i64 ldb, T beta, T* C,
           i64 ldc, cudaStream_t s, int sm_reserve) {
     ++g_launches;
+    NvtxRange nvtx("Gemm_impl.GPU");
     ProfScope prof(g, Grid::PROF_LGEMM, s);
     if constexpr (std::is_same<T, double>::value)
         return lgemm_f64_ex(tA, tB, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, s, sm_reserve);
@@ -106,7 +107,7 @@ int local_trrk(Grid& g, int tri, int tA, int tB, const LocalShape& Lc, i64 kb, T
         }
         if (t1 > t0) {
             const i64 th = t1 - t0, ldt = pad_ld(th, sizeof(T));
-            if (ws_reserve(g.trrk_ws, (size_t)(ldt * w) * sizeof(T))) return 1;
+            if ((size_t)(ldt * w) * sizeof(T) > g.trrk_ws.cap) return set_error("local_trrk: strip %lld x %lld exceeds the reserved workspace", th, w);
             T* D = reinterpret_cast<T*>(g.trrk_ws.buf);
             const T* Ai = tA ? A + t0 * lda : A + t0;
             if (lgemm<T>(g, tA, tB, th, w, kb, alpha, Ai, lda, Bj, ldb, T(0), D, ldt, s, sm_reserve)) return 1;
@@ -123,32 +124,31 @@ int local_update(Grid& g, int tri, int tA, int tB, const LocalShape& Lc, i64 kb,
     return local_trrk<T>(g, tri, tA, tB, Lc, kb, alpha, A, lda, B, ldb, C, ldc, s, sm_reserve);   // beta applied by the caller
 }
 
-// Host images of A's and B's local blocks (hyd_gemm_host_*): SUMMA-C streams them to the device panel by panel
-// on an upload stream, so the H2D copies hide under the previous panels' GEMMs instead of preceding the whole Gemm.
-// With a host image of C as well (C, ldc; cblocks > 1; 1x1 grid) the local C is computed column block by column block and
-// each finished block goes back to the host on a download stream under the next block's GEMMs (summa_c_host_blocked).
-struct HostOperands { const void* A; i64 lda; const void* B; i64 ldb; void* C; i64 ldc; int cblocks; };
+// Host images of A's and B's local blocks (hyd_gemm_host_*): SUMMA-C streams them to the device on an upload stream, so
+// the H2D copies hide under the GEMMs instead of preceding the whole Gemm.  With a host image of C as well the local C is
+// computed column block by column block (host_col_cuts) and each finished block goes back to the host on a download stream
+// under the next block's GEMMs: stationary-C keeps every element of C open until the last k-panel, so a whole-C SUMMA could
+// only start the download when all the flops are done.
+// `download`: the engine also writes C back (decided from global facts, identical on every rank); cblocks: most column blocks.
+struct HostOperands { const void* A; i64 lda; const void* B; i64 ldb; void* C; i64 ldc; int cblocks; bool download; };
 
-// upload the slice of a local block that holds global rows/cols [k0, k0+kb) of the k-dimension
+// upload this rank's part of the global sub-block rows [i0, i0+h) x columns [j0, j0+w) of X from its host image
 template <typename T>
-int upload_k_slice(const GridShape& sh, const DM& X, int mc, int mr, bool k_is_rows, i64 k0, i64 kb, const void* host,
-                   i64 ldh, cudaStream_t us) {
+int upload_rect(const GridShape& sh, const DM& X, int mc, int mr, i64 i0, i64 j0, i64 h, i64 w, const void* host, i64 ldh,
+                cudaStream_t us) {
     const LocalShape L = local_shape(sh, X, mc, mr);
-    if (L.lh == 0 || L.lw == 0) return 0;
-    if (k_is_rows) {
-        const i64 i0 = length_(k0, L.colShift, L.colStride), i1 = length_(k0 + kb, L.colShift, L.colStride);
-        if (i1 <= i0) return 0;
-        return check_cuda(cudaMemcpy2DAsync(static_cast<T*>(X.buf) + i0, (size_t)X.ldim * sizeof(T),
-                                            static_cast<const T*>(host) + i0, (size_t)ldh * sizeof(T),
-                                            (size_t)(i1 - i0) * sizeof(T), (size_t)L.lw, cudaMemcpyHostToDevice, us),
-                          "hyd_gemm_host: H2D rows");
-    }
-    const i64 j0 = length_(k0, L.rowShift, L.rowStride), j1 = length_(k0 + kb, L.rowShift, L.rowStride);
-    if (j1 <= j0) return 0;
-    return check_cuda(cudaMemcpy2DAsync(static_cast<T*>(X.buf) + j0 * X.ldim, (size_t)X.ldim * sizeof(T),
-                                        static_cast<const T*>(host) + j0 * ldh, (size_t)ldh * sizeof(T),
-                                        (size_t)L.lh * sizeof(T), (size_t)(j1 - j0), cudaMemcpyHostToDevice, us),
-                      "hyd_gemm_host: H2D cols");
+    const i64 a0 = length_(i0, L.colShift, L.colStride), a1 = length_(i0 + h, L.colShift, L.colStride);
+    const i64 b0 = length_(j0, L.rowShift, L.rowStride), b1 = length_(j0 + w, L.rowShift, L.rowStride);
+    if (a1 <= a0 || b1 <= b0) return 0;
+    if (!host) return set_error("hyd_gemm_host: NULL host buffer for a non-empty local block");
+    T* d = static_cast<T*>(X.buf) + a0 + b0 * X.ldim;
+    const T* hsrc = static_cast<const T*>(host) + a0 + b0 * ldh;
+    if (a1 - a0 == X.ldim && X.ldim == ldh)   // whole columns, no padding on either side: one contiguous transfer
+        return check_cuda(cudaMemcpyAsync(d, hsrc, (size_t)(X.ldim * (b1 - b0)) * sizeof(T), cudaMemcpyHostToDevice, us),
+                          "hyd_gemm_host: H2D");
+    return check_cuda(cudaMemcpy2DAsync(d, (size_t)X.ldim * sizeof(T), hsrc, (size_t)ldh * sizeof(T), (size_t)(a1 - a0) * sizeof(T),
+                                        (size_t)(b1 - b0), cudaMemcpyHostToDevice, us),
+                      "hyd_gemm_host: H2D (2-D)");
 }
 
 // ---- copy-engine panel gather for SUMMA-C, NN orientation --------------------------------------------------------
@@ -250,81 +250,6 @@ int gather_panels_ce(Grid& g, const DM& A, const DM& B, const DM& C, i64 k0, i64
     return g.world->push_wait(slotA, fromA.data(), cs) || g.world->push_wait(slotB, fromB.data(), cs);
 }
 
-// 1x1 grid, host-resident operands, C in `cblocks` column blocks (hyd_gemm_host_* with HYD_HOST_CBLOCKS > 1).
-// Stationary-C keeps every element of C open until the last k-panel, so a whole-C SUMMA can only start the download when
-// all the flops are done (2 GiB = 40 ms at 16384^2 fp64, the gap between `value` and `e2e`).  Block by block instead:
-//   upload stream   : for block j, panel p: [A(:,K_p) if j == 0] and op(B)(K_p, J_j)       (all enqueued up front)
-//   compute stream  : C(:,J_j) = alpha * sum_p A(:,K_p) op(B)(K_p,J_j) + beta C(:,J_j)      (waits per (j,p) upload event)
-//   download stream : C(:,J_j) -> host as soon as block j's last panel is done, under block j+1's GEMMs
-// A is uploaded once (block 0) and re-read from HBM by the later blocks.  Only the first (narrow) panel's upload and the
-// last block's download stay exposed.  The k-sum of every element is grouped exactly as in the unblocked host path.
-template <typename T>
-int summa_c_host_blocked(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, const DM& B, T beta, const DM& C,
-                         const std::vector<i64>& ks, cudaStream_t s, const HostOperands& ho) {
-    const size_t npanels = ks.size() - 1;
-    // column blocks: multiples of 128 columns (GEMM tile width; keeps every block's C and B pointers 16-byte aligned)
-    const i64 nblk_want = std::max<i64>(1, std::min<i64>(ho.cblocks, (n + 511) / 512));
-    const i64 wb = ((n + nblk_want - 1) / nblk_want + 127) / 128 * 128;
-    std::vector<i64> js;
-    for (i64 j0 = 0; j0 < n; j0 += wb) js.push_back(j0);
-    js.push_back(n);
-    const size_t nblk = js.size() - 1;
-    if (!g.download_stream) {
-        if (check_cuda(cudaStreamCreateWithFlags(&g.download_stream, cudaStreamNonBlocking), "download stream")) return 1;
-        cudaEventCreateWithFlags(&g.ev_block_done, cudaEventDisableTiming);
-        cudaEventCreateWithFlags(&g.ev_download_done, cudaEventDisableTiming);
-    }
-    cudaStream_t us = g.comm_stream[1], ds = g.download_stream;
-    while (g.upload_ev.size() < npanels * nblk) {
-        cudaEvent_t e;
-        cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
-        g.upload_ev.push_back(e);
-    }
-    // uploads may start once everything enqueued so far on the caller's stream (earlier users of the images) is done
-    if (check_cuda(cudaEventRecord(g.ev_join, s), "upload fork")) return 1;
-    cudaStreamWaitEvent(us, g.ev_join, 0);
-    cudaStreamWaitEvent(ds, g.ev_join, 0);
-    const T* hB = static_cast<const T*>(ho.B);
-    T* dB = static_cast<T*>(B.buf);
-    for (size_t j = 0; j < nblk; ++j) {
-        const i64 j0 = js[j], w = js[j + 1] - js[j];
-        for (size_t p = 0; p < npanels; ++p) {
-            const i64 k0 = ks[p], kb = ks[p + 1] - ks[p];
-            if (j == 0 && upload_k_slice<T>(g.shape, A, g.mc, g.mr, oA != 0, k0, kb, ho.A, ho.lda, us)) return 1;
-            // op(B)(k0:k0+kb, j0:j0+w): B is k x n (oB == 0: rows k0.., columns j0..) or n x k (rows j0.., columns k0..)
-            const i64 r0 = oB ? j0 : k0, nr = oB ? w : kb, c0 = oB ? k0 : j0, nc = oB ? kb : w;
-            if (check_cuda(cudaMemcpy2DAsync(dB + r0 + c0 * B.ldim, (size_t)B.ldim * sizeof(T), hB + r0 + c0 * ho.ldb,
-                                             (size_t)ho.ldb * sizeof(T), (size_t)nr * sizeof(T), (size_t)nc,
-                                             cudaMemcpyHostToDevice, us),
-                           "hyd_gemm_host: H2D block of B"))
-                return 1;
-            cudaEventRecord(g.upload_ev[j * npanels + p], us);
-        }
-    }
-    for (size_t j = 0; j < nblk; ++j) {
-        const i64 j0 = js[j], w = js[j + 1] - js[j];
-        T* c = static_cast<T*>(C.buf) + j0 * C.ldim;
-        for (size_t p = 0; p < npanels; ++p) {
-            const i64 k0 = ks[p], kb = ks[p + 1] - ks[p];
-            cudaStreamWaitEvent(s, g.upload_ev[j * npanels + p], 0);
-            const T* a = static_cast<const T*>(A.buf) + (oA ? k0 : k0 * A.ldim);
-            const T* b = dB + (oB ? j0 + k0 * B.ldim : k0 + j0 * B.ldim);
-            if (lgemm<T>(g, oA, oB, m, w, kb, alpha, a, A.ldim, b, B.ldim, k0 == 0 ? beta : T(1), c, C.ldim, s, 0)) return 1;
-        }
-        // block j is final: download it while block j+1 computes (stream order on ds keeps the blocks in sequence)
-        if (check_cuda(cudaEventRecord(g.ev_block_done, s), "block done")) return 1;
-        cudaStreamWaitEvent(ds, g.ev_block_done, 0);
-        if (check_cuda(cudaMemcpy2DAsync(static_cast<T*>(ho.C) + j0 * ho.ldc, (size_t)ho.ldc * sizeof(T), c,
-                                         (size_t)C.ldim * sizeof(T), (size_t)m * sizeof(T), (size_t)w, cudaMemcpyDeviceToHost, ds),
-                       "hyd_gemm_host: D2H block of C"))
-            return 1;
-    }
-    // the caller's stream is complete only when the last download is
-    if (check_cuda(cudaEventRecord(g.ev_download_done, ds), "download join")) return 1;
-    cudaStreamWaitEvent(s, g.ev_download_done, 0);
-    return 0;
-}
-
 // ---- SUMMA-C (stationary C) -------------------------------------------------
 template <typename T>
 int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, const DM& B, T beta, const DM& C, i64 nb,
@@ -334,7 +259,6 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
     // `beta` is applied by the first panel's update (C = alpha A1 B1^T + beta C) instead of a separate
     // Scale(beta, C) pass (reference Gemm.cpp:287): one full read+write of C saved, and beta == 0 never reads C.
     const GridShape& sh = g.shape;
-    const LocalShape Lc = local_shape(sh, C, g.mc, g.mr);
     const int es = sizeof(T);
     if (ensure_engine(g)) return 1;
     // NN with matching alignments on the push transport: panels are gathered by the copy engines alone (gather_panels_ce),
@@ -354,44 +278,106 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
         ks.push_back(k);
     }
     const size_t npanels = ks.size() - 1;
-    if (ho && ho->C && ho->cblocks > 1 && sh.size() == 1 && Lc.lh > 0 && Lc.lw >= 1024)
-        return summa_c_host_blocked<T>(g, oA, oB, m, n, k, alpha, A, B, beta, C, ks, s, *ho);
+    // column blocks of C (GLOBAL column cuts, multiples of 128 * c so that every rank's local cut is the same multiple of
+    // 128 local columns): one block unless the caller's C lives on the host (ho->C), then host_col_cuts (dist.h)
+    std::vector<i64> js(1, 0);
+    if (ho && ho->download && ho->cblocks > 1 && tri < 0) {
+        const i64 c = sh.c, r = sh.r;
+        const i64 tm = (max_length_(m, r) + 127) / 128, tn = (max_length_(n, c) + 127) / 128;
+        // download time of one 128-column tile strip of the local C, in waves of the local GEMM (one wave = one 128 x 128 x k
+        // tile per SM).  Rates are round numbers: ~45 GB/s D2H, 250 GFLOP/s (fp64 DMMA) / 1.4 TFLOP/s (3xTF32) per SM.
+        const double per_sm = es == 8 ? 250e9 : 1.4e12;
+        const double lambda = (double)max_length_(m, r) * es * per_sm / (45e9 * 256.0 * (double)std::max<i64>(k, 1));
+        i64 cuts[9];
+        const int sms = std::max(1, num_sms() - ((overlap && !ce) ? g.sm_reserve : 0));
+        const int nblk = host_col_cuts(tm, tn, sms, lambda, 0.05, std::min(ho->cblocks, 8), cuts);
+        for (int b = 1; b < nblk; ++b) js.push_back(std::min<i64>(n, cuts[b] * 128 * c));
+    }
+    js.push_back(n);
+    const size_t nblk = js.size() - 1;
+    const size_t nsteps = nblk * npanels;
+    cudaStream_t us = g.comm_stream[1], ds = nullptr;
     if (ho) {
-        // all uploads are enqueued now, in panel order, on the upload stream; consumers wait per panel
-        cudaStream_t us = g.comm_stream[1];
-        while (g.upload_ev.size() < npanels) {
+        // every upload is enqueued now, on the upload stream, in the order the steps consume them: for block 0 panel by
+        // panel (A's panel p and the part of B's panel p under block 0), then the rest of B one whole column block at a time
+        // (one big transfer each -- for NN a contiguous one -- a whole block ahead of its first use); consumers wait per event
+        while (g.upload_ev.size() < npanels + nblk) {
             cudaEvent_t e;
             cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
             g.upload_ev.push_back(e);
         }
         if (check_cuda(cudaEventRecord(g.ev_join, s), "upload fork")) return 1;
         cudaStreamWaitEvent(us, g.ev_join, 0);
-        // Experiment knob (default off; DESIGN.md section 8, multi-GPU e2e): HYD_HOST_WHOLE = 1 uploads the operand whose
-        // k-dimension runs along its ROWS (B for NN) as ONE contiguous block before the first panel instead of npanels
-        // row-sliced 2-D copies (4 KiB rows at 8 GPUs, 1 KiB for the narrow first panel); = 2 does so for both operands.
-        static const int whole = getenv("HYD_HOST_WHOLE") ? atoi(getenv("HYD_HOST_WHOLE")) : 0;
-        const bool a_rows = oA != 0, b_rows = oB == 0;
-        const bool wholeA = whole >= 2 || (whole == 1 && a_rows), wholeB = whole >= 2 || (whole == 1 && b_rows);
-        if (wholeA && upload_k_slice<T>(sh, A, g.mc, g.mr, a_rows, 0, k, ho->A, ho->lda, us)) return 1;
-        if (wholeB && upload_k_slice<T>(sh, B, g.mc, g.mr, b_rows, 0, k, ho->B, ho->ldb, us)) return 1;
         for (size_t p = 0; p < npanels; ++p) {
             const i64 k0 = ks[p], kb = ks[p + 1] - ks[p];
-            if (!wholeA && upload_k_slice<T>(sh, A, g.mc, g.mr, a_rows, k0, kb, ho->A, ho->lda, us)) return 1;
-            if (!wholeB && upload_k_slice<T>(sh, B, g.mc, g.mr, b_rows, k0, kb, ho->B, ho->ldb, us)) return 1;
+            if (oB ? upload_rect<T>(sh, B, g.mc, g.mr, js[0], k0, js[1] - js[0], kb, ho->B, ho->ldb, us)
+                   : upload_rect<T>(sh, B, g.mc, g.mr, k0, js[0], kb, js[1] - js[0], ho->B, ho->ldb, us))
+                return 1;
+            if (oA ? upload_rect<T>(sh, A, g.mc, g.mr, k0, 0, kb, m, ho->A, ho->lda, us)
+                   : upload_rect<T>(sh, A, g.mc, g.mr, 0, k0, m, kb, ho->A, ho->lda, us))
+                return 1;
             cudaEventRecord(g.upload_ev[p], us);
         }
+        for (size_t j = 1; j < nblk; ++j) {
+            if (oB ? upload_rect<T>(sh, B, g.mc, g.mr, js[j], 0, js[j + 1] - js[j], k, ho->B, ho->ldb, us)
+                   : upload_rect<T>(sh, B, g.mc, g.mr, 0, js[j], k, js[j + 1] - js[j], ho->B, ho->ldb, us))
+                return 1;
+            cudaEventRecord(g.upload_ev[npanels + j], us);
+        }
+        if (ho->download) {
+            if (!g.download_stream) {
+                if (check_cuda(cudaStreamCreateWithFlags(&g.download_stream, cudaStreamNonBlocking), "download stream")) return 1;
+                cudaEventCreateWithFlags(&g.ev_block_done, cudaEventDisableTiming);
+                cudaEventCreateWithFlags(&g.ev_download_done, cudaEventDisableTiming);
+            }
+            ds = g.download_stream;
+            cudaStreamWaitEvent(ds, g.ev_join, 0);
+        }
     }
+    // stream `w` (compute or comm) must not touch step (j, p)'s operands before their upload has landed
+    auto wait_upload = [&](cudaStream_t w, size_t j, size_t p) {
+        if (!ho) return;
+        if (j == 0) cudaStreamWaitEvent(w, g.upload_ev[p], 0);
+        else if (p == 0) cudaStreamWaitEvent(w, g.upload_ev[npanels + j], 0);
+    };
+    // a finished column block of C goes back to the host under the next block's GEMMs
+    auto download_block = [&](size_t j, const DM& Cj, const LocalShape& Lj) -> int {
+        if (!ds) return 0;
+        if (check_cuda(cudaEventRecord(g.ev_block_done, s), "block done")) return 1;
+        cudaStreamWaitEvent(ds, g.ev_block_done, 0);
+        if (Lj.lh > 0 && Lj.lw > 0) {
+            const LocalShape Lfull = local_shape(sh, C, g.mc, g.mr);
+            const i64 jl = length_(js[j], Lfull.rowShift, Lfull.rowStride);
+            if (!ho->C) return set_error("hyd_gemm_host: NULL host buffer for a non-empty local block of C");
+            if (check_cuda(cudaMemcpy2DAsync(static_cast<T*>(ho->C) + jl * ho->ldc, (size_t)ho->ldc * sizeof(T), Cj.buf,
+                                             (size_t)Cj.ldim * sizeof(T), (size_t)Lj.lh * sizeof(T), (size_t)Lj.lw,
+                                             cudaMemcpyDeviceToHost, ds),
+                           "hyd_gemm_host: D2H block of C"))
+                return 1;
+        }
+        if (j + 1 == nblk) {   // the caller's stream is complete only when the last download is
+            if (check_cuda(cudaEventRecord(g.ev_download_done, ds), "download join")) return 1;
+            cudaStreamWaitEvent(s, g.ev_download_done, 0);
+        }
+        return 0;
+    };
     if (sh.size() == 1) {
         // 1x1 grid: [MC,*] and [MR,*] panels coincide with the operands' own storage
         // (the reference degenerates to local copies, RowAllGather.hpp:35-38); feed views directly.
-        for (size_t p = 0; p < npanels; ++p) {
-            const i64 k0 = ks[p], kb = ks[p + 1] - ks[p];
-            if (ho) cudaStreamWaitEvent(s, g.upload_ev[p], 0);
-            const T* a = static_cast<const T*>(A.buf) + (oA ? k0 : k0 * A.ldim);
-            const T* b = static_cast<const T*>(B.buf) + (oB ? k0 * B.ldim : k0);
-            if (local_update<T>(g, tri, oA, oB, Lc, kb, alpha, a, A.ldim, b, B.ldim, k0 == 0 ? beta : T(1),
-                                static_cast<T*>(C.buf), C.ldim, s, 0))
-                return 1;
+        for (size_t j = 0; j < nblk; ++j) {
+            const i64 j0 = js[j], w = js[j + 1] - js[j];
+            const DM Cj = nblk == 1 ? C : view(sh, C, 0, 0, 0, j0, m, w, es);
+            const LocalShape Lj = local_shape(sh, Cj, 0, 0);
+            for (size_t p = 0; p < npanels; ++p) {
+                const i64 k0 = ks[p], kb = ks[p + 1] - ks[p];
+                wait_upload(s, j, p);
+                const T* a = static_cast<const T*>(A.buf) + (oA ? k0 : k0 * A.ldim);
+                const T* b = static_cast<const T*>(B.buf) + (oB ? j0 + k0 * B.ldim : k0 + j0 * B.ldim);
+                if (local_update<T>(g, tri, oA, oB, Lj, kb, alpha, a, A.ldim, b, B.ldim, k0 == 0 ? beta : T(1),
+                                    static_cast<T*>(Cj.buf), Cj.ldim, s, 0))
+                    return 1;
+            }
+            if (download_block(j, Cj, Lj)) return 1;
         }
         return 0;
     }
@@ -401,25 +387,31 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
         if (check_cuda(cudaEventRecord(g.ev_fork, s), "fork")) return 1;
         cudaStreamWaitEvent(cs, g.ev_fork, 0);
     }
-    for (size_t step = 0; step < npanels; ++step) {
-        const i64 k0 = ks[step], kb = ks[step + 1] - ks[step];
+    for (size_t step = 0; step < nsteps; ++step) {
+        const size_t j = step / npanels, p = step % npanels;
+        const i64 k0 = ks[p], kb = ks[p + 1] - ks[p];
+        const i64 j0 = js[j], w = js[j + 1] - js[j];
         const int buf = (int)(step & 1);
-        if (ho) cudaStreamWaitEvent(cs, g.upload_ev[step], 0);
+        wait_upload(cs, j, p);
+        // this block's columns of C and of op(B): views, so every gather below sees an ordinary (narrower) Gemm
+        const DM Cj = nblk == 1 ? C : view(sh, C, g.mc, g.mr, 0, j0, m, w, es);
+        const DM Bj = nblk == 1 ? B : (oB ? view(sh, B, g.mc, g.mr, j0, 0, w, k, es) : view(sh, B, g.mc, g.mr, 0, j0, k, w, es));
+        const LocalShape Lj = local_shape(sh, Cj, g.mc, g.mr);
         DM Ap, Bp;
         const DM A1 = oA ? view(sh, A, g.mc, g.mr, k0, 0, kb, m, es) : view(sh, A, g.mc, g.mr, 0, k0, m, kb, es);
-        const DM B1 = oB ? view(sh, B, g.mc, g.mr, 0, k0, n, kb, es) : view(sh, B, g.mc, g.mr, k0, 0, kb, n, es);
+        const DM B1 = oB ? view(sh, Bj, g.mc, g.mr, 0, k0, w, kb, es) : view(sh, Bj, g.mc, g.mr, k0, 0, kb, w, es);
         if (overlap && step >= 2) cudaStreamWaitEvent(cs, g.ev_panel_free[buf], 0);
         if (ce) {
-            if (gather_panels_ce<T>(g, A, B, C, k0, kb, nb, buf, cs, Ap, Bp)) return 1;
+            if (gather_panels_ce<T>(g, A, Bj, Cj, k0, kb, nb, buf, cs, Ap, Bp)) return 1;
         } else if (direct) {
             // panels live in peer-mapped regions: every owner stores its columns straight into every reader's panel
-            Ap.height = m; Ap.width = kb; Ap.colDist = MC; Ap.rowDist = STAR; Ap.colAlign = C.colAlign;
-            Bp.height = n; Bp.width = kb; Bp.colDist = MR; Bp.rowDist = STAR; Bp.colAlign = C.rowAlign;
+            Ap.height = m; Ap.width = kb; Ap.colDist = MC; Ap.rowDist = STAR; Ap.colAlign = Cj.colAlign;
+            Bp.height = w; Bp.width = kb; Bp.colDist = MR; Bp.rowDist = STAR; Bp.colAlign = Cj.rowAlign;
             if (redistribute_direct<T>(g, A1, Ap, oA != 0, 4 + buf, nb, cs)) return 1;
             if (redistribute_direct<T>(g, B1, Bp, oB == 0, 6 + buf, nb, cs)) return 1;
         } else {
-            if (make_tmp<T>(g, g.panel[buf], m, nb, MC, STAR, C.colAlign, 0, Ap)) return 1;
-            if (make_tmp<T>(g, g.panel[2 + buf], n, nb, MR, STAR, C.rowAlign, 0, Bp)) return 1;
+            if (make_tmp<T>(g, g.panel[buf], m, nb, MC, STAR, Cj.colAlign, 0, Ap)) return 1;
+            if (make_tmp<T>(g, g.panel[2 + buf], w, nb, MR, STAR, Cj.rowAlign, 0, Bp)) return 1;
             Ap.width = kb;
             Bp.width = kb;
             if (redistribute<T>(g, A1, Ap, oA != 0, 0, cs)) return 1;
@@ -429,16 +421,47 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
             cudaEventRecord(g.ev_panel_ready[buf], cs);
             cudaStreamWaitEvent(s, g.ev_panel_ready[buf], 0);
         }
-        if (local_update<T>(g, tri, 0, ce ? 0 : 1, Lc, kb, alpha, static_cast<const T*>(Ap.buf), Ap.ldim,
-                            static_cast<const T*>(Bp.buf), Bp.ldim, k0 == 0 ? beta : T(1), static_cast<T*>(C.buf), C.ldim, s,
+        if (local_update<T>(g, tri, 0, ce ? 0 : 1, Lj, kb, alpha, static_cast<const T*>(Ap.buf), Ap.ldim,
+                            static_cast<const T*>(Bp.buf), Bp.ldim, k0 == 0 ? beta : T(1), static_cast<T*>(Cj.buf), Cj.ldim, s,
                             (overlap && !ce) ? g.sm_reserve : 0))
             return 1;
         if (overlap) cudaEventRecord(g.ev_panel_free[buf], s);
         // tell the panel's writers it has been consumed (ordered after the GEMM that read it)
         if (direct && (g.world->push_close(4 + buf, s) || g.world->push_close(6 + buf, s))) return 1;
+        if (p + 1 == npanels && download_block(j, Cj, Lj)) return 1;
     }
     return 0;
 }
+
+// ---- SUMMA-A / SUMMA-B / SUMMA-Dot: software pipeline ------------------------------------------------------------------
+// Each panel is  gather (moving operand's panel)  ->  local product  ->  reduce-scatter into C's panel.  The reference runs
+// the three one after the other on one stream (NN.hpp:107-206, 244-287, 792-841).  Here, on more than one rank, they are
+// three stages on three streams with double-buffered temporaries: while panel i is multiplied, panel i+1 is being gathered
+// (comm stream 0, exchange slots 0/1) and panel i-1's partial result is being reduced into C (comm stream 1, slots 2/3).
+// The local GEMM leaves sm_reserve SMs to the pack / reduce kernels.  hyd_grid_set_overlap(g, 0, .) turns it off.
+struct Pipe {
+    Grid& g; cudaStream_t s, cs, rs; bool on;
+    Pipe(Grid& g_, cudaStream_t s_, bool want) : g(g_), s(s_), cs(s_), rs(s_), on(want) {
+        if (!on) return;
+        if (ensure_engine(g)) { on = false; return; }
+        for (cudaEvent_t& e : g.ev_pipe) if (!e) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+        cs = g.comm_stream[0];
+        rs = g.comm_stream[1];
+        cudaEventRecord(g.ev_fork, s);
+        cudaStreamWaitEvent(cs, g.ev_fork, 0);
+        cudaStreamWaitEvent(rs, g.ev_fork, 0);
+    }
+    enum { IN_READY = 0, IN_FREE = 2, OUT_READY = 4, OUT_FREE = 6 };
+    void signal(int what, int buf, cudaStream_t on_stream) { if (on) cudaEventRecord(g.ev_pipe[what + buf], on_stream); }
+    void await(int what, int buf, cudaStream_t on_stream) { if (on) cudaStreamWaitEvent(on_stream, g.ev_pipe[what + buf], 0); }
+    int sm_reserve() const { return on ? g.sm_reserve : 0; }
+    // the caller's stream is complete when the last reduces are (every gather has been consumed by a GEMM on s already)
+    void join() {
+        if (!on) return;
+        cudaEventRecord(g.ev_join, rs);
+        cudaStreamWaitEvent(s, g.ev_join, 0);
+    }
+};
 
 // ---- SUMMA-A (stationary A): panels over n, reduce over the comm A's k-dimension lives on ----
 template <typename T>
@@ -447,27 +470,39 @@ int summa_a(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
     const GridShape& sh = g.shape;
     const LocalShape La = local_shape(sh, A, g.mc, g.mr);
     const int es = sizeof(T);
-    for (i64 n0 = 0; n0 < n; n0 += nb) {
+    Pipe pipe(g, s, sh.size() > 1 && g.overlap != 0 && n > nb);
+    i64 step = 0;
+    for (i64 n0 = 0; n0 < n; n0 += nb, ++step) {
         const i64 w = std::min(nb, n - n0);
+        const int buf = pipe.on ? (int)(step & 1) : 0;
         // op(B)(:, n0:n0+w) is k x w; gather it with k distributed like A's k-dimension
         DM Bp, D1;
         const int kd = oA ? MC : MR;                     // where A's k index lives
         const int ka = oA ? A.colAlign : A.rowAlign;
-        if (make_tmp<T>(g, g.panel[0], k, w, kd, STAR, ka, 0, Bp)) return 1;
+        if (step >= 2) pipe.await(Pipe::IN_FREE, buf, pipe.cs);
+        if (make_tmp<T>(g, g.panel[buf], k, w, kd, STAR, ka, 0, Bp)) return 1;
         const DM B1 = oB ? view(sh, B, g.mc, g.mr, n0, 0, w, k, es) : view(sh, B, g.mc, g.mr, 0, n0, k, w, es);
-        if (redistribute<T>(g, B1, Bp, oB != 0, 0, s)) return 1;
+        if (redistribute<T>(g, B1, Bp, oB != 0, buf, pipe.cs)) return 1;
+        pipe.signal(Pipe::IN_READY, buf, pipe.cs);
+        pipe.await(Pipe::IN_READY, buf, s);
+        if (step >= 2) pipe.await(Pipe::OUT_FREE, buf, s);
         // D1 = alpha op(A_loc) Bp_loc : m_loc x w, [MC,*] (oA = N) or [MR,*] (oA = T), partial over the other comm
         const int md = oA ? MR : MC;
         const int ma = oA ? A.rowAlign : A.colAlign;
-        if (make_tmp<T>(g, g.panel[1], m, w, md, STAR, ma, 0, D1)) return 1;
+        if (make_tmp<T>(g, g.panel[2 + buf], m, w, md, STAR, ma, 0, D1)) return 1;
         const i64 mloc = oA ? La.lw : La.lh, kloc = oA ? La.lh : La.lw;
         if (lgemm<T>(g, oA, 0, mloc, w, kloc, alpha, static_cast<const T*>(A.buf), A.ldim, static_cast<const T*>(Bp.buf),
-                     Bp.ldim, T(0), static_cast<T*>(D1.buf), D1.ldim, s, 0))
+                     Bp.ldim, T(0), static_cast<T*>(D1.buf), D1.ldim, s, pipe.sm_reserve()))
             return 1;
         if (kloc == 0 && scale_local<T>(mloc, w, T(0), static_cast<T*>(D1.buf), D1.ldim, s)) return 1;
+        pipe.signal(Pipe::IN_FREE, buf, s);
+        pipe.signal(Pipe::OUT_READY, buf, s);
+        pipe.await(Pipe::OUT_READY, buf, pipe.rs);
         const DM C1 = view(sh, C, g.mc, g.mr, 0, n0, m, w, es);
-        if (reduce_into<T>(g, T(1), D1, C1, false, 2, s)) return 1;
+        if (reduce_into<T>(g, T(1), D1, C1, false, 2 + buf, pipe.rs)) return 1;
+        pipe.signal(Pipe::OUT_FREE, buf, pipe.rs);
     }
+    pipe.join();
     return 0;
 }
 
@@ -478,27 +513,39 @@ int summa_b(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
     const GridShape& sh = g.shape;
     const LocalShape Lb = local_shape(sh, B, g.mc, g.mr);
     const int es = sizeof(T);
-    for (i64 m0 = 0; m0 < m; m0 += nb) {
+    Pipe pipe(g, s, sh.size() > 1 && g.overlap != 0 && m > nb);
+    i64 step = 0;
+    for (i64 m0 = 0; m0 < m; m0 += nb, ++step) {
         const i64 h = std::min(nb, m - m0);
+        const int buf = pipe.on ? (int)(step & 1) : 0;
         // (op(A)(m0:m0+h, :))^T is k x h; gather it with k distributed like B's k-dimension
         DM Ap, D1t;
         const int kd = oB ? MR : MC;
         const int ka = oB ? B.rowAlign : B.colAlign;
-        if (make_tmp<T>(g, g.panel[0], k, h, kd, STAR, ka, 0, Ap)) return 1;
+        if (step >= 2) pipe.await(Pipe::IN_FREE, buf, pipe.cs);
+        if (make_tmp<T>(g, g.panel[buf], k, h, kd, STAR, ka, 0, Ap)) return 1;
         const DM A1 = oA ? view(sh, A, g.mc, g.mr, 0, m0, k, h, es) : view(sh, A, g.mc, g.mr, m0, 0, h, k, es);
-        if (redistribute<T>(g, A1, Ap, oA == 0, 0, s)) return 1;
+        if (redistribute<T>(g, A1, Ap, oA == 0, buf, pipe.cs)) return 1;
+        pipe.signal(Pipe::IN_READY, buf, pipe.cs);
+        pipe.await(Pipe::IN_READY, buf, s);
+        if (step >= 2) pipe.await(Pipe::OUT_FREE, buf, s);
         // D1t = alpha op(B_loc)^T Ap_loc : n_loc x h, [MR,*] (oB = N) or [MC,*] (oB = T)
         const int nd = oB ? MC : MR;
         const int na = oB ? B.colAlign : B.rowAlign;
-        if (make_tmp<T>(g, g.panel[1], n, h, nd, STAR, na, 0, D1t)) return 1;
+        if (make_tmp<T>(g, g.panel[2 + buf], n, h, nd, STAR, na, 0, D1t)) return 1;
         const i64 nloc = oB ? Lb.lh : Lb.lw, kloc = oB ? Lb.lw : Lb.lh;
         if (lgemm<T>(g, oB ? 0 : 1, 0, nloc, h, kloc, alpha, static_cast<const T*>(B.buf), B.ldim,
-                     static_cast<const T*>(Ap.buf), Ap.ldim, T(0), static_cast<T*>(D1t.buf), D1t.ldim, s, 0))
+                     static_cast<const T*>(Ap.buf), Ap.ldim, T(0), static_cast<T*>(D1t.buf), D1t.ldim, s, pipe.sm_reserve()))
             return 1;
         if (kloc == 0 && scale_local<T>(nloc, h, T(0), static_cast<T*>(D1t.buf), D1t.ldim, s)) return 1;
+        pipe.signal(Pipe::IN_FREE, buf, s);
+        pipe.signal(Pipe::OUT_READY, buf, s);
+        pipe.await(Pipe::OUT_READY, buf, pipe.rs);
         const DM C1 = view(sh, C, g.mc, g.mr, m0, 0, h, n, es);
-        if (reduce_into<T>(g, T(1), D1t, C1, true, 2, s)) return 1;
+        if (reduce_into<T>(g, T(1), D1t, C1, true, 2 + buf, pipe.rs)) return 1;
+        pipe.signal(Pipe::OUT_FREE, buf, pipe.rs);
     }
+    pipe.join();
     return 0;
 }
 
@@ -511,34 +558,38 @@ int summa_dot(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A
     // operands must be  A: [*,VC] (N) / [VC,*] (T),  B: [VC,*] (N) / [*,VC] (T), B aligned to A (proxy, Proxy.hpp:160-260)
     const LocalShape La = local_shape(sh, A, g.mc, g.mr);
     const i64 kloc = oA ? La.lh : La.lw;
+    // two stages: tile i+1 is multiplied while tile i's [*,*] partial result is reduced into C
+    Pipe pipe(g, s, sh.size() > 1 && g.overlap != 0 && (m > blockM || n > blockN));
+    i64 step = 0;
     for (i64 i0 = 0; i0 < m; i0 += blockM) {
         const i64 mb = std::min(blockM, m - i0);
-        for (i64 j0 = 0; j0 < n; j0 += blockN) {
+        for (i64 j0 = 0; j0 < n; j0 += blockN, ++step) {
             const i64 nbk = std::min(blockN, n - j0);
+            const int buf = pipe.on ? (int)(step & 1) : 0;
             DM C11;
-            if (make_tmp<T>(g, g.panel[0], mb, nbk, STAR, STAR, 0, 0, C11)) return 1;
+            if (step >= 2) pipe.await(Pipe::OUT_FREE, buf, s);
+            if (make_tmp<T>(g, g.panel[buf], mb, nbk, STAR, STAR, 0, 0, C11)) return 1;
             const T* a = static_cast<const T*>(A.buf) + (oA ? i0 * A.ldim : i0);
             const T* b = static_cast<const T*>(B.buf) + (oB ? j0 : j0 * B.ldim);
             if (lgemm<T>(g, oA, oB, mb, nbk, kloc, alpha, a, A.ldim, b, B.ldim, T(0), static_cast<T*>(C11.buf), C11.ldim,
-                         s, 0))
+                         s, pipe.sm_reserve()))
                 return 1;
             if (kloc == 0 && scale_local<T>(mb, nbk, T(0), static_cast<T*>(C11.buf), C11.ldim, s)) return 1;
+            pipe.signal(Pipe::OUT_READY, buf, s);
+            pipe.await(Pipe::OUT_READY, buf, pipe.rs);
             const DM Cv = view(sh, C, g.mc, g.mr, i0, j0, mb, nbk, es);
-            if (reduce_into<T>(g, T(1), C11, Cv, false, 2, s)) return 1;
+            if (reduce_into<T>(g, T(1), C11, Cv, false, 2 + buf, pipe.rs)) return 1;
+            pipe.signal(Pipe::OUT_FREE, buf, pipe.rs);
         }
     }
+    pipe.join();
     return 0;
 }
 
-struct TempPool {
-    std::vector<void*> bufs;
-    ~TempPool() { for (void* p : bufs) cudaFree(p); }
-};
-
 // read-proxy: return `a` itself if it already has the wanted distribution (and alignment when constrained),
-// else a freshly redistributed temporary (reference: DistMatrixReadProxy, include/El/core/Proxy.hpp:174-260)
+// else a redistributed temporary from the grid's pool (reference: DistMatrixReadProxy, include/El/core/Proxy.hpp:174-260)
 template <typename T>
-int read_proxy(Grid& g, TempPool& pool, const DM& a, int cd, int rd, bool colCon, int ca, bool rowCon, int ra, DM& out,
+int read_proxy(Grid& g, TempScope& pool, const DM& a, int cd, int rd, bool colCon, int ca, bool rowCon, int ra, DM& out,
                cudaStream_t s) {
     const bool ok = a.colDist == cd && a.rowDist == rd && (!colCon || a.colAlign == ca) && (!rowCon || a.rowAlign == ra);
     if (ok) { out = a; return 0; }
@@ -550,10 +601,8 @@ int read_proxy(Grid& g, TempPool& pool, const DM& a, int cd, int rd, bool colCon
     out.rowAlign = rowCon ? ra : adopted_align(g.shape, a.rowDist, a.rowAlign, rd);
     const LocalShape L = local_shape(g.shape, out, g.mc, g.mr);
     out.ldim = pad_ld(L.lh, sizeof(T));
-    void* p = nullptr;
-    if (check_cuda(cudaMalloc(&p, (size_t)(out.ldim * std::max<i64>(L.lw, 1)) * sizeof(T)), "proxy cudaMalloc")) return 1;
-    pool.bufs.push_back(p);
-    out.buf = p;
+    out.buf = pool.take((size_t)(out.ldim * std::max<i64>(L.lw, 1)) * sizeof(T));   // pooled: no allocation in steady state
+    if (!out.buf) return 1;
     return redistribute<T>(g, a, out, false, 3, s);
 }
 
@@ -561,8 +610,7 @@ int read_proxy(Grid& g, TempPool& pool, const DM& a, int cd, int rd, bool colCon
 
 template <typename T>
 int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A0, const DM& B0, T beta, const DM& C0,
-              i64 blocksize, cudaStream_t s, const void* hostA, i64 hostLdA, const void* hostB, i64 hostLdB, void* hostC,
-              i64 hostLdC, int* c_downloaded) {
+              i64 blocksize, cudaStream_t s, HostImages* host) {
     oA = oA ? 1 : 0;
     oB = oB ? 1 : 0;
     const i64 m = C0.height, n = C0.width;
@@ -574,26 +622,33 @@ int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A0, const DM&
     if (alg == 5) return set_error("hyd_gemm: GEMM_CANNON is CPU-only in the reference (NN.hpp:20-103) and not provided");
     if (alg < 0 || alg > 5) return set_error("hyd_gemm: unsupported Gemm option");
     if (alg == 0) alg = gemm_default_alg(m, n, k);   // GEMM_DEFAULT heuristic, NN.hpp:910-925 (identical in NT/TN/TT)
-    TempPool pool;
+    TempScope pool(g, s);
     const LocalShape Lc0 = local_shape(g.shape, C0, g.mc, g.mr);
     if (m == 0 || n == 0) return 0;
     // host-resident A/B (hyd_gemm_host_*): SUMMA-C on [MC,MR] operands streams them panel by panel under the
     // GEMMs; every other path uploads both blocks first.
-    // HYD_HOST_CBLOCKS = n > 1: column-blocked host path on a 1x1 grid (summa_c_host_blocked); default 1 = whole-C download
-    static const int cblocks_env = getenv("HYD_HOST_CBLOCKS") ? std::max(1, atoi(getenv("HYD_HOST_CBLOCKS"))) : 1;
-    HostOperands ho{hostA, hostLdA, hostB, hostLdB, hostC, hostLdC, cblocks_env};
-    if (c_downloaded) *c_downloaded = 0;
-    const bool stream_ops = hostA && hostB && alg == 3 && k > 0 && A0.colDist == MC && A0.rowDist == MR &&
+    HostOperands ho{host ? host->A : nullptr, host ? host->lda : 0, host ? host->B : nullptr, host ? host->ldb : 0,
+                    host ? host->C : nullptr, host ? host->ldc : 0, g.host_cblocks, false};
+    if (host) host->c_downloaded = 0;
+    // Decided from GLOBAL facts only (the call is a host call, the algorithm, k, the distributions): a rank whose local
+    // block of A or B is empty may pass a NULL host pointer (hydrogen_b200.h: buf may be NULL for an empty block) and must
+    // still take the same path -- same panel schedule, same push rounds -- as every other rank.
+    const bool stream_ops = host && alg == 3 && k > 0 && A0.colDist == MC && A0.rowDist == MR &&
                             B0.colDist == MC && B0.rowDist == MR;
-    if (hostA && hostB && !stream_ops) {
-        if (upload_k_slice<T>(g.shape, A0, g.mc, g.mr, false, 0, A0.width, hostA, hostLdA, s)) return 1;
-        if (upload_k_slice<T>(g.shape, B0, g.mc, g.mr, false, 0, B0.width, hostB, hostLdB, s)) return 1;
+    if (host && !stream_ops) {   // each operand on its own; an empty local block uploads nothing
+        if (upload_rect<T>(g.shape, A0, g.mc, g.mr, 0, 0, A0.height, A0.width, host->A, host->lda, s)) return 1;
+        if (upload_rect<T>(g.shape, B0, g.mc, g.mr, 0, 0, B0.height, B0.width, host->B, host->ldb, s)) return 1;
     }
     // Scale(beta, C) (reference Gemm.cpp:287).  SUMMA-C on a C that needs no proxy folds it into the first panel's
     // epilogue; every other path (and k == 0) scales first, as the reference does.
     const bool fuse_beta = (alg == 3) && k > 0 && C0.colDist == MC && C0.rowDist == MR;
     if (!fuse_beta && scale_local<T>(Lc0.lh, Lc0.lw, beta, static_cast<T*>(C0.buf), C0.ldim, s)) return 1;
     DM A, B, C;
+    static const char* const kRegion[4][4] = {{"SUMMA.NNA", "SUMMA.NNB", "SUMMA.NNC", "SUMMA.NNDot"},
+                                              {"SUMMA.NTA", "SUMMA.NTB", "SUMMA.NTC", "SUMMA.NTDot"},
+                                              {"SUMMA.TNA", "SUMMA.TNB", "SUMMA.TNC", "SUMMA.TNDot"},
+                                              {"SUMMA.TTA", "SUMMA.TTB", "SUMMA.TTC", "SUMMA.TTDot"}};
+    NvtxRange nvtx(kRegion[2 * oA + oB][alg - 1]);
     if (read_proxy<T>(g, pool, C0, MC, MR, false, 0, false, 0, C, s)) return 1;
     int rc;
     if (alg == 4) {
@@ -616,21 +671,18 @@ int dist_gemm(Grid& g, int oA, int oB, int alg, T alpha, const DM& A0, const DM&
         if (alg == 1) rc = summa_a<T>(g, oA, oB, m, n, k, alpha, A, B, C, blocksize, s);
         else if (alg == 2) rc = summa_b<T>(g, oA, oB, m, n, k, alpha, A, B, C, blocksize, s);
         else {
-            // the blocked host path writes C's blocks to the host itself; it applies when nothing sits between the caller's
-            // blocks and the engine (no proxies) on a 1x1 grid with a C wide enough to split
-            const bool blocked = stream_ops && hostC && cblocks_env > 1 && g.shape.size() == 1 && C.buf == C0.buf &&
-                                 A.buf == A0.buf && B.buf == B0.buf && Lc0.lh > 0 && Lc0.lw >= 1024 && fuse_beta;
-            if (!blocked) ho.C = nullptr;
+            // the host path writes C's column blocks back itself when nothing sits between the caller's blocks and the
+            // engine: A, B, C all [MC,MR] (stream_ops, fuse_beta), hence no proxies -- global facts, the same on every rank
+            ho.download = stream_ops && fuse_beta;
             rc = summa_c<T>(g, oA, oB, m, n, k, alpha, A, B, fuse_beta ? beta : T(1), C, blocksize, s, stream_ops ? &ho : nullptr);
-            if (!rc && blocked && c_downloaded) *c_downloaded = 1;
+            if (!rc && ho.download) host->c_downloaded = 1;
         }
     }
     if (rc) return rc;
     if (C.buf != C0.buf) {  // write-back half of the ReadWrite proxy
         if (redistribute<T>(g, C, C0, false, 3, s)) return 1;
     }
-    if (!pool.bufs.empty() && check_cuda(cudaStreamSynchronize(s), "proxy sync")) return 1;
-    return 0;
+    return 0;   // proxies go back to the pool with an event on s (TempScope): no host synchronisation
 }
 
 // El::Trrk(uplo, orientA, orientB, alpha, A, B, beta, C) -- src/blas_like/level3/Trrk.cpp:98-115 -> ScaleTrapezoid(beta, uplo, C),
@@ -654,7 +706,7 @@ int dist_trrk(Grid& g, int uplo, int oA, int oB, T alpha, const DM& A0, const DM
                                             nullptr, 0, static_cast<T*>(C0.buf), C0.ldim, s))
         return 1;
     if (k == 0) return 0;
-    TempPool pool;
+    TempScope pool(g, s);
     DM A, B, C;
     if (read_proxy<T>(g, pool, C0, MC, MR, false, 0, false, 0, C, s)) return 1;
     if ((double)k > 10.0 * (double)n) {
@@ -665,22 +717,19 @@ int dist_trrk(Grid& g, int uplo, int oA, int oB, T alpha, const DM& A0, const DM
         const LocalShape Lc = local_shape(g.shape, C, g.mc, g.mr);
         DM Z = C;
         Z.ldim = pad_ld(Lc.lh, sizeof(T));
-        void* z = nullptr;
-        if (check_cuda(cudaMalloc(&z, (size_t)(Z.ldim * std::max<i64>(Lc.lw, 1)) * sizeof(T)), "Trrk (Dot) cudaMalloc")) return 1;
-        pool.bufs.push_back(z);
-        Z.buf = z;
-        if (dist_gemm<T>(g, oA, oB, 4, alpha, A0, B0, T(0), Z, blocksize, s, nullptr, 0, nullptr, 0, nullptr, 0, nullptr)) return 1;
+        Z.buf = pool.take((size_t)(Z.ldim * std::max<i64>(Lc.lw, 1)) * sizeof(T));
+        if (!Z.buf) return 1;
+        if (dist_gemm<T>(g, oA, oB, 4, alpha, A0, B0, T(0), Z, blocksize, s, nullptr)) return 1;
         if (trapezoid_local<T>(1, uplo, Lc.lh, Lc.lw, Lc.colShift, Lc.colStride, Lc.rowShift, Lc.rowStride, 0, T(1),
                                static_cast<const T*>(Z.buf), Z.ldim, static_cast<T*>(C.buf), C.ldim, s))
             return 1;
         if (C.buf != C0.buf && redistribute<T>(g, C, C0, false, 3, s)) return 1;
-        return check_cuda(cudaStreamSynchronize(s), "Trrk (Dot) sync");
+        return 0;
     }
     if (read_proxy<T>(g, pool, A0, MC, MR, false, 0, false, 0, A, s)) return 1;
     if (read_proxy<T>(g, pool, B0, MC, MR, false, 0, false, 0, B, s)) return 1;
     if (summa_c<T>(g, oA, oB, n, n, k, alpha, A, B, T(1), C, blocksize, s, nullptr, uplo)) return 1;
     if (C.buf != C0.buf && redistribute<T>(g, C, C0, false, 3, s)) return 1;
-    if (!pool.bufs.empty() && check_cuda(cudaStreamSynchronize(s), "proxy sync")) return 1;
     return 0;
 }
 
@@ -690,10 +739,20 @@ template <typename T>
 int dist_trapezoid(Grid& g, int op, int uplo, T alpha, const DM* X, const DM& Y, i64 offset, cudaStream_t s) {
     if (uplo != 0 && uplo != 1) return set_error("trapezoid: uplo must be LOWER (0) or UPPER (1)");
     const LocalShape L = local_shape(g.shape, Y, g.mc, g.mr);
+    TempScope pool(g, s);
+    DM Xt;
     if (X) {
         if (X->height != Y.height || X->width != Y.width) return set_error("AxpyTrapezoid: nonconformal matrices");
-        if (X->colDist != Y.colDist || X->rowDist != Y.rowDist || X->colAlign != Y.colAlign || X->rowAlign != Y.rowAlign)
-            return set_error("AxpyTrapezoid: X and Y must share distribution and alignments");
+        if (X->colDist != Y.colDist || X->rowDist != Y.rowDist || X->colAlign != Y.colAlign || X->rowAlign != Y.rowAlign) {
+            // the reference's else-branch (AxpyTrapezoid.hpp:87-98): XCopy(Y.Grid()) aligned with Y, XCopy = X, then the
+            // local update.  Collective over the grid (every rank sees the same metadata).
+            Xt = Y;
+            Xt.ldim = pad_ld(L.lh, sizeof(T));
+            Xt.buf = pool.take((size_t)(Xt.ldim * std::max<i64>(L.lw, 1)) * sizeof(T));
+            if (!Xt.buf) return 1;
+            if (redistribute<T>(g, *X, Xt, false, 3, s)) return 1;
+            X = &Xt;
+        }
     }
     return trapezoid_local<T>(op, uplo, L.lh, L.lw, L.colShift, L.colStride, L.rowShift, L.rowStride, offset, alpha,
                               X ? static_cast<const T*>(X->buf) : nullptr, X ? X->ldim : 0, static_cast<T*>(Y.buf), Y.ldim, s);
@@ -711,18 +770,14 @@ int dist_make_symmetric(Grid& g, int uplo, const DM& A, cudaStream_t s) {
     if (trapezoid_local<T>(3, uplo, L.lh, L.lw, L.colShift, L.colStride, L.rowShift, L.rowStride, 0, T(0), nullptr, 0,
                            static_cast<T*>(A.buf), A.ldim, s))
         return 1;
-    TempPool pool;
+    TempScope pool(g, s);
     DM At = A;
     At.ldim = pad_ld(L.lh, sizeof(T));
-    void* p = nullptr;
-    if (check_cuda(cudaMalloc(&p, (size_t)(At.ldim * std::max<i64>(L.lw, 1)) * sizeof(T)), "MakeSymmetric cudaMalloc")) return 1;
-    pool.bufs.push_back(p);
-    At.buf = p;
+    At.buf = pool.take((size_t)(At.ldim * std::max<i64>(L.lw, 1)) * sizeof(T));
+    if (!At.buf) return 1;
     if (redistribute<T>(g, A, At, true, 3, s)) return 1;
-    if (trapezoid_local<T>(1, 1 - uplo, L.lh, L.lw, L.colShift, L.colStride, L.rowShift, L.rowStride, uplo == 0 ? 1 : -1, T(1),
-                           static_cast<const T*>(At.buf), At.ldim, static_cast<T*>(A.buf), A.ldim, s))
-        return 1;
-    return check_cuda(cudaStreamSynchronize(s), "MakeSymmetric sync");
+    return trapezoid_local<T>(1, 1 - uplo, L.lh, L.lw, L.colShift, L.colStride, L.rowShift, L.rowStride, uplo == 0 ? 1 : -1, T(1),
+                              static_cast<const T*>(At.buf), At.ldim, static_cast<T*>(A.buf), A.ldim, s);
 }
 // El::Symm(side, uplo, alpha, A, B, beta, C) -- src/blas_like/level3/Symm.cpp:56-80 (C *= beta; symm::{LL,LU,RL,RU}): C := alpha A B +
 // beta C (LEFT) or alpha B A + beta C (RIGHT) with A symmetric and only its `uplo` triangle read.  The reference reads the
@@ -738,7 +793,7 @@ int dist_symm(Grid& g, int side, int uplo, T alpha, const DM& A0, const DM& B0, 
     if (A0.height != na || A0.width != na || B0.height != m || B0.width != n)
         return set_error("hyd_symm: nonconformal matrices: A %lldx%lld, B %lldx%lld, C %lldx%lld", A0.height, A0.width, B0.height,
                          B0.width, m, n);
-    TempPool pool;
+    TempScope pool(g, s);
     DM Ah;
     Ah.height = na; Ah.width = na; Ah.colDist = MC; Ah.rowDist = MR;
     const bool mcmr = A0.colDist == MC && A0.rowDist == MR;
@@ -746,18 +801,14 @@ int dist_symm(Grid& g, int side, int uplo, T alpha, const DM& A0, const DM& B0, 
     Ah.rowAlign = mcmr ? A0.rowAlign : 0;
     const LocalShape L = local_shape(g.shape, Ah, g.mc, g.mr);
     Ah.ldim = pad_ld(L.lh, sizeof(T));
-    void* p = nullptr;
-    if (check_cuda(cudaMalloc(&p, (size_t)(Ah.ldim * std::max<i64>(L.lw, 1)) * sizeof(T)), "Symm cudaMalloc")) return 1;
-    pool.bufs.push_back(p);
-    Ah.buf = p;
+    Ah.buf = pool.take((size_t)(Ah.ldim * std::max<i64>(L.lw, 1)) * sizeof(T));
+    if (!Ah.buf) return 1;
     if (na > 0) {
         if (redistribute<T>(g, A0, Ah, false, 3, s)) return 1;
         if (dist_make_symmetric<T>(g, uplo, Ah, s)) return 1;
     }
-    const int rc = side == 0 ? dist_gemm<T>(g, 0, 0, 0, alpha, Ah, B0, beta, C0, blocksize, s, nullptr, 0, nullptr, 0, nullptr, 0, nullptr)
-                             : dist_gemm<T>(g, 0, 0, 0, alpha, B0, Ah, beta, C0, blocksize, s, nullptr, 0, nullptr, 0, nullptr, 0, nullptr);
-    if (rc) return rc;
-    return check_cuda(cudaStreamSynchronize(s), "Symm sync");
+    return side == 0 ? dist_gemm<T>(g, 0, 0, 0, alpha, Ah, B0, beta, C0, blocksize, s, nullptr)
+                     : dist_gemm<T>(g, 0, 0, 0, alpha, B0, Ah, beta, C0, blocksize, s, nullptr);
 }
 template int dist_symm<double>(Grid&, int, int, double, const DM&, const DM&, double, const DM&, i64, cudaStream_t);
 template int dist_symm<float>(Grid&, int, int, float, const DM&, const DM&, float, const DM&, i64, cudaStream_t);
@@ -769,7 +820,7 @@ template int dist_trrk<double>(Grid&, int, int, int, double, const DM&, const DM
 template int dist_trrk<float>(Grid&, int, int, int, float, const DM&, const DM&, float, const DM&, i64, cudaStream_t);
 template int dist_trapezoid<double>(Grid&, int, int, double, const DM*, const DM&, i64, cudaStream_t);
 template int dist_trapezoid<float>(Grid&, int, int, float, const DM*, const DM&, i64, cudaStream_t);
-template int dist_gemm<double>(Grid&, int, int, int, double, const DM&, const DM&, double, const DM&, i64, cudaStream_t, const void*, i64, const void*, i64, void*, i64, int*);
-template int dist_gemm<float>(Grid&, int, int, int, float, const DM&, const DM&, float, const DM&, i64, cudaStream_t, const void*, i64, const void*, i64, void*, i64, int*);
+template int dist_gemm<double>(Grid&, int, int, int, double, const DM&, const DM&, double, const DM&, i64, cudaStream_t, HostImages*);
+template int dist_gemm<float>(Grid&, int, int, int, float, const DM&, const DM&, float, const DM&, i64, cudaStream_t, HostImages*);
 
 }  // namespace hyd

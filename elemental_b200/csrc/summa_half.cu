@@ -22,13 +22,8 @@ namespace {
 
 inline i64 pad8(i64 lh) { return std::max<i64>(8, (lh + 7) / 8 * 8); }   // 16-byte columns of 2-byte elements
 
-struct Pool {
-    std::vector<void*> bufs;
-    ~Pool() { for (void* p : bufs) cudaFree(p); }
-};
-
 // DistMatrixReadProxy<T,T,MC,MR> (include/El/core/Proxy.hpp:174-260): `a` itself when it is already [MC,MR], else a copy
-int proxy_mcmr(Grid& g, Pool& pool, const DM& a, DM& out, cudaStream_t s) {
+int proxy_mcmr(Grid& g, TempScope& pool, const DM& a, DM& out, cudaStream_t s) {
     if (a.colDist == MC && a.rowDist == MR) { out = a; return 0; }
     out = DM();
     out.height = a.height; out.width = a.width; out.colDist = MC; out.rowDist = MR;
@@ -36,10 +31,8 @@ int proxy_mcmr(Grid& g, Pool& pool, const DM& a, DM& out, cudaStream_t s) {
     out.rowAlign = adopted_align(g.shape, a.rowDist, a.rowAlign, MR);
     const LocalShape L = local_shape(g.shape, out, g.mc, g.mr);
     out.ldim = pad8(L.lh);
-    void* p = nullptr;
-    if (check_cuda(cudaMalloc(&p, (size_t)(out.ldim * std::max<i64>(L.lw, 1)) * 2), "half proxy cudaMalloc")) return 1;
-    pool.bufs.push_back(p);
-    out.buf = p;
+    out.buf = pool.take((size_t)(out.ldim * std::max<i64>(L.lw, 1)) * 2);
+    if (!out.buf) return 1;
     return redistribute<h16>(g, a, out, false, 3, s);
 }
 
@@ -65,7 +58,7 @@ int dist_gemm_half(Grid& g, int bf16, int oA, int oB, int alg, float alpha, cons
     if (alg != 0 && alg != 3) return set_error("hyd_gemm(half): only GEMM_DEFAULT / GEMM_SUMMA_C are provided in half precision");
     if (m == 0 || n == 0) return 0;
     const GridShape& sh = g.shape;
-    Pool pool;
+    TempScope pool(g, s);
     DM A, B, C;
     if (proxy_mcmr(g, pool, C0, C, s) || proxy_mcmr(g, pool, A0, A, s) || proxy_mcmr(g, pool, B0, B, s)) return 1;
     const LocalShape Lc = local_shape(sh, C, g.mc, g.mr);
@@ -100,7 +93,6 @@ int dist_gemm_half(Grid& g, int bf16, int oA, int oB, int alg, float alpha, cons
             return 1;
     }
     if (C.buf != C0.buf && redistribute<h16>(g, C, C0, false, 3, s)) return 1;   // write-back half of the ReadWrite proxy
-    if (!pool.bufs.empty() && check_cuda(cudaStreamSynchronize(s), "half proxy sync")) return 1;
     return 0;
 }
 

@@ -60,8 +60,14 @@ def _stream_ptr(stream=None):
 class World:
     """Communication world: one rank per GPU over NCCL, or P rank-threads on one GPU (tests)."""
 
-    def __init__(self, handle, rank, size, kind):
-        self.h, self.rank, self.size, self.kind = handle, rank, size, kind
+    def __init__(self, handle, rank, size):
+        self.h, self.rank, self.size = handle, rank, size
+
+    @property
+    def kind(self):
+        """The data plane the library actually set up (hyd_world_kind): "nvlink-push(ipc)+nccl", "nccl" (also what a failed
+        IPC mapping falls back to), "local-push" or "local"."""
+        return lib.hyd_world_kind(self.h).decode()
 
     @staticmethod
     def nccl_unique_id():
@@ -73,7 +79,7 @@ class World:
     def nccl(cls, uid, rank, size):
         h = C.c_void_p()
         check(lib.hyd_world_create_nccl(C.c_char_p(uid), rank, size, C.byref(h)))
-        return cls(h, rank, size, "nccl")
+        return cls(h, rank, size)
 
     @classmethod
     def from_torch_distributed(cls):
@@ -88,7 +94,7 @@ class World:
     def local(cls, group, rank):
         h = C.c_void_p()
         check(lib.hyd_world_create_local(group.h, rank, C.byref(h)))
-        return cls(h, rank, group.size, "local")
+        return cls(h, rank, group.size)
 
     @classmethod
     def single(cls):
@@ -142,6 +148,9 @@ class Grid:
 
     def SetOverlap(self, overlap=True, sm_reserve=-1):
         check(lib.hyd_grid_set_overlap(self.h, int(overlap), sm_reserve))
+
+    def SetHostBlocks(self, max_blocks):
+        check(lib.hyd_grid_set_host_blocks(self.h, int(max_blocks)))
 
     def Profile(self, enable=True):
         check(lib.hyd_grid_profile(self.h, int(enable)))
@@ -301,6 +310,24 @@ def TransposeAxpy(alpha, X, Y, stream=None):
     x, y = X.desc(), Y.desc()
     check(getattr(lib, "hyd_axpy_dist_" + _sfx(Y.dtype))(Y.grid.h, _scalar(Y.dtype, alpha), C.byref(x), C.byref(y), 1,
                                                          _stream_ptr(stream)))
+
+
+class MultiSync:
+    """MakeMultiSync(master, others...) (include/hydrogen/SyncInfo.hpp:136-186): on entry the master stream waits for the
+    work enqueued so far on the other streams, on exit the others wait for the master.  No host synchronisation."""
+
+    def __init__(self, master, *others):
+        self.m = _stream_ptr(master)
+        self.n = len(others)
+        self.o = (C.c_void_p * max(1, self.n))(*[_stream_ptr(o).value for o in others])
+
+    def __enter__(self):
+        check(lib.hyd_multisync_begin(self.m, self.o, self.n))
+        return self
+
+    def __exit__(self, *exc):
+        check(lib.hyd_multisync_end(self.m, self.o, self.n))
+        return False
 
 
 def _same_dist(A, B):

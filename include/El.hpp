@@ -17,6 +17,7 @@
 
 #include <cuda_runtime.h>
 #include <cstdint>
+#include <initializer_list>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -64,6 +65,28 @@ inline void PopBlocksizeStack() { detail::blocksizes().pop_back(); }
 
 // ---- SyncInfo<Device::GPU> (include/hydrogen/SyncInfo.hpp:51-60): the stream work is enqueued on ----
 struct SyncInfoGPU { cudaStream_t stream_ = nullptr; };
+
+// ---- MultiSync (include/hydrogen/SyncInfo.hpp:136-186) ----
+// MakeMultiSync(master, others...): on construction the master stream -- the OUTPUT matrix's -- waits for everything already
+// enqueued on the other (input) streams; on destruction the others wait for the master, so an input may be overwritten on
+// its own stream right after the call.  No host synchronisation.  Every distributed operation of this header brackets its
+// C-ABI call with one (as the reference does at Gemm.cpp:117-119, Copy/RowAllGather.hpp:25-28, ...), so matrices produced
+// on different streams can be combined without any explicit fence by the caller.
+class MultiSync {
+public:
+    MultiSync(cudaStream_t master, std::initializer_list<cudaStream_t> others) : master_(master), n_(0) {
+        for (cudaStream_t o : others) if (n_ < 8) others_[n_++] = o;
+        if (hyd_multisync_begin(master_, others_, n_)) throw std::runtime_error(hyd_last_error());
+    }
+    ~MultiSync() { hyd_multisync_end(master_, others_, n_); }
+    MultiSync(const MultiSync&) = delete;
+    MultiSync& operator=(const MultiSync&) = delete;
+    operator SyncInfoGPU() const { SyncInfoGPU si; si.stream_ = master_; return si; }   // usable wherever the master SyncInfo is
+private:
+    cudaStream_t master_;
+    hyd_stream_t others_[8];
+    int n_;
+};
 
 // ---- communicator: one process per GPU over NCCL (or P rank-threads on one GPU for tests) ----
 namespace mpi {
@@ -440,10 +463,12 @@ void Copy(const AbstractDistMatrix<T>& A, AbstractDistMatrix<T>& B) {
         if (A.ColDist() != B.ColDist() || A.RowDist() != B.RowDist() || A.ColAlign() != B.ColAlign() || A.RowAlign() != B.RowAlign())
             LogicError("cross-device B = A needs equal distributions and alignments; redistribute on the GPU side");
         const int kind = A.GetLocalDevice() == Device::CPU ? 0 : 1;
+        MultiSync fence(B.Stream(), {A.Stream()});
         detail::check(hyd_memcopy2d_async(B.desc()->buf, B.LDim(), A.desc()->buf, A.LDim(), A.LocalHeight(), A.LocalWidth(),
                                           (int)sizeof(T), kind, B.Stream()));
         return;
     }
+    MultiSync fence(B.Stream(), {A.Stream()});
     detail::check(detail::Sfx<T>::redist(B.Grid().handle(), A.desc(), B.desc(), 0, B.Stream()));
 }
 // B = A^T (Transpose.hpp:318-356); conjugate is a no-op for real T
@@ -464,18 +489,21 @@ void Transpose(const AbstractDistMatrix<T>& A, AbstractDistMatrix<T>& B, bool /*
         B.AlignAndResize(ca, ra, A.Width(), A.Height(), false, false);
     }
     B.Resize(A.Width(), A.Height());
+    MultiSync fence(B.Stream(), {A.Stream()});
     detail::check(detail::Sfx<T>::redist(B.Grid().handle(), A.desc(), B.desc(), 1, B.Stream()));
 }
 template <typename T>
 void AxpyContract(T alpha, const AbstractDistMatrix<T>& A, AbstractDistMatrix<T>& B) {  // AxpyContract.hpp:483-544
     detail::require_gpu(A, "AxpyContract");
     detail::require_gpu(B, "AxpyContract");
+    MultiSync fence(B.Stream(), {A.Stream()});
     detail::check(detail::Sfx<T>::contract(B.Grid().handle(), alpha, A.desc(), B.desc(), 0, B.Stream()));
 }
 template <typename T>
 void TransposeAxpyContract(T alpha, const AbstractDistMatrix<T>& A, AbstractDistMatrix<T>& B, bool = false) {  // TransposeAxpyContract.hpp:14-48
     detail::require_gpu(A, "TransposeAxpyContract");
     detail::require_gpu(B, "TransposeAxpyContract");
+    MultiSync fence(B.Stream(), {A.Stream()});
     detail::check(detail::Sfx<T>::contract(B.Grid().handle(), alpha, A.desc(), B.desc(), 1, B.Stream()));
 }
 
@@ -497,6 +525,7 @@ template <typename T>
 void Gemm(Orientation orientA, Orientation orientB, T alpha, const AbstractDistMatrix<T>& A, const AbstractDistMatrix<T>& B,
           T beta, AbstractDistMatrix<T>& C, GemmAlgorithm alg = GEMM_DEFAULT) {
     const int ncpu = (A.GetLocalDevice() == Device::CPU) + (B.GetLocalDevice() == Device::CPU) + (C.GetLocalDevice() == Device::CPU);
+    MultiSync fence(C.Stream(), {A.Stream(), B.Stream()});   // Gemm.cpp:117-119
     if (ncpu == 3) {
         // all three blocks in (pinned) host memory: the library uploads them panel by panel under the GEMMs and brings C back
         // (what a CPU-resident caller of the reference does with three cross-device assignments around Gemm); returns synchronised
@@ -525,6 +554,7 @@ void Trrk(UpperOrLower uplo, Orientation orientA, Orientation orientB, T alpha, 
     detail::require_gpu(A, "Trrk");
     detail::require_gpu(B, "Trrk");
     detail::require_gpu(C, "Trrk");
+    MultiSync fence(C.Stream(), {A.Stream(), B.Stream()});
     detail::check(detail::Sfx<T>::trrk(C.Grid().handle(), uplo, orientA, orientB, alpha, A.desc(), B.desc(), beta, C.desc(), Blocksize(),
                                        C.Stream()));
 }
@@ -534,6 +564,7 @@ void Syrk(UpperOrLower uplo, Orientation orientation, T alpha, const AbstractDis
           bool /*conjugate*/ = false) {
     detail::require_gpu(A, "Syrk");
     detail::require_gpu(C, "Syrk");
+    MultiSync fence(C.Stream(), {A.Stream()});
     detail::check(detail::Sfx<T>::syrk(C.Grid().handle(), uplo, orientation, alpha, A.desc(), beta, C.desc(), Blocksize(), C.Stream()));
 }
 // C resized to n x n and zeroed first (Syrk.cpp:92-103)
@@ -564,6 +595,7 @@ template <typename T>
 void AxpyTrapezoid(UpperOrLower uplo, T alpha, const AbstractDistMatrix<T>& X, AbstractDistMatrix<T>& Y, Int offset = 0) {
     detail::require_gpu(X, "AxpyTrapezoid");
     detail::require_gpu(Y, "AxpyTrapezoid");
+    MultiSync fence(Y.Stream(), {X.Stream()});
     detail::check(detail::Sfx<T>::axpy_trap(Y.Grid().handle(), uplo, alpha, X.desc(), Y.desc(), offset, Y.Stream()));
 }
 template <typename T>
@@ -586,6 +618,7 @@ void Symm(LeftOrRight side, UpperOrLower uplo, T alpha, const AbstractDistMatrix
     detail::require_gpu(A, "Symm");
     detail::require_gpu(B, "Symm");
     detail::require_gpu(C, "Symm");
+    MultiSync fence(C.Stream(), {A.Stream(), B.Stream()});
     detail::check(detail::Sfx<T>::symm(C.Grid().handle(), side, uplo, alpha, A.desc(), B.desc(), beta, C.desc(), Blocksize(), C.Stream()));
 }
 template <typename T>
@@ -751,6 +784,7 @@ void LocalGemm(Orientation orientA, Orientation orientB, T alpha, const Abstract
     const Int kB = tB ? B.Width() : B.Height(), n = tB ? B.Height() : B.Width();
     if (m != C.Height() || k != kB || n != C.Width()) LogicError("Nonconformal LocalGemm");
     const Int kLoc = tA ? A.LocalHeight() : A.LocalWidth();
+    MultiSync fence(C.Stream(), {A.Stream(), B.Stream()});
     detail::check(detail::Sfx<T>::lgemm(tA, tB, C.LocalHeight(), C.LocalWidth(), kLoc, alpha, A.LockedBuffer(), A.LDim(), B.LockedBuffer(),
                                         B.LDim(), beta, C.Buffer(), C.LDim(), C.Stream()));
 }
@@ -777,11 +811,13 @@ void Zero(AbstractDistMatrix<T>& A) { Fill(A, T(0)); }
 // distribution and alignment first
 template <typename T>
 void Axpy(T alpha, const AbstractDistMatrix<T>& X, AbstractDistMatrix<T>& Y) {
+    MultiSync fence(Y.Stream(), {X.Stream()});
     detail::check(detail::Sfx<T>::axpy_dist(Y.Grid().handle(), alpha, X.desc(), Y.desc(), 0, Y.Stream()));
 }
 // Y += alpha X^T (TransposeAxpy.hpp); conjugate is a no-op for real T
 template <typename T>
 void TransposeAxpy(T alpha, const AbstractDistMatrix<T>& X, AbstractDistMatrix<T>& Y, bool /*conjugate*/ = false) {
+    MultiSync fence(Y.Stream(), {X.Stream()});
     detail::check(detail::Sfx<T>::axpy_dist(Y.Grid().handle(), alpha, X.desc(), Y.desc(), 1, Y.Stream()));
 }
 template <typename T>
@@ -795,6 +831,7 @@ void Hadamard(const AbstractDistMatrix<T>& A, const AbstractDistMatrix<T>& B, Ab
     if (A.ColAlign() != B.ColAlign() || A.RowAlign() != B.RowAlign()) LogicError("A and B must be aligned");
     if (C.ColAlign() != A.ColAlign() || C.RowAlign() != A.RowAlign()) C.Align(A.ColAlign(), A.RowAlign());
     if (C.Height() != A.Height() || C.Width() != A.Width()) C.Resize(A.Height(), A.Width());
+    MultiSync fence(C.Stream(), {A.Stream(), B.Stream()});
     detail::check(detail::Sfx<T>::hadamard(A.LocalHeight(), A.LocalWidth(), A.LockedBuffer(), 1, A.LDim(), B.LockedBuffer(), 1, B.LDim(),
                                            C.Buffer(), 1, C.LDim(), C.Stream()));
 }

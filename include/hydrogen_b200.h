@@ -33,6 +33,21 @@ const char* hyd_last_error(void);
 int hyd_version(void);
 /* number of kernels this library has launched in the calling process (bench.py's gpu_launches) */
 long long hyd_launch_count(void);
+/* device allocations (cudaMalloc) made and host-blocking synchronisations (cudaStream/DeviceSynchronize) issued by this
+ * library in the calling process: a steady-state hyd_gemm_* / hyd_redist_* / hyd_trrk_* call adds nothing to either
+ * (ref: the pooled simple_buffer temporaries, include/hydrogen/utils/SimpleBuffer.hpp + src/core/imports/cub.cpp, and the
+ * asynchronous SyncInfo contract, include/hydrogen/SyncInfo.hpp).  hyd_gemm_host_* ends with one synchronisation by contract. */
+long long hyd_alloc_count(void);
+long long hyd_sync_count(void);
+
+/* Stream fences at the API edge.  ref: MakeMultiSync(master, others...) include/hydrogen/SyncInfo.hpp:136-186, used at
+ * src/blas_like/level3/Gemm.cpp:117-119 and include/El/blas_like/level1/Copy/RowAllGather.hpp:25-28: at construction the
+ * master (the OUTPUT matrix's stream) waits for the work already enqueued on every other (INPUT) stream, at destruction
+ * every other stream waits for the master.  begin/end bracket any hyd_* call that runs on `master` and reads matrices
+ * produced on `others`; streams equal to master (or repeated) are skipped.  No host synchronisation.  (The reference's
+ * AddSynchronizationPoint has the stream comparison inverted, SyncInfo.hpp:92-107; this is the documented semantic.) */
+int hyd_multisync_begin(hyd_stream_t master, const hyd_stream_t* others, int n);
+int hyd_multisync_end(hyd_stream_t master, const hyd_stream_t* others, int n);
 
 /* ---- seam S2: local (per-rank) kernels ------------------------------------- */
 
@@ -213,6 +228,10 @@ int hyd_world_create_local(hyd_local_group* grp, int rank, hyd_world** out);
 int hyd_world_destroy(hyd_world* w);
 int hyd_world_barrier(hyd_world* w);
 /* mpi::Size / mpi::Rank of the owning communicator (include/El/core/imports/mpi.hpp) */
+/* the data plane this world moves redistribution traffic on: "nvlink-push(ipc)+nccl" (peer-mapped NVLink stores, NCCL only
+ * for bootstrap and barriers), "nccl" (staged pack -> grouped ncclSend/ncclRecv -> unpack; also what a failed IPC mapping
+ * falls back to -- the string is how a caller sees which one it got), "local-push" / "local" (rank-threads on one GPU) */
+const char* hyd_world_kind(const hyd_world* w);
 int hyd_world_size(const hyd_world* w);
 int hyd_world_rank(const hyd_world* w);
 
@@ -235,6 +254,11 @@ int hyd_grid_vr_rank(const hyd_grid* g);
  * 0 = off, 1 = on); SMs the GEMM leaves to communication kernels while overlapping (default 4, < 0 keeps the value) */
 int hyd_grid_set_overlap(hyd_grid* g, int overlap, int sm_reserve);
 
+/* hyd_gemm_host_*: the most column blocks the local C may be cut into so that finished blocks download under the next
+ * block's GEMMs (default 8, or HYD_HOST_CBLOCKS at grid creation; 1 = one download after the last panel).  Same value on
+ * every rank.  The cuts themselves come from hyd_host_block_plan. */
+int hyd_grid_set_host_blocks(hyd_grid* g, int max_blocks);
+
 /* per-kernel device timing: enable (also resets), then read launches and summed CUDA-event time of
  * kind 0 = local GEMM launches, 1 = redistributions, 2 = reduce-scatters issued through this grid,
  * 3 = pack (+ peer push) kernel groups, 4 = unpack kernel groups inside the redistributions. */
@@ -252,6 +276,13 @@ int hyd_local_shape_of(int gridHeight, int gridWidth, int order, int rank, const
 /* view of rows [i,i+h) x cols [j,j+w): alignment and buffer offset as El::View / operator()(IR,IR) */
 int hyd_view(const hyd_grid* g, const hyd_dm* a, int64_t i, int64_t j, int64_t h, int64_t w, int elemSize,
              hyd_dm* out);
+
+/* Host-only planner of hyd_gemm_host_*: the column blocks (in 128-column tiles of a tm x tn-tile local C) the host-resident
+ * stationary-C Gemm computes one after the other so that block j downloads under block j+1's GEMMs.  Minimises
+ * sum_j ceil(tm*w_j/sms) + lambda*w_last + mu*(blocks-1) over at most max_blocks (<= 8) blocks; writes the nblk+1 cuts
+ * 0 = t_0 < ... < t_nblk = tn and returns nblk.  (No counterpart in the reference: its Gemm has no host-resident form on
+ * Device::GPU; the caller copies whole matrices, include/El/blas_like/level1/Copy.hpp:140-207.) */
+int hyd_host_block_plan(int64_t tm, int64_t tn, int64_t sms, double lambda, double mu, int max_blocks, int64_t* cuts);
 
 /* Host-only planner: bytes `rank` of an r x c grid sends to / receives from every rank for dst := src (transpose: src^T)
  * in the one-hop exchange that replaces the reference's pack -> collective -> unpack chains

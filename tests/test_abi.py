@@ -177,3 +177,19 @@ def test_abi_header_is_plain_c():
     import subprocess
     hdr = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "hydrogen_b200.h")
     subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Werror", "-fsyntax-only", "-x", "c", hdr])
+
+
+def test_host_block_plan():
+    """hyd_host_block_plan (no GPU work): cuts cover [0, tn] in order; 128 x 128 tiles on 148 SMs split 37|37|37|17 --
+    128*37 = 32*148, so the blocked run loses no wave against the unblocked one and the exposed download is 17/128 of C."""
+    import ctypes as C
+    from elemental_b200 import lib
+    cuts = (C.c_int64 * 9)()
+    nb = lib.hyd_host_block_plan(128, 128, 148, 0.17, 0.05, 8, cuts)
+    got = list(cuts[: nb + 1])
+    assert got[0] == 0 and got[-1] == 128 and all(x < y for x, y in zip(got, got[1:]))
+    waves = sum(-(-128 * (y - x) // 148) for x, y in zip(got, got[1:]))
+    assert waves <= -(-128 * 128 // 148), (got, waves)
+    assert got[-1] - got[-2] <= 40, got
+    assert lib.hyd_host_block_plan(64, 1, 148, 0.1, 0.05, 8, cuts) == 1 and list(cuts[:2]) == [0, 1]
+    assert lib.hyd_host_block_plan(64, 32, 148, 0.1, 0.05, 1, cuts) == 1

@@ -17,7 +17,6 @@ def test_basicgemm_cpp_driver():
         assert out.returncode == 0 and "PASSED" in out.stdout, out.stdout + out.stderr
 
 
-@pytest.mark.skipif(os.environ.get("HYD_TEST_EXPERIMENTAL") != "1", reason="not yet run on a GPU; set HYD_TEST_EXPERIMENTAL=1")
 def test_basicsyrk_cpp_driver():
     """examples/BasicSyrk.cpp: tests/blas_like/Syrk.cpp restated against the shim (Align, MakeSymmetric, Syrk, both triangles
     and orientations) plus the shim's alignment rules (adoption in B = A, AlignWith)."""

@@ -3,12 +3,12 @@ redistribution engine, bit-exact) and hyd_gemm_{f16,bf16} (stationary-C SUMMA, t
 
 Reference: El::Gemm on DistMatrix<gpu_half_type,...,Device::GPU> (Gemm.cpp:278-307, local product cublasHgemm,
 Gemm.cpp:460-467): C lives in half precision, so every k-panel's update rounds it once.  The checker restates exactly that
-in numpy: per panel C = round(alpha * A1 B1 + beta' * C) with the product in float64.  Tolerance: one unit in the last
-place of the storage type (2^-10 relative for fp16, 2^-7 for bf16) on every entry -- the device accumulates in fp32, so a
-result that sits next to a rounding boundary may land on the neighbouring value -- and at least 98 % of the entries equal
-bit for bit.
-
-Written after this round's GPU budget was spent: gated by HYD_TEST_EXPERIMENTAL=1 until it has run on a B200 once."""
+in numpy: per panel C = round(alpha * A1 B1 + beta' * C) with the product in float64.  Tolerance: the device accumulates
+in fp32, so a panel result that sits next to a rounding boundary may land on the neighbouring storage value, and that one
+unit in the last place (2^-10 relative for fp16, 2^-7 for bf16) OF THE INTERMEDIATE is carried through the later panels:
+every entry within 2 ulp of the largest magnitude its running value took, and at least 98 % of the entries equal bit for
+bit.  (First run on a B200 in round 2: the bound was 1 ulp of the FINAL value, which an entry that passed through a
+higher binade on the way -- 17.4 -> 9.1 -- misses by construction; the kernel was right.)"""
 import itertools
 import os
 
@@ -21,8 +21,7 @@ from oracle_lib import MC, MR, VC, VR, STAR
 from elemental_b200 import host as H
 import gpu_util as U
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("HYD_TEST_EXPERIMENTAL") != "1", reason="not yet run on a GPU; set HYD_TEST_EXPERIMENTAL=1")]
+pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("r,c", [(1, 1), (2, 2), (2, 4), (3, 2)])
@@ -82,16 +81,20 @@ def test_gemm_half_summa_c(r, c, kind):
         GC = _round(rng.uniform(-1, 1, size=(m, n)), kind)
         opA, opB = (GA.T if oA else GA), (GB.T if oB else GB)
         exp = GC.copy()
+        big = np.abs(exp)
         for k0 in range(0, k, nb):          # the reference's panel loop: C is rounded to its storage type after every panel
             exp = _round(2.0 * (opA[:, k0:k0 + nb] @ opB[k0:k0 + nb, :]) + (3.0 if k0 == 0 else 1.0) * exp, kind)
+            big = np.maximum(big, np.abs(exp))
         al = [int(rng.integers(0, s)) for s in (r, c, r, c, r, c)]
-        cases.append((oA, oB, nb, GA, GB, GC, exp, al))
+        cases.append((oA, oB, nb, GA, GB, GC, (exp, big), al))
     # operands in other distributions go through the [MC,MR] proxies
     m, n, k, nb = 140, 150, 130, 32
     GA, GB, GC = (_round(rng.uniform(-1, 1, size=s), kind) for s in ((m, k), (k, n), (m, n)))
     exp = GC.copy()
+    big = np.abs(exp)
     for k0 in range(0, k, nb):
         exp = _round(2.0 * (GA[:, k0:k0 + nb] @ GB[k0:k0 + nb, :]) + (3.0 if k0 == 0 else 1.0) * exp, kind)
+        big = np.maximum(big, np.abs(exp))
 
     def body(grid):
         res = []
@@ -115,13 +118,14 @@ def test_gemm_half_summa_c(r, c, kind):
     out = H.run_ranks(r * c, body, height=r)
     ulp = 2.0 ** -10 if kind == "f16" else 2.0 ** -7
 
-    def check(got, want, tag):
+    def check(got, want_big, tag):
+        want, big_ = want_big
         d = np.abs(got - want)
-        assert (d <= ulp * np.maximum(np.abs(want), 2.0 ** -14)).all(), (tag, d.max())
+        assert (d <= 2 * ulp * np.maximum(big_, 2.0 ** -14)).all(), (tag, d.max())
         assert (d == 0).mean() >= 0.98, (tag, (d == 0).mean())
 
     for i, (oA, oB, nb_, A_, B_, C_, want, al) in enumerate(cases):
-        got = np.full_like(want, np.nan)
+        got = np.full_like(want[0], np.nan)
         for p in range(r * c):
             cs, rs, blk = out[p][i]
             got[cs::r, rs::c] = blk
@@ -130,4 +134,4 @@ def test_gemm_half_summa_c(r, c, kind):
     for p in range(r * c):
         cs, rs, cst, rst, blk = out[p][-1]
         got[cs::cst, rs::rst] = blk
-    check(got, exp, "proxies")
+    check(got, (exp, big), "proxies")

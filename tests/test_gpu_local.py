@@ -191,8 +191,6 @@ def test_launch_counter_and_probe():
     assert lib.hyd_launch_count() > n0
 
 
-@pytest.mark.skipif(__import__("os").environ.get("HYD_TEST_EXPERIMENTAL") != "1",
-                    reason="hyd_memcopy{1d,2d}_async were added after round 1's last GPU call; set HYD_TEST_EXPERIMENTAL=1")
 def test_interdevice_copies_roundtrip():
     """hyd_memcopy{2d,1d}_async = InterDeviceCopy<..>::MemCopy{2D,1D}Async (include/hydrogen/device/gpu/CUDA.hpp:229-420;
     Copy(Matrix<T,CPU>, Matrix<T,GPU>) and back, Copy.hpp:140-207): block with leading dimensions up, down, device to device;
@@ -224,9 +222,6 @@ def test_interdevice_copies_roundtrip():
         assert lib.hyd_memcopy2d_async(p(dB), ldb, p(hA), lda, 0, n, es, 0, st) == 0         # empty
 
 
-@pytest.mark.skipif(__import__("os").environ.get("HYD_TEST_EXPERIMENTAL") != "1",
-                    reason="hyd_lgemm_{f16,bf16} (tcgen05 kind::f16, csrc/lgemm_f16_tc.cu) was written after round 1's GPU budget "
-                           "was spent and has not run on a GPU yet; set HYD_TEST_EXPERIMENTAL=1")
 @pytest.mark.parametrize("tdt,name", [(torch.bfloat16, "bf16"), (torch.float16, "f16")])
 def test_lgemm_half(tdt, name):
     """fp16 / bf16 operands and result, fp32 accumulation: against torch's fp32 product of the same half inputs, rounded once

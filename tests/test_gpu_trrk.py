@@ -7,8 +7,7 @@ printed associativity residual: inside the triangle the Gemm tolerances of test_
 <= 1e-13*sqrt(k) fp64 / 1e-5*sqrt(k) fp32; |x-y| <= 1e-10 / 1e-3), outside it every entry keeps its bits.  The trapezoid
 routines are bit-exact (one multiply / one add per entry; alpha chosen so that no FMA contraction can change the result).
 
-SURVEY 8(f) N2.  Written after this round's GPU budget was spent: gated by HYD_TEST_EXPERIMENTAL=1 until it has run on a
-B200 once (tools/gpu_first_call.sh runs it)."""
+SURVEY 8(f) N2.  Green on a B200 since round 2's first GPU call (profiles/r02_first_call_summary.json)."""
 import itertools
 import os
 
@@ -20,8 +19,7 @@ from oracle_lib import MC, MR, VC, VR, STAR
 from elemental_b200 import host as H
 import gpu_util as U
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("HYD_TEST_EXPERIMENTAL") != "1", reason="not yet run on a GPU; set HYD_TEST_EXPERIMENTAL=1")]
+pytestmark = pytest.mark.gpu
 
 
 def _mask_dm(og, n, d, ca, ra, uplo, dtype, offset=0, m=None):
