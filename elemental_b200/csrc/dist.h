@@ -7,6 +7,8 @@
 // No CUDA in this header: it is also used by the CPU-only C-ABI entry points.
 #pragma once
 #include <stdint.h>
+#include <algorithm>
+#include <vector>
 
 namespace hyd {
 
@@ -116,43 +118,83 @@ inline TrrkCuts trrk_cuts(int tri, const LocalShape& L, i64 j0, i64 w, i64 q) {
 
 // Column blocks of the local C for the host-resident stationary-C Gemm (summa.cu): C is computed block by block so that a
 // finished block downloads under the next block's GEMMs.  Cuts are in 128-column tiles of the LOCAL block (tm x tn tiles).
-// Every block's GEMMs run ceil(tm*w/sms) waves of the persistent kernel, so the cuts are chosen (dynamic programme, <= 8
-// blocks) to minimise   sum_j ceil(tm*w_j/sms)  +  lambda*w_last  +  mu*(blocks-1)
-// -- total waves, the exposed download of the last block (lambda = download time of one tile column in waves) and a small
-// per-block cost (the A panels are gathered again for every block).  Example: tm = tn = 128, 148 SMs -> 37|37|37|17:
-// 128*37 = 32*148 exactly, no wave is lost against the unblocked run.  Returns the cuts 0 = t_0 < ... < t_nblk = tn.
+// Model: a block of w tile columns costs ceil(tm*w/sms) waves of the persistent GEMM and lambda*w waves of download.
+// Plans are restricted to those whose every download hides under the NEXT block's GEMMs (lambda*w_j <= waves(w_{j+1})), so
+// only the last block's download is exposed; among them minimise   sum_j waves(w_j) + lambda*w_last + mu*(blocks-1).
+// Widths therefore shrink geometrically towards the end.  Example: tm = tn = 128, 148 SMs, lambda = 0.17 -> 100|23|4|1.
+// Dynamic programme from the right end over (columns left, width of the block to the right); returns the cuts
+// 0 = t_0 < ... < t_nblk = tn (at most max_blocks <= 8 blocks; one block if nothing better exists).
 inline int host_col_cuts(i64 tm, i64 tn, i64 sms, double lambda, double mu, int max_blocks, i64* cuts /*[max_blocks+1]*/) {
-    if (tn <= 0 || tm <= 0 || sms <= 0 || max_blocks < 1) { cuts[0] = 0; cuts[1] = tn > 0 ? tn : 0; return 1; }
+    cuts[0] = 0;
+    cuts[1] = tn > 0 ? tn : 0;
+    if (tn <= 1 || tm <= 0 || sms <= 0 || max_blocks <= 1 || !(lambda > 0)) return 1;
     if (max_blocks > 8) max_blocks = 8;
-    if (tn > 4096) tn = 4096;
-    auto waves = [&](i64 w) { return (double)((tm * w + sms - 1) / sms); };
-    const double INF = 1e300;
-    // best[b][t]: least cost of covering tiles [0, t) with exactly b blocks (no last-block term); from[b][t]: start of block b
-    static thread_local double best[9][4097];
-    static thread_local int from[9][4097];
-    for (int b = 0; b <= max_blocks; ++b) for (i64 t = 0; t <= tn; ++t) best[b][t] = INF;
-    best[0][0] = 0;
-    for (int b = 1; b <= max_blocks; ++b)
-        for (i64 t = b; t <= tn; ++t)
-            for (i64 u = b - 1; u < t; ++u) {
-                if (best[b - 1][u] >= INF) continue;
-                const double c = best[b - 1][u] + waves(t - u) + (b > 1 ? mu : 0.0);
-                if (c < best[b][t]) { best[b][t] = c; from[b][t] = (int)u; }
+    // the plan of the previous call (per thread): a Gemm in a loop asks for the same one every time (the table costs ~10 ms)
+    struct Memo { i64 tm, tn, sms; double lambda, mu; int max_blocks, nb; i64 cuts[9]; };
+    static thread_local Memo memo = {0, 0, 0, 0, 0, 0, 0, {0}};
+    if (memo.nb > 0 && memo.tm == tm && memo.tn == tn && memo.sms == sms && memo.lambda == lambda && memo.mu == mu &&
+        memo.max_blocks == max_blocks) {
+        for (int i = 0; i <= memo.nb; ++i) cuts[i] = memo.cuts[i];
+        return memo.nb;
+    }
+    auto remember = [&](int nb) {
+        memo.tm = tm; memo.tn = tn; memo.sms = sms; memo.lambda = lambda; memo.mu = mu; memo.max_blocks = max_blocks; memo.nb = nb;
+        for (int i = 0; i <= nb; ++i) memo.cuts[i] = cuts[i];
+        return nb;
+    };
+    const i64 unit = (tn + 191) / 192;                    // coarsen very wide blocks: the table stays <= 192 x 192 x 8
+    const i64 n = (tn + unit - 1) / unit;
+    auto waves = [&](i64 w) { return (double)((tm * w * unit + sms - 1) / sms); };
+    const double lam = lambda * (double)unit, INF = 1e300;
+    // best[b][t][w]: least cost of covering [0, t) with at most b more blocks when the block to the right of t has width w
+    static thread_local std::vector<double> best;
+    static thread_local std::vector<short> pick;
+    const size_t plane = (size_t)(n + 1) * (size_t)(n + 1);
+    best.assign(plane * (size_t)max_blocks, INF);
+    pick.assign(plane * (size_t)max_blocks, 0);
+    auto at = [&](int b, i64 t, i64 w) { return (size_t)b * plane + (size_t)t * (size_t)(n + 1) + (size_t)w; };
+    for (i64 w = 1; w <= n; ++w) best[at(0, 0, w)] = 0;   // nothing left: zero further blocks
+    for (int b = 1; b < max_blocks; ++b)
+        for (i64 t = 0; t <= n; ++t)
+            for (i64 w = 1; w + t <= n; ++w) {
+                if (t == 0) { best[at(b, 0, w)] = 0; continue; }
+                const i64 cap = std::min<i64>(t, (i64)(waves(w) / lam));   // widths whose download hides under the block to the right
+                double bc = INF;
+                short bp = 0;
+                for (i64 v = 1; v <= cap; ++v) {
+                    const double sub = best[at(b - 1, t - v, v)];
+                    if (sub >= INF) continue;
+                    const double c = waves(v) + mu + sub;
+                    if (c < bc) { bc = c; bp = (short)v; }
+                }
+                best[at(b, t, w)] = bc;
+                pick[at(b, t, w)] = bp;
             }
-    int nb = 1;
-    i64 ulast = 0;
-    double bc = INF;
-    for (int b = 1; b <= max_blocks && b <= tn; ++b)     // the last block [u, tn) also pays for its exposed download
-        for (i64 u = b - 1; u < tn; ++u) {
-            if (best[b - 1][u] >= INF) continue;
-            const double c = best[b - 1][u] + waves(tn - u) + (b > 1 ? mu : 0.0) + lambda * (double)(tn - u);
-            if (c < bc - 1e-9) { bc = c; nb = b; ulast = u; }
-        }
+    double bc = waves(n) + lam * (double)n;               // one block: everything exposed
+    i64 wl = n;
+    for (i64 w = 1; w < n; ++w) {
+        const double sub = best[at(max_blocks - 1, n - w, w)];
+        if (sub >= INF) continue;
+        const double c = waves(w) + lam * (double)w + sub;
+        if (c < bc - 1e-9) { bc = c; wl = w; }
+    }
+    if (wl == n) return remember(1);
+    i64 rev[9];
+    int nb = 0;
+    rev[nb++] = wl;
+    i64 t = n - wl, w = wl;
+    for (int b = max_blocks - 1; t > 0 && b >= 1; --b) {
+        const i64 v = pick[at(b, t, w)];
+        if (v <= 0) return 1;                             // cannot happen for a finite cost
+        rev[nb++] = v;
+        t -= v;
+        w = v;
+    }
+    if (t != 0) return 1;
+    i64 run = 0;
+    for (int i = 0; i < nb; ++i) { run += rev[nb - 1 - i] * unit; cuts[i + 1] = std::min(run, tn); }
     cuts[nb] = tn;
-    i64 t = ulast;
-    cuts[nb - 1] = t;
-    for (int b = nb - 1; b >= 1; --b) { t = from[b][t]; cuts[b - 1] = t; }
-    return nb;
+    return remember(nb);
 }
 
 // One arithmetic progression of global indices i = first + t*step, t < count,

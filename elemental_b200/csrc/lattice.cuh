@@ -236,10 +236,13 @@ __global__ void __launch_bounds__(256) lattice_copy_kernel(const __grid_constant
 // transpose), unpacking them one after the other writes every 32-byte sector S times, a quarter or half at a time,
 // and each pass is a read-modify-write in DRAM.  Here one pass writes full 16-byte vectors of consecutive
 // destination rows, fetching each element from the part that owns it (part k stored contiguously: element t of
-// column b at src[k][t + b*s_cs[k]]); across a warp every part is still read as contiguous runs.
+// column b at src[k][t*s_rs[k] + b*s_cs[k]], s_rs = 1 for a packed message); across a warp every part is still read as
+// contiguous runs.  A part may also be a lattice of the SOURCE matrix itself (the rank's own share of a non-transposing
+// redistribution, s_rs = its row step): it is then never packed at all.
 constexpr int kMaxMerge = 16;
 struct MergeDesc {
     const void* src[kMaxMerge];
+    i64 s_rs[kMaxMerge];
     i64 s_cs[kMaxMerge];
     void* dst;      // element (0, 0) of the destination block (rows contiguous)
     i64 d_cs;
@@ -270,7 +273,7 @@ __global__ void __launch_bounds__(256) lattice_merge_kernel(const __grid_constan
         for (int e = 0; e < V; ++e) {
             const i64 ae = (a + e < nr) ? a + e : a;   // clamp: the value is not stored
             const int k = (int)(ae % S);
-            p[e] = static_cast<const T*>(D.src[k]) + ae / S;
+            p[e] = static_cast<const T*>(D.src[k]) + (ae / S) * D.s_rs[k];
             cs[e] = D.s_cs[k];
         }
         T v[CP][V];

@@ -338,6 +338,47 @@ static cudaError_t dispatch(int typeA, int typeB, const CUtensorMap& ma, const C
     return launch<KT, KT, BN, BK>(ma, mb, C, ldc, M, N, K, alpha, beta, s, sm_reserve);
 }
 
+// ---- TF32 tensor-pipe probe: the roofline denominator of the split-TF32 kernel ------------------------------------------
+// One CTA per SM; one thread issues `iters` x 4 tcgen05.mma.kind::tf32 of shape 128 x 256 x 8 (the kernel's own instruction
+// shape, both operands K-major SWIZZLE_128B in shared memory, zero-filled, never reloaded) into one TMEM accumulator and
+// commits once at the end.  No TMA, no splitter, no epilogue: what is left is the rate at which the tensor core can execute
+// SS-form MMAs.  TFLOP/s returned = 2*128*256*8 flops per MMA (dense TF32); the 3xTF32 kernel's bound is a third of it.
+__global__ void __launch_bounds__(128, 1) tf32_probe_kernel(int iters) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+    const uint32_t sA = smem_base, sB = smem_base + 128 * 128, bar = smem_base + 128 * 128 + 256 * 128, slot = bar + 8;
+    volatile uint32_t* slot_gen = reinterpret_cast<volatile uint32_t*>(smem_gen + (slot - smem_base));
+    for (int i = threadIdx.x; i < (128 + 256) * 128 / 16; i += blockDim.x) reinterpret_cast<float4*>(smem_gen)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    const int warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) { mbar_init(bar, 1); mbar_fence_init(); }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(slot), "r"(256u));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *slot_gen;
+    if (threadIdx.x == 0) {
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(256 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks)
+                tc_mma_tf32(tmem_base, make_desc(sA + ks * 32, 16, 1024, 2u), make_desc(sB + ks * 32, 16, 1024, 2u), idesc, (it | ks) != 0);
+        }
+        tc_commit(bar);
+        mbar_wait(bar, 0);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256u));
+    }
+}
+
 }  // namespace tc32
 
 // returns 0 = launched, 1 = error (hyd_last_error set), -1 = not applicable (caller falls back to the FFMA kernel)
@@ -371,6 +412,29 @@ int lgemm_f32_tc(int tA, int tB, long long m, long long n, long long k, float al
         e = dispatch<128, 32>(typeA, typeB, ma, mb, C, ldc, (int)m, (int)n, (int)k, alpha, beta, s, sm_reserve);
     }
     return check_cuda(e, "sgemm_tc_kernel");
+}
+
+// dense TF32 tcgen05 rate (TFLOP/s) of this GPU: see tf32_probe_kernel
+int probe_tf32_peak(int iters, double* tflops) {
+    using namespace tc32;
+    const int smem = (128 + 256) * 128 + 1024 + 64;
+    if (check_cuda(cudaFuncSetAttribute(tf32_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem), "tf32 probe attr")) return 1;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    const int grid = num_sms();
+    for (int rep = 0; rep < 2; ++rep) {   // rep 0 = warm-up
+        cudaEventRecord(e0);
+        tf32_probe_kernel<<<grid, 128, smem>>>(iters);
+        cudaEventRecord(e1);
+        if (check_cuda(cudaEventSynchronize(e1), "tf32 probe kernel")) return 1;
+    }
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *tflops = 2.0 * 128 * 256 * 8 * 4.0 * (double)iters * grid / (ms * 1e-3) / 1e12;
+    return 0;
 }
 
 }  // namespace hyd

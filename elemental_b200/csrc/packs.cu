@@ -60,7 +60,7 @@ int launch_merge(int S, T* const* src_of_residue, const i64* cs_of_residue, T* d
     if (nr == 0 || nc == 0) return 0;
     MergeDesc md;
     md.S = S;
-    for (int r = 0; r < S; ++r) { md.src[r] = src_of_residue[r]; md.s_cs[r] = cs_of_residue[r]; }
+    for (int r = 0; r < S; ++r) { md.src[r] = src_of_residue[r]; md.s_rs[r] = 1; md.s_cs[r] = cs_of_residue[r]; }
     md.dst = dst;
     md.d_cs = d_cs;
     md.nr = nr;

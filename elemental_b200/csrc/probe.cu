@@ -64,8 +64,11 @@ __global__ void __launch_bounds__(256) probe_kernel(int iters, double* sink) {
     }
 }
 
-// Returns achieved TFLOP/s for the probe `kind` (0 DFMA, 1 DMMA m8n8k4, 2 DMMA m16n8k16, 3 FFMA).
+int probe_tf32_peak(int iters, double* tflops);   // lgemm_f32_tc.cu
+
+// Returns achieved TFLOP/s for the probe `kind` (0 DFMA, 1 DMMA m8n8k4, 2 DMMA m16n8k16, 3 FFMA, 4 tcgen05 dense TF32).
 int probe_peak(int kind, int iters, int ctas_per_sm, double* tflops) {
+    if (kind == 4) return probe_tf32_peak(iters, tflops);
     double* sink = nullptr;
     if (check_cuda(cudaMalloc(&sink, 64), "probe malloc")) return 1;
     const int grid = num_sms() * ctas_per_sm, block = 256;

@@ -303,6 +303,10 @@ int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot
             }
         }
     }
+    // The rank's own part of a non-transposing merged redistribution is read by the merge kernel straight from the source
+    // lattice (its rows are contiguous there): no pack, one read + one write less of that part (half of the block when two
+    // grid rows feed a [*,VR] block).  A transposed own part keeps the tiled pack (its rows are ldim apart in the source).
+    const bool self_direct = merge && has_self && !transpose && self_msg.pa.srcStep == 1;
     static const int chunk_ctas = getenv("HYD_CHUNK_CTAS_PER_SM") ? std::max(1, atoi(getenv("HYD_CHUNK_CTAS_PER_SM"))) : 3;
     const int per_sm = K > 1 ? chunk_ctas : 8;
     cudaStream_t us = s;
@@ -328,7 +332,9 @@ int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot
         for (const Msg& m : sends)
             if (chunk(m, q, c))
                 descs.push_back(pack_desc<T>(src, transpose, c, push ? g.world->shared_peer(slot, c.peer) + c.off : send_base + c.off));
-        if (has_self && merge) {
+        if (has_self && merge && self_direct) {
+            // nothing to pack: see the merge descriptor below
+        } else if (has_self && merge) {
             Msg m = self_msg;
             m.off = self_off;
             if (chunk(m, q, c)) descs.push_back(pack_desc<T>(src, transpose, c, recv_base + c.off));
@@ -359,11 +365,19 @@ int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot
             md.S = (int)parts.size();
             md.nr = 0;
             md.nc = 0;
-            for (const Msg& m : parts) {
+            for (size_t pi = 0; pi < parts.size(); ++pi) {
+                const Msg& m = parts[pi];
                 md.nr += m.pa.count;
                 if (!chunk(m, q, c)) continue;
-                md.src[m.pa.dst0] = recv_base + c.off;
-                md.s_cs[m.pa.dst0] = c.pa.count;
+                if (self_direct && pi + 1 == parts.size()) {   // my own part (always the last one): a lattice of the source
+                    md.src[m.pa.dst0] = static_cast<const T*>(src.buf) + c.pa.src0 + c.pb.src0 * src.ldim;
+                    md.s_rs[m.pa.dst0] = c.pa.srcStep;
+                    md.s_cs[m.pa.dst0] = c.pb.srcStep * src.ldim;
+                } else {
+                    md.src[m.pa.dst0] = recv_base + c.off;
+                    md.s_rs[m.pa.dst0] = 1;
+                    md.s_cs[m.pa.dst0] = c.pa.count;
+                }
                 md.nc = c.pb.count;
                 md.dst = static_cast<T*>(dst.buf) + c.pb.dst0 * dst.ldim;
                 md.d_cs = c.pb.dstStep * dst.ldim;

@@ -435,7 +435,10 @@ int hyd_memcopy2d_async(void* dst, int64_t dst_ldim, const void* src, int64_t sr
 int hyd_memcopy1d_async(void* dst, const void* src, int64_t count, int elem_size, int kind, hyd_stream_t stream);
 
 /* Pipe-peak probe (register-resident loops): kind 0 = FP64 DFMA, 1 = DMMA m8n8k4, 2 = DMMA m16n8k16,
- * 3 = FP32 FFMA.  Writes achieved TFLOP/s.  Measurement aid for the roofline denominator. */
+ * 3 = FP32 FFMA, 4 = dense TF32 on the 5th-generation tensor cores (tcgen05.mma.kind::tf32, 128 x 256 x 8 per instruction,
+ * operands resident in shared memory, accumulator in TMEM; ctas_per_sm is ignored: one CTA per SM).  Writes achieved
+ * TFLOP/s.  Measurement aid for the roofline denominators: the fp64 kernel is bounded by kind 2, the split-TF32 fp32
+ * kernel (three TF32 MMAs per fp32 product) by a third of kind 4. */
 int hyd_probe_peak(int kind, int iters, int ctas_per_sm, double* tflops);
 
 #ifdef __cplusplus

@@ -180,16 +180,21 @@ def test_abi_header_is_plain_c():
 
 
 def test_host_block_plan():
-    """hyd_host_block_plan (no GPU work): cuts cover [0, tn] in order; 128 x 128 tiles on 148 SMs split 37|37|37|17 --
-    128*37 = 32*148, so the blocked run loses no wave against the unblocked one and the exposed download is 17/128 of C."""
+    """hyd_host_block_plan (no GPU work): the column blocks of the host-resident Gemm.  Cuts cover [0, tn] in order; every
+    block's download hides under the next block's GEMMs (lambda*w_j <= waves(w_{j+1})), the last block is small (its
+    download is the only exposed one) and blocking costs at most a wave or two against the unblocked run."""
     import ctypes as C
     from elemental_b200 import lib
     cuts = (C.c_int64 * 9)()
-    nb = lib.hyd_host_block_plan(128, 128, 148, 0.17, 0.05, 8, cuts)
-    got = list(cuts[: nb + 1])
-    assert got[0] == 0 and got[-1] == 128 and all(x < y for x, y in zip(got, got[1:]))
-    waves = sum(-(-128 * (y - x) // 148) for x, y in zip(got, got[1:]))
-    assert waves <= -(-128 * 128 // 148), (got, waves)
-    assert got[-1] - got[-2] <= 40, got
+    for (tm, tn, sms, lam) in ((128, 128, 148, 0.1736), (64, 32, 148, 0.087), (128, 128, 148, 0.49), (128, 256, 148, 0.17), (64, 64, 144, 0.087)):
+        nb = lib.hyd_host_block_plan(tm, tn, sms, lam, 0.05, 8, cuts)
+        got = list(cuts[: nb + 1])
+        w = [y - x for x, y in zip(got, got[1:])]
+        waves = [-(-tm * x // sms) for x in w]
+        assert 2 <= nb <= 8 and got[0] == 0 and got[-1] == tn and all(x > 0 for x in w), got
+        assert all(lam * w[j] <= waves[j + 1] + 1e-9 for j in range(nb - 1)), (got, waves)
+        assert sum(waves) <= -(-tm * tn // sms) + 2, (got, sum(waves))
+        assert w[-1] * 3 <= tn, got
     assert lib.hyd_host_block_plan(64, 1, 148, 0.1, 0.05, 8, cuts) == 1 and list(cuts[:2]) == [0, 1]
-    assert lib.hyd_host_block_plan(64, 32, 148, 0.1, 0.05, 1, cuts) == 1
+    assert lib.hyd_host_block_plan(64, 32, 148, 0.1, 0.05, 1, cuts) == 1 and list(cuts[:2]) == [0, 32]
+    assert lib.hyd_host_block_plan(3, 4, 148, 0.1, 0.05, 8, cuts) == 1     # one wave either way: nothing to gain

@@ -26,3 +26,20 @@ def test_basicsyrk_cpp_driver():
     for args in (["1", "1", "257", "128", "64"], ["4", "2", "300", "200", "64"], ["6", "3", "1301", "96", "32"]):
         out = subprocess.run([exe] + args, capture_output=True, text=True, timeout=180)
         assert out.returncode == 0 and "PASSED" in out.stdout, out.stdout + out.stderr
+
+
+def test_shimops_cpp_driver():
+    """examples/ShimOps.cpp: El::LocalGemm (SURVEY 8a a8: conformity checks + local product, against a host long-double
+    product) and MultiSync (a24: A, B, C on three streams with no host synchronisation, bit-identical to the synchronised run)."""
+    exe = os.path.join(ROOT, "examples", "ShimOps")
+    if not os.path.exists(exe):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "examples")])
+    for args in (["1", "1", "257", "64"], ["4", "2", "300", "64"], ["6", "3", "333", "32"]):
+        out = subprocess.run([exe] + args, capture_output=True, text=True, timeout=180)
+        assert out.returncode == 0 and "PASSED" in out.stdout, out.stdout + out.stderr
+
+
+def test_shim_header_instantiates_every_wrapper():
+    """tests/shim_check.cpp: every wrapper of include/El.hpp instantiates for double and float against the C ABI (compile-only)."""
+    subprocess.check_call(["g++", "-std=c++17", "-fsyntax-only", "-I" + os.path.join(ROOT, "include"), "-I/usr/local/cuda/include",
+                           os.path.join(ROOT, "tests", "shim_check.cpp")])

@@ -178,7 +178,11 @@ def test_gemm_host_column_blocked_path(r, c, dtype):
             d = out[p][i].astype(np.float64) - exp
             num += float((d * d).sum())
             den += float((exp ** 2).sum())
-            assert np.array_equal(out[p][i], out[p][nc + i]) and np.array_equal(out[p][i], out[p][2 * nc + i]), (oA, oB, p)
+            for alt in (out[p][nc + i], out[p][2 * nc + i]):
+                if dtype == np.float64:   # one fp64 kernel, one tile shape: the k-sum of an element does not depend on the cuts
+                    assert np.array_equal(out[p][i], alt), (oA, oB, p)
+                else:                     # the fp32 dispatcher picks its kernel / tile by the block's width: tolerance only
+                    assert np.abs(out[p][i] - alt).max() <= 1e-3, (oA, oB, p)
         assert (num / max(den, 1e-300)) ** 0.5 <= tol * k ** 0.5, (oA, oB, num, den)
 
 
@@ -253,3 +257,81 @@ def test_gemm_associativity_at_scale(r, c, n, dtype, oA, oB):
     rel = (e2 / y2) ** 0.5
     tol = (1e-13 if dtype == np.float64 else 1e-5) * n ** 0.5
     assert rel <= tol, (rel, tol)
+
+
+def test_multisync_three_streams_bit_identical():
+    """hyd_multisync_begin / _end = MakeMultiSync (include/hydrogen/SyncInfo.hpp:136-186, Gemm.cpp:117-119): A produced on
+    stream 1, B on stream 2, C on stream 3, no host synchronisation; the fenced Gemm equals the single-stream run bit for bit.
+    Both input streams are kept busy first, so an unfenced Gemm would read the zeros A and B still hold."""
+    r, c, n, nb = 2, 2, 512, 128
+
+    def body(grid):
+        gen = torch.Generator(device="cuda").manual_seed(5 + grid.Rank())
+        mk = lambda: H.DistMatrix(grid, n, n, H.MC, H.MR)
+        A0, B0, A, B, C1, C2 = mk(), mk(), mk(), mk(), mk(), mk()
+        for d in (A0, B0, C1):
+            d.store.copy_(torch.rand(d.store.shape, dtype=torch.float64, device="cuda", generator=gen) * 2 - 1)
+        C2.store.copy_(C1.store)
+        cur = torch.cuda.current_stream()
+        H.Gemm(0, 0, 2.0, A0, B0, 3.0, C1, H.GEMM_SUMMA_C, blocksize=nb)
+        cur.synchronize()
+        s1, s2, s3 = torch.cuda.Stream(), torch.cuda.Stream(), torch.cuda.Stream()
+        busy = torch.empty(64 << 20, dtype=torch.float64, device="cuda")
+        torch.cuda.synchronize()
+        grid.world.barrier()
+        with torch.cuda.stream(s1):
+            for _ in range(20):
+                busy[: 32 << 20].fill_(1.0)
+            A.store.copy_(A0.store, non_blocking=True)
+        with torch.cuda.stream(s2):
+            for _ in range(20):
+                busy[32 << 20:].fill_(2.0)
+            B.store.copy_(B0.store, non_blocking=True)
+        with H.MultiSync(s3, s1, s2):
+            H.Gemm(0, 0, 2.0, A, B, 3.0, C2, H.GEMM_SUMMA_C, stream=s3, blocksize=nb)
+        with torch.cuda.stream(s1):      # exit half of the fence: A's stream may overwrite A at once
+            A.store.fill_(-7.0)
+        s3.synchronize()
+        s1.synchronize()
+        s2.synchronize()
+        return bool(torch.equal(C1.store, C2.store))
+
+    assert all(H.run_ranks(r * c, body, height=r))
+
+
+def test_steady_state_calls_allocate_nothing_and_never_block_the_host():
+    """a24: the reference takes its temporaries from a pool (simple_buffer on the CUB allocator) and stays asynchronous.  After a
+    warm-up call, Gemm with proxied operands (every operand in a foreign distribution), Syrk, Symm and a redistribution add
+    nothing to hyd_alloc_count / hyd_sync_count."""
+    from elemental_b200 import lib
+    r, c = 2, 2
+
+    def body(grid):
+        mk = lambda h, w, cd, rd: H.DistMatrix(grid, h, w, cd, rd)
+        A, B, Cm = mk(300, 280, VC, STAR), mk(280, 260, STAR, VR), mk(300, 260, MR, MC)
+        S, Sq = mk(300, 300, MC, MR), mk(300, 300, MC, MR)
+        out_, A2 = mk(300, 260, MC, MR), mk(300, 280, MR, MC)
+        for d in (A, B, Cm, S, Sq):
+            d.store.uniform_(-1, 1)
+
+        def work():
+            for alg in (H.GEMM_SUMMA_A, H.GEMM_SUMMA_B, H.GEMM_SUMMA_C, H.GEMM_SUMMA_DOT):
+                H.Gemm(0, 0, 1.0, A, B, 0.5, Cm, alg, blocksize=64)
+            H.Syrk(H.LOWER, H.NORMAL, 1.0, A, 0.0, Sq, blocksize=64)
+            H.Symm(H.LEFT, H.UPPER, 1.0, S, Cm, 0.0, out_, blocksize=64)
+            H.Copy(A, A2)
+
+        work()
+        work()
+        torch.cuda.current_stream().synchronize()
+        grid.world.barrier()
+        a0, s0 = lib.hyd_alloc_count(), lib.hyd_sync_count()
+        grid.world.barrier()
+        for _ in range(3):
+            work()
+        torch.cuda.current_stream().synchronize()
+        grid.world.barrier()
+        return lib.hyd_alloc_count() - a0, lib.hyd_sync_count() - s0
+
+    out = H.run_ranks(r * c, body, height=r)
+    assert all(o == (0, 0) for o in out), out
