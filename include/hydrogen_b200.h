@@ -434,6 +434,27 @@ int hyd_memcopy2d_async(void* dst, int64_t dst_ldim, const void* src, int64_t sr
                         int elem_size, int kind, hyd_stream_t stream);
 int hyd_memcopy1d_async(void* dst, const void* src, int64_t count, int elem_size, int kind, hyd_stream_t stream);
 
+/* ---- allocation-free variant of the triangular local update -----------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).
+ * Triangle `uplo` (0 LOWER, 1 UPPER, of the GLOBAL matrix) of   C := alpha op(A) op(B) + beta C   on ONE rank's local block:
+ * local entry (i, j) of the localHeight x localWidth block C is global (colShift + i*colStride, rowShift + j*rowStride);
+ * op(A) is localHeight x k, op(B) is k x localWidth, all column-major device buffers of the caller.  It is what hyd_trrk_f64 /
+ * hyd_syrk_f64 run per k-panel on every rank (shifts 0 and strides 1: a plain local Trrk), with the one temporary of that
+ * computation -- the strip of each 512-column block that the diagonal crosses -- held in a file-scope static __device__
+ * array of HYD_LOCAL_TRRK_STATIC_SCRATCH_BYTES instead of a workspace that grows with cudaMalloc.
+ *   - calls no cudaMalloc / cudaFree / allocating routine; asynchronous on `stream`;
+ *   - a strip larger than the array (about 512 * rowStride / colStride rows x 512 columns) is rejected with an error before
+ *     anything is launched -- use hyd_trrk_f64 then;
+ *   - every call in the process shares the array, which keeps the last call's contents (nothing in it needs to start at zero:
+ *     each strip is written with beta = 0 before it is read); calls that overlap on the GPU race on it -- serialise them;
+ *   - every GPU that loads the library holds the array until the process exits. */
+#define HYD_LOCAL_TRRK_STATIC_SCRATCH_BYTES (4 * 1024 * 1024)
+int hyd_local_trrk_static_f64(int uplo, int transA, int transB, int64_t localHeight, int64_t localWidth, int64_t k,
+                              int64_t colShift, int64_t colStride, int64_t rowShift, int64_t rowStride, double alpha,
+                              const double* A, int64_t lda, const double* B, int64_t ldb, double beta, double* C, int64_t ldc,
+                              hyd_stream_t stream);
+
 /* Pipe-peak probe (register-resident loops): kind 0 = FP64 DFMA, 1 = DMMA m8n8k4, 2 = DMMA m16n8k16,
  * 3 = FP32 FFMA, 4 = dense TF32 on the 5th-generation tensor cores (tcgen05.mma.kind::tf32, 128 x 256 x 8 per instruction,
  * operands resident in shared memory, accumulator in TMEM; ctas_per_sm is ignored: one CTA per SM).  Writes achieved
