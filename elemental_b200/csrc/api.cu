@@ -3,6 +3,8 @@
 #include "grid.h"
 #include "hyd_internal.h"
 #include <string.h>
+#include <stdio.h>
+#include <unistd.h>
 #include <stdlib.h>
 #include <algorithm>
 
@@ -139,6 +141,59 @@ int hyd_world_create_nccl(const void* id128, int rank, int nranks, hyd_world** o
     if (!id128 || !out || nranks <= 0 || rank < 0 || rank >= nranks) return set_error("hyd_world_create_nccl: bad arguments");
     hyd::World* w = hyd::make_nccl_world(id128, rank, nranks);
     if (!w) return 1;
+    *out = new hyd_world{w};
+    return 0;
+}
+// One process per GPU without any launcher library: rank / size / local rank from the environment the usual launchers export,
+// the NCCL id through a rendezvous file (one node: the scope of this library's transports).
+static int env_int(const char* const* names, int fallback) {
+    for (int i = 0; names[i]; ++i)
+        if (const char* e = getenv(names[i])) return atoi(e);
+    return fallback;
+}
+int hyd_world_create_env(hyd_world** out) {
+    if (!out) return set_error("hyd_world_create_env: bad arguments");
+    static const char* const kRank[] = {"RANK", "OMPI_COMM_WORLD_RANK", "PMI_RANK", "SLURM_PROCID", nullptr};
+    static const char* const kSize[] = {"WORLD_SIZE", "OMPI_COMM_WORLD_SIZE", "PMI_SIZE", "SLURM_NTASKS", nullptr};
+    static const char* const kLocal[] = {"LOCAL_RANK", "OMPI_COMM_WORLD_LOCAL_RANK", "MPI_LOCALRANKID", "SLURM_LOCALID", nullptr};
+    const int rank = env_int(kRank, 0), size = env_int(kSize, 1);
+    if (size <= 0 || rank < 0 || rank >= size) return set_error("hyd_world_create_env: rank %d of %d from the environment", rank, size);
+    int ndev = 0;
+    if (hyd::check_cuda(cudaGetDeviceCount(&ndev), "hyd_world_create_env") || ndev <= 0) return set_error("hyd_world_create_env: no CUDA device");
+    const int local = env_int(kLocal, rank);
+    if (hyd::check_cuda(cudaSetDevice(local % ndev), "hyd_world_create_env: cudaSetDevice")) return 1;
+    // rendezvous file, unique per launch on this node: ranks of one launch share their parent (torchrun agent, mpirun daemon, shell)
+    char path[512];
+    const char* dir = getenv("HYD_RENDEZVOUS_DIR");
+    const char* port = getenv("MASTER_PORT");
+    if (const char* f = getenv("HYD_RENDEZVOUS_FILE")) snprintf(path, sizeof(path), "%s", f);
+    else snprintf(path, sizeof(path), "%s/hyd_rdv_%d_%s_%d", dir ? dir : "/tmp", (int)getuid(), port ? port : "0", (int)getppid());
+    unsigned char id[128];
+    if (rank == 0) {
+        if (hyd::nccl_unique_id(id)) return 1;
+        char tmp[600];
+        snprintf(tmp, sizeof(tmp), "%s.tmp%d", path, (int)getpid());
+        FILE* f = fopen(tmp, "wb");
+        if (!f || fwrite(id, 1, 128, f) != 128) { if (f) fclose(f); return set_error("hyd_world_create_env: cannot write %s", tmp); }
+        fclose(f);
+        if (rename(tmp, path) != 0) return set_error("hyd_world_create_env: cannot publish %s", path);
+    } else {
+        bool got = false;
+        for (int tries = 0; tries < 1200 && !got; ++tries) {   // up to 2 minutes
+            FILE* f = fopen(path, "rb");
+            if (f) {
+                got = fread(id, 1, 128, f) == 128;
+                fclose(f);
+            }
+            if (!got) usleep(100000);
+        }
+        if (!got) return set_error("hyd_world_create_env: rank 0 never published %s", path);
+    }
+    hyd::World* w = hyd::make_nccl_world(id, rank, size);
+    if (!w) { if (rank == 0) unlink(path); return 1; }
+    const int rc = w->barrier();   // every rank has read the id
+    if (rank == 0) unlink(path);
+    if (rc) { delete w; return 1; }
     *out = new hyd_world{w};
     return 0;
 }

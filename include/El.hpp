@@ -17,7 +17,10 @@
 
 #include <cuda_runtime.h>
 #include <cstdint>
+#include <chrono>
 #include <initializer_list>
+#include <iostream>
+#include <sstream>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -97,6 +100,9 @@ public:
     static Comm NCCL(const void* id128, int rank, int size) { Comm c; detail::check(hyd_world_create_nccl(id128, rank, size, &c.w_)); return c; }
     static Comm Local(hyd_local_group* grp, int rank) { Comm c; detail::check(hyd_world_create_local(grp, rank, &c.w_)); return c; }
     static Comm Self() { Comm c; detail::check(hyd_local_group_create(1, &c.grp_)); detail::check(hyd_world_create_local(c.grp_, 0, &c.w_)); return c; }
+    // the world of a one-process-per-GPU launch (mpi::COMM_WORLD to a Hydrogen program): rank / size / device from the
+    // launcher's environment, no MPI library involved (hyd_world_create_env)
+    static Comm World() { Comm c; detail::check(hyd_world_create_env(&c.w_)); return c; }
     hyd_world* handle() const { return w_; }
     int Size() const { return hyd_world_size(w_); }
     int Rank() const { return hyd_world_rank(w_); }
@@ -106,12 +112,46 @@ private:
     hyd_world* w_ = nullptr;
     hyd_local_group* grp_ = nullptr;
 };
+// the free functions Hydrogen client code uses on a communicator (include/El/core/imports/mpi.hpp:204-217,263)
+inline Comm NewWorldComm() { return Comm::World(); }
+inline int Rank(const Comm& comm) { return comm.Rank(); }
+inline int Size(const Comm& comm) { return comm.Size(); }
+inline void Barrier(const Comm& comm) { comm.Barrier(); }
 }  // namespace mpi
+
+// ---- El::Initialize / Finalize / Environment (src/core/environment.cpp:217-300, include/El/core/environment/decl.hpp) ----
+// The reference initialises MPI, the GPU manager (device = local rank) and cuBLAS here.  None of that exists in this build:
+// the device is chosen when the world communicator is created (mpi::NewWorldComm), there is no global handle.  Kept so that
+// client code written against the reference compiles unchanged.
+inline void Initialize() {}
+inline void Initialize(int& /*argc*/, char**& /*argv*/) {}
+inline void Finalize() {}
+inline bool Initialized() { return true; }
+class Environment {
+public:
+    Environment() { Initialize(); }
+    Environment(int& argc, char**& argv) { Initialize(argc, argv); }
+    ~Environment() { Finalize(); }
+};
+// El::Output(args...) (include/El/core/environment/impl.hpp): one line on stdout
+namespace detail {
+inline void out_all(std::ostream&) {}
+template <typename A, typename... R> void out_all(std::ostream& os, const A& a, const R&... r) { os << a; out_all(os, r...); }
+}  // namespace detail
+template <typename... Args> void Output(const Args&... args) { std::ostringstream os; detail::out_all(os, args...); os << "\n"; std::cout << os.str() << std::flush; }
+// El::Timer (include/El/core/Timer.hpp): Start() / Stop() returns the seconds since Start()
+class Timer {
+public:
+    void Start() { t0_ = std::chrono::steady_clock::now(); }
+    double Stop() { return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0_).count(); }
+private:
+    std::chrono::steady_clock::time_point t0_;
+};
 
 // ---- El::Grid (Grid.hpp:15-146; Grid.cpp:66-216) ----
 class Grid {
 public:
-    Grid(const mpi::Comm& comm, int height, GridOrder order = COLUMN_MAJOR) { detail::check(hyd_grid_create(comm.handle(), height, order, &g_)); }
+    Grid(const mpi::Comm& comm, int height, GridOrder order = COLUMN_MAJOR) : world_(comm) { detail::check(hyd_grid_create(comm.handle(), height, order, &g_)); }
     // Grid(comm, order): height = Grid::DefaultHeight(size) (Grid.cpp:58-64,70-72)
     explicit Grid(const mpi::Comm& comm, GridOrder order = COLUMN_MAJOR) : Grid(comm, hyd_grid_default_height(comm.Size()), order) {}
     static int DefaultHeight(int gridSize) { return hyd_grid_default_height(gridSize); }
@@ -135,43 +175,48 @@ public:
     hyd_grid* handle() const { return g_; }
     // sub-communicators (Grid.hpp:31-54): a (grid, kind) pair -- every member is one NVSwitch hop away, there is no
     // communicator object to create.  ColComm == MCComm (my grid column), RowComm == MRComm (my grid row).
-    struct Comm {
+    struct SubComm {
         hyd_grid* g; int kind;
         int Size() const { return hyd_comm_size(g, kind); }
         int Rank() const { return hyd_comm_rank(g, kind); }
     };
-    Comm MCComm() const { return Comm{g_, HYD_COMM_MC}; }
-    Comm MRComm() const { return Comm{g_, HYD_COMM_MR}; }
-    Comm VCComm() const { return Comm{g_, HYD_COMM_VC}; }
-    Comm VRComm() const { return Comm{g_, HYD_COMM_VR}; }
-    Comm ColComm() const { return MCComm(); }
-    Comm RowComm() const { return MRComm(); }
+    SubComm MCComm() const { return SubComm{g_, HYD_COMM_MC}; }
+    SubComm MRComm() const { return SubComm{g_, HYD_COMM_MR}; }
+    SubComm VCComm() const { return SubComm{g_, HYD_COMM_VC}; }
+    SubComm VRComm() const { return SubComm{g_, HYD_COMM_VR}; }
+    SubComm ColComm() const { return MCComm(); }
+    SubComm RowComm() const { return MRComm(); }
+    // the communicator the grid was built on (Grid.hpp:24-30): Comm() / OwningComm() / ViewingComm() coincide here
+    const mpi::Comm& Comm() const { return world_; }
+    const mpi::Comm& OwningComm() const { return world_; }
+    const mpi::Comm& ViewingComm() const { return world_; }
 private:
     hyd_grid* g_ = nullptr;
+    mpi::Comm world_;   // a handle copy; the caller keeps ownership (mpi::Comm::Free)
 };
 
 // ---- typed collectives on device buffers (src/core/imports/mpi/*.hpp, Device::GPU overloads): counts in elements ----
 namespace mpi {
 template <typename T>
-void AllGather(const T* sbuf, Int sc, T* rbuf, Int /*rc*/, const Grid::Comm& comm, const SyncInfoGPU& si) {
+void AllGather(const T* sbuf, Int sc, T* rbuf, Int /*rc*/, const Grid::SubComm& comm, const SyncInfoGPU& si) {
     detail::check(hyd_allgather(comm.g, comm.kind, sbuf, sc * (Int)sizeof(T), rbuf, si.stream_));
 }
 template <typename T>
-void AllToAll(const T* sbuf, Int sc, T* rbuf, Int /*rc*/, const Grid::Comm& comm, const SyncInfoGPU& si) {
+void AllToAll(const T* sbuf, Int sc, T* rbuf, Int /*rc*/, const Grid::SubComm& comm, const SyncInfoGPU& si) {
     detail::check(hyd_alltoall(comm.g, comm.kind, sbuf, sc * (Int)sizeof(T), rbuf, si.stream_));
 }
 template <typename T>
-void SendRecv(const T* sbuf, Int sc, int to, T* rbuf, Int rc, int from, const Grid::Comm& comm, const SyncInfoGPU& si) {
+void SendRecv(const T* sbuf, Int sc, int to, T* rbuf, Int rc, int from, const Grid::SubComm& comm, const SyncInfoGPU& si) {
     detail::check(hyd_sendrecv(comm.g, comm.kind, sbuf, sc * (Int)sizeof(T), to, rbuf, rc * (Int)sizeof(T), from, si.stream_));
 }
 template <typename T>
-void Broadcast(T* buf, Int count, int root, const Grid::Comm& comm, const SyncInfoGPU& si) {
+void Broadcast(T* buf, Int count, int root, const Grid::SubComm& comm, const SyncInfoGPU& si) {
     detail::check(hyd_bcast(comm.g, comm.kind, buf, count * (Int)sizeof(T), root, si.stream_));
 }
-inline void ReduceScatter(const double* sbuf, double* rbuf, Int rc, const Grid::Comm& comm, const SyncInfoGPU& si) {
+inline void ReduceScatter(const double* sbuf, double* rbuf, Int rc, const Grid::SubComm& comm, const SyncInfoGPU& si) {
     detail::check(hyd_reducescatter_f64(comm.g, comm.kind, sbuf, rbuf, rc, si.stream_));
 }
-inline void ReduceScatter(const float* sbuf, float* rbuf, Int rc, const Grid::Comm& comm, const SyncInfoGPU& si) {
+inline void ReduceScatter(const float* sbuf, float* rbuf, Int rc, const Grid::SubComm& comm, const SyncInfoGPU& si) {
     detail::check(hyd_reducescatter_f32(comm.g, comm.kind, sbuf, rbuf, rc, si.stream_));
 }
 }  // namespace mpi

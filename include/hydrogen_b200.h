@@ -221,6 +221,13 @@ typedef struct hyd_local_group hyd_local_group;
 
 int hyd_nccl_unique_id(void* out128);
 int hyd_world_create_nccl(const void* id128, int rank, int nranks, hyd_world** out);
+/* One process per GPU with no launcher library (what mpi::COMM_WORLD / mpi::NewWorldComm() is to a Hydrogen program,
+ * include/El/core/imports/mpi.hpp:86,217; src/core/imports/mpi.cpp): rank, size and local rank come from the environment the
+ * usual launchers export (RANK / WORLD_SIZE / LOCAL_RANK of torchrun; OMPI_COMM_WORLD_*, PMI_*, SLURM_* otherwise; one rank
+ * when none is set), the device is set to local rank mod device count (as hydrogen::gpu::Initialize picks it), and the NCCL id
+ * travels through a rendezvous file (HYD_RENDEZVOUS_FILE, else $HYD_RENDEZVOUS_DIR or /tmp /hyd_rdv_<uid>_<MASTER_PORT>_<ppid>:
+ * unique per launch on a node; rank 0 removes it once every rank has joined).  One node. */
+int hyd_world_create_env(hyd_world** out);
 /* P rank-threads of one process on one GPU (single-GPU multi-rank runs / tests); each thread takes one rank. */
 int hyd_local_group_create(int nranks, hyd_local_group** out);
 int hyd_local_group_destroy(hyd_local_group* grp);

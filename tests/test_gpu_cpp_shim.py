@@ -43,3 +43,14 @@ def test_shim_header_instantiates_every_wrapper():
     """tests/shim_check.cpp: every wrapper of include/El.hpp instantiates for double and float against the C ABI (compile-only)."""
     subprocess.check_call(["g++", "-std=c++17", "-fsyntax-only", "-I" + os.path.join(ROOT, "include"), "-I/usr/local/cuda/include",
                            os.path.join(ROOT, "tests", "shim_check.cpp")])
+
+
+def test_distgemm_one_process_world_from_the_environment():
+    """examples/DistGemm.cpp: the client-program form (El::Environment, mpi::NewWorldComm(), Grid(std::move(comm), height)) with
+    the world taken from the launcher's environment (hyd_world_create_env).  One process here; tools/gpu_multi.sh launches N."""
+    exe = os.path.join(ROOT, "examples", "DistGemm")
+    if not os.path.exists(exe):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "examples")])
+    env = dict(os.environ, RANK="0", WORLD_SIZE="1", LOCAL_RANK="0")
+    out = subprocess.run([exe, "1", "300", "64"], capture_output=True, text=True, timeout=180, env=env)
+    assert out.returncode == 0 and "PASSED" in out.stdout, out.stdout + out.stderr

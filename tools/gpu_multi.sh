@@ -14,6 +14,9 @@ timeout 900 $TR --master-port 29513 bench.py --gpus $N --steps 5 --warmup 3 > gp
 grep -v "OMP_NUM_THREADS\|\*\*\*\*" gpurun_out/bench_${N}gpu.err | tail -c 2000
 timeout 600 $TR --master-port 29514 bench.py --gpus $N --steps 5 --warmup 3 --transport nccl --no-extra > gpurun_out/bench_${N}gpu_nccl.json 2> gpurun_out/bench_${N}gpu_nccl.err; echo "bench(nccl) rc=$?"
 grep -v "OMP_NUM_THREADS\|\*\*\*\*" gpurun_out/bench_${N}gpu_nccl.err | tail -c 1000
+# the C++ client-program form, one process per GPU, world from the environment (no torch, no MPI)
+for r in $(seq 0 $((N-1))); do RANK=$r WORLD_SIZE=$N LOCAL_RANK=$r timeout 300 examples/DistGemm 0 1500 128 > gpurun_out/distgemm_${N}gpu_rank$r.log 2>&1 & done; wait
+cat gpurun_out/distgemm_${N}gpu_rank*.log | grep -E "DistGemm|Distributed|PASSED|FAILED|rror" | sort | uniq -c | head -12
 timeout 600 $TR --master-port 29515 tools/redist_bench.py > gpurun_out/redist_bench_${N}gpu.log 2>&1; echo "redist_bench rc=$?"
 python - $N <<'PY'
 import json, sys
