@@ -53,6 +53,7 @@ _sig("hyd_sync_count", C.c_longlong, [])
 _sig("hyd_multisync_begin", i32, [vp, C.POINTER(vp), i32])
 _sig("hyd_multisync_end", i32, [vp, C.POINTER(vp), i32])
 _sig("hyd_grid_set_host_blocks", i32, [vp, i32])
+_sig("hyd_grid_profile_trace", i32, [vp, i32, i32, C.POINTER(f64), C.POINTER(f64), i32])
 _sig("hyd_local_trrk_static_f64", i32, [i32, i32, i32, i64, i64, i64, i64, i64, i64, i64, f64, vp, i64, vp, i64, f64, vp, i64, vp])
 _sig("hyd_host_block_plan", i32, [i64, i64, i64, f64, f64, i32, C.POINTER(i64)])
 _sig("hyd_lgemm_f64", i32, [i32, i32, i64, i64, i64, f64, vp, i64, vp, i64, f64, vp, i64, vp])

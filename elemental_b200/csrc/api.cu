@@ -287,6 +287,25 @@ int hyd_grid_profile_read(hyd_grid* g, int kind, long long* launches, double* to
     if (total_ms) *total_ms = tot;
     return 0;
 }
+int hyd_grid_profile_trace(hyd_grid* g, int kind, int ref_kind, double* start_ms, double* end_ms, int max_entries) {
+    hyd::Grid& G = *g->g;
+    if (kind < 0 || kind >= hyd::Grid::PROF_KINDS || ref_kind < 0 || ref_kind >= hyd::Grid::PROF_KINDS || !start_ms || !end_ms)
+        return set_error("hyd_grid_profile_trace: bad arguments"), -1;
+    if (hyd::check_cuda(cudaDeviceSynchronize(), "hyd_grid_profile_trace")) return -1;
+    if (G.prof_used[ref_kind] < 2) return 0;
+    cudaEvent_t t0 = G.prof_ev[ref_kind][0];
+    int n = 0;
+    for (size_t i = 0; i + 1 < G.prof_used[kind] && n < max_entries; i += 2, ++n) {
+        float a = 0, b = 0;
+        if (cudaEventElapsedTime(&a, t0, G.prof_ev[kind][i]) != cudaSuccess || cudaEventElapsedTime(&b, t0, G.prof_ev[kind][i + 1]) != cudaSuccess) {
+            cudaGetLastError();
+            break;
+        }
+        start_ms[n] = a;
+        end_ms[n] = b;
+    }
+    return n;
+}
 int hyd_dist_stride(const hyd_grid* g, int dist) { return g->g->shape.stride(dist); }
 int hyd_dist_rank(const hyd_grid* g, int dist) { return g->g->shape.dist_rank(dist, g->g->mc, g->g->mr); }
 

@@ -56,7 +56,7 @@ struct Grid {
     int host_cblocks = 8; // hyd_gemm_host_*: most column blocks of C (1 = one download after the last panel); hyd_grid_set_host_blocks
     long long launches = 0;
     // optional per-kernel timing (bench.py's roofline leg): CUDA event pairs around each launch of a kind
-    enum { PROF_LGEMM = 0, PROF_REDIST = 1, PROF_REDUCE = 2, PROF_PACK = 3, PROF_UNPACK = 4, PROF_KINDS = 5 };
+    enum { PROF_LGEMM = 0, PROF_REDIST = 1, PROF_REDUCE = 2, PROF_PACK = 3, PROF_UNPACK = 4, PROF_UPLOAD = 5, PROF_DOWNLOAD = 6, PROF_KINDS = 7 };
     bool profile = false;
     std::vector<cudaEvent_t> prof_ev[PROF_KINDS];   // start/stop pairs, in launch order
     size_t prof_used[PROF_KINDS] = {};

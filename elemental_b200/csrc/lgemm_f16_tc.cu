@@ -7,9 +7,8 @@
 // -> gpu_blas::Gemm<__half> -> cublasHgemm (src/core/imports/cublas.cpp:213 ADD_GEMM_IMPL(__half, H)); the reference has
 // no bf16 type, bf16 is offered because it is the B200's native training format.
 //
-// STATUS: written after round 1's GPU budget was spent -- compiles for sm_100a, HAS NOT RUN ON A GPU YET.  Nothing in the
-// engine calls it; the entry points hyd_lgemm_{f16,bf16} exist so that the first GPU call of the next round can test
-// it (tests/test_gpu_local.py::test_lgemm_half, gated by HYD_TEST_EXPERIMENTAL=1).
+// STATUS: parity-tested on a B200 since round 2 (tests/test_gpu_local.py::test_lgemm_half, tests/test_gpu_half.py); the local
+// product of hyd_gemm_{f16,bf16} (summa_half.cu).
 //
 // Structure = lgemm_f32_tc.cu without the splitter stage (one persistent CTA per SM, warp-specialised):
 //   warp 0     TMA producer: 128 x 64 tile of A and BN x 64 tile of B per stage (cp.async.bulk.tensor.2d, SWIZZLE_128B,

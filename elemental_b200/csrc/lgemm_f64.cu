@@ -29,7 +29,8 @@ constexpr int BM = 128, BK = 16;
 //   WN = 4 : 128 x 128 tile, 8 consumer warps (2 x 4), 6-stage ring, ONE CTA per SM  (setmaxnreg split)
 //   WN = 2 : 128 x  64 tile, 4 consumer warps (2 x 2), 4-stage ring, TWO CTAs per SM -- while one CTA
 //            runs its epilogue (C read-modify-write) the other keeps the DMMA pipe busy (HYD_DGEMM_WN=2; the
-//            setmaxnreg split that makes it spill-free was added after round 1's last GPU call: unmeasured).
+//            measured in round 2 against WN = 4 on the SUMMA panel shapes (profiles/r02_first_call_summary.json): 27.3 / 34.3 / 35.6
+//            TFLOP/s vs 27.2 / 34.5 / 35.8 -- no gain, WN = 4 stays the default).
 template <int WN> struct Cfg {
     static constexpr int BN = 32 * WN;
     static constexpr int kConsumerWarps = 2 * WN;

@@ -307,6 +307,14 @@ int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot
     // lattice (its rows are contiguous there): no pack, one read + one write less of that part (half of the block when two
     // grid rows feed a [*,VR] block).  A transposed own part keeps the tiled pack (its rows are ldim apart in the source).
     const bool self_direct = merge && has_self && !transpose && self_msg.pa.srcStep == 1;
+    // Copy-engine push: a message whose rows are contiguous in the source (no transpose, the destination's row set is the
+    // source's: [MC,MR] -> [*,VR] between the ranks of a grid column, a whole-block shift, ...) is a strided 2-D copy.  The copy
+    // engines move it at the full peer-copy rate (SM stores reach ~80 % of it) and leave every SM to the merge / unpack
+    // kernel of the previous chunk.  Only for large exchanges over real peer links (one process per GPU), all messages of
+    // this rank qualifying, at most two peers (the copies of one rank are issued one after the other).  HYD_REDIST_CE=0 disables.
+    static const bool ce_env = !(getenv("HYD_REDIST_CE") && atoi(getenv("HYD_REDIST_CE")) == 0);
+    bool ce_push = ce_env && push && K > 1 && !transpose && !sends.empty() && sends.size() <= 2 && g.world->push_chunks();
+    for (const Msg& m : sends) ce_push = ce_push && m.pa.srcStep == 1 && m.count() * (i64)sizeof(T) >= ((i64)8 << 20);
     static const int chunk_ctas = getenv("HYD_CHUNK_CTAS_PER_SM") ? std::max(1, atoi(getenv("HYD_CHUNK_CTAS_PER_SM"))) : 3;
     const int per_sm = K > 1 ? chunk_ctas : 8;
     cudaStream_t us = s;
@@ -329,9 +337,21 @@ int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot
         if (q > 0) g.world->push_next(slot);
         descs.clear();
         Msg c;
-        for (const Msg& m : sends)
-            if (chunk(m, q, c))
-                descs.push_back(pack_desc<T>(src, transpose, c, push ? g.world->shared_peer(slot, c.peer) + c.off : send_base + c.off));
+        for (const Msg& m : sends) {
+            if (!chunk(m, q, c)) continue;
+            if (ce_push) {
+                // whole (strided) columns of the source: one 2-D copy-engine transfer straight into the peer's region
+                const char* sp = static_cast<const char*>(src.buf) + (c.pa.src0 + c.pb.src0 * src.ldim) * (i64)sizeof(T);
+                ProfScope pk(g, Grid::PROF_PACK, s);
+                if (check_cuda(cudaMemcpy2DAsync(g.world->shared_peer(slot, c.peer) + c.off, (size_t)c.pa.count * sizeof(T), sp,
+                                                 (size_t)(c.pb.srcStep * src.ldim) * sizeof(T), (size_t)c.pa.count * sizeof(T),
+                                                 (size_t)c.pb.count, cudaMemcpyDeviceToDevice, s),
+                               "hyd_redist: copy-engine push"))
+                    return 1;
+                continue;
+            }
+            descs.push_back(pack_desc<T>(src, transpose, c, push ? g.world->shared_peer(slot, c.peer) + c.off : send_base + c.off));
+        }
         if (has_self && merge && self_direct) {
             // nothing to pack: see the merge descriptor below
         } else if (has_self && merge) {

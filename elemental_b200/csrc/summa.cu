@@ -132,6 +132,12 @@ int local_update(Grid& g, int tri, int tA, int tB, const LocalShape& Lc, i64 kb,
 // `download`: the engine also writes C back (decided from global facts, identical on every rank); cblocks: most column blocks.
 struct HostOperands { const void* A; i64 lda; const void* B; i64 ldb; void* C; i64 ldc; int cblocks; bool download; };
 
+// size of one host <-> device copy of the host-resident Gemm (HYD_HOST_CHUNK_BYTES, default 4 MiB; 0 = whole pieces)
+inline i64 host_chunk_bytes() {
+    static const i64 v = getenv("HYD_HOST_CHUNK_BYTES") ? atoll(getenv("HYD_HOST_CHUNK_BYTES")) : ((i64)4 << 20);
+    return v > 0 ? v : ((i64)1 << 60);
+}
+
 // upload this rank's part of the global sub-block rows [i0, i0+h) x columns [j0, j0+w) of X from its host image
 template <typename T>
 int upload_rect(const GridShape& sh, const DM& X, int mc, int mr, i64 i0, i64 j0, i64 h, i64 w, const void* host, i64 ldh,
@@ -141,14 +147,24 @@ int upload_rect(const GridShape& sh, const DM& X, int mc, int mr, i64 i0, i64 j0
     const i64 b0 = length_(j0, L.rowShift, L.rowStride), b1 = length_(j0 + w, L.rowShift, L.rowStride);
     if (a1 <= a0 || b1 <= b0) return 0;
     if (!host) return set_error("hyd_gemm_host: NULL host buffer for a non-empty local block");
-    T* d = static_cast<T*>(X.buf) + a0 + b0 * X.ldim;
-    const T* hsrc = static_cast<const T*>(host) + a0 + b0 * ldh;
-    if (a1 - a0 == X.ldim && X.ldim == ldh)   // whole columns, no padding on either side: one contiguous transfer
-        return check_cuda(cudaMemcpyAsync(d, hsrc, (size_t)(X.ldim * (b1 - b0)) * sizeof(T), cudaMemcpyHostToDevice, us),
-                          "hyd_gemm_host: H2D");
-    return check_cuda(cudaMemcpy2DAsync(d, (size_t)X.ldim * sizeof(T), hsrc, (size_t)ldh * sizeof(T), (size_t)(a1 - a0) * sizeof(T),
-                                        (size_t)(b1 - b0), cudaMemcpyHostToDevice, us),
-                      "hyd_gemm_host: H2D (2-D)");
+    // In pieces of host_chunk_bytes(): the copy engines serve the streams' copies one whole copy at a time, and the SUMMA
+    // panel gathers are copy-engine peer copies too -- behind a 16 MiB upload piece (or a 184 MiB download issued as one copy)
+    // every gather waited for the whole transfer, and a step took 2.6 - 5 ms instead of 1.5 while host traffic was in flight
+    // (profiles/r02_e2e_probe_8gpu_trace.log).  Small pieces let the peer copies in after at most one of them.
+    const i64 cols_per = std::max<i64>(1, host_chunk_bytes() / std::max<i64>(1, (a1 - a0) * (i64)sizeof(T)));
+    for (i64 c0 = b0; c0 < b1; c0 += cols_per) {
+        const i64 c1 = std::min(b1, c0 + cols_per);
+        T* d = static_cast<T*>(X.buf) + a0 + c0 * X.ldim;
+        const T* hsrc = static_cast<const T*>(host) + a0 + c0 * ldh;
+        if (a1 - a0 == X.ldim && X.ldim == ldh) {   // whole columns, no padding on either side: a contiguous transfer
+            if (check_cuda(cudaMemcpyAsync(d, hsrc, (size_t)(X.ldim * (c1 - c0)) * sizeof(T), cudaMemcpyHostToDevice, us), "hyd_gemm_host: H2D"))
+                return 1;
+        } else if (check_cuda(cudaMemcpy2DAsync(d, (size_t)X.ldim * sizeof(T), hsrc, (size_t)ldh * sizeof(T), (size_t)(a1 - a0) * sizeof(T),
+                                                (size_t)(c1 - c0), cudaMemcpyHostToDevice, us),
+                              "hyd_gemm_host: H2D (2-D)"))
+            return 1;
+    }
+    return 0;
 }
 
 // ---- copy-engine panel gather for SUMMA-C, NN orientation --------------------------------------------------------
@@ -291,12 +307,22 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
         i64 cuts[9];
         const int sms = std::max(1, num_sms() - ((overlap && !ce) ? g.sm_reserve : 0));
         const int nblk = host_col_cuts(tm, tn, sms, lambda, 0.05, std::min(ho->cblocks, 8), cuts);
+        // experiment knob: HYD_HOST_FIRST_TILES = t cuts the first block at t tile columns (a short first block makes the
+        // whole-column upload of its part of B short: see b0_whole below)
+        static const i64 first_tiles = getenv("HYD_HOST_FIRST_TILES") ? atoll(getenv("HYD_HOST_FIRST_TILES")) : 0;
+        if (first_tiles > 0 && first_tiles < (nblk > 1 ? cuts[1] : tn)) js.push_back(std::min<i64>(n, first_tiles * 128 * c));
         for (int b = 1; b < nblk; ++b) js.push_back(std::min<i64>(n, cuts[b] * 128 * c));
     }
     js.push_back(n);
     const size_t nblk = js.size() - 1;
     const size_t nsteps = nblk * npanels;
     cudaStream_t us = g.comm_stream[1], ds = nullptr;
+    // HYD_HOST_B0 = 1: the part of op(B) under the FIRST column block is uploaded whole (full-height columns) before the first
+    // panel instead of panel by panel.  The per-panel slices of an operand whose k runs along its rows (B for NN) are 2-D
+    // copies with short rows (k_panel / r elements: 4 KiB on the 2 x 4 grid), which the host link moves far below its
+    // contiguous rate when every GPU of the box transfers at once.
+    static const int b0_env = getenv("HYD_HOST_B0") ? atoi(getenv("HYD_HOST_B0")) : 0;
+    const bool b0_whole = ho && b0_env == 1 && oB == 0 && nblk > 1;
     if (ho) {
         // every upload is enqueued now, on the upload stream, in the order the steps consume them: for block 0 panel by
         // panel (A's panel p and the part of B's panel p under block 0), then the rest of B one whole column block at a time
@@ -308,10 +334,17 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
         }
         if (check_cuda(cudaEventRecord(g.ev_join, s), "upload fork")) return 1;
         cudaStreamWaitEvent(us, g.ev_join, 0);
+        ProfScope prof_up(g, Grid::PROF_UPLOAD, us);   // first to last H2D of this Gemm on the upload stream
+        if (b0_whole) {   // block 0's columns of op(B) as one transfer, before the first panel of A
+            if (oB ? upload_rect<T>(sh, B, g.mc, g.mr, js[0], 0, js[1] - js[0], k, ho->B, ho->ldb, us)
+                   : upload_rect<T>(sh, B, g.mc, g.mr, 0, js[0], k, js[1] - js[0], ho->B, ho->ldb, us))
+                return 1;
+            cudaEventRecord(g.upload_ev[npanels], us);
+        }
         for (size_t p = 0; p < npanels; ++p) {
             const i64 k0 = ks[p], kb = ks[p + 1] - ks[p];
-            if (oB ? upload_rect<T>(sh, B, g.mc, g.mr, js[0], k0, js[1] - js[0], kb, ho->B, ho->ldb, us)
-                   : upload_rect<T>(sh, B, g.mc, g.mr, k0, js[0], kb, js[1] - js[0], ho->B, ho->ldb, us))
+            if (!b0_whole && (oB ? upload_rect<T>(sh, B, g.mc, g.mr, js[0], k0, js[1] - js[0], kb, ho->B, ho->ldb, us)
+                                 : upload_rect<T>(sh, B, g.mc, g.mr, k0, js[0], kb, js[1] - js[0], ho->B, ho->ldb, us)))
                 return 1;
             if (oA ? upload_rect<T>(sh, A, g.mc, g.mr, k0, 0, kb, m, ho->A, ho->lda, us)
                    : upload_rect<T>(sh, A, g.mc, g.mr, 0, k0, m, kb, ho->A, ho->lda, us))
@@ -337,23 +370,30 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
     // stream `w` (compute or comm) must not touch step (j, p)'s operands before their upload has landed
     auto wait_upload = [&](cudaStream_t w, size_t j, size_t p) {
         if (!ho) return;
-        if (j == 0) cudaStreamWaitEvent(w, g.upload_ev[p], 0);
-        else if (p == 0) cudaStreamWaitEvent(w, g.upload_ev[npanels + j], 0);
+        if (j == 0) {
+            cudaStreamWaitEvent(w, g.upload_ev[p], 0);
+            if (b0_whole && p == 0) cudaStreamWaitEvent(w, g.upload_ev[npanels], 0);
+        } else if (p == 0) cudaStreamWaitEvent(w, g.upload_ev[npanels + j], 0);
     };
     // a finished column block of C goes back to the host under the next block's GEMMs
     auto download_block = [&](size_t j, const DM& Cj, const LocalShape& Lj) -> int {
         if (!ds) return 0;
         if (check_cuda(cudaEventRecord(g.ev_block_done, s), "block done")) return 1;
         cudaStreamWaitEvent(ds, g.ev_block_done, 0);
+        ProfScope prof_down(g, Grid::PROF_DOWNLOAD, ds);
         if (Lj.lh > 0 && Lj.lw > 0) {
             const LocalShape Lfull = local_shape(sh, C, g.mc, g.mr);
             const i64 jl = length_(js[j], Lfull.rowShift, Lfull.rowStride);
             if (!ho->C) return set_error("hyd_gemm_host: NULL host buffer for a non-empty local block of C");
-            if (check_cuda(cudaMemcpy2DAsync(static_cast<T*>(ho->C) + jl * ho->ldc, (size_t)ho->ldc * sizeof(T), Cj.buf,
-                                             (size_t)Cj.ldim * sizeof(T), (size_t)Lj.lh * sizeof(T), (size_t)Lj.lw,
-                                             cudaMemcpyDeviceToHost, ds),
-                           "hyd_gemm_host: D2H block of C"))
-                return 1;
+            const i64 cols_per = std::max<i64>(1, host_chunk_bytes() / std::max<i64>(1, Lj.lh * (i64)sizeof(T)));
+            for (i64 c0 = 0; c0 < Lj.lw; c0 += cols_per) {   // in pieces: see upload_rect
+                const i64 nc = std::min(cols_per, Lj.lw - c0);
+                if (check_cuda(cudaMemcpy2DAsync(static_cast<T*>(ho->C) + (jl + c0) * ho->ldc, (size_t)ho->ldc * sizeof(T),
+                                                 static_cast<const T*>(Cj.buf) + c0 * Cj.ldim, (size_t)Cj.ldim * sizeof(T),
+                                                 (size_t)Lj.lh * sizeof(T), (size_t)nc, cudaMemcpyDeviceToHost, ds),
+                               "hyd_gemm_host: D2H block of C"))
+                    return 1;
+            }
         }
         if (j + 1 == nblk) {   // the caller's stream is complete only when the last download is
             if (check_cuda(cudaEventRecord(g.ev_download_done, ds), "download join")) return 1;

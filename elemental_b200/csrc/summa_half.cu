@@ -9,7 +9,7 @@
 // one-hop redistribution on 2-byte elements (redistribute<h16>: bits are moved, never interpreted) and multiplied by the
 // tcgen05 kind::f16 kernel (lgemm_f16_tc.cu).  No panel double-buffering yet: at ~1.5 PFLOP/s the local product is so short
 // that the gathers dominate on more than one GPU; overlapping them is the next step once this has run on a GPU.
-// HAS NOT RUN ON A GPU (written after the round's GPU budget was spent); tests/test_gpu_half.py is gated.
+// Parity-tested on a B200 since round 2 (tests/test_gpu_half.py: four grids, every orientation, proxied operands).
 #include "grid.h"
 #include "hyd_internal.h"
 #include "lattice.cuh"

@@ -66,7 +66,7 @@ int hyd_lgemm_f32(int transA, int transB, int64_t m, int64_t n, int64_t k, float
  * in fp32, one rounding to the half type at the store.  SURVEY 8f N3.
  * ref: Gemm on Matrix<gpu_half_type,Device::GPU> (src/blas_like/level3/Gemm.cpp:460-467) -> cublasHgemm
  *      (src/core/imports/cublas.cpp:213); bf16 has no counterpart in the reference.
- * EXPERIMENTAL: added after round 1's last GPU call -- compiles for sm_100a, not yet run on a GPU; not used by hyd_gemm_*. */
+ * Parity-tested on a B200 since round 2 (tests/test_gpu_local.py::test_lgemm_half); the local product of hyd_gemm_{f16,bf16}. */
 int hyd_lgemm_f16(int transA, int transB, int64_t m, int64_t n, int64_t k, float alpha, const void* A, int64_t lda,
                   const void* B, int64_t ldb, float beta, void* C, int64_t ldc, hyd_stream_t stream);
 int hyd_lgemm_bf16(int transA, int transB, int64_t m, int64_t n, int64_t k, float alpha, const void* A, int64_t lda,
@@ -268,9 +268,13 @@ int hyd_grid_set_host_blocks(hyd_grid* g, int max_blocks);
 
 /* per-kernel device timing: enable (also resets), then read launches and summed CUDA-event time of
  * kind 0 = local GEMM launches, 1 = redistributions, 2 = reduce-scatters issued through this grid,
- * 3 = pack (+ peer push) kernel groups, 4 = unpack kernel groups inside the redistributions. */
+ * 3 = pack (+ peer push) kernel groups, 4 = unpack kernel groups inside the redistributions,
+ * 5 = the upload stream of hyd_gemm_host_* (first to last host-to-device copy of a call), 6 = its downloads of finished blocks. */
 int hyd_grid_profile(hyd_grid* g, int enable);
 int hyd_grid_profile_read(hyd_grid* g, int kind, long long* launches, double* total_ms);
+/* the recorded intervals of `kind` as (start, end) in ms after the first recorded start of `ref_kind` (e.g. kind 0, ref 5: when
+ * every local GEMM of a hyd_gemm_host_* call ran, counted from the call's first upload); returns the entries written, -1 on error */
+int hyd_grid_profile_trace(hyd_grid* g, int kind, int ref_kind, double* start_ms, double* end_ms, int max_entries);
 
 /* stride / rank / local shape of a distribution on this grid (host; valid for any rank via mc,mr) */
 int hyd_dist_stride(const hyd_grid* g, int dist);
@@ -411,7 +415,7 @@ int hyd_make_trapezoidal_dist_f32(hyd_grid* g, int uplo, const hyd_dm* A, int64_
 int hyd_make_symmetric_dist_f64(hyd_grid* g, int uplo, const hyd_dm* A, hyd_stream_t stream);
 int hyd_make_symmetric_dist_f32(hyd_grid* g, int uplo, const hyd_dm* A, hyd_stream_t stream);
 
-/* ---- fp16 / bf16 storage, fp32 accumulation.  EXPERIMENTAL: not yet run on a GPU. ----
+/* ---- fp16 / bf16 storage, fp32 accumulation (parity-tested on a B200: tests/test_gpu_half.py). ----
  * El::Gemm on DistMatrix<gpu_half_type,...,Device::GPU> (Gemm.cpp:278-307 with cublasHgemm as the local product, Gemm.cpp:460-467);
  * bf16 has no counterpart in the reference.  Stationary-C only (alg = GEMM_DEFAULT or GEMM_SUMMA_C); C is rounded to its
  * storage type once per k-panel, as in the reference's loop.  Any supported distribution for A, B, C. */

@@ -30,7 +30,7 @@ def main():
         world = H.World.from_torch_distributed()
     else:
         world = H.World.single()
-    out = {"gpus": size, "numa": numa, "env": {k: os.environ[k] for k in ("HYD_PANEL_CE", "HYD_HOST_CBLOCKS", "HYD_BENCH_NUMA") if k in os.environ}}
+    out = {"gpus": size, "numa": numa, "env": {k: os.environ[k] for k in ("HYD_PANEL_CE", "HYD_HOST_CBLOCKS", "HYD_BENCH_NUMA", "HYD_HOST_B0", "HYD_HOST_FIRST_TILES") if k in os.environ}}
 
     def sync():
         if size > 1:
@@ -73,17 +73,21 @@ def main():
 
         run(True, True)
         out["raw_GBps_per_gpu_all_gpus_at_once"] = {"h2d_alone": run(True, False), "d2h_alone": run(False, True), "both_each_direction": run(True, True)}
-        # 2-D: 65536 rows of 4 KiB out of an 8 KiB pitch (a row-sliced operand)
-        h2 = hbuf.view(-1, 8192)
-        d2 = dbuf[: nbytes // 2].view(-1, 4096)
-        sync()
-        e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
-        e0.record()
-        for _ in range(4):
-            d2.copy_(h2[:, :4096], non_blocking=True)
-        e1.record()
-        torch.cuda.synchronize()
-        out["raw_GBps_per_gpu_all_gpus_at_once"]["h2d_2d_4KiB_rows"] = round(nbytes / 2 / (worst(e0.elapsed_time(e1)) / 4) / 1e6, 1)
+        # 2-D, as the engine issues it (cudaMemcpy2DAsync through hyd_memcopy2d_async): the k-panels of a row-sliced operand --
+        # 16 panels of 512 rows (4 KiB) x 4096 columns out of an 8192-row (64 KiB pitch) column-major block -- and 2 KiB / 16 KiB rows
+        import ctypes as C
+        from elemental_b200 import lib, check
+        for rows in (256, 512, 2048):
+            sync()
+            e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+            e0.record()
+            npan = 8192 // rows
+            for pnl in range(npan):
+                check(lib.hyd_memcopy2d_async(C.c_void_p(dbuf.data_ptr() + pnl * rows * 8), 8192, C.c_void_p(hbuf.data_ptr() + pnl * rows * 8), 8192,
+                                              rows, 4096, 8, 0, C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+            e1.record()
+            torch.cuda.synchronize()
+            out["raw_GBps_per_gpu_all_gpus_at_once"][f"h2d_2d_{rows * 8 // 1024}KiB_rows"] = round(nbytes / worst(e0.elapsed_time(e1)) / 1e6, 1)
         del hbuf, hbuf2, dbuf, dbuf2
 
     n, nb = int(os.environ.get("E2E_N", "16384")), 1024
@@ -111,6 +115,26 @@ def main():
 
         dev_ms = timeit(lambda: H.Gemm(0, 0, 1.0, A, B, 0.0, Cm, H.GEMM_SUMMA_C, blocksize=nb))
         host_ms = timeit(lambda: H.Gemm(0, 0, 1.0, hA, hB, 0.0, hC, H.GEMM_SUMMA_C, blocksize=nb))
+        # one profiled call: where the device time goes (sum of GEMM launches, upload stream first-to-last copy, downloads)
+        grid.Profile(True)
+        e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        sync()
+        e0.record(st)
+        H.Gemm(0, 0, 1.0, hA, hB, 0.0, hC, H.GEMM_SUMMA_C, blocksize=nb)
+        e1.record(st)
+        torch.cuda.synchronize()
+        prof = {"call_ms": round(e0.elapsed_time(e1), 2)}
+        for kind, name in ((0, "gemm"), (5, "upload_stream"), (6, "downloads")):
+            cnt, ms_ = grid.ProfileRead(kind)
+            prof[name] = {"n": cnt, "ms": round(ms_, 2)}
+        import ctypes as C
+        from elemental_b200 import lib
+        for kind, name in ((0, "gemm"), (5, "upload_stream"), (6, "downloads")):
+            a, b = (C.c_double * 64)(), (C.c_double * 64)()
+            cnt = lib.hyd_grid_profile_trace(grid.h, kind, 5, a, b, 64)
+            prof[name + "_intervals_ms"] = [[round(a[i], 2), round(b[i], 2)] for i in range(max(cnt, 0))]
+        grid.Profile(False)
+        out["rank0_profile_of_one_call"] = prof
         ok = bool(torch.allclose(hC.store.cuda(), Cm.store, rtol=1e-9, atol=1e-9))
         out.update({"n": n, "device_resident_ms": round(dev_ms, 2), "host_resident_ms": round(host_ms, 2), "exposed_ms": round(host_ms - dev_ms, 2),
                     "e2e_tflops": round(2.0 * n ** 3 / host_ms / 1e9, 1), "matches_device_run": ok,
