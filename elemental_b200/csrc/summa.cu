@@ -25,6 +25,7 @@
 #include "hyd_internal.h"
 #include <algorithm>
 #include <stdlib.h>
+#include <string.h>
 #include <type_traits>
 #include <vector>
 
@@ -266,6 +267,8 @@ int gather_panels_ce(Grid& g, const DM& A, const DM& B, const DM& C, i64 k0, i64
     return g.world->push_wait(slotA, fromA.data(), cs) || g.world->push_wait(slotB, fromB.data(), cs);
 }
 
+constexpr int kHostGatherSmDefault = 0;   // see host_gather_sm in summa_c
+
 // ---- SUMMA-C (stationary C) -------------------------------------------------
 template <typename T>
 int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, const DM& B, T beta, const DM& C, i64 nb,
@@ -280,11 +283,17 @@ int summa_c(Grid& g, int oA, int oB, i64 m, i64 n, i64 k, T alpha, const DM& A, 
     // NN with matching alignments on the push transport: panels are gathered by the copy engines alone (gather_panels_ce),
     // so the gather always runs under the previous GEMM and the GEMM keeps every SM.
     static const bool ce_enabled = !(getenv("HYD_PANEL_CE") && atoi(getenv("HYD_PANEL_CE")) == 0);
+    // Host-resident operands (ho): HYD_HOST_GATHER=sm gathers the panels with SM kernels (peer stores) under the GEMM instead of
+    // with the copy engines, which the host <-> device transfers of the same call keep busy (a copy-engine gather step took
+    // 2.3 - 5 ms instead of 1.5 while host DMA was in flight: profiles/r02_e2e_probe_8gpu_*.log)
+    static const int host_gather_sm = (getenv("HYD_HOST_GATHER") && !strcmp(getenv("HYD_HOST_GATHER"), "sm")) ? 1 :
+                                      (getenv("HYD_HOST_GATHER") && !strcmp(getenv("HYD_HOST_GATHER"), "ce")) ? 0 : kHostGatherSmDefault;
+    const bool host_sm = ho && host_gather_sm && sh.size() > 1 && g.world->can_push();
     const bool ce = ce_enabled && sh.size() > 1 && g.world->can_push() && oA == 0 && oB == 0 && A.colAlign == C.colAlign &&
-                    B.rowAlign == C.rowAlign && g.overlap != 0;
+                    B.rowAlign == C.rowAlign && g.overlap != 0 && !host_sm;
     // Otherwise: with the push transport a panel gather costs a few % of its GEMM, less than the wave the persistent GEMM
     // loses when it leaves SMs to communication kernels: auto mode overlaps only the staged (NCCL) transport
-    const bool overlap = sh.size() > 1 && (ce || (g.overlap < 0 ? !g.world->can_push() : g.overlap != 0));
+    const bool overlap = sh.size() > 1 && (ce || host_sm || (g.overlap < 0 ? !g.world->can_push() : g.overlap != 0));
     // panel schedule.  The first panel's gather / upload cannot hide under a GEMM, so it is narrower
     // (nb/4, >= 128): the exposed prologue shrinks 4x; only the grouping of the k-sum changes.
     std::vector<i64> ks;

@@ -30,7 +30,7 @@ def main():
         world = H.World.from_torch_distributed()
     else:
         world = H.World.single()
-    out = {"gpus": size, "numa": numa, "env": {k: os.environ[k] for k in ("HYD_PANEL_CE", "HYD_HOST_CBLOCKS", "HYD_BENCH_NUMA", "HYD_HOST_B0", "HYD_HOST_FIRST_TILES") if k in os.environ}}
+    out = {"gpus": size, "numa": numa, "env": {k: os.environ[k] for k in ("HYD_PANEL_CE", "HYD_HOST_CBLOCKS", "HYD_BENCH_NUMA", "HYD_HOST_B0", "HYD_HOST_FIRST_TILES", "HYD_HOST_GATHER", "E2E_SM_RESERVE") if k in os.environ}}
 
     def sync():
         if size > 1:
@@ -92,6 +92,8 @@ def main():
 
     n, nb = int(os.environ.get("E2E_N", "16384")), 1024
     grid = H.Grid(world, GRIDS[size])
+    if os.environ.get("E2E_SM_RESERVE"):
+        grid.SetOverlap(-1, int(os.environ["E2E_SM_RESERVE"]))
     st = torch.cuda.Stream()
     with torch.cuda.stream(st):
         mk = lambda dev: H.DistMatrix(grid, n, n, H.MC, H.MR, **({"device": "cpu", "pinned": True} if dev == "cpu" else {}))
