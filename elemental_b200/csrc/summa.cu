@@ -267,7 +267,7 @@ int gather_panels_ce(Grid& g, const DM& A, const DM& B, const DM& C, i64 k0, i64
     return g.world->push_wait(slotA, fromA.data(), cs) || g.world->push_wait(slotB, fromB.data(), cs);
 }
 
-constexpr int kHostGatherSmDefault = 0;   // see host_gather_sm in summa_c
+constexpr int kHostGatherSmDefault = 1;   // see host_gather_sm in summa_c (8 GPUs: e2e 140 -> 156 TFLOP/s, profiles/r02_e2e_probe_8gpu_sm_gather.log)
 
 // ---- SUMMA-C (stationary C) -------------------------------------------------
 template <typename T>
