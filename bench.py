@@ -185,7 +185,7 @@ class Clocks:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                                          "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
         except OSError:
@@ -474,10 +474,14 @@ def run_ours(args):
             esteps = max(1, min(args.steps, 5))
             ems = timed(estep, esteps, min(args.warmup, 2))
             es = 8
+            h2d_mine, d2h_mine = float((hA.lh * hA.lw + hB.lh * hB.lw) * es), float(hC.lh * hC.lw * es)
+            # whole-job bytes (summed over the ranks, like `value`), and this rank's share
             e2e = {"value": round(flops / (ems * 1e-3) / 1e12, 3), "unit": "TFLOP/s", "ms_per_step": round(ems, 3),
-                   "h2d_bytes_per_step": int((hA.lh * hA.lw + hB.lh * hB.lw) * es), "d2h_bytes_per_step": int(hC.lh * hC.lw * es),
+                   "h2d_bytes_per_step": int(reduce_over_ranks(h2d_mine, "sum")), "d2h_bytes_per_step": int(reduce_over_ranks(d2h_mine, "sum")),
+                   "h2d_bytes_per_step_rank0": int(h2d_mine), "d2h_bytes_per_step_rank0": int(d2h_mine),
                    "api": "hyd_gemm_host_f64 (El::Gemm on host-resident DistMatrix blocks): A by k-panels and B by column blocks "
-                          "upload under the GEMMs, C is computed in column blocks and each finished block downloads under the next",
+                          "upload under the GEMMs, C is computed in column blocks and each finished block downloads under the next; "
+                          "on several GPUs the panels are gathered by SM kernels because the copy engines carry the host transfers",
                    "steps": esteps}
             # the host path streams a narrower first panel, so the k-sum is grouped differently: compare with the
             # device-resident run in the relative Frobenius norm (BASELINE.json tolerance 1e-13*sqrt(k) for fp64)
