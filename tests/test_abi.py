@@ -198,3 +198,50 @@ def test_host_block_plan():
     assert lib.hyd_host_block_plan(64, 1, 148, 0.1, 0.05, 8, cuts) == 1 and list(cuts[:2]) == [0, 1]
     assert lib.hyd_host_block_plan(64, 32, 148, 0.1, 0.05, 1, cuts) == 1 and list(cuts[:2]) == [0, 32]
     assert lib.hyd_host_block_plan(3, 4, 148, 0.1, 0.05, 8, cuts) == 1     # one wave either way: nothing to gain
+
+
+def test_static_scratch_trrk_rejects_bad_arguments_before_touching_the_gpu():
+    """hyd_local_trrk_static_f64 (the allocation-free entry point): argument errors and a diagonal strip beyond the static
+    scratch are reported before any CUDA call, so they can be checked without a GPU (dummy non-null pointers are never
+    dereferenced).  The computation itself is tested on a B200 in tests/test_zz_no_alloc.py."""
+    import ctypes as C
+    from elemental_b200 import lib
+    dummy = C.c_void_p(4096)
+
+    def call(uplo, lh, lw, k, cs, cst, rs, rst, lda=None, ldb=None, ldc=None):
+        return lib.hyd_local_trrk_static_f64(uplo, 0, 0, lh, lw, k, cs, cst, rs, rst, C.c_double(1.0), dummy, lda or max(lh, 1), dummy,
+                                             ldb or max(k, 1), C.c_double(1.0), dummy, ldc or max(lh, 1), None)
+    assert call(2, 8, 8, 8, 0, 1, 0, 1) != 0 and b"uplo" in lib.hyd_last_error()
+    assert call(0, -1, 8, 8, 0, 1, 0, 1) != 0 and b"negative" in lib.hyd_last_error()
+    assert call(0, 8, 8, 8, 2, 2, 0, 1) != 0 and b"shift" in lib.hyd_last_error()
+    assert call(0, 8, 8, 8, 0, 1, 0, 0) != 0 and b"stride" in lib.hyd_last_error()
+    assert call(0, 8, 8, 8, 0, 1, 0, 1, ldc=4) != 0 and b"ldc" in lib.hyd_last_error()
+    assert call(0, 8, 8, 8, 0, 1, 0, 1, lda=4) != 0 and b"leading dimension" in lib.hyd_last_error()
+    # 512 local columns, 64 global columns apart, unit row stride: the strip is ~32 k rows x 512 columns of doubles
+    assert call(0, 40000, 512, 8, 0, 1, 0, 64) != 0
+    msg = lib.hyd_last_error().decode()
+    assert "beyond the static scratch" in msg and "hyd_trrk_f64" in msg and str(4 * 1024 * 1024) in msg
+    assert call(0, 0, 8, 8, 0, 1, 0, 1) == 0 and call(1, 8, 0, 8, 0, 1, 0, 1) == 0       # empty local block: nothing to do
+
+
+def test_multisync_and_world_env_fail_loudly_on_bad_input():
+    import ctypes as C
+    from elemental_b200 import lib
+    assert lib.hyd_multisync_begin(None, None, 2) != 0 and b"bad arguments" in lib.hyd_last_error()
+    assert lib.hyd_multisync_end(None, None, -1) != 0
+    assert lib.hyd_multisync_begin(None, None, 0) == 0 and lib.hyd_multisync_end(None, None, 0) == 0   # nothing to fence
+    assert lib.hyd_world_create_env(None) != 0
+    import torch
+    if not torch.cuda.is_available():       # no device: the product must say so, not fall back to anything
+        w = C.c_void_p()
+        env_keep = {k: os.environ.get(k) for k in ("RANK", "WORLD_SIZE")}
+        os.environ["RANK"], os.environ["WORLD_SIZE"] = "3", "2"
+        try:
+            assert lib.hyd_world_create_env(C.byref(w)) != 0 and b"rank 3 of 2" in lib.hyd_last_error()
+        finally:
+            for k, v in env_keep.items():
+                if v is None:
+                    os.environ.pop(k, None)
+                else:
+                    os.environ[k] = v
+        assert lib.hyd_world_create_env(C.byref(w)) != 0 and b"CUDA" in lib.hyd_last_error()
