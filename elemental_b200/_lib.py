@@ -84,6 +84,9 @@ _sig("hyd_world_size", i32, [vp])
 _sig("hyd_world_rank", i32, [vp])
 _sig("hyd_world_kind", C.c_char_p, [vp])
 _sig("hyd_world_create_env", i32, [C.POINTER(vp)])
+_sig("hyd_env_world_info", i32, [C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)])
+_sig("hyd_env_exchange_id", i32, [i32, vp, i32])
+_sig("hyd_env_exchange_done", i32, [i32])
 _sig("hyd_grid_create", i32, [vp, i32, i32, C.POINTER(vp)])
 _sig("hyd_grid_destroy", i32, [vp])
 for _n in ("hyd_grid_height", "hyd_grid_width", "hyd_grid_size", "hyd_grid_rank", "hyd_grid_row", "hyd_grid_col",

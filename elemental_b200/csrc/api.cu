@@ -151,48 +151,74 @@ static int env_int(const char* const* names, int fallback) {
         if (const char* e = getenv(names[i])) return atoi(e);
     return fallback;
 }
-int hyd_world_create_env(hyd_world** out) {
-    if (!out) return set_error("hyd_world_create_env: bad arguments");
+// host-only pieces of hyd_world_create_env (exported: tests/test_multirank_cpu.py runs them in two processes without a GPU)
+int hyd_env_world_info(int* rank, int* size, int* local_rank) {
     static const char* const kRank[] = {"RANK", "OMPI_COMM_WORLD_RANK", "PMI_RANK", "SLURM_PROCID", nullptr};
     static const char* const kSize[] = {"WORLD_SIZE", "OMPI_COMM_WORLD_SIZE", "PMI_SIZE", "SLURM_NTASKS", nullptr};
     static const char* const kLocal[] = {"LOCAL_RANK", "OMPI_COMM_WORLD_LOCAL_RANK", "MPI_LOCALRANKID", "SLURM_LOCALID", nullptr};
-    const int rank = env_int(kRank, 0), size = env_int(kSize, 1);
-    if (size <= 0 || rank < 0 || rank >= size) return set_error("hyd_world_create_env: rank %d of %d from the environment", rank, size);
-    int ndev = 0;
-    if (hyd::check_cuda(cudaGetDeviceCount(&ndev), "hyd_world_create_env") || ndev <= 0) return set_error("hyd_world_create_env: no CUDA device");
-    const int local = env_int(kLocal, rank);
-    if (hyd::check_cuda(cudaSetDevice(local % ndev), "hyd_world_create_env: cudaSetDevice")) return 1;
-    // rendezvous file, unique per launch on this node: ranks of one launch share their parent (torchrun agent, mpirun daemon, shell)
-    char path[512];
+    const int r = env_int(kRank, 0), n = env_int(kSize, 1);
+    if (n <= 0 || r < 0 || r >= n) return set_error("hyd_world_create_env: rank %d of %d from the environment", r, n);
+    if (rank) *rank = r;
+    if (size) *size = n;
+    if (local_rank) *local_rank = env_int(kLocal, r);
+    return 0;
+}
+// rendezvous file, unique per launch on this node: ranks of one launch share their parent (torchrun agent, mpirun daemon, shell)
+static void env_rendezvous_path(char* path, size_t cap) {
     const char* dir = getenv("HYD_RENDEZVOUS_DIR");
     const char* port = getenv("MASTER_PORT");
-    if (const char* f = getenv("HYD_RENDEZVOUS_FILE")) snprintf(path, sizeof(path), "%s", f);
-    else snprintf(path, sizeof(path), "%s/hyd_rdv_%d_%s_%d", dir ? dir : "/tmp", (int)getuid(), port ? port : "0", (int)getppid());
-    unsigned char id[128];
+    if (const char* f = getenv("HYD_RENDEZVOUS_FILE")) snprintf(path, cap, "%s", f);
+    else snprintf(path, cap, "%s/hyd_rdv_%d_%s_%d", dir ? dir : "/tmp", (int)getuid(), port ? port : "0", (int)getppid());
+}
+// rank 0 publishes its 128 bytes (written to a temporary name, then renamed: readers never see a partial file); every other
+// rank polls for the file (up to timeout_s seconds) and reads them
+int hyd_env_exchange_id(int rank, void* id128, int timeout_s) {
+    if (!id128 || rank < 0) return set_error("hyd_env_exchange_id: bad arguments");
+    char path[512];
+    env_rendezvous_path(path, sizeof(path));
     if (rank == 0) {
-        if (hyd::nccl_unique_id(id)) return 1;
         char tmp[600];
         snprintf(tmp, sizeof(tmp), "%s.tmp%d", path, (int)getpid());
         FILE* f = fopen(tmp, "wb");
-        if (!f || fwrite(id, 1, 128, f) != 128) { if (f) fclose(f); return set_error("hyd_world_create_env: cannot write %s", tmp); }
+        if (!f || fwrite(id128, 1, 128, f) != 128) { if (f) fclose(f); return set_error("hyd_world_create_env: cannot write %s", tmp); }
         fclose(f);
         if (rename(tmp, path) != 0) return set_error("hyd_world_create_env: cannot publish %s", path);
-    } else {
-        bool got = false;
-        for (int tries = 0; tries < 1200 && !got; ++tries) {   // up to 2 minutes
-            FILE* f = fopen(path, "rb");
-            if (f) {
-                got = fread(id, 1, 128, f) == 128;
-                fclose(f);
-            }
-            if (!got) usleep(100000);
-        }
-        if (!got) return set_error("hyd_world_create_env: rank 0 never published %s", path);
+        return 0;
     }
+    for (int tries = 0; tries < 10 * (timeout_s > 0 ? timeout_s : 120); ++tries) {
+        FILE* f = fopen(path, "rb");
+        if (f) {
+            const bool got = fread(id128, 1, 128, f) == 128;
+            fclose(f);
+            if (got) return 0;
+        }
+        usleep(100000);
+    }
+    return set_error("hyd_world_create_env: rank 0 never published %s", path);
+}
+// rank 0, once every rank has read the id: remove the file
+int hyd_env_exchange_done(int rank) {
+    if (rank == 0) {
+        char path[512];
+        env_rendezvous_path(path, sizeof(path));
+        unlink(path);
+    }
+    return 0;
+}
+int hyd_world_create_env(hyd_world** out) {
+    if (!out) return set_error("hyd_world_create_env: bad arguments");
+    int rank = 0, size = 1, local = 0;
+    if (hyd_env_world_info(&rank, &size, &local)) return 1;
+    int ndev = 0;
+    if (hyd::check_cuda(cudaGetDeviceCount(&ndev), "hyd_world_create_env") || ndev <= 0) return set_error("hyd_world_create_env: no CUDA device");
+    if (hyd::check_cuda(cudaSetDevice(local % ndev), "hyd_world_create_env: cudaSetDevice")) return 1;
+    unsigned char id[128];
+    if (rank == 0 && hyd::nccl_unique_id(id)) return 1;
+    if (hyd_env_exchange_id(rank, id, 120)) return 1;
     hyd::World* w = hyd::make_nccl_world(id, rank, size);
-    if (!w) { if (rank == 0) unlink(path); return 1; }
+    if (!w) { hyd_env_exchange_done(rank); return 1; }
     const int rc = w->barrier();   // every rank has read the id
-    if (rank == 0) unlink(path);
+    hyd_env_exchange_done(rank);
     if (rc) { delete w; return 1; }
     *out = new hyd_world{w};
     return 0;

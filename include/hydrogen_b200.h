@@ -228,6 +228,12 @@ int hyd_world_create_nccl(const void* id128, int rank, int nranks, hyd_world** o
  * travels through a rendezvous file (HYD_RENDEZVOUS_FILE, else $HYD_RENDEZVOUS_DIR or /tmp /hyd_rdv_<uid>_<MASTER_PORT>_<ppid>:
  * unique per launch on a node; rank 0 removes it once every rank has joined).  One node. */
 int hyd_world_create_env(hyd_world** out);
+/* Its host-only pieces (no GPU needed; exported so that the two-process CPU test can run them): rank / size / local rank
+ * from the environment; rank 0 publishes 128 bytes through the rendezvous file and every other rank reads them (polling up to
+ * timeout_s seconds); rank 0 removes the file once everybody has joined. */
+int hyd_env_world_info(int* rank, int* size, int* local_rank);
+int hyd_env_exchange_id(int rank, void* id128, int timeout_s);
+int hyd_env_exchange_done(int rank);
 /* P rank-threads of one process on one GPU (single-GPU multi-rank runs / tests); each thread takes one rank. */
 int hyd_local_group_create(int nranks, hyd_local_group** out);
 int hyd_local_group_destroy(hyd_local_group* grp);

@@ -58,6 +58,27 @@ def _worker(rank, size, port, ret):
         t = torch.tensor([float(rank + 1)], dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         assert t.item() == float(size)
+        # 5. the launcher-environment bootstrap of hyd_world_create_env (mpi::NewWorldComm() of the shim), its host-only part:
+        # rank / size from the environment, rank 0's 128 bytes reach the other rank through the rendezvous file (both
+        # processes share their parent, as the ranks of one launch do), and rank 0 removes the file afterwards
+        os.environ.update(RANK=str(rank), WORLD_SIZE=str(size), LOCAL_RANK=str(rank))
+        r_, n_, l_ = C.c_int(-1), C.c_int(-1), C.c_int(-1)
+        assert lib.hyd_env_world_info(C.byref(r_), C.byref(n_), C.byref(l_)) == 0 and (r_.value, n_.value, l_.value) == (rank, size, rank)
+        ident = (C.c_ubyte * 128)(*([(7 * i + 3) % 256 for i in range(128)] if rank == 0 else [0] * 128))
+        assert lib.hyd_env_exchange_id(rank, ident, 30) == 0, lib.hyd_last_error()
+        assert list(ident) == [(7 * i + 3) % 256 for i in range(128)]
+        dist.barrier()
+        assert lib.hyd_env_exchange_done(rank) == 0
+        dist.barrier()
+        import glob
+        assert not glob.glob(f"/tmp/hyd_rdv_{os.getuid()}_{port}_{os.getppid()}*"), "rendezvous file left behind"
+        # 6. the column-block plan of the host-resident Gemm is a pure function of global facts: identical on every rank
+        cuts = (C.c_int64 * 9)()
+        nb = lib.hyd_host_block_plan(64, 32, 144, 0.087, 0.05, 8, cuts)
+        mine = torch.tensor([nb] + list(cuts[: nb + 1]) + [0] * (9 - nb), dtype=torch.int64)
+        both = [torch.zeros_like(mine) for _ in range(size)]
+        dist.all_gather(both, mine)
+        assert all(torch.equal(b, mine) for b in both)
         ret[rank] = 1
     finally:
         dist.destroy_process_group()
