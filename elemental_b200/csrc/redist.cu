@@ -313,7 +313,9 @@ int redistribute(Grid& g, const DM& src, const DM& dst, bool transpose, int slot
     // kernel of the previous chunk.  Only for large exchanges over real peer links (one process per GPU), all messages of
     // this rank qualifying, at most two peers (the copies of one rank are issued one after the other).  HYD_REDIST_CE=0 disables.
     static const bool ce_env = !(getenv("HYD_REDIST_CE") && atoi(getenv("HYD_REDIST_CE")) == 0);
-    bool ce_push = ce_env && push && K > 1 && !transpose && !sends.empty() && sends.size() <= 2 && g.world->push_chunks();
+    // (restricted to exchanges that end in the merged unpack -- the form measured and round-trip-verified on 8 GPUs; a plain
+    // whole-block shift would qualify too but has not run on real peer links yet)
+    bool ce_push = ce_env && push && merge && K > 1 && !transpose && !sends.empty() && sends.size() <= 2 && g.world->push_chunks();
     for (const Msg& m : sends) ce_push = ce_push && m.pa.srcStep == 1 && m.count() * (i64)sizeof(T) >= ((i64)8 << 20);
     static const int chunk_ctas = getenv("HYD_CHUNK_CTAS_PER_SM") ? std::max(1, atoi(getenv("HYD_CHUNK_CTAS_PER_SM"))) : 3;
     const int per_sm = K > 1 ? chunk_ctas : 8;
