@@ -150,6 +150,8 @@ __global__ void sscale_kernel(long long M, long long N, float beta, float* __res
 }
 }  // namespace f32
 
+constexpr long long kSplitTf32MaxK = 200000;   // HYD_LGEMM_F32_SPLIT_TF32_MAX_K in include/hydrogen_b200.h
+
 int lgemm_f32(int tA, int tB, long long m, long long n, long long k, float alpha, const float* A, long long lda,
               const float* B, long long ldb, float beta, float* C, long long ldc, cudaStream_t s) {
     return lgemm_f32_ex(tA, tB, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, s, 0);
@@ -171,7 +173,11 @@ int lgemm_f32_ex(int tA, int tB, long long m, long long n, long long k, float al
         }
         return 0;
     }
-    {   // large, TMA-compatible operands: split-TF32 on the tcgen05 tensor cores (lgemm_f32_tc.cu)
+    // The split-TF32 kernel's error grows in proportion to k (the tensor core's fp32 accumulator truncates: measured relative
+    // Frobenius error 7.4e-6 at k = 1024, 5.8e-5 at k = 8192, i.e. ~7e-9 * k) while the stated tolerance is 1e-5 * sqrt(k); the two
+    // cross near k = 2e6 by that fit, near 2e5 with a margin of three.  Above kSplitTf32MaxK one launch falls back to the exact-
+    // product FFMA kernel.  (The SUMMA engines never get there: a local product's k is at most the panel width, or k / P in Dot.)
+    if (k <= kSplitTf32MaxK) {   // large, TMA-compatible operands: split-TF32 on the tcgen05 tensor cores (lgemm_f32_tc.cu)
         const int rc = lgemm_f32_tc(tA, tB, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, s, sm_reserve);
         if (rc >= 0) return rc;
     }

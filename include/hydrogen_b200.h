@@ -61,6 +61,11 @@ int hyd_lgemm_f64(int transA, int transB, int64_t m, int64_t n, int64_t k, doubl
 int hyd_lgemm_f32(int transA, int transB, int64_t m, int64_t n, int64_t k, float alpha,
                   const float* A, int64_t lda, const float* B, int64_t ldb, float beta,
                   float* C, int64_t ldc, hyd_stream_t stream);
+/* fp32 accuracy: large TMA-compatible shapes run as split TF32 (three tcgen05 kind::tf32 MMAs per product: exact products,
+ * the tensor core's truncating fp32 accumulation).  Relative Frobenius error ~ 7e-9 * k (7.4e-6 at k = 1024, 5.8e-5 at 8192),
+ * inside the stated tolerance 1e-5 * sqrt(k) for every k up to this bound; a launch with a larger k runs on the exact-product
+ * FFMA kernel instead (as does everything under HYD_SGEMM=ffma). */
+#define HYD_LGEMM_F32_SPLIT_TF32_MAX_K 200000
 
 /* Half-precision operands and result (IEEE fp16 / bfloat16 storage, 2 bytes per element), fp32 accumulation, alpha and beta
  * in fp32, one rounding to the half type at the store.  SURVEY 8f N3.
