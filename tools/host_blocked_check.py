@@ -1,12 +1,11 @@
-"""Column-blocked host path of hyd_gemm_host_* (HYD_HOST_CBLOCKS > 1, csrc/summa.cu: summa_c_host_blocked) against the
-default whole-C host path: same operands, every orientation, beta = 0 and beta != 0; results must be bit-identical (the k-sum
-of every element is grouped the same way), then both are timed at the bench size.
-
-The knob is read once per process, so each variant runs in its own subprocess:
+"""Column blocks of the host-resident Gemm hyd_gemm_host_* (csrc/summa.cu summa_c; cuts from hyd_host_block_plan) against
+one block (HYD_HOST_CBLOCKS=1: one download after the last panel): same operands, every orientation, beta = 0 and beta != 0;
+fp64 results must be bit-identical (the k-sum of every element is grouped the same way whatever the column cuts), then both
+are timed at the bench size.  The knob is read when the grid is created, so each variant runs in its own subprocess:
     python tools/host_blocked_check.py            # driver: runs the variants, compares, prints one JSON line
     HBC_N=16384 HBC_TIME=1 python tools/host_blocked_check.py
-UNVERIFIED ON A GPU in round 1 (written after the round's GPU budget was spent): run this first in round 2, then make
-HYD_HOST_CBLOCKS=4 the default if it is green and faster.
+Round 2, one B200: 30.1 (1 block) -> 33.2 (4 blocks, first planner) -> 34.4 TFLOP/s (wave-aware planner, default 8 blocks).
+(The in-process form of the same check, on every grid: tests/test_gpu_gemm.py::test_gemm_host_column_blocked_path.)
 """
 import hashlib
 import json
