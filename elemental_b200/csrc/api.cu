@@ -5,6 +5,8 @@
 #include <string.h>
 #include <stdio.h>
 #include <unistd.h>
+#include <sys/stat.h>
+#include <time.h>
 #include <stdlib.h>
 #include <algorithm>
 
@@ -163,12 +165,25 @@ int hyd_env_world_info(int* rank, int* size, int* local_rank) {
     if (local_rank) *local_rank = env_int(kLocal, r);
     return 0;
 }
-// rendezvous file, unique per launch on this node: ranks of one launch share their parent (torchrun agent, mpirun daemon, shell)
+// Rendezvous file, one per launch on this node.  The launch is identified by what its ranks share: the launcher's job id when
+// there is one (torchrun's TORCHELASTIC_RUN_ID, SLURM_JOB_ID, PMIX_NAMESPACE) plus MASTER_PORT, else the SESSION id -- not the
+// parent pid: wrappers such as `timeout`, `env` or `numactl` give every rank a parent of its own (found the hard way: two ranks
+// under `timeout` waited for two different files), while the session survives them.  HYD_RENDEZVOUS_FILE overrides.
 static void env_rendezvous_path(char* path, size_t cap) {
+    if (const char* f = getenv("HYD_RENDEZVOUS_FILE")) { snprintf(path, cap, "%s", f); return; }
     const char* dir = getenv("HYD_RENDEZVOUS_DIR");
     const char* port = getenv("MASTER_PORT");
-    if (const char* f = getenv("HYD_RENDEZVOUS_FILE")) snprintf(path, cap, "%s", f);
-    else snprintf(path, cap, "%s/hyd_rdv_%d_%s_%d", dir ? dir : "/tmp", (int)getuid(), port ? port : "0", (int)getppid());
+    const char* job = getenv("TORCHELASTIC_RUN_ID");
+    if (!job || !*job || !strcmp(job, "none")) job = getenv("SLURM_JOB_ID");
+    if (!job || !*job) job = getenv("PMIX_NAMESPACE");
+    char key[160];
+    if (job && *job) {
+        snprintf(key, sizeof(key), "job%.120s", job);
+        for (char* c = key; *c; ++c) if (*c == '/' || *c == ' ') *c = '_';
+    } else {
+        snprintf(key, sizeof(key), "sid%d", (int)getsid(0));
+    }
+    snprintf(path, cap, "%s/hyd_rdv_%d_%s_%s", dir ? dir : "/tmp", (int)getuid(), port ? port : "0", key);
 }
 // rank 0 publishes its 128 bytes (written to a temporary name, then renamed: readers never see a partial file); every other
 // rank polls for the file (up to timeout_s seconds) and reads them
@@ -186,11 +201,15 @@ int hyd_env_exchange_id(int rank, void* id128, int timeout_s) {
         return 0;
     }
     for (int tries = 0; tries < 10 * (timeout_s > 0 ? timeout_s : 120); ++tries) {
-        FILE* f = fopen(path, "rb");
-        if (f) {
-            const bool got = fread(id128, 1, 128, f) == 128;
-            fclose(f);
-            if (got) return 0;
+        struct stat st;
+        // a file older than a minute is the leftover of a launch that died between publishing and joining: not ours
+        if (stat(path, &st) == 0 && time(nullptr) - st.st_mtime <= 60) {
+            FILE* f = fopen(path, "rb");
+            if (f) {
+                const bool got = fread(id128, 1, 128, f) == 128;
+                fclose(f);
+                if (got) return 0;
+            }
         }
         usleep(100000);
     }

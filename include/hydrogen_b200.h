@@ -230,8 +230,11 @@ int hyd_world_create_nccl(const void* id128, int rank, int nranks, hyd_world** o
  * include/El/core/imports/mpi.hpp:86,217; src/core/imports/mpi.cpp): rank, size and local rank come from the environment the
  * usual launchers export (RANK / WORLD_SIZE / LOCAL_RANK of torchrun; OMPI_COMM_WORLD_*, PMI_*, SLURM_* otherwise; one rank
  * when none is set), the device is set to local rank mod device count (as hydrogen::gpu::Initialize picks it), and the NCCL id
- * travels through a rendezvous file (HYD_RENDEZVOUS_FILE, else $HYD_RENDEZVOUS_DIR or /tmp /hyd_rdv_<uid>_<MASTER_PORT>_<ppid>:
- * unique per launch on a node; rank 0 removes it once every rank has joined).  One node. */
+ * travels through a rendezvous file (HYD_RENDEZVOUS_FILE, else $HYD_RENDEZVOUS_DIR or /tmp /hyd_rdv_<uid>_<MASTER_PORT>_<key>,
+ * key = the launcher's job id -- TORCHELASTIC_RUN_ID, SLURM_JOB_ID, PMIX_NAMESPACE -- else the session id, which unlike the
+ * parent pid survives wrappers such as `timeout` or `numactl`; two launches at the same time from one shell session without a
+ * job id need different MASTER_PORT values or HYD_RENDEZVOUS_FILE).  Rank 0 removes the file once every rank has joined; a
+ * file older than a minute is ignored as the leftover of a dead launch.  One node. */
 int hyd_world_create_env(hyd_world** out);
 /* Its host-only pieces (no GPU needed; exported so that the two-process CPU test can run them): rank / size / local rank
  * from the environment; rank 0 publishes 128 bytes through the rendezvous file and every other rank reads them (polling up to

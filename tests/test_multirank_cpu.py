@@ -71,7 +71,7 @@ def _worker(rank, size, port, ret):
         assert lib.hyd_env_exchange_done(rank) == 0
         dist.barrier()
         import glob
-        assert not glob.glob(f"/tmp/hyd_rdv_{os.getuid()}_{port}_{os.getppid()}*"), "rendezvous file left behind"
+        assert not glob.glob(f"/tmp/hyd_rdv_{os.getuid()}_{port}_*"), "rendezvous file left behind"
         # 6. the column-block plan of the host-resident Gemm is a pure function of global facts: identical on every rank
         cuts = (C.c_int64 * 9)()
         nb = lib.hyd_host_block_plan(64, 32, 144, 0.087, 0.05, 8, cuts)
@@ -90,3 +90,45 @@ def test_two_rank_host_logic_gloo():
     ret = mgr.dict()
     mp.spawn(_worker, args=(size, _free_port(), ret), nprocs=size, join=True)
     assert dict(ret) == {0: 1, 1: 1}
+
+
+_RANK_SNIPPET = r"""
+import ctypes as C, os, sys
+sys.path.insert(0, sys.argv[1])
+from elemental_b200 import lib
+rank = int(os.environ["RANK"])
+r_, n_, l_ = C.c_int(-1), C.c_int(-1), C.c_int(-1)
+assert lib.hyd_env_world_info(C.byref(r_), C.byref(n_), C.byref(l_)) == 0 and (r_.value, n_.value) == (rank, 2)
+ident = (C.c_ubyte * 128)(*([(11 * i + 5) % 256 for i in range(128)] if rank == 0 else [0] * 128))
+assert lib.hyd_env_exchange_id(rank, ident, 30) == 0, lib.hyd_last_error()
+assert list(ident) == [(11 * i + 5) % 256 for i in range(128)]
+print("RANK", rank, "GOT THE ID", flush=True)
+"""
+
+
+def test_env_rendezvous_survives_wrapper_processes(tmp_path):
+    """The ranks of one launch need not share their parent: under `timeout` (or `env`, `numactl`, ...) every rank has a wrapper
+    process of its own.  The first N > 1 run of examples/DistGemm on real GPUs hung exactly there (the rendezvous file was keyed
+    by the parent pid; it is keyed by the launcher's job id or the session now).  Two rank processes, each under its own
+    `timeout`, in this session: rank 1 must receive rank 0's 128 bytes; also a stale file (older than a minute) is ignored."""
+    import subprocess
+    import time
+    port = str(_free_port())
+    env = {k: v for k, v in os.environ.items() if k not in ("TORCHELASTIC_RUN_ID", "SLURM_JOB_ID", "PMIX_NAMESPACE", "HYD_RENDEZVOUS_FILE")}
+    env.update(WORLD_SIZE="2", MASTER_PORT=port, HYD_RENDEZVOUS_DIR=str(tmp_path))
+    procs = []
+    for rank in (1, 0):        # rank 1 first: it has to wait for the file
+        procs.append(subprocess.Popen(["timeout", "60", sys.executable, "-c", _RANK_SNIPPET, ROOT], env=dict(env, RANK=str(rank), LOCAL_RANK=str(rank)),
+                                      stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
+        time.sleep(0.3)
+    outs = [p.communicate(timeout=90)[0] for p in procs]
+    assert all(p.returncode == 0 for p in procs), outs
+    assert "RANK 1 GOT THE ID" in outs[0] and "RANK 0 GOT THE ID" in outs[1], outs
+    files = list(tmp_path.iterdir())
+    assert len(files) == 1 and f"_{port}_sid" in files[0].name, files       # keyed by the session, not by a parent pid
+    # the same name, left behind by a dead launch long ago: a new rank 1 must not take it for its own
+    old = time.time() - 600
+    os.utime(files[0], (old, old))
+    p = subprocess.run([sys.executable, "-c", _RANK_SNIPPET.replace(", 30)", ", 2)"), ROOT], env=dict(env, RANK="1", LOCAL_RANK="1"),
+                       capture_output=True, text=True, timeout=60)
+    assert p.returncode != 0 and "never published" in (p.stdout + p.stderr), p.stdout + p.stderr
